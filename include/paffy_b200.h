@@ -1,0 +1,135 @@
+/*
+ * paffy_b200.h - C ABI of the B200-native add_mismatches path (libpaffy_b200.so).
+ *
+ * Plain pointers and sizes only; no torch / C++ types cross this boundary. Every entry point cites
+ * the reference interface it replaces (paths relative to the paffy source tree). The reference-side
+ * binding a maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - A CIGAR op is one 64-bit word with the bit layout of the reference's CigarRecord
+ *     (inc/paf.h:61-65): bits 0..55 length, bits 56..63 op; op codes per inc/paf.h:52-58
+ *     (0 M, 1 I, 2 D, 3 =, 4 X). Host arrays of these words ARE CigarRecord arrays.
+ *   - All functions return 0 on success or a negative PAFGPU_E* code; pafgpu_last_error() gives the
+ *     message. There is no CPU fallback: without a CUDA device every call fails with
+ *     PAFGPU_ENODEVICE.
+ *   - "device" buffers are plain CUDA device pointers on the context's device.
+ */
+#ifndef PAFFY_B200_H_
+#define PAFFY_B200_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PAFGPU_ABI_VERSION 1
+
+enum {
+    PAFGPU_OK = 0,
+    PAFGPU_ENODEVICE = -1, /* no usable CUDA device / CUDA runtime error */
+    PAFGPU_EINVAL = -2,    /* bad argument */
+    PAFGPU_ENOCONTIG = -3, /* unknown contig name / id */
+    PAFGPU_EBOUNDS = -4,   /* a record's CIGAR walks outside its contig (reference: undefined behaviour) */
+    PAFGPU_EFASTA = -5,    /* inadmissible byte in FASTA (reference: st_errAbort, bioioC.c:196-199) */
+    PAFGPU_EIO = -6,
+    PAFGPU_ESTATE = -7     /* call out of order (e.g. fetch before submit) */
+};
+
+typedef struct pafgpu_ctx pafgpu_ctx;
+
+int pafgpu_abi_version(void);
+/* Number of CUDA devices visible (0 if none / no driver). */
+int pafgpu_device_count(void);
+/* Create a context bound to one CUDA device (one context per GPU; multi-GPU = one per rank). */
+int pafgpu_create(int device, pafgpu_ctx **out);
+void pafgpu_destroy(pafgpu_ctx *ctx);
+const char *pafgpu_last_error(const pafgpu_ctx *ctx); /* ctx may be NULL: last creation error */
+
+/* ---- genome store: replaces the name -> char* hash the reference fills with
+ *      fastaReadToFunction + fastaRead_readToMapFunction (sonLib bioioC.c:155-232;
+ *      impl/paf_add_mismatches.c:89-96) and queries with stHash_search (:116,:123). -------------------
+ * Contigs are packed to 2 bits/base in HBM; bytes other than ACGT (any case) are kept exactly in a
+ * sparse exception plane so the byte-compare semantics of impl/paf.c:755-757 are preserved. */
+int pafgpu_genome_reserve(pafgpu_ctx *ctx, int64_t total_bases);
+/* Add one contig from host ASCII (not NUL-terminated needed). A repeated name replaces the earlier
+ * contig (sonLibHash.c:68-73). Returns the contig id (>=0) or a negative error. */
+int64_t pafgpu_genome_add_contig(pafgpu_ctx *ctx, const char *name, const char *seq, int64_t len);
+/* Same, sequence bytes already in device memory (synthetic genomes generated on the GPU). */
+int64_t pafgpu_genome_add_contig_device(pafgpu_ctx *ctx, const char *name, const void *seq_dev, int64_t len);
+/* Read a FASTA file with the reference reader's admission rules (whole header line is the name; '>'
+ * anywhere ends a record; newline/space/tab skipped; any other non-letter except '-' is an error). */
+int pafgpu_genome_load_fasta(pafgpu_ctx *ctx, const char *path);
+int64_t pafgpu_genome_find(const pafgpu_ctx *ctx, const char *name); /* id or PAFGPU_ENOCONTIG */
+int64_t pafgpu_genome_contig_length(const pafgpu_ctx *ctx, int64_t contig);
+int64_t pafgpu_genome_num_contigs(const pafgpu_ctx *ctx);
+/* Read bases [start, start+len) of a contig back as the upper-cased bytes the kernel compares. */
+int pafgpu_genome_fetch(pafgpu_ctx *ctx, int64_t contig, int64_t start, int64_t len, char *out);
+
+/* ---- batch description: replaces the per-record fields paf_encode_mismatches reads from Paf
+ *      (impl/paf.c:746,751-752: target_start, query_start, query_end, same_strand) and the
+ *      Cigar array (inc/paf.h:67-73), flattened for a whole batch of records. ---------------------- */
+typedef struct {
+    int64_t n_records;
+    int64_t n_ops;            /* == op_begin[n_records] */
+    const int64_t *op_begin;  /* n_records + 1 offsets into ops; every record has >= 1 op */
+    const uint64_t *ops;      /* n_ops CigarRecord words, records back to back; no zero-length M ops */
+    const int32_t *q_contig;  /* per record: contig ids from pafgpu_genome_find */
+    const int32_t *t_contig;
+    const int64_t *q_start;   /* Paf.query_start */
+    const int64_t *q_end;     /* Paf.query_end */
+    const int64_t *t_start;   /* Paf.target_start */
+    const uint8_t *same_strand; /* 1 for '+', 0 for '-' */
+} pafgpu_batch;
+
+typedef struct {
+    int64_t n_out_ops;      /* total output CigarRecord words */
+    int64_t aligned_bases;  /* sum of input M lengths (the unit of the throughput metric) */
+    int64_t n_windows;      /* 32-base work windows scheduled */
+    int64_t n_tiles;        /* warp tiles scheduled */
+    int64_t retried;        /* 1 if the output buffer overflowed and the scan was re-run */
+    float ms_ingest;        /* CUDA-event time of the CIGAR ingest kernels */
+    float ms_encode;        /* CUDA-event time of the base-comparison kernel (+ stitch) */
+} pafgpu_result;
+
+/* Run CIGAR ingest + the base-comparison kernel on one batch (a1 + a7 of SURVEY.md section 8).
+ * _host: arrays are host memory; they are copied H2D (pinned staging) inside the call.
+ * _device: arrays are device memory already (inputs resident in HBM).
+ * Results stay on the device until fetched. Synchronous on return. */
+int pafgpu_encode_batch_host(pafgpu_ctx *ctx, const pafgpu_batch *b, pafgpu_result *res);
+int pafgpu_encode_batch_device(pafgpu_ctx *ctx, const pafgpu_batch *b, pafgpu_result *res);
+
+/* Copy results of the last batch to host memory. Any pointer may be NULL to skip it.
+ *   out_ops       n_out_ops words           (the =/X CIGARs, records back to back)
+ *   out_op_begin  n_records + 1 offsets into out_ops
+ *   rec_mismatch  n_records: number of mismatching aligned bases found in each record's M ops
+ *                 (matches = sum of M lengths - this; with the I/D/=/X totals of the input CIGAR
+ *                 this is everything paf_stats_calc, impl/paf.c:236-260, returns) */
+int pafgpu_fetch_ops(pafgpu_ctx *ctx, uint64_t *out_ops, int64_t *out_op_begin, int64_t *rec_mismatch);
+/* Device pointers to the same results (valid until the next batch on this context). */
+int pafgpu_result_device_ptrs(pafgpu_ctx *ctx, const uint64_t **out_ops, const int64_t **out_op_begin,
+                              const int64_t **rec_mismatch);
+
+/* ---- device serialiser: replaces paf_write_to_buffer's CIGAR loop (impl/paf.c:367-380) and
+ *      int64_to_str (:10-34) for the whole batch. The caller supplies, per record, the text that
+ *      precedes the CIGAR ("...\tcg:Z:", fields 1-12 and tags rendered per :320-365); the device
+ *      appends <len><op>... and '\n'. ------------------------------------------------------------- */
+int pafgpu_serialise(pafgpu_ctx *ctx, const char *prefix_bytes, const int64_t *prefix_begin /* n_records+1 */,
+                     int64_t *text_bytes_out, float *ms_out);
+/* Copy the serialised text (text_bytes_out bytes) and optionally per-record line offsets (n_records+1). */
+int pafgpu_fetch_text(pafgpu_ctx *ctx, char *text, int64_t *line_begin);
+
+/* ---- one-record convenience used by the paf.h-compatible paf_encode_mismatches
+ *      (impl/paf.c:739-784): sequences are whole-contig host strings, indexed by absolute coordinate.
+ *      Packs only the spans the record touches. out_ops is malloc'd (caller frees). ----------------- */
+int pafgpu_encode_one(pafgpu_ctx *ctx, const uint64_t *ops, int64_t n_ops, int same_strand, int64_t query_start,
+                      int64_t query_end, int64_t target_start, const char *query_seq, const char *target_seq,
+                      uint64_t **out_ops, int64_t *n_out, int64_t *mismatches);
+
+/* Kernel self-timing for bench.py: re-run the encode kernel of the last submitted batch `reps` times
+ * (inputs and genome resident in HBM) and return the mean CUDA-event milliseconds per launch. */
+int pafgpu_time_encode(pafgpu_ctx *ctx, int reps, float *ms_mean, float *ms_min);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PAFFY_B200_H_ */

@@ -1,0 +1,710 @@
+// pafgpu.cu - C ABI (include/paffy_b200.h) over the sm_100a kernels: genome store, CIGAR ingest,
+// batch encode, result fetch. One context per GPU; no CPU fallback anywhere in this file.
+#include "../../include/paffy_b200.h"
+#include "kernels.cuh"
+#include "serialise.cuh"
+
+#include <algorithm>
+#include <cctype>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+using namespace pafgpu;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    // grow to at least `bytes`; keep the first `keep` bytes
+    cudaError_t ensure(size_t bytes, size_t keep = 0, bool zero_new = false) {
+        if (bytes <= cap) return cudaSuccess;
+        size_t want = std::max(bytes, cap + cap / 2);
+        void *q = nullptr;
+        cudaError_t e = cudaMalloc(&q, want);
+        if (e != cudaSuccess) {  // retry with the exact size before giving up
+            want = bytes;
+            e = cudaMalloc(&q, want);
+            if (e != cudaSuccess) return e;
+        }
+        if (zero_new) cudaMemset(q, 0, want);
+        if (keep && p) cudaMemcpy(q, p, std::min(keep, cap), cudaMemcpyDeviceToDevice);
+        if (p) cudaFree(p);
+        p = q;
+        cap = want;
+        return cudaSuccess;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T> T *as() const { return static_cast<T *>(p); }
+};
+
+struct GenomeStore {
+    DevBuf words, flags, rank, exc;
+    int64_t cap_bases = 0;                // multiple of ARENA_ALIGN
+    int64_t next_off = ARENA_ALIGN;       // first free arena position (front pad of one block)
+    uint32_t exc_total = 0;               // flagged words so far
+    std::vector<std::string> names;
+    std::vector<int64_t> off, len;
+    std::unordered_map<std::string, int64_t> index;
+    DevBuf d_off, d_len;
+    bool table_dirty = true;
+
+    Genome view() const { return Genome{words.as<uint64_t>(), flags.as<uint32_t>(), rank.as<uint32_t>(), exc.as<uint8_t>()}; }
+    void reset() {
+        next_off = ARENA_ALIGN;
+        exc_total = 0;
+        names.clear(); off.clear(); len.clear(); index.clear();
+        table_dirty = true;
+    }
+    void release() { words.release(); flags.release(); rank.release(); exc.release(); d_off.release(); d_len.release(); }
+};
+
+}  // namespace
+
+struct pafgpu_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {};
+    std::string err;
+    std::mutex mu;  // library callers may encode from several threads (SURVEY 8b threading row)
+
+    GenomeStore genome, scratch;
+
+    // staging for host batches
+    DevBuf in_op_begin, in_ops, in_qc, in_tc, in_qs, in_qe, in_ts, in_strand, in_seq;
+    // per-batch work buffers
+    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, tile_desc, tile_first_closer, tile_open_slot;
+    DevBuf out, rec_out_begin, rec_mism, scalars;
+    // serialiser
+    DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
+    int64_t ser_text_bytes = 0;
+
+    // last batch
+    bool have_batch = false;
+    int64_t n_records = 0, n_ops = 0, n_out = 0, n_tiles = 0;
+    uint64_t n_win = 0;
+    EncodeParams last{};
+};
+
+namespace {
+
+constexpr int ITERS = 8;
+constexpr uint32_t TILE_WINDOWS = 32u * ITERS;
+enum { SC_BAD = 0, SC_ALIGNED = 1, SC_TICKET = 2, SC_TOTAL = 3, SC_NWIN = 4, SC_TMP = 5, SC_COUNT = 8 };
+
+int fail(pafgpu_ctx *c, int code, const std::string &msg) {
+    if (c) c->err = msg; else g_create_error = msg;
+    return code;
+}
+#define CU(call)                                                                                    \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess)                                                                      \
+            return fail(c, PAFGPU_ENODEVICE, std::string(#call) + ": " + cudaGetErrorString(e_));   \
+    } while (0)
+
+inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+inline unsigned blocks_for(int64_t n, int per) { return (unsigned)std::max<int64_t>(1, (n + per - 1) / per); }
+
+// exclusive scan of n u32 values into out[0..n] (u64); total also lands in *total_dev if non-null
+int scan_u32(pafgpu_ctx *c, const uint32_t *in, int64_t n, uint64_t *out, uint64_t *total_dev) {
+    if (n == 0) {
+        CU(cudaMemsetAsync(out, 0, sizeof(uint64_t), c->stream));
+        if (total_dev) CU(cudaMemsetAsync(total_dev, 0, sizeof(uint64_t), c->stream));
+        return 0;
+    }
+    const int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    CU(c->scan_sums.ensure((size_t)nb * 8));
+    uint64_t *tot = total_dev ? total_dev : c->scalars.as<uint64_t>() + SC_TMP;
+    scan_sums_kernel<<<(unsigned)nb, SCAN_THREADS, 0, c->stream>>>(in, n, c->scan_sums.as<uint64_t>());
+    scan_spine_kernel<<<1, SCAN_THREADS, 0, c->stream>>>(c->scan_sums.as<uint64_t>(), nb, tot);
+    scan_apply_kernel<<<(unsigned)nb, SCAN_THREADS, 0, c->stream>>>(in, n, c->scan_sums.as<uint64_t>(), out);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int genome_grow(pafgpu_ctx *c, GenomeStore &g, int64_t need_bases) {
+    if (need_bases <= g.cap_bases) return 0;
+    int64_t cap = std::max<int64_t>(need_bases, g.cap_bases + g.cap_bases / 2);
+    cap = align_up(cap, ARENA_ALIGN);
+    CU(cudaStreamSynchronize(c->stream));
+    // +2 words / +2 groups of slack so fetch32's second word and rank lookups one past the end stay in bounds
+    CU(g.words.ensure((size_t)(cap / 32 + 2) * 8, (size_t)(g.cap_bases / 32 + 2) * 8, true));
+    CU(g.flags.ensure((size_t)(cap / 1024 + 2) * 4, (size_t)(g.cap_bases / 1024 + 2) * 4, true));
+    CU(g.rank.ensure((size_t)(cap / 1024 + 2) * 4, (size_t)(g.cap_bases / 1024 + 2) * 4, true));
+    g.cap_bases = cap;
+    return 0;
+}
+
+// pack `len` ASCII bytes at device pointer src as a new contig
+int64_t genome_add_device(pafgpu_ctx *c, GenomeStore &g, const char *name, const uint8_t *src, int64_t len) {
+    if (len < 0 || !name) return fail(c, PAFGPU_EINVAL, "bad contig");
+    const int64_t off = g.next_off;
+    const int64_t span = align_up(len, ARENA_ALIGN) + ARENA_ALIGN;  // contig + trailing pad block
+    if (int rc = genome_grow(c, g, off + span + ARENA_ALIGN)) return rc;
+    const int64_t n_words = span / 32, n_groups = span / 1024;
+    if (len > 0) {
+        pack_kernel<<<blocks_for(n_words, 256), 256, 0, c->stream>>>(src, len, (uint64_t)off / 32, g.words.as<uint64_t>(),
+                                                                      g.flags.as<uint32_t>(), n_words);
+    }
+    // rank directory for the new groups
+    CU(c->nwin.ensure((size_t)n_groups * 4));
+    CU(c->woff.ensure((size_t)(n_groups + 1) * 8));
+    flag_popc_kernel<<<blocks_for(n_groups, 256), 256, 0, c->stream>>>(g.flags.as<uint32_t>() + off / 1024, n_groups,
+                                                                        c->nwin.as<uint32_t>());
+    if (int rc = scan_u32(c, c->nwin.as<uint32_t>(), n_groups, c->woff.as<uint64_t>(), nullptr)) return rc;
+    rank_fill_kernel<<<blocks_for(n_groups, 256), 256, 0, c->stream>>>(c->woff.as<uint64_t>(), n_groups, g.exc_total,
+                                                                        g.rank.as<uint32_t>() + off / 1024);
+    uint64_t n_exc = 0;
+    CU(cudaMemcpyAsync(&n_exc, c->woff.as<uint64_t>() + n_groups, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (n_exc) {
+        CU(g.exc.ensure((size_t)(g.exc_total + n_exc) * 32, (size_t)g.exc_total * 32));
+        exc_fill_kernel<<<blocks_for(n_words, 256), 256, 0, c->stream>>>(src, len, (uint64_t)off / 32, g.flags.as<uint32_t>(),
+                                                                          g.rank.as<uint32_t>(), g.exc.as<uint8_t>(), n_words);
+        g.exc_total += (uint32_t)n_exc;
+    } else if (!g.exc.p) {
+        CU(g.exc.ensure(32));
+    }
+    // groups after this contig (up to capacity) must report the new running total
+    {
+        const int64_t g0 = (off + span) / 1024, g1 = g.cap_bases / 1024 + 2;
+        std::vector<uint32_t> fill((size_t)std::min<int64_t>(g1 - g0, 4), g.exc_total);
+        // only the next pad / next contig start is ever consulted before being rewritten; set a few groups
+        CU(cudaMemcpyAsync(g.rank.as<uint32_t>() + g0, fill.data(), fill.size() * 4, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    }
+    CU(cudaGetLastError());
+    const int64_t id = (int64_t)g.names.size();
+    g.names.emplace_back(name);
+    g.off.push_back(off);
+    g.len.push_back(len);
+    g.index[g.names.back()] = id;  // a repeated name points at the newest contig (sonLibHash.c:68-73)
+    g.next_off = off + span;
+    g.table_dirty = true;
+    return id;
+}
+
+int64_t genome_add_host(pafgpu_ctx *c, GenomeStore &g, const char *name, const char *seq, int64_t len) {
+    CU(c->in_seq.ensure((size_t)std::max<int64_t>(len, 16)));
+    if (len > 0) CU(cudaMemcpyAsync(c->in_seq.p, seq, (size_t)len, cudaMemcpyHostToDevice, c->stream));
+    return genome_add_device(c, g, name, c->in_seq.as<uint8_t>(), len);
+}
+
+int genome_sync_table(pafgpu_ctx *c, GenomeStore &g) {
+    if (!g.table_dirty) return 0;
+    const size_t n = g.off.size();
+    CU(g.d_off.ensure(std::max<size_t>(n, 1) * 8));
+    CU(g.d_len.ensure(std::max<size_t>(n, 1) * 8));
+    if (n) {
+        CU(cudaMemcpyAsync(g.d_off.p, g.off.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(g.d_len.p, g.len.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    }
+    g.table_dirty = false;
+    return 0;
+}
+
+// (re)launch the base-comparison kernel + stitch + record offsets for c->last
+int launch_encode(pafgpu_ctx *c) {
+    EncodeParams &P = c->last;
+    uint64_t *sc = c->scalars.as<uint64_t>();
+    CU(cudaMemsetAsync(sc + SC_TICKET, 0, 16, c->stream));  // ticket + total
+    CU(cudaMemsetAsync(c->tile_desc.p, 0, (size_t)c->n_tiles * 8, c->stream));
+    CU(cudaMemsetAsync(c->tile_open_slot.p, 0xff, (size_t)c->n_tiles * 8, c->stream));
+    CU(cudaMemsetAsync(c->rec_mism.p, 0, (size_t)c->n_records * 8, c->stream));
+    if (c->n_tiles > 0) {
+        const unsigned grid = (unsigned)std::min<int64_t>((c->n_tiles + 3) / 4, (int64_t)c->sm_count * 8);
+        encode_kernel<ITERS><<<grid, 128, 0, c->stream>>>(P);
+        stitch_kernel<<<blocks_for(c->n_tiles, 256), 256, 0, c->stream>>>(c->n_tiles, P.tile_open_slot, P.tile_first_closer,
+                                                                          P.out, P.out_cap);
+    }
+    rec_out_fix_kernel<<<blocks_for(c->n_records + 1, 256), 256, 0, c->stream>>>(c->n_records, P.rec_out_begin, P.tile_desc,
+                                                                                 P.total_out);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// all arrays of *b are device pointers here
+int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_result *res) {
+    if (!b || b->n_records < 0 || b->n_ops < 0) return fail(c, PAFGPU_EINVAL, "bad batch");
+    if (b->n_ops >= (1ll << 32) || b->n_records >= (1ll << 32)) return fail(c, PAFGPU_EINVAL, "batch too large: split it");
+    if (int rc = genome_sync_table(c, g)) return rc;
+    c->have_batch = false;
+    const int64_t R = b->n_records, N = b->n_ops;
+    CU(c->scalars.ensure(SC_COUNT * 8));
+    CU(c->tpos.ensure((size_t)std::max<int64_t>(N, 1) * 8));
+    CU(c->qpos.ensure((size_t)std::max<int64_t>(N, 1) * 8));
+    CU(c->op_rec.ensure((size_t)std::max<int64_t>(N, 1) * 4));
+    CU(c->nwin.ensure((size_t)std::max<int64_t>(N, 1) * 4));
+    CU(c->woff.ensure((size_t)(N + 1) * 8));
+    CU(c->rec_out_begin.ensure((size_t)(R + 1) * 8));
+    CU(c->rec_mism.ensure((size_t)std::max<int64_t>(R, 1) * 8));
+    uint64_t *sc = c->scalars.as<uint64_t>();
+    const uint64_t init[SC_COUNT] = {~0ull, 0, 0, 0, 0, 0, 0, 0};
+    CU(cudaMemcpyAsync(sc, init, sizeof init, cudaMemcpyHostToDevice, c->stream));
+
+    CU(cudaEventRecord(c->ev[0], c->stream));
+    IngestParams I{};
+    I.n_records = R; I.n_ops = N;
+    I.op_begin = b->op_begin; I.ops = b->ops;
+    I.q_contig = b->q_contig; I.t_contig = b->t_contig;
+    I.q_start = b->q_start; I.q_end = b->q_end; I.t_start = b->t_start; I.same_strand = b->same_strand;
+    I.contig_off = g.d_off.as<int64_t>(); I.contig_len = g.d_len.as<int64_t>(); I.n_contigs = (int64_t)g.off.size();
+    I.G = g.view();
+    I.tpos = c->tpos.as<uint64_t>(); I.qpos = c->qpos.as<uint64_t>();
+    I.op_rec = c->op_rec.as<uint32_t>(); I.nwin = c->nwin.as<uint32_t>();
+    I.bad_record = (unsigned long long *)(sc + SC_BAD);
+    I.aligned = (unsigned long long *)(sc + SC_ALIGNED);
+    if (R > 0) ingest_kernel<<<blocks_for(R * 32, 256), 256, 0, c->stream>>>(I);
+    if (int rc = scan_u32(c, c->nwin.as<uint32_t>(), N, c->woff.as<uint64_t>(), sc + SC_NWIN)) return rc;
+    uint64_t host_sc[SC_COUNT];
+    CU(cudaMemcpyAsync(host_sc, sc, sizeof host_sc, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (host_sc[SC_BAD] != ~0ull) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "record %llu: CIGAR/coordinates walk outside the contig (or unknown contig id)",
+                 (unsigned long long)host_sc[SC_BAD]);
+        return fail(c, PAFGPU_EBOUNDS, msg);
+    }
+    const uint64_t n_win = host_sc[SC_NWIN];
+    const int64_t aligned = (int64_t)host_sc[SC_ALIGNED];
+    const int64_t n_tiles = (int64_t)((n_win + TILE_WINDOWS - 1) / TILE_WINDOWS);
+    CU(c->tile_first_op.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 4));
+    CU(c->tile_desc.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
+    CU(c->tile_first_closer.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
+    CU(c->tile_open_slot.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
+    if (N > 0)
+        tile_first_op_kernel<<<blocks_for(N, 256), 256, 0, c->stream>>>(c->woff.as<uint64_t>(), N, TILE_WINDOWS,
+                                                                        c->tile_first_op.as<uint32_t>());
+    CU(cudaEventRecord(c->ev[1], c->stream));
+
+    // output capacity: every input op + ~6% of aligned bases as run starts; grown and re-run if short
+    int64_t cap = std::max<int64_t>((int64_t)(c->out.cap / 8), N + aligned / 16 + 1024);
+    CU(c->out.ensure((size_t)cap * 8));
+    cap = (int64_t)(c->out.cap / 8);
+
+    EncodeParams &P = c->last;
+    P.G = g.view();
+    P.ops = b->ops; P.woff = c->woff.as<uint64_t>(); P.tpos = c->tpos.as<uint64_t>(); P.qpos = c->qpos.as<uint64_t>();
+    P.op_rec = c->op_rec.as<uint32_t>(); P.tile_first_op = c->tile_first_op.as<uint32_t>();
+    P.n_ops = N; P.n_win = n_win; P.n_tiles = n_tiles;
+    P.out = c->out.as<uint64_t>(); P.out_cap = cap;
+    P.tile_desc = c->tile_desc.as<unsigned long long>();
+    P.tile_first_closer = c->tile_first_closer.as<uint64_t>();
+    P.tile_open_slot = c->tile_open_slot.as<int64_t>();
+    P.rec_out_begin = c->rec_out_begin.as<int64_t>();
+    P.rec_mism = c->rec_mism.as<unsigned long long>();
+    P.ticket = (unsigned int *)(sc + SC_TICKET);
+    P.total_out = (unsigned long long *)(sc + SC_TOTAL);
+    c->n_records = R; c->n_ops = N; c->n_tiles = n_tiles; c->n_win = n_win;
+
+    int retried = 0;
+    uint64_t total = 0;
+    for (;;) {
+        CU(cudaEventRecord(c->ev[2], c->stream));
+        if (int rc = launch_encode(c)) return rc;
+        CU(cudaEventRecord(c->ev[3], c->stream));
+        CU(cudaMemcpyAsync(&total, sc + SC_TOTAL, 8, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        if ((int64_t)total <= P.out_cap) break;
+        if (retried) return fail(c, PAFGPU_ENODEVICE, "output capacity still short after retry");
+        retried = 1;
+        CU(c->out.ensure((size_t)total * 8));
+        P.out = c->out.as<uint64_t>();
+        P.out_cap = (int64_t)(c->out.cap / 8);
+    }
+    c->n_out = (int64_t)total;
+    c->have_batch = true;
+    if (res) {
+        memset(res, 0, sizeof *res);
+        res->n_out_ops = c->n_out;
+        res->aligned_bases = aligned;
+        res->n_windows = (int64_t)n_win;
+        res->n_tiles = n_tiles;
+        res->retried = retried;
+        cudaEventElapsedTime(&res->ms_ingest, c->ev[0], c->ev[1]);
+        cudaEventElapsedTime(&res->ms_encode, c->ev[2], c->ev[3]);
+    }
+    return 0;
+}
+
+int encode_host(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_result *res) {
+    if (!b) return fail(c, PAFGPU_EINVAL, "null batch");
+    const int64_t R = b->n_records, N = b->n_ops;
+    auto up = [&](DevBuf &d, const void *src, size_t bytes) -> int {
+        CU(d.ensure(std::max<size_t>(bytes, 8)));
+        if (bytes) CU(cudaMemcpyAsync(d.p, src, bytes, cudaMemcpyHostToDevice, c->stream));
+        return 0;
+    };
+    int rc;
+    if ((rc = up(c->in_op_begin, b->op_begin, (size_t)(R + 1) * 8))) return rc;
+    if ((rc = up(c->in_ops, b->ops, (size_t)N * 8))) return rc;
+    if ((rc = up(c->in_qc, b->q_contig, (size_t)R * 4))) return rc;
+    if ((rc = up(c->in_tc, b->t_contig, (size_t)R * 4))) return rc;
+    if ((rc = up(c->in_qs, b->q_start, (size_t)R * 8))) return rc;
+    if ((rc = up(c->in_qe, b->q_end, (size_t)R * 8))) return rc;
+    if ((rc = up(c->in_ts, b->t_start, (size_t)R * 8))) return rc;
+    if ((rc = up(c->in_strand, b->same_strand, (size_t)R))) return rc;
+    pafgpu_batch d = *b;
+    d.op_begin = c->in_op_begin.as<int64_t>(); d.ops = c->in_ops.as<uint64_t>();
+    d.q_contig = c->in_qc.as<int32_t>(); d.t_contig = c->in_tc.as<int32_t>();
+    d.q_start = c->in_qs.as<int64_t>(); d.q_end = c->in_qe.as<int64_t>(); d.t_start = c->in_ts.as<int64_t>();
+    d.same_strand = c->in_strand.as<uint8_t>();
+    return encode_device(c, g, &d, res);
+}
+
+int fetch_ops(pafgpu_ctx *c, uint64_t *out_ops, int64_t *out_op_begin, int64_t *rec_mismatch) {
+    if (!c->have_batch) return fail(c, PAFGPU_ESTATE, "no batch has been encoded");
+    if (out_ops && c->n_out) CU(cudaMemcpyAsync(out_ops, c->out.p, (size_t)c->n_out * 8, cudaMemcpyDeviceToHost, c->stream));
+    if (out_op_begin)
+        CU(cudaMemcpyAsync(out_op_begin, c->rec_out_begin.p, (size_t)(c->n_records + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+    if (rec_mismatch && c->n_records)
+        CU(cudaMemcpyAsync(rec_mismatch, c->rec_mism.p, (size_t)c->n_records * 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+}  // namespace
+
+// ================================================================================================
+extern "C" {
+
+int pafgpu_abi_version(void) { return PAFGPU_ABI_VERSION; }
+
+int pafgpu_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int pafgpu_create(int device, pafgpu_ctx **out) {
+    pafgpu_ctx *c = nullptr;
+    if (!out) return fail(c, PAFGPU_EINVAL, "null out");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(c, PAFGPU_ENODEVICE, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "count is 0") +
+                                             " (paffy_b200 has no CPU fallback)");
+    if (device < 0 || device >= n) return fail(c, PAFGPU_EINVAL, "device index out of range");
+    CU(cudaSetDevice(device));
+    pafgpu_ctx *ctx = new pafgpu_ctx();
+    ctx->device = device;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
+    c = ctx;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ctx;
+        c = nullptr;
+        return fail(c, PAFGPU_ENODEVICE, "cudaStreamCreate failed");
+    }
+    for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    ctx->scalars.ensure(SC_COUNT * 8);
+    *out = ctx;
+    return 0;
+}
+
+void pafgpu_destroy(pafgpu_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    c->genome.release();
+    c->scratch.release();
+    DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
+                      &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
+                      &c->tile_desc, &c->tile_first_closer, &c->tile_open_slot, &c->out, &c->rec_out_begin, &c->rec_mism,
+                      &c->scalars, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
+                      &c->ser_text};
+    for (DevBuf *b : bufs) b->release();
+    for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char *pafgpu_last_error(const pafgpu_ctx *c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+// ---- genome store ------------------------------------------------------------------------------
+int pafgpu_genome_reserve(pafgpu_ctx *c, int64_t total_bases) {
+    if (!c) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    return genome_grow(c, c->genome, c->genome.next_off + total_bases + 2 * ARENA_ALIGN);
+}
+
+int64_t pafgpu_genome_add_contig(pafgpu_ctx *c, const char *name, const char *seq, int64_t len) {
+    if (!c || !name || (!seq && len)) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    return genome_add_host(c, c->genome, name, seq, len);
+}
+
+int64_t pafgpu_genome_add_contig_device(pafgpu_ctx *c, const char *name, const void *seq_dev, int64_t len) {
+    if (!c || !name || (!seq_dev && len)) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    CU(cudaDeviceSynchronize());  // the producer of seq_dev may be on another stream
+    return genome_add_device(c, c->genome, name, static_cast<const uint8_t *>(seq_dev), len);
+}
+
+int pafgpu_genome_load_fasta(pafgpu_ctx *c, const char *path) {
+    if (!c || !path) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    FILE *fh = fopen(path, "rb");
+    if (!fh) return fail(c, PAFGPU_EIO, std::string("cannot open ") + path);
+    // Reader state machine with the admission rules of bioioC.c:155-209: everything before the first
+    // '>' is skipped; the header is the whole line; a '>' anywhere in the sequence starts a new record.
+    std::vector<char> buf(1 << 22);
+    std::string name, seq;
+    enum { PRE, HEADER, SEQ } st = PRE;
+    int rc = 0;
+    size_t got;
+    auto flush = [&]() -> int {
+        const int64_t id = genome_add_host(c, c->genome, name.c_str(), seq.data(), (int64_t)seq.size());
+        return id < 0 ? (int)id : 0;
+    };
+    while (rc == 0 && (got = fread(buf.data(), 1, buf.size(), fh)) > 0) {
+        size_t i = 0;
+        while (i < got && rc == 0) {
+            if (st == PRE) {
+                const char *p = (const char *)memchr(buf.data() + i, '>', got - i);
+                if (!p) { i = got; break; }
+                i = (size_t)(p - buf.data()) + 1;
+                st = HEADER; name.clear(); seq.clear();
+            } else if (st == HEADER) {
+                const char *p = (const char *)memchr(buf.data() + i, '\n', got - i);
+                const size_t e = p ? (size_t)(p - buf.data()) : got;
+                name.append(buf.data() + i, e - i);
+                i = e;
+                if (p) { i++; st = SEQ; }
+            } else {
+                const char ch = buf[i];
+                if (ch == '>') {
+                    rc = flush();
+                    st = HEADER; name.clear(); seq.clear();
+                    i++;
+                } else if (ch == '\n' || ch == ' ' || ch == '\t') {
+                    i++;
+                } else {
+                    // consume a run of admissible bytes up to the next separator
+                    size_t e = i;
+                    while (e < got) {
+                        const unsigned char u = (unsigned char)buf[e];
+                        if (u == '\n' || u == ' ' || u == '\t' || u == '>') break;
+                        if (!isalpha(u) && u != '-') {
+                            char msg[96];
+                            snprintf(msg, sizeof msg, "!!Got an unexpected character in input fasta sequence: '%c' ", (char)u);
+                            rc = fail(c, PAFGPU_EFASTA, msg);
+                            break;
+                        }
+                        e++;
+                    }
+                    seq.append(buf.data() + i, e - i);
+                    i = e;
+                }
+            }
+        }
+    }
+    fclose(fh);
+    if (rc == 0 && st != PRE) rc = flush();  // EOF right after a header still yields an (empty) contig
+    return rc;
+}
+
+int64_t pafgpu_genome_find(const pafgpu_ctx *c, const char *name) {
+    if (!c || !name) return PAFGPU_EINVAL;
+    auto it = c->genome.index.find(name);
+    return it == c->genome.index.end() ? (int64_t)PAFGPU_ENOCONTIG : it->second;
+}
+
+int64_t pafgpu_genome_contig_length(const pafgpu_ctx *c, int64_t id) {
+    if (!c || id < 0 || id >= (int64_t)c->genome.len.size()) return PAFGPU_ENOCONTIG;
+    return c->genome.len[(size_t)id];
+}
+
+int64_t pafgpu_genome_num_contigs(const pafgpu_ctx *c) { return c ? (int64_t)c->genome.index.size() : PAFGPU_EINVAL; }
+
+int pafgpu_genome_fetch(pafgpu_ctx *c, int64_t id, int64_t start, int64_t len, char *out) {
+    if (!c || !out) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (id < 0 || id >= (int64_t)c->genome.len.size()) return fail(c, PAFGPU_ENOCONTIG, "bad contig id");
+    if (start < 0 || len < 0 || start + len > c->genome.len[(size_t)id]) return fail(c, PAFGPU_EBOUNDS, "range outside contig");
+    if (len == 0) return 0;
+    CU(cudaSetDevice(c->device));
+    CU(c->in_seq.ensure((size_t)len));
+    unpack_kernel<<<blocks_for(len, 256), 256, 0, c->stream>>>(c->genome.view(), (uint64_t)(c->genome.off[(size_t)id] + start), len,
+                                                               c->in_seq.as<uint8_t>());
+    CU(cudaMemcpyAsync(out, c->in_seq.p, (size_t)len, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// ---- batch encode ------------------------------------------------------------------------------
+int pafgpu_encode_batch_host(pafgpu_ctx *c, const pafgpu_batch *b, pafgpu_result *res) {
+    if (!c) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    return encode_host(c, c->genome, b, res);
+}
+
+int pafgpu_encode_batch_device(pafgpu_ctx *c, const pafgpu_batch *b, pafgpu_result *res) {
+    if (!c) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    CU(cudaDeviceSynchronize());  // inputs may have been produced on another stream
+    return encode_device(c, c->genome, b, res);
+}
+
+int pafgpu_fetch_ops(pafgpu_ctx *c, uint64_t *out_ops, int64_t *out_op_begin, int64_t *rec_mismatch) {
+    if (!c) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    return fetch_ops(c, out_ops, out_op_begin, rec_mismatch);
+}
+
+int pafgpu_result_device_ptrs(pafgpu_ctx *c, const uint64_t **out_ops, const int64_t **out_op_begin, const int64_t **rec_mismatch) {
+    if (!c) return PAFGPU_EINVAL;
+    if (!c->have_batch) return fail(c, PAFGPU_ESTATE, "no batch has been encoded");
+    if (out_ops) *out_ops = c->out.as<uint64_t>();
+    if (out_op_begin) *out_op_begin = c->rec_out_begin.as<int64_t>();
+    if (rec_mismatch) *rec_mismatch = c->rec_mism.as<int64_t>();
+    return 0;
+}
+
+int pafgpu_time_encode(pafgpu_ctx *c, int reps, float *ms_mean, float *ms_min) {
+    if (!c || reps <= 0) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!c->have_batch) return fail(c, PAFGPU_ESTATE, "no batch has been encoded");
+    CU(cudaSetDevice(c->device));
+    double sum = 0;
+    float best = 1e30f;
+    for (int i = 0; i < reps; i++) {
+        CU(cudaEventRecord(c->ev[2], c->stream));
+        if (int rc = launch_encode(c)) return rc;
+        CU(cudaEventRecord(c->ev[3], c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]);
+        sum += ms;
+        best = std::min(best, ms);
+    }
+    if (ms_mean) *ms_mean = (float)(sum / reps);
+    if (ms_min) *ms_min = best;
+    return 0;
+}
+
+// ---- one record with raw host strings (paf_encode_mismatches, impl/paf.c:739-784) ----------------
+int pafgpu_encode_one(pafgpu_ctx *c, const uint64_t *ops, int64_t n_ops, int same_strand, int64_t query_start, int64_t query_end,
+                      int64_t target_start, const char *query_seq, const char *target_seq, uint64_t **out_ops, int64_t *n_out,
+                      int64_t *mismatches) {
+    if (!c || !ops || n_ops < 0 || !out_ops || !n_out || !query_seq || !target_seq) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    // spans the record touches; zero-length M ops vanish (a1-edge ii)
+    std::vector<uint64_t> kept;
+    kept.reserve((size_t)n_ops);
+    int64_t t_span = 0, q_span = 0;
+    for (int64_t k = 0; k < n_ops; k++) {
+        const int code = (int)(ops[k] >> 56);
+        const int64_t len = (int64_t)(ops[k] & LEN_MASK);
+        if (code == OP_M && len == 0) continue;
+        kept.push_back(ops[k]);
+        if (code != OP_I) t_span += len;
+        if (code != OP_D) q_span += len;
+    }
+    *out_ops = nullptr;
+    *n_out = 0;
+    if (mismatches) *mismatches = 0;
+    if (kept.empty()) { *out_ops = (uint64_t *)malloc(8); return 0; }
+    const int64_t q_lo = same_strand ? query_start : query_end - q_span;
+    if (q_lo < 0 || target_start < 0) return fail(c, PAFGPU_EBOUNDS, "record walks before the start of a sequence");
+    GenomeStore &g = c->scratch;
+    g.reset();
+    const int64_t tid = genome_add_host(c, g, "t", target_seq + target_start, t_span);
+    if (tid < 0) return (int)tid;
+    const int64_t qid = genome_add_host(c, g, "q", query_seq + q_lo, q_span);
+    if (qid < 0) return (int)qid;
+    const int64_t op_begin[2] = {0, (int64_t)kept.size()};
+    const int32_t qc = (int32_t)qid, tc = (int32_t)tid;
+    const int64_t qs = 0, qe = q_span, ts = 0;
+    const uint8_t strand = same_strand ? 1 : 0;
+    pafgpu_batch b{1, (int64_t)kept.size(), op_begin, kept.data(), &qc, &tc, &qs, &qe, &ts, &strand};
+    pafgpu_result res;
+    if (int rc = encode_host(c, g, &b, &res)) return rc;
+    uint64_t *o = (uint64_t *)malloc((size_t)std::max<int64_t>(res.n_out_ops, 1) * 8);
+    int64_t mm = 0;
+    if (int rc = fetch_ops(c, o, nullptr, &mm)) { free(o); return rc; }
+    *out_ops = o;
+    *n_out = res.n_out_ops;
+    if (mismatches) *mismatches = mm;
+    return 0;
+}
+
+// ---- device serialiser ---------------------------------------------------------------------------
+int pafgpu_serialise(pafgpu_ctx *c, const char *prefix_bytes, const int64_t *prefix_begin, int64_t *text_bytes_out, float *ms_out) {
+    if (!c || !prefix_bytes || !prefix_begin) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!c->have_batch) return fail(c, PAFGPU_ESTATE, "no batch has been encoded");
+    CU(cudaSetDevice(c->device));
+    const int64_t R = c->n_records, K = c->n_out;
+    const int64_t pre_bytes = prefix_begin[R];
+    CU(c->ser_prefix.ensure((size_t)std::max<int64_t>(pre_bytes, 8)));
+    CU(c->ser_prefix_begin.ensure((size_t)(R + 1) * 8));
+    CU(cudaMemcpyAsync(c->ser_prefix.p, prefix_bytes, (size_t)pre_bytes, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->ser_prefix_begin.p, prefix_begin, (size_t)(R + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    CU(c->ser_oplen.ensure((size_t)std::max<int64_t>(K, 1) * 4));
+    CU(c->ser_optoff.ensure((size_t)(K + 1) * 8));
+    CU(c->ser_line_begin.ensure((size_t)(R + 1) * 8));
+    CU(cudaEventRecord(c->ev[0], c->stream));
+    if (K > 0) op_text_len_kernel<<<blocks_for(K, 256), 256, 0, c->stream>>>(c->out.as<uint64_t>(), K, c->ser_oplen.as<uint32_t>());
+    if (int rc = scan_u32(c, c->ser_oplen.as<uint32_t>(), K, c->ser_optoff.as<uint64_t>(), nullptr)) return rc;
+    // line_begin[r] = prefix_begin[r] + optoff[rec_out_begin[r]] + r   (prefixes + cigar text + newlines before r)
+    line_begin_kernel<<<blocks_for(R + 1, 256), 256, 0, c->stream>>>(R, c->ser_prefix_begin.as<int64_t>(), c->rec_out_begin.as<int64_t>(),
+                                                                     c->ser_optoff.as<uint64_t>(), c->ser_line_begin.as<int64_t>());
+    int64_t total = 0;
+    CU(cudaMemcpyAsync(&total, c->ser_line_begin.as<int64_t>() + R, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(c->ser_text.ensure((size_t)std::max<int64_t>(total, 8)));
+    SerialiseParams S{};
+    S.n_records = R; S.n_out = K;
+    S.out = c->out.as<uint64_t>(); S.rec_out_begin = c->rec_out_begin.as<int64_t>();
+    S.op_toff = c->ser_optoff.as<uint64_t>();
+    S.prefix = c->ser_prefix.as<char>(); S.prefix_begin = c->ser_prefix_begin.as<int64_t>();
+    S.line_begin = c->ser_line_begin.as<int64_t>(); S.text = c->ser_text.as<char>();
+    if (R > 0) prefix_copy_kernel<<<blocks_for(R * 32, 256), 256, 0, c->stream>>>(S);
+    if (K > 0) op_text_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(S);
+    CU(cudaEventRecord(c->ev[1], c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    c->ser_text_bytes = total;
+    if (text_bytes_out) *text_bytes_out = total;
+    if (ms_out) cudaEventElapsedTime(ms_out, c->ev[0], c->ev[1]);
+    return 0;
+}
+
+int pafgpu_fetch_text(pafgpu_ctx *c, char *text, int64_t *line_begin) {
+    if (!c) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!c->have_batch) return fail(c, PAFGPU_ESTATE, "no batch has been serialised");
+    CU(cudaSetDevice(c->device));
+    if (text && c->ser_text_bytes)
+        CU(cudaMemcpyAsync(text, c->ser_text.p, (size_t)c->ser_text_bytes, cudaMemcpyDeviceToHost, c->stream));
+    if (line_begin)
+        CU(cudaMemcpyAsync(line_begin, c->ser_line_begin.p, (size_t)(c->n_records + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+}  // extern "C"

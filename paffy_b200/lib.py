@@ -1,0 +1,214 @@
+"""ctypes binding of libpaffy_b200.so (the C ABI declared in include/paffy_b200.h).
+
+Plumbing only: every computation happens in the CUDA library. There is no CPU fallback; creating a
+Context without a CUDA device raises PafGpuError.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libpaffy_b200.so")
+
+# symbols include/paffy_b200.h declares (tests check that the library exports every one)
+ABI_SYMBOLS = [
+    "pafgpu_abi_version", "pafgpu_device_count", "pafgpu_create", "pafgpu_destroy", "pafgpu_last_error",
+    "pafgpu_genome_reserve", "pafgpu_genome_add_contig", "pafgpu_genome_add_contig_device", "pafgpu_genome_load_fasta",
+    "pafgpu_genome_find", "pafgpu_genome_contig_length", "pafgpu_genome_num_contigs", "pafgpu_genome_fetch",
+    "pafgpu_encode_batch_host", "pafgpu_encode_batch_device", "pafgpu_fetch_ops", "pafgpu_result_device_ptrs",
+    "pafgpu_serialise", "pafgpu_fetch_text", "pafgpu_encode_one", "pafgpu_time_encode",
+]
+
+
+class PafGpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"paffy_b200 error {code}: {msg}")
+        self.code = code
+
+
+class Batch(C.Structure):
+    _fields_ = [("n_records", C.c_int64), ("n_ops", C.c_int64), ("op_begin", C.c_void_p), ("ops", C.c_void_p),
+                ("q_contig", C.c_void_p), ("t_contig", C.c_void_p), ("q_start", C.c_void_p), ("q_end", C.c_void_p),
+                ("t_start", C.c_void_p), ("same_strand", C.c_void_p)]
+
+
+class Result(C.Structure):
+    _fields_ = [("n_out_ops", C.c_int64), ("aligned_bases", C.c_int64), ("n_windows", C.c_int64), ("n_tiles", C.c_int64),
+                ("retried", C.c_int64), ("ms_ingest", C.c_float), ("ms_encode", C.c_float)]
+
+
+_lib = None
+
+
+def load():
+    """Load (building if stale and nvcc is present) the CUDA library. Fails loudly when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH) or (_build.stale() and os.path.exists("/usr/local/cuda/bin/nvcc")):
+        _build.build()
+    if not os.path.exists(LIB_PATH):
+        raise PafGpuError(-1, f"{LIB_PATH} is missing: run `python -m paffy_b200.build` (no CPU fallback exists)")
+    L = C.CDLL(LIB_PATH)
+    vp, i64, i64p = C.c_void_p, C.c_int64, C.POINTER(C.c_int64)
+    L.pafgpu_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.pafgpu_destroy.argtypes = [vp]
+    L.pafgpu_destroy.restype = None
+    L.pafgpu_last_error.argtypes = [vp]
+    L.pafgpu_last_error.restype = C.c_char_p
+    L.pafgpu_genome_reserve.argtypes = [vp, i64]
+    L.pafgpu_genome_add_contig.argtypes = [vp, C.c_char_p, vp, i64]
+    L.pafgpu_genome_add_contig.restype = i64
+    L.pafgpu_genome_add_contig_device.argtypes = [vp, C.c_char_p, vp, i64]
+    L.pafgpu_genome_add_contig_device.restype = i64
+    L.pafgpu_genome_load_fasta.argtypes = [vp, C.c_char_p]
+    L.pafgpu_genome_find.argtypes = [vp, C.c_char_p]
+    L.pafgpu_genome_find.restype = i64
+    L.pafgpu_genome_contig_length.argtypes = [vp, i64]
+    L.pafgpu_genome_contig_length.restype = i64
+    L.pafgpu_genome_num_contigs.argtypes = [vp]
+    L.pafgpu_genome_num_contigs.restype = i64
+    L.pafgpu_genome_fetch.argtypes = [vp, i64, i64, i64, vp]
+    L.pafgpu_encode_batch_host.argtypes = [vp, C.POINTER(Batch), C.POINTER(Result)]
+    L.pafgpu_encode_batch_device.argtypes = [vp, C.POINTER(Batch), C.POINTER(Result)]
+    L.pafgpu_fetch_ops.argtypes = [vp, vp, vp, vp]
+    L.pafgpu_result_device_ptrs.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    L.pafgpu_serialise.argtypes = [vp, vp, vp, i64p, C.POINTER(C.c_float)]
+    L.pafgpu_fetch_text.argtypes = [vp, vp, vp]
+    L.pafgpu_encode_one.argtypes = [vp, vp, i64, C.c_int, i64, i64, i64, vp, vp, C.POINTER(vp), i64p, i64p]
+    L.pafgpu_time_encode.argtypes = [vp, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    """Host numpy array or torch tensor (any device) -> raw pointer."""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()  # torch tensor
+
+
+def _is_device(a):
+    return not isinstance(a, np.ndarray) and getattr(a, "is_cuda", False)
+
+
+class Context:
+    """One GPU context: a packed genome store plus the batch encode / serialise pipeline."""
+
+    def __init__(self, device=0):
+        self.L = load()
+        h = C.c_void_p()
+        rc = self.L.pafgpu_create(device, C.byref(h))
+        if rc:
+            raise PafGpuError(rc, self.L.pafgpu_last_error(None).decode())
+        self.h = h
+        self.n_records = 0
+        self.result = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.pafgpu_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _check(self, rc):
+        if rc < 0:
+            raise PafGpuError(rc, self.L.pafgpu_last_error(self.h).decode())
+        return rc
+
+    # ---- genome store
+    def reserve(self, total_bases):
+        self._check(self.L.pafgpu_genome_reserve(self.h, total_bases))
+
+    def add_contig(self, name, seq):
+        """seq: bytes / numpy uint8 (host) or a torch cuda uint8 tensor (device resident)."""
+        if _is_device(seq):
+            assert seq.is_contiguous()
+            return self._check(self.L.pafgpu_genome_add_contig_device(self.h, name.encode(), seq.data_ptr(), seq.numel()))
+        if isinstance(seq, (bytes, bytearray)):
+            buf = (C.c_char * len(seq)).from_buffer_copy(seq) if len(seq) else None
+            return self._check(self.L.pafgpu_genome_add_contig(self.h, name.encode(), C.cast(buf, C.c_void_p), len(seq)))
+        seq = np.ascontiguousarray(seq, dtype=np.uint8)
+        return self._check(self.L.pafgpu_genome_add_contig(self.h, name.encode(), seq.ctypes.data, seq.size))
+
+    def load_fasta(self, path):
+        self._check(self.L.pafgpu_genome_load_fasta(self.h, path.encode()))
+
+    def find(self, name):
+        return self.L.pafgpu_genome_find(self.h, name.encode())
+
+    def contig_length(self, cid):
+        return self.L.pafgpu_genome_contig_length(self.h, cid)
+
+    def num_contigs(self):
+        return self.L.pafgpu_genome_num_contigs(self.h)
+
+    def fetch_bases(self, cid, start, length):
+        out = np.empty(length, dtype=np.uint8)
+        self._check(self.L.pafgpu_genome_fetch(self.h, cid, start, length, out.ctypes.data))
+        return out.tobytes()
+
+    # ---- batch encode
+    def encode_batch(self, op_begin, ops, q_contig, t_contig, q_start, q_end, t_start, same_strand):
+        """All eight arrays either host numpy (int64/uint64/int32/uint8) or torch cuda tensors."""
+        arrs = [op_begin, ops, q_contig, t_contig, q_start, q_end, t_start, same_strand]
+        dev = _is_device(ops)
+        if not dev:
+            want = [np.int64, np.uint64, np.int32, np.int32, np.int64, np.int64, np.int64, np.uint8]
+            arrs = [a if not isinstance(a, np.ndarray) else np.ascontiguousarray(a, dtype=t) for a, t in zip(arrs, want)]
+        n_records = int(arrs[0].shape[0]) - 1
+        n_ops = int(arrs[1].shape[0])
+        b = Batch(n_records, n_ops, *[_ptr(a) for a in arrs])
+        res = Result()
+        fn = self.L.pafgpu_encode_batch_device if dev else self.L.pafgpu_encode_batch_host
+        self._check(fn(self.h, C.byref(b), C.byref(res)))
+        self._keep = arrs  # device inputs are referenced by pafgpu_time_encode
+        self.n_records = n_records
+        self.result = res
+        return res
+
+    def fetch_ops(self, want_ops=True, pinned=None):
+        """-> (out_ops uint64[n_out], out_op_begin int64[R+1], rec_mismatch int64[R])"""
+        n_out, R = self.result.n_out_ops, self.n_records
+        ops = np.empty(n_out, dtype=np.uint64) if want_ops and pinned is None else pinned
+        begin = np.empty(R + 1, dtype=np.int64)
+        mism = np.empty(R, dtype=np.int64)
+        self._check(self.L.pafgpu_fetch_ops(self.h, _ptr(ops) if want_ops else None, begin.ctypes.data, mism.ctypes.data))
+        return ops, begin, mism
+
+    def time_encode(self, reps):
+        mean, best = C.c_float(), C.c_float()
+        self._check(self.L.pafgpu_time_encode(self.h, reps, C.byref(mean), C.byref(best)))
+        return mean.value, best.value
+
+    def serialise(self, prefix_bytes, prefix_begin):
+        prefix_begin = np.ascontiguousarray(prefix_begin, dtype=np.int64)
+        pb = np.frombuffer(prefix_bytes, dtype=np.uint8) if isinstance(prefix_bytes, (bytes, bytearray)) else prefix_bytes
+        n, ms = C.c_int64(), C.c_float()
+        self._check(self.L.pafgpu_serialise(self.h, _ptr(pb), prefix_begin.ctypes.data, C.byref(n), C.byref(ms)))
+        self.text_bytes = n.value
+        return n.value, ms.value
+
+    def fetch_text(self, pinned=None):
+        buf = np.empty(self.text_bytes, dtype=np.uint8) if pinned is None else pinned
+        lines = np.empty(self.n_records + 1, dtype=np.int64)
+        self._check(self.L.pafgpu_fetch_text(self.h, _ptr(buf), lines.ctypes.data))
+        return buf, lines
+
+    def encode_one(self, ops, same_strand, q_start, q_end, t_start, query_seq, target_seq):
+        """paf_encode_mismatches on one record with whole-contig host strings -> (uint64 ops, mismatches)."""
+        ops = np.ascontiguousarray(ops, dtype=np.uint64)
+        out, n, mm = C.c_void_p(), C.c_int64(), C.c_int64()
+        q = C.create_string_buffer(query_seq, len(query_seq) + 1)
+        t = C.create_string_buffer(target_seq, len(target_seq) + 1)
+        self._check(self.L.pafgpu_encode_one(self.h, ops.ctypes.data, ops.size, int(same_strand), q_start, q_end, t_start,
+                                             C.cast(q, C.c_void_p), C.cast(t, C.c_void_p), C.byref(out), C.byref(n), C.byref(mm)))
+        res = np.ctypeslib.as_array(C.cast(out, C.POINTER(C.c_uint64)), shape=(max(n.value, 1),))[: n.value].copy()
+        C.CDLL(None).free(out)
+        return res, mm.value
