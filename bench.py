@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""bench.py - add_mismatches aligned bp/s on synthetic genomes + PAFs of BASELINE.json's shapes.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C2|C3|C4|small|tiny] [--scale f]
+  python bench.py --impl reference ...      (the reference's own CPU code on the host cores)
+
+One process per GPU (torchrun for N > 1; records are sharded, the packed genome is replicated, no
+data-path collective). A step is one pass of the hot path (CIGAR ingest + base-comparison kernel +
+stitch) over one batch of records. `value`: inputs resident in HBM. `e2e`: the C-ABI host call with
+pinned host buffers - H2D of the batch, ingest + kernel + device serialiser, D2H of the PAF text.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = "add_mismatches aligned bp/sec"
+UNIT = "aligned bp/s"
+KERNELS_PER_STEP = 8       # ingest, 3x scan, tile_first_op, encode, stitch, rec_out_fix
+KERNELS_PER_E2E_STEP = 15  # + op_text_len, 3x scan, line_begin, prefix_copy, op_text
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class Clocks:
+    """Sample nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        self.p.wait()
+        self.f.flush()
+        rows = [r.strip().split(", ") for r in open(self.f.name) if r.strip()]
+        os.unlink(self.f.name)
+        sm = [float(r[0]) for r in rows if r[0].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in rows for i in range(4) if len(r) >= 6 and r[2 + i].strip() == "Active"})
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": float(rows[0][1]) if rows and rows[0][1].replace(".", "").isdigit() else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def render_prefixes(rec):
+    """Host-rendered text of every record up to and including '\\tcg:Z:' (what paf_write_to_buffer emits
+    before the CIGAR, impl/paf.c:320-368) -> (uint8 array, int64 offsets)."""
+    c = {k: rec[k].cpu().numpy() for k in ("contig", "ts", "te", "qs", "qe", "strand", "sum_m", "q_len")}
+    ob = rec["op_begin"].cpu().numpy()
+    ops = rec["ops"].cpu().numpy()
+    tot = np.add.reduceat(ops & ((1 << 56) - 1), ob[:-1])
+    clen = rec["clen"]
+    parts = [f"q{ci + 1}\t{ql}\t{qs}\t{qe}\t{'+' if st else '-'}\tt{ci + 1}\t{clen}\t{ts}\t{te}\t{sm}\t{tt}\t60\ttp:A:P\tAS:i:{sm}\tcg:Z:"
+             for ci, ql, qs, qe, st, ts, te, sm, tt in zip(c["contig"].tolist(), c["q_len"].tolist(), c["qs"].tolist(), c["qe"].tolist(),
+                                                           c["strand"].tolist(), c["ts"].tolist(), c["te"].tolist(), c["sum_m"].tolist(),
+                                                           tot.tolist())]
+    lens = np.fromiter((len(p) for p in parts), dtype=np.int64, count=len(parts))
+    begin = np.zeros(len(parts) + 1, dtype=np.int64)
+    np.cumsum(lens, out=begin[1:])
+    return np.frombuffer("".join(parts).encode(), dtype=np.uint8), begin
+
+
+def cpu_sample(workload, scale, n_sample, device):
+    """A bounded sample of the same workload (same generator, law and rates) restricted to contig pairs
+    1 and 2 (one '+', one '-'), written as FASTA + PAF for the compiled reference."""
+    from paffy_b200 import synth
+    n_contigs, clen, n_rec, law, s, g = synth.CONFIGS[workload]
+    d = tempfile.mkdtemp(prefix="paffy_b200_cpu_")
+    fa, paf = os.path.join(d, "sample.fa"), os.path.join(d, "sample.paf")
+    total_m = 0
+    with open(fa, "wb") as ffa, open(paf, "w") as fpaf:
+        for i in range(min(2, n_contigs)):
+            c = synth.make_contig(i, clen, s, g, synth.MASTER_SEED, device, keep_truth=False)
+            p = synth.contig_records(c, n_sample // 2, law, synth.MASTER_SEED + 4242, device)
+            p["q_len"] = torch.full((p["n"],), c.Lq, dtype=torch.int64)
+            p["clen"] = clen
+            for name, asc in ((c.name_t, c.t_ascii), (c.name_q, c.q_ascii)):
+                ffa.write(b">" + name.encode() + b"\n")
+                ffa.write(asc.cpu().numpy().tobytes())
+                ffa.write(b"\n")
+            fpaf.write("\n".join(synth.paf_lines(p, range(p["n"]))) + "\n")
+            total_m += int(p["sum_m"].sum().item())
+            del c, p
+    return d, fa, paf, total_m
+
+
+def run_reference(fa, paf, threads, reps):
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_bench")
+    if not os.access(exe, os.X_OK):
+        return None
+    env = dict(os.environ, REF_BENCH_REPS=str(reps))
+    r = subprocess.run([exe, str(threads), paf, fa], capture_output=True, text=True, env=env)
+    if r.returncode:
+        sys.stderr.write(r.stderr)
+        return None
+    return json.loads(r.stdout)
+
+
+def reference_arm(args, rank):
+    """The reference's own CPU implementation (oracle/_ref/ref_bench: unmodified paf_encode_mismatches on all
+    host threads) on a bounded sample of the same workload. Rank 0 only."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    device = "cuda" if torch.cuda.is_available() else "cpu"
+    n_sample = args.cpu_sample
+    d, fa, paf, total_m = cpu_sample(args.workload, args.scale, n_sample, device)
+    t0 = time.time()
+    out = run_reference(fa, paf, cores, args.warmup + args.steps)
+    if out is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_bench is not built (needs /root/reference at build time)"}))
+        return
+    reps = out["reps"][args.warmup:]
+    secs = sum(r["encode_s"] for r in reps)
+    bp = sum(r["aligned_bp"] for r in reps)
+    value = bp / secs
+    sample = (f"{reps[0]['records']} records of workload {args.workload} on contig pairs t1/q1 (+) and t2/q2 (-), {reps[0]['aligned_bp']} aligned bp per step; "
+              f"paf_encode_mismatches only (FASTA load {out['load_s']:.1f}s and PAF parse {reps[0]['parse_s']:.2f}s excluded)")
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * secs / len(reps), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic", "impl": "reference",
+            "config": {"workload": f"{args.workload} (sampled)", "records_per_step": reps[0]["records"]},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "wall_s": time.time() - t0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="paffy_b200")
+    ap.add_argument("--workload", default="C2")
+    ap.add_argument("--scale", type=float, default=1.0, help="fraction of the workload's record count")
+    ap.add_argument("--cpu-sample", type=int, default=100000, help="records in the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+
+    import paffy_b200
+    from paffy_b200 import synth
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: paffy_b200 has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    ctx = paffy_b200.Context(local)
+    t_gen = time.time()
+    rec = synth.build_workload(ctx, args.workload, dev, scale=args.scale, rank=rank)
+    torch.cuda.synchronize()
+    t_gen = time.time() - t_gen
+    R, N = rec["n"], rec["ops"].numel()
+    dev_arrays = [rec["op_begin"], rec["ops"], rec["q_contig"], rec["t_contig"], rec["qs"], rec["qe"], rec["ts"], rec["strand"]]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident steps ------------------------------------------------------------------
+    res = None
+    for _ in range(args.warmup):
+        res = ctx.encode_batch(*dev_arrays)
+    # size-independent parity properties at full size (generator truth)
+    _, begin, mism = ctx.fetch_ops(want_ops=False)
+    true_mism = rec["true_mism"].cpu().numpy()
+    true_out = rec["true_out_ops"].cpu().numpy()
+    parity = {"records": int(R), "mismatch_counts_equal": bool((mism == true_mism).all()),
+              "output_op_counts_equal": bool((np.diff(begin) == true_out).all()), "n_out_ops": int(res.n_out_ops)}
+    if not (parity["mismatch_counts_equal"] and parity["output_op_counts_equal"]):
+        raise SystemExit(f"parity check against generator truth failed: {parity}")
+
+    clocks = Clocks(local) if rank == 0 else None
+    barrier()
+    t0 = time.perf_counter()
+    ms_kernel = ms_stage = ms_ingest = 0.0
+    for _ in range(args.steps):
+        res = ctx.encode_batch(*dev_arrays)
+        ms_kernel += res.ms_kernel
+        ms_stage += res.ms_encode
+        ms_ingest += res.ms_ingest
+    barrier()
+    elapsed = time.perf_counter() - t0
+    clk = clocks.stop() if clocks else None
+    A, n_out = int(res.aligned_bases), int(res.n_out_ops)
+    t = torch.tensor([elapsed, float(A)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        elapsed, A_total = tmax[0].item(), t[1].item()
+    else:
+        A_total = float(A)
+    value = A_total * args.steps / elapsed
+
+    # ---- end to end through the host C ABI ----------------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        host = [a.cpu().pin_memory() for a in dev_arrays]
+        host_np = [h.numpy() for h in host]
+        host_np[1] = host_np[1].view(np.uint64)
+        pre_b, pre_o = render_prefixes(rec)
+        pre_pin = torch.from_numpy(pre_b.copy()).pin_memory()
+        out_pin = None
+        h2d = sum(h.numel() * h.element_size() for h in host) + pre_pin.numel() + pre_o.nbytes
+
+        def e2e_step():
+            nonlocal out_pin
+            ctx.encode_batch(*host_np)
+            nbytes, _ = ctx.serialise(pre_pin.numpy(), pre_o)
+            if out_pin is None or out_pin.numel() < nbytes:
+                out_pin = torch.empty(int(nbytes * 1.05), dtype=torch.uint8).pin_memory()
+            ctx.fetch_text(pinned=out_pin.numpy())
+            return nbytes
+
+        for _ in range(args.warmup):
+            nbytes = e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            nbytes = e2e_step()
+        barrier()
+        el = time.perf_counter() - t0
+        if dist is not None:
+            tt = torch.tensor([el], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            el = tt.item()
+        e2e = {"value": A_total * args.steps / el, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(nbytes + 8 * (R + 1)), "ms_per_step": 1e3 * el / args.steps,
+               "output": "serialised PAF text (device serialiser) copied to pinned host memory"}
+
+    # ---- roofline of the dominant kernel ---------------------------------------------------------------
+    peak, peak_src = peaks()
+    b_alg = 0.5 * A + 8.0 * N + 8.0 * n_out  # 2 x A/4 sequence bytes + 8 B per input op + 8 B per output op
+    k_ms = ms_kernel / args.steps
+    achieved = b_alg / (k_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "kernel": "encode_kernel<8>", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": b_alg,
+                "bytes_per_aligned_bp": b_alg / A, "peak_source": peak_src, "kernel_share_of_step": ms_kernel / (elapsed * 1e3) if world == 1 else None}
+    tr = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr):
+        try:
+            roofline["traffic"] = json.load(open(tr)).get(args.workload)
+        except Exception:
+            pass
+
+    # ---- CPU baseline (rank 0, N = 1 only) ---------------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        d, fa, paf, _ = cpu_sample(args.workload, args.scale, args.cpu_sample, dev)
+        out = run_reference(fa, paf, cores, 2)
+        if out is not None:
+            r = out["reps"][-1]
+            one = run_reference(fa, paf, 1, 1)["reps"][0] if cores > 1 else r
+            cpu = {"value": r["aligned_bp"] / r["encode_s"], "unit": UNIT, "cores": cores, "kind": "reference",
+                   "sample": f"{r['records']} records of {args.workload}'s generator on contig pairs t1/q1 (+) and t2/q2 (-), {r['aligned_bp']} aligned bp; "
+                             f"unmodified paf_encode_mismatches on {cores} pthreads, FASTA load ({out['load_s']:.1f} s) and PAF parse ({r['parse_s']:.2f} s) excluded",
+                   "single_thread_value": one["aligned_bp"] / one["encode_s"], "fasta_load_s": out["load_s"], "parse_s": r["parse_s"]}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "u8", "data": "synthetic",
+                "config": {"workload": f"{args.workload}: {synth.CONFIGS[args.workload][0]}x{synth.CONFIGS[args.workload][1]} bp target+query genomes, "
+                                       f"{R} records/GPU, scale {args.scale}", "records_per_gpu": int(R), "input_ops": int(N), "output_ops": n_out,
+                           "aligned_bp_per_step_per_gpu": A, "sharding": "records sharded by rank, packed genome replicated, no collective",
+                           "l2": "inputs larger than L2 (packed genome 1.5 GB + op arrays); no flush needed",
+                           "timing": "K synchronous steps between barrier+synchronize; per-stage CUDA events inside the library"},
+                "device_ms": {"ingest": ms_ingest / args.steps, "encode_stage": ms_stage / args.steps, "encode_kernel": k_ms},
+                "gpu_launches": KERNELS_PER_STEP * args.steps, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clk,
+                "parity": parity, "gen_s": t_gen}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -88,7 +88,8 @@ typedef struct {
     int64_t n_tiles;        /* warp tiles scheduled */
     int64_t retried;        /* 1 if the output buffer overflowed and the scan was re-run */
     float ms_ingest;        /* CUDA-event time of the CIGAR ingest kernels */
-    float ms_encode;        /* CUDA-event time of the base-comparison kernel (+ stitch) */
+    float ms_encode;        /* CUDA-event time of the base-comparison kernel + stitch + offsets + resets */
+    float ms_kernel;        /* CUDA-event time of the base-comparison kernel alone (the roofline kernel) */
 } pafgpu_result;
 
 /* Run CIGAR ingest + the base-comparison kernel on one batch (a1 + a7 of SURVEY.md section 8).
@@ -125,9 +126,10 @@ int pafgpu_encode_one(pafgpu_ctx *ctx, const uint64_t *ops, int64_t n_ops, int s
                       int64_t query_end, int64_t target_start, const char *query_seq, const char *target_seq,
                       uint64_t **out_ops, int64_t *n_out, int64_t *mismatches);
 
-/* Kernel self-timing for bench.py: re-run the encode kernel of the last submitted batch `reps` times
- * (inputs and genome resident in HBM) and return the mean CUDA-event milliseconds per launch. */
-int pafgpu_time_encode(pafgpu_ctx *ctx, int reps, float *ms_mean, float *ms_min);
+/* Kernel self-timing for bench.py: re-run the encode stage of the last submitted batch `reps` times
+ * (inputs and genome resident in HBM). ms_stage: mean CUDA-event ms of resets + kernel + stitch;
+ * ms_kernel: mean CUDA-event ms of the base-comparison kernel alone. */
+int pafgpu_time_encode(pafgpu_ctx *ctx, int reps, float *ms_stage, float *ms_kernel);
 
 #ifdef __cplusplus
 }

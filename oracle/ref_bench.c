@@ -6,7 +6,8 @@
  * through fastaReadToFunction, paf_read, then paf_encode_mismatches on T pthreads (the function is
  * re-entrant; records are dealt round-robin). Prints one JSON line.
  *
- *   ref_bench <threads> <in.paf> <fasta>... [--write out.paf]
+ *   [REF_BENCH_REPS=n] ref_bench <threads> <in.paf> <fasta>... [--write out.paf]
+ *   Each rep re-reads the PAF (untimed) and times the encode of every record.
  */
 #include <pthread.h>
 #include <time.h>
@@ -48,37 +49,44 @@ int main(int argc, char **argv) {
         fclose(fh);
     }
     double t_load = now() - t0;
-    t0 = now();
-    FILE *in = fopen(argv[2], "r");
-    if (!in) { fprintf(stderr, "ref_bench: cannot open %s\n", argv[2]); return 2; }
-    stList *pafs = read_pafs(in, 1);
-    fclose(in);
-    double t_parse = now() - t0;
-    int64_t aligned = 0;
-    for (int64_t i = 0; i < stList_length(pafs); i++) {
-        Paf *p = stList_get(pafs, i);
-        for (int64_t k = 0; k < cigar_count(p->cigar); k++)
-            if (cigar_get(p->cigar, k)->op == match) aligned += cigar_get(p->cigar, k)->length;
-    }
+    int reps = 1;
+    const char *reps_env = getenv("REF_BENCH_REPS");
+    if (reps_env) reps = atoi(reps_env) > 0 ? atoi(reps_env) : 1;
     pthread_t *th = malloc(sizeof(pthread_t) * nthreads);
     Job *jobs = calloc(nthreads, sizeof(Job));
-    t0 = now();
-    for (int t = 0; t < nthreads; t++) {
-        jobs[t] = (Job){pafs, seqs, t, nthreads, 0};
-        pthread_create(&th[t], NULL, worker, &jobs[t]);
+    printf("{\"threads\": %d, \"load_s\": %.6f, \"reps\": [", nthreads, t_load);
+    for (int rep = 0; rep < reps; rep++) {
+        t0 = now();
+        FILE *in = fopen(argv[2], "r");
+        if (!in) { fprintf(stderr, "ref_bench: cannot open %s\n", argv[2]); return 2; }
+        stList *pafs = read_pafs(in, 1);
+        fclose(in);
+        double t_parse = now() - t0;
+        int64_t aligned = 0;
+        for (int64_t i = 0; i < stList_length(pafs); i++) {
+            Paf *p = stList_get(pafs, i);
+            for (int64_t k = 0; k < cigar_count(p->cigar); k++)
+                if (cigar_get(p->cigar, k)->op == match) aligned += cigar_get(p->cigar, k)->length;
+        }
+        t0 = now();
+        for (int t = 0; t < nthreads; t++) {
+            jobs[t] = (Job){pafs, seqs, t, nthreads, 0};
+            pthread_create(&th[t], NULL, worker, &jobs[t]);
+        }
+        int64_t out_ops = 0;
+        for (int t = 0; t < nthreads; t++) { pthread_join(th[t], NULL); out_ops += jobs[t].out_ops; }
+        double t_encode = now() - t0;
+        t0 = now();
+        if (write_path && rep == 0) {
+            FILE *out = fopen(write_path, "w");
+            for (int64_t i = 0; i < stList_length(pafs); i++) { paf_check(stList_get(pafs, i)); paf_write(stList_get(pafs, i), out); }
+            fclose(out);
+        }
+        double t_write = now() - t0;
+        printf("%s{\"records\": %lld, \"aligned_bp\": %lld, \"out_ops\": %lld, \"parse_s\": %.6f, \"encode_s\": %.6f, \"write_s\": %.6f}",
+               rep ? ", " : "", (long long)stList_length(pafs), (long long)aligned, (long long)out_ops, t_parse, t_encode, t_write);
+        stList_destruct(pafs);
     }
-    int64_t out_ops = 0;
-    for (int t = 0; t < nthreads; t++) { pthread_join(th[t], NULL); out_ops += jobs[t].out_ops; }
-    double t_encode = now() - t0;
-    t0 = now();
-    if (write_path) {
-        FILE *out = fopen(write_path, "w");
-        for (int64_t i = 0; i < stList_length(pafs); i++) { paf_check(stList_get(pafs, i)); paf_write(stList_get(pafs, i), out); }
-        fclose(out);
-    }
-    double t_write = now() - t0;
-    printf("{\"records\": %lld, \"aligned_bp\": %lld, \"out_ops\": %lld, \"threads\": %d, \"load_s\": %.6f, "
-           "\"parse_s\": %.6f, \"encode_s\": %.6f, \"write_s\": %.6f}\n",
-           (long long)stList_length(pafs), (long long)aligned, (long long)out_ops, nthreads, t_load, t_parse, t_encode, t_write);
+    printf("]}\n");
     return 0;
 }

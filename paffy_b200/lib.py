@@ -37,7 +37,7 @@ class Batch(C.Structure):
 
 class Result(C.Structure):
     _fields_ = [("n_out_ops", C.c_int64), ("aligned_bases", C.c_int64), ("n_windows", C.c_int64), ("n_tiles", C.c_int64),
-                ("retried", C.c_int64), ("ms_ingest", C.c_float), ("ms_encode", C.c_float)]
+                ("retried", C.c_int64), ("ms_ingest", C.c_float), ("ms_encode", C.c_float), ("ms_kernel", C.c_float)]
 
 
 _lib = None
@@ -183,9 +183,9 @@ class Context:
         return ops, begin, mism
 
     def time_encode(self, reps):
-        mean, best = C.c_float(), C.c_float()
-        self._check(self.L.pafgpu_time_encode(self.h, reps, C.byref(mean), C.byref(best)))
-        return mean.value, best.value
+        stage, kernel = C.c_float(), C.c_float()
+        self._check(self.L.pafgpu_time_encode(self.h, reps, C.byref(stage), C.byref(kernel)))
+        return stage.value, kernel.value
 
     def serialise(self, prefix_bytes, prefix_begin):
         prefix_begin = np.ascontiguousarray(prefix_begin, dtype=np.int64)
