@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
         const uint64_t w = have ? P.ops[j] : 0;
         const int code = (int)(w >> 56);
         const uint64_t len = w & LEN_MASK;
-        if (have && (len >> 47)) overflow = true;  // negative or absurd length
+        if (have && ((len >> 47) || (code == OP_M && len == 0))) overflow = true;  // negative / absurd length, or a 0M (callers drop those)
         const uint64_t tl = (have && code != OP_I) ? len : 0, ql = (have && code != OP_D) ? len : 0;
         const uint64_t t_inc = warp_incl_scan(tl, lane), q_inc = warp_incl_scan(ql, lane);
         if (have) {
@@ -348,13 +348,16 @@ struct EncodeParams {
     int64_t n_tiles;
     uint64_t *out;
     int64_t out_cap;
-    unsigned long long *tile_desc;  // look-back: status << 62 | count
+    unsigned long long *tile_desc;  // look-back over CTA tiles: status << 62 | count
+    uint64_t *tile_excl;            // exclusive output rank of every warp tile
+    int64_t n_btiles;               // CTA tiles = ceil(n_tiles / warps per CTA)
     uint64_t *tile_first_closer;    // absolute window-axis position of the first run start / op end
     int64_t *tile_open_slot;        // output slot of a run left open, -1 if none (pre-set)
     int64_t *rec_out_begin;
     unsigned long long *rec_mism;
     unsigned int *ticket;
     unsigned long long *total_out;
+    int debug;  // experiments only (PAFGPU_DEBUG): 1 skip look-back, 2 skip emission, 4 skip tallies
 };
 
 constexpr unsigned long long DESC_AGG = 1ull << 62, DESC_PREFIX = 2ull << 62, DESC_VAL = (1ull << 62) - 1;
@@ -376,137 +379,215 @@ __device__ __forceinline__ unsigned slow_mismatch(const Genome &G, uint64_t tp, 
     return t != q;
 }
 
-template <int ITERS>
-__global__ void __launch_bounds__(128) encode_kernel(EncodeParams P) {
-    constexpr uint32_t TW = 32u * ITERS;
-    const unsigned lane = threadIdx.x & 31;
-    const uint64_t *__restrict__ gw = P.G.words;
+// sign-extend the low 56 bits
+__device__ __forceinline__ int64_t sext56(uint64_t v) { return (int64_t)(v << 8) >> 8; }
+// 2-bit code (A0 C1 G2 T3) at arena position p of a plain word
+__device__ __forceinline__ unsigned code_of(uint64_t word, uint64_t p) { return (unsigned)(word >> ((p & 31) * 2)) & 3u; }
 
+// table flags (top byte of the tB entry)
+constexpr uint64_t EF_HEAD = 1ull << 56, EF_PASS = 1ull << 57, EF_REV = 1ull << 58, EF_EXC = 1ull << 59;
+// META bits
+constexpr uint32_t MB_PASS = 1u << 6, MB_LAST = 1u << 7, MB_ACTIVE = 1u << 8, MB_WI0 = 1u << 9, MB_REV = 1u << 10,
+                   MB_SLOW = 1u << 11, MB_PM = 1u << 12;
+constexpr int MS_SHT = 13, MS_SHQ = 18, MS_IDX = 23;
+
+template <int ITERS, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
+    constexpr uint32_t TW = 32u * ITERS;
+    constexpr int TAB = (int)TW + 32;  // a tile of TW windows overlaps at most TW + 1 ops
+    const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint64_t *__restrict__ gw = P.G.words;
+    __shared__ unsigned s_ticket;
+    __shared__ uint32_t s_cnt[WARPS];
+    __shared__ uint64_t s_excl;
+    // per-warp op table of the current tile: everything a window needs to know about its op
+    __shared__ uint64_t t_tb[WARPS][TAB];   // flags << 56 | (arena position of the op's base under tile window 0) & 2^56-1
+    __shared__ int64_t t_qb[WARPS][TAB];    // same for the query (walks down on '-' strands)
+    __shared__ uint64_t t_rem[WARPS][TAB];  // M: op bases left at tile window 0 (signed); pass-through: the op word itself
+    __shared__ uint32_t t_rec[WARPS][TAB];
+    __shared__ uint32_t s_bm[WARPS][ITERS];  // bit p: an op starts at tile window p
+
+    unsigned nxt = 0;
+    if (threadIdx.x == 0) nxt = atomicAdd(P.ticket, 1u);
     for (;;) {
-        unsigned ticket = 0;
-        if (lane == 0) ticket = atomicAdd(P.ticket, 1u);
-        ticket = __shfl_sync(FULL, ticket, 0);
-        const int64_t tile = ticket;
-        if (tile >= P.n_tiles) return;
+        // one ticket per CTA tile (WARPS consecutive warp tiles): one look-back link per CTA. The next ticket
+        // is drawn a tile ahead so its round trip hides behind the work.
+        if (threadIdx.x == 0) {
+            s_ticket = nxt;
+            nxt = atomicAdd(P.ticket, 1u);
+        }
+        __syncthreads();
+        const int64_t btile = s_ticket;
+        if (btile >= P.n_btiles) return;
+        const int64_t tile = btile * WARPS + wid;
+        const bool live = tile < P.n_tiles;
         const uint64_t s0 = (uint64_t)tile * TW;
-        int64_t cur = P.tile_first_op[tile];
+        const uint64_t tile_end = min(s0 + TW, P.n_win);
+
+        // ---- op table: lane k of group g owns op cur + 32 g + k (all loads independent: one round trip)
+        unsigned adj = 0;
+        if (lane < ITERS) s_bm[wid][lane] = 0;
+        __syncwarp();
+        if (live) {
+            const int64_t cur = P.tile_first_op[tile];
+            bool more = true;
+            for (int g = 0; more; g++) {
+                const int64_t k = cur + 32 * g + lane;
+                const bool valid = k < P.n_ops;
+                uint64_t wo = INF64, opw = 0, tpw = 0, qpw = 0;
+                uint32_t rec = 0;
+                if (valid) {
+                    wo = __ldg(P.woff + k); opw = __ldg(P.ops + k); tpw = __ldg(P.tpos + k); qpw = __ldg(P.qpos + k);
+                    rec = __ldg(P.op_rec + k);
+                }
+                const bool in = valid && wo < tile_end;
+                if (in) {
+                    const int e = 32 * g + (int)lane;
+                    const int64_t back = 32 * (int64_t)(s0 - wo);  // op bases before tile window 0 (negative: op starts inside)
+                    const bool rev = (qpw & QFLAG_REV) != 0, pass = (int)(opw >> 56) != OP_M;
+                    uint64_t fl = (tpw & TFLAG_HEAD) ? EF_HEAD : 0;
+                    if (pass) fl |= EF_PASS;
+                    if (rev) fl |= EF_REV;
+                    if (qpw & QFLAG_EXC) fl |= EF_EXC;
+                    t_tb[wid][e] = fl | ((uint64_t)((int64_t)(tpw & POS_MASK) + back) & LEN_MASK);
+                    t_qb[wid][e] = rev ? (int64_t)(qpw & POS_MASK) - back : (int64_t)(qpw & POS_MASK) + back;
+                    t_rem[wid][e] = pass ? opw : (uint64_t)((int64_t)(opw & LEN_MASK) - back);
+                    t_rec[wid][e] = rec;
+                    if (wo >= s0) atomicOr(&s_bm[wid][(wo - s0) >> 5], 1u << ((wo - s0) & 31));
+                }
+                if (g == 0) adj = __shfl_sync(FULL, (unsigned)(wo == s0), 0);
+                more = __all_sync(FULL, in);
+            }
+        }
+        __syncwarp();
 
         uint64_t D[ITERS], MM[ITERS];
-        uint32_t META[ITERS];  // bits 0-5 n, 6 pass-through, 7 last piece of its op, 8 active
-        uint32_t FC[ITERS];    // first closer (tile-relative window-axis position), later: my closer
-        uint32_t EX[ITERS];    // exclusive output rank inside the tile
+        uint32_t META[ITERS];
+        uint32_t FC[ITERS];  // first closer (tile-relative window-axis position), later: my closer
+        uint32_t EX[ITERS];  // exclusive output rank inside the tile
         uint32_t tile_count = 0;
         unsigned carry_pm = 0;
         uint32_t acc_rec = INF32, acc_mm = 0;
 
+        // ---- phase A: window -> op through the start bitmap, then issue every sequence load of the tile
+        uint64_t TL[ITERS], TH[ITERS], QL[ITERS], QH[ITERS];
+        uint64_t pm_t = 0, pm_q = 0;  // lane 0, first window only: words holding the base before the window
+        uint32_t pre = 0;
 #pragma unroll
         for (int it = 0; it < ITERS; it++) {
-            const uint64_t s_first = s0 + 32u * it;
-            const uint64_t s = s_first + lane;
-            const bool active = s < P.n_win;
-            // ---- window -> op: 32 candidate ops from the cursor, searched with shuffles
-            uint32_t wrel;
-            {
-                const int64_t k = cur + lane + 1;
-                const uint64_t wend = k <= P.n_ops ? __ldg(P.woff + k) : INF64;
-                const uint64_t d = wend - s_first;  // >= 1 for in-range ops
-                wrel = (wend == INF64 || d > 0xfffffffeull) ? INF32 : (uint32_t)d;
-            }
-            uint32_t idx = 0;
-#pragma unroll
-            for (int step = 16; step >= 1; step >>= 1) {
-                const uint32_t v = __shfl_sync(FULL, wrel, (idx + step - 1) & 31);
-                if (v <= lane) idx += step;
-            }
-            {
-                const uint32_t v = __shfl_sync(FULL, wrel, 31);
-                if (idx == 31 && v <= lane) idx = 32;
-            }
-            int64_t j = cur + idx;
-            if (__any_sync(FULL, active && idx == 32)) {
-                // more than 32 ops inside 32 windows (only with zero-window ops): global search
-                if (active) {
-                    int64_t lo = cur, hi = P.n_ops;
-                    while (hi - lo > 1) {
-                        const int64_t mid = (lo + hi) >> 1;
-                        if (__ldg(P.woff + mid) <= s) lo = mid; else hi = mid;
+            const uint32_t srel = 32u * it + lane;
+            const bool active = live && s0 + srel < P.n_win;
+            const uint32_t w = s_bm[wid][it];
+            const uint32_t idx = pre + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
+            pre += __popc(w);
+            uint32_t meta = 0;
+            TL[it] = TH[it] = QL[it] = QH[it] = 0;
+            if (active) {
+                const uint64_t F = t_tb[wid][idx];
+                meta = MB_ACTIVE | (idx << MS_IDX) | (((w >> lane) & 1u) ? MB_WI0 : 0u);
+                if (F & EF_PASS) {
+                    meta |= MB_PASS;
+                } else {
+                    const int64_t back = 32 * (int64_t)srel;
+                    const bool rev = (F & EF_REV) != 0;
+                    const uint64_t tp = (uint64_t)(sext56(F) + back);
+                    const int64_t qb = t_qb[wid][idx];
+                    const uint64_t qp = (uint64_t)(rev ? qb - back : qb + back);
+                    const int64_t rem = (int64_t)t_rem[wid][idx] - back;
+                    const uint32_t n = rem < 32 ? (uint32_t)rem : 32u;
+                    if (rem <= 32) meta |= MB_LAST;
+                    if (rev) meta |= MB_REV;
+                    const uint64_t qlo = rev ? qp - 31 : qp;  // first base of the 32 the query word is cut from
+                    bool slow = false;
+                    if (F & EF_EXC) {
+                        const uint64_t ql = rev ? qp - (n - 1) : qp;
+                        slow = span_has_exception(P.G, tp, tp + n - 1) || span_has_exception(P.G, ql, ql + n - 1);
                     }
-                    j = lo;
+                    if (slow) meta |= MB_SLOW;
+                    meta |= n | ((uint32_t)(tp & 31) << MS_SHT) | ((uint32_t)(qlo & 31) << MS_SHQ);
+                    TL[it] = ldg64(gw + (tp >> 5)); TH[it] = ldg64(gw + (tp >> 5) + 1);
+                    QL[it] = ldg64(gw + (qlo >> 5)); QH[it] = ldg64(gw + (qlo >> 5) + 1);
+                    if (it == 0 && lane == 0 && !(meta & MB_WI0)) {
+                        // mismatch state of the base just before the tile (same op)
+                        const uint64_t qprev = rev ? qp + 1 : qp - 1;
+                        if (F & EF_EXC) {
+                            if (slow_mismatch(P.G, tp - 1, qprev, rev)) meta |= MB_PM;
+                        } else {
+                            pm_t = ldg64(gw + ((tp - 1) >> 5));
+                            pm_q = ldg64(gw + (qprev >> 5));
+                        }
+                    }
                 }
             }
-            if (s_first + 32 < P.n_win) {  // cursor for the next iteration: op owning window s_first + 32 (or just before)
-                const int64_t jl = __shfl_sync(FULL, j, 31);
-                cur = __ldg(P.woff + jl + 1) <= s_first + 32 ? jl + 1 : jl;
-            }
+            META[it] = meta;
+        }
 
+        // ---- phase B: mismatch bits, run starts, output ranks
+#pragma unroll
+        for (int it = 0; it < ITERS; it++) {
+            uint32_t meta = META[it];
+            const bool active = (meta & MB_ACTIVE) != 0;
+            const uint32_t idx = meta >> MS_IDX;
+            const uint32_t n = meta & 63u;
+            const bool wi0 = (meta & MB_WI0) != 0;
             uint64_t m = 0, d = 0;
-            uint32_t meta = 0, n = 0, fc = INF32, rec = INF32;
-            bool wi0 = false, head = false;
+            uint32_t fc = INF32, rec = INF32;
+            bool head = false;
             if (active) {
-                const uint64_t opw = __ldg(P.ops + j);
-                const uint64_t tpw = __ldg(P.tpos + j);
-                const uint32_t wi = (uint32_t)(s - __ldg(P.woff + j));
-                rec = __ldg(P.op_rec + j);
-                meta = 1u << 8;
-                wi0 = wi == 0;
-                head = wi0 && (tpw & TFLAG_HEAD);
-                if ((int)(opw >> 56) != OP_M) {
-                    meta |= 1u << 6;
-                    m = opw;
+                rec = t_rec[wid][idx];
+                head = wi0 && (t_tb[wid][idx] & EF_HEAD);
+                if (meta & MB_PASS) {
+                    m = t_rem[wid][idx];
                     d = 1;
                 } else {
-                    const uint64_t qpw = __ldg(P.qpos + j);
-                    const uint64_t len = opw & LEN_MASK;
-                    const uint64_t i0 = (uint64_t)wi << 5;
-                    const uint64_t rem = len - i0;
-                    n = rem < 32 ? (uint32_t)rem : 32u;
-                    if (rem <= 32) meta |= 1u << 7;
-                    const bool rev = (qpw & QFLAG_REV) != 0;
-                    const uint64_t tp = (tpw & POS_MASK) + i0;
-                    const uint64_t qp = rev ? (qpw & POS_MASK) - i0 : (qpw & POS_MASK) + i0;
+                    const bool rev = (meta & MB_REV) != 0;
                     const uint64_t valid = n == 32 ? ~0ull : ((1ull << (2 * n)) - 1);
-                    bool slow = false;
-                    if (qpw & QFLAG_EXC) {
-                        const uint64_t qlo = rev ? qp - (n - 1) : qp;
-                        slow = span_has_exception(P.G, tp, tp + n - 1) || span_has_exception(P.G, qlo, qlo + n - 1);
-                    }
-                    if (!slow) {
-                        const uint64_t t = fetch32(gw, tp);
-                        const uint64_t q = rev ? revcomp32(fetch32(gw, qp - 31)) : fetch32(gw, qp);
+                    if (!(meta & MB_SLOW)) {
+                        const unsigned sht = ((meta >> MS_SHT) & 31u) * 2, shq = ((meta >> MS_SHQ) & 31u) * 2;
+                        const uint64_t t = sht ? (TL[it] >> sht) | (TH[it] << (64 - sht)) : TL[it];
+                        uint64_t q = shq ? (QL[it] >> shq) | (QH[it] << (64 - shq)) : QL[it];
+                        if (rev) q = revcomp32(q);
                         const uint64_t x = t ^ q;
                         m = (x | (x >> 1)) & EVEN_BITS & valid;
                     } else {
+                        const int64_t back = 32 * (int64_t)(32u * it + lane);
+                        const uint64_t tp = (uint64_t)(sext56(t_tb[wid][idx]) + back);
+                        const int64_t qb = t_qb[wid][idx];
+                        const uint64_t qp = (uint64_t)(rev ? qb - back : qb + back);
                         for (uint32_t k = 0; k < n; k++)
                             m |= (uint64_t)slow_mismatch(P.G, tp + k, rev ? qp - k : qp + k, rev) << (2 * k);
                     }
-                    // mismatch state of the base just before this window (same op), needed when wi > 0
-                    unsigned pm = 0;
-                    if (it == 0 && lane == 0 && wi > 0)
-                        pm = slow_mismatch(P.G, tp - 1, rev ? qp + 1 : qp - 1, rev);
-                    meta |= pm << 10;
+                    if (it == 0 && lane == 0 && !wi0 && !(t_tb[wid][idx] & EF_EXC)) {
+                        const int64_t qb = t_qb[wid][idx];
+                        const uint64_t tp = (uint64_t)sext56(t_tb[wid][idx]);
+                        const uint64_t qprev = (uint64_t)(rev ? qb + 1 : qb - 1);
+                        const unsigned tc = code_of(pm_t, tp - 1);
+                        unsigned qc = code_of(pm_q, qprev);
+                        if (rev) qc ^= 3u;
+                        if (tc != qc) meta |= MB_PM;
+                    }
                     // per-record mismatch tally, flushed when the lane moves to another record
                     const uint32_t mm = __popcll(m);
-                    if (rec != acc_rec) {
+                    if (rec != acc_rec && !(P.debug & 4)) {
                         if (acc_mm) atomicAdd(P.rec_mism + acc_rec, (unsigned long long)acc_mm);
                         acc_rec = rec;
                         acc_mm = 0;
                     }
                     acc_mm += mm;
                 }
-                meta |= n;
             }
             // previous base's mismatch bit: lane-1 (same iteration) or lane 31 of the last iteration
             {
                 const unsigned hi = (unsigned)(m >> 62) & 1u;
                 unsigned pm = __shfl_up_sync(FULL, hi, 1);
-                if (lane == 0) pm = it == 0 ? (meta >> 10) & 1u : carry_pm;
+                if (lane == 0) pm = it == 0 ? ((meta & MB_PM) ? 1u : 0u) : carry_pm;
                 carry_pm = __shfl_sync(FULL, hi, 31);
-                if (active && !(meta & (1u << 6))) {
+                if (active && !(meta & MB_PASS)) {
                     const uint64_t valid = n == 32 ? ~0ull : ((1ull << (2 * n)) - 1);
                     d = ((m ^ ((m << 2) | pm)) & EVEN_BITS & valid) | (wi0 && n ? 1ull : 0ull);
                     const uint32_t xrel = 32u * (32u * it + lane);
                     if (d) fc = xrel + ((uint32_t)(__ffsll((long long)d) - 1) >> 1);
-                    else if (meta & (1u << 7)) fc = xrel + n;
+                    else if (meta & MB_LAST) fc = xrel + n;
                 }
             }
             const uint32_t cnt = __popcll(d);
@@ -534,34 +615,54 @@ __global__ void __launch_bounds__(128) encode_kernel(EncodeParams P) {
             }
         }
 
-        // ---- decoupled look-back over tile aggregates -> exclusive output rank of this tile
-        uint64_t excl = 0;
-        if (tile > 0) {
-            if (lane == 0) st_relaxed(P.tile_desc + tile, DESC_AGG | tile_count);
-            int64_t look = tile - 1;
-            for (;;) {
-                const int64_t i = look - lane;
-                unsigned long long dsc = DESC_PREFIX;
-                if (i >= 0) {
-                    do { dsc = ld_relaxed(P.tile_desc + i); } while ((dsc >> 62) == 0);
-                }
-                const unsigned has_prefix = __ballot_sync(FULL, (dsc >> 62) == 2);
-                uint64_t v = dsc & DESC_VAL;
-                if (has_prefix) {
-                    const unsigned first = __ffs(has_prefix) - 1;
-                    if (lane > first) v = 0;
-                }
+        // ---- output rank of this warp tile: CTA-level sum, then one decoupled look-back per CTA (warp 0)
+        if (lane == 0) s_cnt[wid] = tile_count;
+        __syncthreads();
+        uint32_t warp_off = 0, cta_count = 0;
 #pragma unroll
-                for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
-                excl += v;
-                if (has_prefix) break;
-                look -= 32;
+        for (int k = 0; k < WARPS; k++) {
+            const uint32_t c = s_cnt[k];
+            if (k < (int)wid) warp_off += c;
+            cta_count += c;
+        }
+        if (wid == 0) {
+            uint64_t bex = 0;
+            if (btile > 0 && !(P.debug & 1)) {
+                if (lane == 0) st_relaxed(P.tile_desc + btile, DESC_AGG | cta_count);
+                int64_t look = btile - 1;
+                for (;;) {
+                    const int64_t i = look - lane;
+                    unsigned long long dsc = DESC_PREFIX;
+                    if (i >= 0) {
+                        unsigned ns = 32;
+                        while (((dsc = ld_relaxed(P.tile_desc + i)) >> 62) == 0) {
+                            __nanosleep(ns);
+                            if (ns < 256) ns <<= 1;
+                        }
+                    }
+                    const unsigned has_prefix = __ballot_sync(FULL, (dsc >> 62) == 2);
+                    uint64_t v = dsc & DESC_VAL;
+                    if (has_prefix) {
+                        const unsigned first = __ffs(has_prefix) - 1;
+                        if (lane > first) v = 0;
+                    }
+#pragma unroll
+                    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+                    bex += v;
+                    if (has_prefix) break;
+                    look -= 32;
+                }
+            }
+            if (lane == 0) {
+                st_relaxed(P.tile_desc + btile, DESC_PREFIX | (bex + cta_count));
+                if (btile == P.n_btiles - 1) *P.total_out = bex + cta_count;
+                s_excl = bex;
             }
         }
-        if (lane == 0) {
-            st_relaxed(P.tile_desc + tile, DESC_PREFIX | (excl + tile_count));
-            if (tile == P.n_tiles - 1) *P.total_out = excl + tile_count;
-        }
+        __syncthreads();
+        const uint64_t excl = s_excl + warp_off;
+        if (!live || (P.debug & 2)) continue;
+        if (lane == 0) P.tile_excl[tile] = excl;
 
         // ---- emission, last iteration first so each lane knows where its trailing run closes
         uint32_t later_min = INF32;
@@ -623,16 +724,14 @@ __global__ void stitch_kernel(int64_t n_tiles, const int64_t *tile_open_slot, co
     out[slot] = (tile_first_closer[u] - (rec & LEN_MASK)) | (rec & ~LEN_MASK);
 }
 
-// rec_out_begin holds (tile << 16 | rank inside tile); add the tile's exclusive rank from the look-back chain
-__global__ void rec_out_fix_kernel(int64_t n_records, int64_t *rec_out_begin, const unsigned long long *tile_desc,
+// rec_out_begin holds (warp tile << 16 | rank inside the tile); add the tile's exclusive rank
+__global__ void rec_out_fix_kernel(int64_t n_records, int64_t *rec_out_begin, const uint64_t *tile_excl,
                                    const unsigned long long *total_out) {
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r > n_records) return;
     if (r == n_records) { rec_out_begin[r] = (int64_t)*total_out; return; }
     const uint64_t v = (uint64_t)rec_out_begin[r];
-    const uint64_t tile = v >> 16;
-    const uint64_t base = tile ? (tile_desc[tile - 1] & DESC_VAL) : 0;
-    rec_out_begin[r] = (int64_t)(base + (v & 0xffff));
+    rec_out_begin[r] = (int64_t)(tile_excl[v >> 16] + (v & 0xffff));
 }
 
 }  // namespace pafgpu

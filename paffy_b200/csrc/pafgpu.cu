@@ -75,6 +75,8 @@ struct GenomeStore {
 struct pafgpu_ctx {
     int device = 0;
     int sm_count = 148;
+    int enc_ctas_per_sm = 2;
+    int enc_warps = 4;  // warp tiles per CTA tile (one look-back link per CTA); PAFGPU_ENC_WARPS=2|4
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[6] = {};
     std::string err;
@@ -85,7 +87,7 @@ struct pafgpu_ctx {
     // staging for host batches
     DevBuf in_op_begin, in_ops, in_qc, in_tc, in_qs, in_qe, in_ts, in_strand, in_seq;
     // per-batch work buffers
-    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, tile_desc, tile_first_closer, tile_open_slot;
+    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, tile_desc, tile_excl, tile_first_closer, tile_open_slot;
     DevBuf out, rec_out_begin, rec_mism, scalars;
     // serialiser
     DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
@@ -222,18 +224,21 @@ int launch_encode(pafgpu_ctx *c) {
     EncodeParams &P = c->last;
     uint64_t *sc = c->scalars.as<uint64_t>();
     CU(cudaMemsetAsync(sc + SC_TICKET, 0, 16, c->stream));  // ticket + total
-    CU(cudaMemsetAsync(c->tile_desc.p, 0, (size_t)c->n_tiles * 8, c->stream));
+    CU(cudaMemsetAsync(c->tile_desc.p, 0, (size_t)std::max<int64_t>(P.n_btiles, 1) * 8, c->stream));
     CU(cudaMemsetAsync(c->tile_open_slot.p, 0xff, (size_t)c->n_tiles * 8, c->stream));
     CU(cudaMemsetAsync(c->rec_mism.p, 0, (size_t)c->n_records * 8, c->stream));
     if (c->n_tiles > 0) {
-        const unsigned grid = (unsigned)std::min<int64_t>((c->n_tiles + 3) / 4, (int64_t)c->sm_count * 8);
+        const unsigned grid = (unsigned)std::min<int64_t>(P.n_btiles, (int64_t)c->sm_count * c->enc_ctas_per_sm);
         CU(cudaEventRecord(c->ev[4], c->stream));
-        encode_kernel<ITERS><<<grid, 128, 0, c->stream>>>(P);
+        switch (c->enc_warps) {
+            case 2: encode_kernel<ITERS, 2><<<grid, 64, 0, c->stream>>>(P); break;
+            default: encode_kernel<ITERS, 4><<<grid, 128, 0, c->stream>>>(P); break;
+        }
         CU(cudaEventRecord(c->ev[5], c->stream));
         stitch_kernel<<<blocks_for(c->n_tiles, 256), 256, 0, c->stream>>>(c->n_tiles, P.tile_open_slot, P.tile_first_closer,
                                                                           P.out, P.out_cap);
     }
-    rec_out_fix_kernel<<<blocks_for(c->n_records + 1, 256), 256, 0, c->stream>>>(c->n_records, P.rec_out_begin, P.tile_desc,
+    rec_out_fix_kernel<<<blocks_for(c->n_records + 1, 256), 256, 0, c->stream>>>(c->n_records, P.rec_out_begin, P.tile_excl,
                                                                                  P.total_out);
     CU(cudaGetLastError());
     return 0;
@@ -285,7 +290,9 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     const int64_t aligned = (int64_t)host_sc[SC_ALIGNED];
     const int64_t n_tiles = (int64_t)((n_win + TILE_WINDOWS - 1) / TILE_WINDOWS);
     CU(c->tile_first_op.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 4));
-    CU(c->tile_desc.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
+    const int64_t n_btiles = (n_tiles + c->enc_warps - 1) / c->enc_warps;
+    CU(c->tile_desc.ensure((size_t)std::max<int64_t>(n_btiles, 1) * 8));
+    CU(c->tile_excl.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
     CU(c->tile_first_closer.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
     CU(c->tile_open_slot.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
     if (N > 0)
@@ -305,6 +312,9 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     P.n_ops = N; P.n_win = n_win; P.n_tiles = n_tiles;
     P.out = c->out.as<uint64_t>(); P.out_cap = cap;
     P.tile_desc = c->tile_desc.as<unsigned long long>();
+    P.tile_excl = c->tile_excl.as<uint64_t>();
+    P.n_btiles = n_btiles;
+    P.debug = getenv("PAFGPU_DEBUG") ? atoi(getenv("PAFGPU_DEBUG")) : 0;
     P.tile_first_closer = c->tile_first_closer.as<uint64_t>();
     P.tile_open_slot = c->tile_open_slot.as<int64_t>();
     P.rec_out_begin = c->rec_out_begin.as<int64_t>();
@@ -415,6 +425,16 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
         return fail(c, PAFGPU_ENODEVICE, "cudaStreamCreate failed");
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    {
+        if (const char *e = getenv("PAFGPU_ENC_WARPS")) {
+            const int w = atoi(e);
+            if (w == 2 || w == 4) ctx->enc_warps = w;
+        }
+        int per_sm = 0;
+        cudaError_t oe = ctx->enc_warps == 2 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<ITERS, 2>, 64, 0)
+                                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<ITERS, 4>, 128, 0);
+        if (oe == cudaSuccess && per_sm > 0) ctx->enc_ctas_per_sm = per_sm;
+    }
     ctx->scalars.ensure(SC_COUNT * 8);
     *out = ctx;
     return 0;
@@ -428,7 +448,7 @@ void pafgpu_destroy(pafgpu_ctx *c) {
     c->scratch.release();
     DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
                       &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
-                      &c->tile_desc, &c->tile_first_closer, &c->tile_open_slot, &c->out, &c->rec_out_begin, &c->rec_mism,
+                      &c->tile_desc, &c->tile_excl, &c->tile_first_closer, &c->tile_open_slot, &c->out, &c->rec_out_begin, &c->rec_mism,
                       &c->scalars, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
                       &c->ser_text};
     for (DevBuf *b : bufs) b->release();
