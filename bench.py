@@ -214,12 +214,13 @@ def main():
     clocks = Clocks(local) if rank == 0 else None
     barrier()
     t0 = time.perf_counter()
-    ms_kernel = ms_stage = ms_ingest = 0.0
+    ms_kernel = ms_stage = ms_ingest = ms_emit = 0.0
     for _ in range(args.steps):
         res = ctx.encode_batch(*dev_arrays)
         ms_kernel += res.ms_kernel
         ms_stage += res.ms_encode
         ms_ingest += res.ms_ingest
+        ms_emit += res.ms_emit
     barrier()
     elapsed = time.perf_counter() - t0
     clk = clocks.stop() if clocks else None
@@ -308,7 +309,8 @@ def main():
                            "aligned_bp_per_step_per_gpu": A, "sharding": "records sharded by rank, packed genome replicated, no collective",
                            "l2": "inputs larger than L2 (packed genome 1.5 GB + op arrays); no flush needed",
                            "timing": "K synchronous steps between barrier+synchronize; per-stage CUDA events inside the library"},
-                "device_ms": {"ingest": ms_ingest / args.steps, "encode_stage": ms_stage / args.steps, "encode_kernel": k_ms},
+                "device_ms": {"ingest": ms_ingest / args.steps, "encode_stage": ms_stage / args.steps, "compare_kernel": k_ms,
+                              "emit_kernel_and_stitch": ms_emit / args.steps},
                 "gpu_launches": KERNELS_PER_STEP * args.steps, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clk,
                 "parity": parity, "gen_s": t_gen}
         print(json.dumps(line))

@@ -84,12 +84,13 @@ typedef struct {
 typedef struct {
     int64_t n_out_ops;      /* total output CigarRecord words */
     int64_t aligned_bases;  /* sum of input M lengths (the unit of the throughput metric) */
-    int64_t n_windows;      /* 32-base work windows scheduled */
+    int64_t n_windows;      /* 64-base work windows scheduled */
     int64_t n_tiles;        /* warp tiles scheduled */
-    int64_t retried;        /* 1 if the output buffer overflowed and the scan was re-run */
+    int64_t retried;        /* always 0 (kept for ABI stability) */
     float ms_ingest;        /* CUDA-event time of the CIGAR ingest kernels */
-    float ms_encode;        /* CUDA-event time of the base-comparison kernel + stitch + offsets + resets */
-    float ms_kernel;        /* CUDA-event time of the base-comparison kernel alone (the roofline kernel) */
+    float ms_encode;        /* CUDA-event time of the whole encode stage: resets + compare + scan + emit + stitch */
+    float ms_kernel;        /* CUDA-event time of compare_kernel alone (reads the sequences; the roofline kernel) */
+    float ms_emit;          /* CUDA-event time of emit_kernel + stitch (writes the output ops) */
 } pafgpu_result;
 
 /* Run CIGAR ingest + the base-comparison kernel on one batch (a1 + a7 of SURVEY.md section 8).

@@ -2,6 +2,7 @@
 // batch encode, result fetch. One context per GPU; no CPU fallback anywhere in this file.
 #include "../../include/paffy_b200.h"
 #include "kernels.cuh"
+#include "encode.cuh"
 #include "serialise.cuh"
 
 #include <algorithm>
@@ -75,11 +76,11 @@ struct GenomeStore {
 struct pafgpu_ctx {
     int device = 0;
     int sm_count = 148;
-    int enc_ctas_per_sm = 2;
-    int enc_warps = 4;  // warp tiles per CTA tile (one look-back link per CTA); PAFGPU_ENC_WARPS=2|4
+    int cmp_ctas_per_sm = 4, emit_ctas_per_sm = 4;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[6] = {};
+    cudaEvent_t ev[8] = {};
     std::string err;
+    uint64_t host_total = 0;
     std::mutex mu;  // library callers may encode from several threads (SURVEY 8b threading row)
 
     GenomeStore genome, scratch;
@@ -87,7 +88,7 @@ struct pafgpu_ctx {
     // staging for host batches
     DevBuf in_op_begin, in_ops, in_qc, in_tc, in_qs, in_qe, in_ts, in_strand, in_seq;
     // per-batch work buffers
-    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, tile_desc, tile_excl, tile_first_closer, tile_open_slot;
+    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, tile_count, masks, tile_excl, tile_first_closer, tile_open_slot;
     DevBuf out, rec_out_begin, rec_mism, scalars;
     // serialiser
     DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
@@ -104,7 +105,7 @@ namespace {
 
 constexpr int ITERS = 8;
 constexpr uint32_t TILE_WINDOWS = 32u * ITERS;
-enum { SC_BAD = 0, SC_ALIGNED = 1, SC_TICKET = 2, SC_TOTAL = 3, SC_NWIN = 4, SC_TMP = 5, SC_COUNT = 8 };
+enum { SC_BAD = 0, SC_ALIGNED = 1, SC_SPARE = 2, SC_TOTAL = 3, SC_NWIN = 4, SC_TMP = 5, SC_COUNT = 8 };
 
 int fail(pafgpu_ctx *c, int code, const std::string &msg) {
     if (c) c->err = msg; else g_create_error = msg;
@@ -142,8 +143,9 @@ int genome_grow(pafgpu_ctx *c, GenomeStore &g, int64_t need_bases) {
     int64_t cap = std::max<int64_t>(need_bases, g.cap_bases + g.cap_bases / 2);
     cap = align_up(cap, ARENA_ALIGN);
     CU(cudaStreamSynchronize(c->stream));
-    // +2 words / +2 groups of slack so fetch32's second word and rank lookups one past the end stay in bounds
-    CU(g.words.ensure((size_t)(cap / 32 + 2) * 8, (size_t)(g.cap_bases / 32 + 2) * 8, true));
+    // +4 words / +2 groups of slack so a window's third word and rank lookups one past the end stay in bounds
+    if (cap >= (1ll << 36)) return fail(c, PAFGPU_EINVAL, "genome arena limited to 2^36 bases per GPU (32-bit word indices)");
+    CU(g.words.ensure((size_t)(cap / 32 + 4) * 8, (size_t)(g.cap_bases / 32 + 4) * 8, true));
     CU(g.flags.ensure((size_t)(cap / 1024 + 2) * 4, (size_t)(g.cap_bases / 1024 + 2) * 4, true));
     CU(g.rank.ensure((size_t)(cap / 1024 + 2) * 4, (size_t)(g.cap_bases / 1024 + 2) * 4, true));
     g.cap_bases = cap;
@@ -219,35 +221,45 @@ int genome_sync_table(pafgpu_ctx *c, GenomeStore &g) {
     return 0;
 }
 
-// (re)launch the base-comparison kernel + stitch + record offsets for c->last
+constexpr int ENC_WARPS = 4, CMP_BATCH = 4;
+
+// (re)launch compare -> scan -> emit -> stitch for c->last; leaves the output op count in c->n_out
 int launch_encode(pafgpu_ctx *c) {
     EncodeParams &P = c->last;
     uint64_t *sc = c->scalars.as<uint64_t>();
-    CU(cudaMemsetAsync(sc + SC_TICKET, 0, 16, c->stream));  // ticket + total
-    CU(cudaMemsetAsync(c->tile_desc.p, 0, (size_t)std::max<int64_t>(P.n_btiles, 1) * 8, c->stream));
-    CU(cudaMemsetAsync(c->tile_open_slot.p, 0xff, (size_t)c->n_tiles * 8, c->stream));
-    CU(cudaMemsetAsync(c->rec_mism.p, 0, (size_t)c->n_records * 8, c->stream));
-    if (c->n_tiles > 0) {
-        const unsigned grid = (unsigned)std::min<int64_t>(P.n_btiles, (int64_t)c->sm_count * c->enc_ctas_per_sm);
-        CU(cudaEventRecord(c->ev[4], c->stream));
-        switch (c->enc_warps) {
-            case 2: encode_kernel<ITERS, 2><<<grid, 64, 0, c->stream>>>(P); break;
-            default: encode_kernel<ITERS, 4><<<grid, 128, 0, c->stream>>>(P); break;
-        }
-        CU(cudaEventRecord(c->ev[5], c->stream));
-        stitch_kernel<<<blocks_for(c->n_tiles, 256), 256, 0, c->stream>>>(c->n_tiles, P.tile_open_slot, P.tile_first_closer,
-                                                                          P.out, P.out_cap);
+    const int64_t T = c->n_tiles;
+    CU(cudaMemsetAsync(c->tile_open_slot.p, 0xff, (size_t)std::max<int64_t>(T, 1) * 8, c->stream));
+    CU(cudaMemsetAsync(c->rec_mism.p, 0, (size_t)std::max<int64_t>(c->n_records, 1) * 8, c->stream));
+    CU(cudaEventRecord(c->ev[4], c->stream));
+    if (T > 0) {
+        const unsigned grid = (unsigned)std::min<int64_t>((T + ENC_WARPS - 1) / ENC_WARPS, (int64_t)c->sm_count * c->cmp_ctas_per_sm);
+        compare_kernel<ENC_WARPS, CMP_BATCH><<<grid, 32 * ENC_WARPS, 0, c->stream>>>(P);
     }
-    rec_out_fix_kernel<<<blocks_for(c->n_records + 1, 256), 256, 0, c->stream>>>(c->n_records, P.rec_out_begin, P.tile_excl,
-                                                                                 P.total_out);
+    CU(cudaEventRecord(c->ev[5], c->stream));
+    if (int rc = scan_u32(c, c->tile_count.as<uint32_t>(), T, c->tile_excl.as<uint64_t>(), sc + SC_TOTAL)) return rc;
+    CU(cudaMemcpyAsync(&c->host_total, sc + SC_TOTAL, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    const int64_t total = (int64_t)c->host_total;
+    CU(c->out.ensure((size_t)std::max<int64_t>(total, 1) * 8));
+    P.out = c->out.as<uint64_t>();
+    P.out_cap = (int64_t)(c->out.cap / 8);
+    CU(cudaEventRecord(c->ev[6], c->stream));
+    if (T > 0) {
+        const unsigned grid = (unsigned)std::min<int64_t>((T + ENC_WARPS - 1) / ENC_WARPS, (int64_t)c->sm_count * c->emit_ctas_per_sm);
+        emit_kernel<ENC_WARPS><<<grid, 32 * ENC_WARPS, 0, c->stream>>>(P);
+        stitch_kernel<<<blocks_for(T, 256), 256, 0, c->stream>>>(T, P.tile_open_slot, P.tile_first_closer, P.out, P.out_cap);
+    }
+    CU(cudaMemcpyAsync(P.rec_out_begin + c->n_records, sc + SC_TOTAL, 8, cudaMemcpyDeviceToDevice, c->stream));
+    CU(cudaEventRecord(c->ev[7], c->stream));
     CU(cudaGetLastError());
+    c->n_out = total;
     return 0;
 }
 
 // all arrays of *b are device pointers here
 int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_result *res) {
     if (!b || b->n_records < 0 || b->n_ops < 0) return fail(c, PAFGPU_EINVAL, "bad batch");
-    if (b->n_ops >= (1ll << 32) || b->n_records >= (1ll << 32)) return fail(c, PAFGPU_EINVAL, "batch too large: split it");
+    if (b->n_ops >= (1ll << 32) || b->n_records >= (1ll << 31)) return fail(c, PAFGPU_EINVAL, "batch too large: split it");
     if (int rc = genome_sync_table(c, g)) return rc;
     c->have_batch = false;
     const int64_t R = b->n_records, N = b->n_ops;
@@ -290,9 +302,9 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     const int64_t aligned = (int64_t)host_sc[SC_ALIGNED];
     const int64_t n_tiles = (int64_t)((n_win + TILE_WINDOWS - 1) / TILE_WINDOWS);
     CU(c->tile_first_op.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 4));
-    const int64_t n_btiles = (n_tiles + c->enc_warps - 1) / c->enc_warps;
-    CU(c->tile_desc.ensure((size_t)std::max<int64_t>(n_btiles, 1) * 8));
-    CU(c->tile_excl.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
+    CU(c->tile_count.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 4));
+    CU(c->tile_excl.ensure((size_t)(n_tiles + 1) * 8));
+    CU(c->masks.ensure((size_t)std::max<uint64_t>(n_win, 1) * 8));
     CU(c->tile_first_closer.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
     CU(c->tile_open_slot.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
     if (N > 0)
@@ -300,45 +312,26 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
                                                                         c->tile_first_op.as<uint32_t>());
     CU(cudaEventRecord(c->ev[1], c->stream));
 
-    // output capacity: every input op + ~6% of aligned bases as run starts; grown and re-run if short
-    int64_t cap = std::max<int64_t>((int64_t)(c->out.cap / 8), N + aligned / 16 + 1024);
-    CU(c->out.ensure((size_t)cap * 8));
-    cap = (int64_t)(c->out.cap / 8);
-
     EncodeParams &P = c->last;
     P.G = g.view();
     P.ops = b->ops; P.woff = c->woff.as<uint64_t>(); P.tpos = c->tpos.as<uint64_t>(); P.qpos = c->qpos.as<uint64_t>();
     P.op_rec = c->op_rec.as<uint32_t>(); P.tile_first_op = c->tile_first_op.as<uint32_t>();
     P.n_ops = N; P.n_win = n_win; P.n_tiles = n_tiles;
-    P.out = c->out.as<uint64_t>(); P.out_cap = cap;
-    P.tile_desc = c->tile_desc.as<unsigned long long>();
+    P.out = c->out.as<uint64_t>(); P.out_cap = (int64_t)(c->out.cap / 8);
+    P.masks = c->masks.as<uint64_t>();
+    P.tile_count = c->tile_count.as<uint32_t>();
     P.tile_excl = c->tile_excl.as<uint64_t>();
-    P.n_btiles = n_btiles;
     P.debug = getenv("PAFGPU_DEBUG") ? atoi(getenv("PAFGPU_DEBUG")) : 0;
     P.tile_first_closer = c->tile_first_closer.as<uint64_t>();
     P.tile_open_slot = c->tile_open_slot.as<int64_t>();
     P.rec_out_begin = c->rec_out_begin.as<int64_t>();
     P.rec_mism = c->rec_mism.as<unsigned long long>();
-    P.ticket = (unsigned int *)(sc + SC_TICKET);
-    P.total_out = (unsigned long long *)(sc + SC_TOTAL);
     c->n_records = R; c->n_ops = N; c->n_tiles = n_tiles; c->n_win = n_win;
 
-    int retried = 0;
-    uint64_t total = 0;
-    for (;;) {
-        CU(cudaEventRecord(c->ev[2], c->stream));
-        if (int rc = launch_encode(c)) return rc;
-        CU(cudaEventRecord(c->ev[3], c->stream));
-        CU(cudaMemcpyAsync(&total, sc + SC_TOTAL, 8, cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
-        if ((int64_t)total <= P.out_cap) break;
-        if (retried) return fail(c, PAFGPU_ENODEVICE, "output capacity still short after retry");
-        retried = 1;
-        CU(c->out.ensure((size_t)total * 8));
-        P.out = c->out.as<uint64_t>();
-        P.out_cap = (int64_t)(c->out.cap / 8);
-    }
-    c->n_out = (int64_t)total;
+    CU(cudaEventRecord(c->ev[2], c->stream));
+    if (int rc = launch_encode(c)) return rc;
+    CU(cudaEventRecord(c->ev[3], c->stream));
+    CU(cudaStreamSynchronize(c->stream));
     c->have_batch = true;
     if (res) {
         memset(res, 0, sizeof *res);
@@ -346,10 +339,11 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
         res->aligned_bases = aligned;
         res->n_windows = (int64_t)n_win;
         res->n_tiles = n_tiles;
-        res->retried = retried;
+        res->retried = 0;
         cudaEventElapsedTime(&res->ms_ingest, c->ev[0], c->ev[1]);
         cudaEventElapsedTime(&res->ms_encode, c->ev[2], c->ev[3]);
-        if (n_tiles > 0) cudaEventElapsedTime(&res->ms_kernel, c->ev[4], c->ev[5]);
+        cudaEventElapsedTime(&res->ms_kernel, c->ev[4], c->ev[5]);
+        cudaEventElapsedTime(&res->ms_emit, c->ev[6], c->ev[7]);
     }
     return 0;
 }
@@ -426,14 +420,11 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
     {
-        if (const char *e = getenv("PAFGPU_ENC_WARPS")) {
-            const int w = atoi(e);
-            if (w == 2 || w == 4) ctx->enc_warps = w;
-        }
         int per_sm = 0;
-        cudaError_t oe = ctx->enc_warps == 2 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<ITERS, 2>, 64, 0)
-                                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<ITERS, 4>, 128, 0);
-        if (oe == cudaSuccess && per_sm > 0) ctx->enc_ctas_per_sm = per_sm;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, compare_kernel<ENC_WARPS, CMP_BATCH>, 32 * ENC_WARPS, 0) == cudaSuccess && per_sm > 0)
+            ctx->cmp_ctas_per_sm = per_sm;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, emit_kernel<ENC_WARPS>, 32 * ENC_WARPS, 0) == cudaSuccess && per_sm > 0)
+            ctx->emit_ctas_per_sm = per_sm;
     }
     ctx->scalars.ensure(SC_COUNT * 8);
     *out = ctx;
@@ -448,7 +439,7 @@ void pafgpu_destroy(pafgpu_ctx *c) {
     c->scratch.release();
     DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
                       &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
-                      &c->tile_desc, &c->tile_excl, &c->tile_first_closer, &c->tile_open_slot, &c->out, &c->rec_out_begin, &c->rec_mism,
+                      &c->tile_count, &c->masks, &c->tile_excl, &c->tile_first_closer, &c->tile_open_slot, &c->out, &c->rec_out_begin, &c->rec_mism,
                       &c->scalars, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
                       &c->ser_text};
     for (DevBuf *b : bufs) b->release();
@@ -620,7 +611,7 @@ int pafgpu_time_encode(pafgpu_ctx *c, int reps, float *ms_stage, float *ms_kerne
         float ms = 0;
         cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]);
         sum += ms;
-        if (c->n_tiles > 0) { cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]); ksum += ms; }
+        cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]); ksum += ms;
     }
     if (ms_stage) *ms_stage = (float)(sum / reps);
     if (ms_kernel) *ms_kernel = (float)(ksum / reps);

@@ -37,7 +37,8 @@ class Batch(C.Structure):
 
 class Result(C.Structure):
     _fields_ = [("n_out_ops", C.c_int64), ("aligned_bases", C.c_int64), ("n_windows", C.c_int64), ("n_tiles", C.c_int64),
-                ("retried", C.c_int64), ("ms_ingest", C.c_float), ("ms_encode", C.c_float), ("ms_kernel", C.c_float)]
+                ("retried", C.c_int64), ("ms_ingest", C.c_float), ("ms_encode", C.c_float), ("ms_kernel", C.c_float),
+                ("ms_emit", C.c_float)]
 
 
 _lib = None
