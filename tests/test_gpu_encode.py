@@ -84,17 +84,6 @@ def test_bounds_error(ctx):
     assert e.value.code == -4 and "record 1" in str(e.value)
 
 
-def case_lines(case):
-    """PAF text lines for a random case (coordinates valid for paf_check)."""
-    lines = []
-    for r in case["records"]:
-        ql, tl = len(case["contigs"][r["q"]]), len(case["contigs"][r["t"]])
-        t_span = sum(n for n, c in r["ops"] if c != "I")
-        lines.append(f"{r['q']}\t{ql}\t{r['qs']}\t{r['qe']}\t{'+' if r['strand'] else '-'}\t{r['t']}\t{tl}\t{r['ts']}\t{r['ts'] + t_span}"
-                     f"\t0\t0\t60\ttp:A:P\tcg:Z:{O.cigar_str(r['ops'])}")
-    return lines
-
-
 @pytest.mark.parametrize("seed", [61, 62])
 def test_serialiser_matches_oracle_text(ctx, seed, tmp_path):
     """Device serialiser output == the oracle's add_mismatches file output, byte for byte."""
@@ -103,7 +92,7 @@ def test_serialiser_matches_oracle_text(ctx, seed, tmp_path):
     for n, s in case["contigs"].items():
         fa.add(n, s)
     inp, outp = tmp_path / "in.paf", tmp_path / "out.paf"
-    inp.write_text("\n".join(case_lines(case)) + "\n")
+    inp.write_text("\n".join(util.case_lines(case)) + "\n")
     rc, stats, aligned = fa.add_mismatches_file(str(inp), str(outp))
     assert rc == 0
     want = outp.read_bytes()

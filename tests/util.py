@@ -108,3 +108,49 @@ def gpu_encode(ctx, case):
     out, begin, mism = ctx.fetch_ops()
     assert begin[0] == 0 and begin[-1] == res.n_out_ops
     return [(pairs_of(out[begin[i]:begin[i + 1]]), int(mism[i])) for i in range(len(case["records"]))], res
+
+
+def case_lines(case):
+    """PAF text lines for a random case (coordinates valid for paf_check)."""
+    lines = []
+    for r in case["records"]:
+        ql, tl = len(case["contigs"][r["q"]]), len(case["contigs"][r["t"]])
+        t_span = sum(n for n, c in r["ops"] if c != "I")
+        lines.append(f"{r['q']}\t{ql}\t{r['qs']}\t{r['qe']}\t{'+' if r['strand'] else '-'}\t{r['t']}\t{tl}\t{r['ts']}\t{r['ts'] + t_span}"
+                     f"\t0\t0\t60\ttp:A:P\tcg:Z:{O.cigar_str(r['ops'])}")
+    return lines
+
+
+# ---- config C1: the reference's own fixture + a seeded synthetic chr10 (SURVEY.md section 8d) -------------
+C1_LEN = 133797422
+C1_SEED = 20261104
+
+
+def c1_genome():
+    """The synthetic chr10 (query and target share the name, so one contig serves both): uint8 ASCII array."""
+    rng = np.random.default_rng(C1_SEED)
+    return np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, C1_LEN, dtype=np.uint8)]
+
+
+def write_c1_fasta(path, width=100):
+    g = c1_genome()
+    full = (C1_LEN // width) * width
+    body = np.empty((C1_LEN // width, width + 1), dtype=np.uint8)
+    body[:, :width] = g[:full].reshape(-1, width)
+    body[:, width] = 10
+    with open(path, "wb") as fh:
+        fh.write(b">chr10\n")
+        fh.write(body.tobytes())
+        if full < C1_LEN:
+            fh.write(g[full:].tobytes() + b"\n")
+
+
+def view_summary(stats):
+    """The `paffy view -s` line (impl/paf_view.c:187-192) from the seven totals: float32 quotients printed with %f."""
+    m, mm, qi, qd, qib, qdb, n = stats
+    f = np.float32
+    with np.errstate(all="ignore"):
+        ident = f(m) / f(m + mm)
+        ident_gaps = f(m) / f(m + mm + qib + qdb)
+    return (f"Total-alignments:{n}\tAvg-Identity:{float(ident):f}\tAvg-Identity-with-gaps:{float(ident_gaps):f}\t"
+            f"Aligned-bases:{m + mm}\tAligned-bases-with-gaps:{m + mm + qib + qdb}\tQuery-inserts:{qi}\tQuery-deletes:{qd}\n")
