@@ -2,23 +2,25 @@
 // Restates paf_encode_mismatches (impl/paf.c:739-784); nothing is copied from it.
 //
 // Work axis = 64-base windows of all ops of the batch (an M op of length n owns ceil(n/64) windows,
-// every other op owns one), cut into warp tiles of 256 windows, so megabase CIGARs spread over the
-// whole grid and no CTA ever waits for another. Two kernels, one pass over the sequences:
-//   compare_kernel  per tile: op lanes load the tile's ops once and leave, per op, everything a window
-//                   needs in shared memory (word index + bit phase of target and query, bases left,
-//                   flags) plus a bitmap of the windows at which an op starts, so a window finds its op
-//                   with one popcount. Every lane then issues the 6 x 64-bit loads of several windows
-//                   at once, funnel-shifts the bit planes into phase, BREV + NOT the query on '-'
-//                   strands, one LOP3 per plane -> one mismatch bit per base. It stores the 64-bit
-//                   mismatch mask of every window, counts run starts per tile and tallies mismatches
-//                   per record.
-//   (scan of the per-tile counts -> output rank of every tile)
-//   emit_kernel     per tile: re-reads the masks (1/4 of the sequence bytes), scatters run starts into a
-//                   per-warp list in shared memory; a run's length is the distance to the next entry,
-//                   so the list is turned into CigarRecord words and stored with coalesced 8-byte
-//                   stores. A run still open at the end of a tile is closed by stitch_kernel.
-// An earlier single-kernel version (decoupled look-back between tiles) lost more time waiting on
-// predecessor tiles than the mask round trip costs; see DESIGN.md.
+// every other op owns one), cut into warp tiles of 256 windows; a CTA takes the next CTA tile (one warp
+// tile per warp) from a ticket counter, so megabase CIGARs spread over the whole grid. ONE kernel, one
+// pass over the sequences, no scratch round trip through HBM:
+//   A  op table     op lanes load the tile's ops once and leave, per op, everything a window needs in
+//                   shared memory (word index + bit phase of target and query, bases left, flags) plus a
+//                   bitmap of the windows at which an op starts, so a window finds its op with a popcount.
+//   B  compare      striped (window = 32 * iteration + lane, coalesced): every lane issues the 6 x 64-bit
+//                   loads of several windows at once, funnel-shifts the bit planes into phase, BREV + NOT
+//                   the query on '-' strands, one LOP3 per plane -> one mismatch bit per base. The 64-bit
+//                   mask of every window goes to shared memory; mismatches are tallied per record.
+//   C  count        blocked (lane owns 8 consecutive windows): run starts per lane, warp scan.
+//   D  look-back    the CTA publishes its number of output ops and obtains the number before it with a
+//                   decoupled look-back over the tiles ticketed earlier (those are already running, so the
+//                   wait is short and cannot deadlock).
+//   E  emit         blocked: a lane walks its windows, a run's length is the distance to the next run start
+//                   (in-lane; the last run of a lane closes at the first event of a later lane, found with
+//                   a suffix-min over lanes). CigarRecord words are staged in shared memory and stored with
+//                   coalesced 8-byte stores. A run still open at the end of a warp tile is closed by
+//                   stitch_kernel.
 #pragma once
 #include "kernels.cuh"
 
@@ -30,23 +32,27 @@ struct EncodeParams {
     const uint32_t *op_rec, *tile_first_op;
     int64_t n_ops;
     uint64_t n_win;
-    int64_t n_tiles;
+    int64_t n_tiles;                // warp tiles
+    int64_t n_cta_tiles;
     uint64_t *out;
-    int64_t out_cap;
-    uint64_t *masks;                // n_win mismatch masks (scratch between the two kernels)
-    uint32_t *tile_count;           // run starts + pass-through ops per warp tile
-    const uint64_t *tile_excl;      // exclusive scan of tile_count: output rank of every warp tile
-    uint64_t *tile_first_closer;    // absolute window-axis coordinate (64 * window + base) of the tile's first run start / op end
+    int64_t out_cap;                // words; stores beyond it are dropped (the host grows the buffer and re-runs)
+    unsigned long long *status;     // per CTA tile: look-back word (2 flag bits + 62 value bits), pre-set to 0
+    unsigned int *ticket;           // pre-set to 0
+    unsigned long long *total_out;  // number of output ops of the whole batch
+    uint64_t *tile_first_closer;    // absolute window-axis coordinate (64 * window + base) of the warp tile's first run start / op end
     int64_t *tile_open_slot;        // output slot of a run left open, -1 if none (pre-set)
     int64_t *rec_out_begin;
     unsigned long long *rec_mism;
-    int debug;  // experiments only (PAFGPU_DEBUG): 4 skip tallies
 };
 
 constexpr int WIN_BASES = 64;
 constexpr int TILE_ITERS = 8;                 // windows per lane per warp tile
 constexpr int TILE_WIN = 32 * TILE_ITERS;     // windows per warp tile
 constexpr int TILE_TAB = TILE_WIN + 2;        // a tile overlaps at most TILE_WIN + 1 ops
+constexpr int MASK_PAD = TILE_WIN + TILE_WIN / 8;  // mask of window p sits at p + (p >> 3): conflict-free blocked reads
+constexpr int LIST_CAP = 512;                 // staged output words per round
+constexpr uint32_t COORD_OPEN = 0xffffffffu;
+constexpr unsigned long long ST_AGG = 1ull << 62, ST_INCL = 2ull << 62, ST_VAL = (1ull << 62) - 1;
 
 // mismatch bit of one aligned base of an op, through the byte plane (slow, exact)
 __device__ __forceinline__ unsigned slow_mismatch(const Genome &G, uint64_t tp, uint64_t qp, bool rev) {
@@ -56,467 +62,432 @@ __device__ __forceinline__ unsigned slow_mismatch(const Genome &G, uint64_t tp, 
     return t != q;
 }
 
-
-// per-op table entry of compare_kernel (16 bytes, read with one LDS.128)
+// per-op table entry (16 bytes, read with one LDS.128)
+//   M op:          tw / qw = word index of the target base / lowest query base under tile window 0,
+//                  rem = op bases left at tile window 0 = tile-relative coordinate of the op's end
+//   any other op:  tw / qw = low / high half of the op word (copied through)
 struct __align__(16) OpEntry {
-    int32_t tw;      // word index of the target base under tile window 0 (may be negative for ops starting later)
-    int32_t qw;      // word index of the lowest query base of tile window 0's span
-    int32_t rem;     // M: op bases left at tile window 0, clamped to 2^30
+    int32_t tw, qw, rem;
     uint32_t misc;   // bits 0-4 target phase, 5-9 query phase, then flags
 };
-constexpr uint32_t EF_HEAD = 1u << 10, EF_PASS = 1u << 11, EF_REV = 1u << 12, EF_EXC = 1u << 13;
+constexpr uint32_t EF_PASS = 1u << 11, EF_REV = 1u << 12, EF_EXC = 1u << 13;
+constexpr int32_t REM_CLAMP = 1 << 30;
 
-// META bits of one window
-constexpr uint32_t MB_N = 127u, MB_PASS = 1u << 7, MB_LAST = 1u << 8, MB_ACTIVE = 1u << 9, MB_WI0 = 1u << 10,
-                   MB_REV = 1u << 11, MB_SLOW = 1u << 12, MB_PM = 1u << 13, MB_HEAD = 1u << 14;
-constexpr int MS_IDX = 16;  // table index, 9 bits
-constexpr int MS_GAP = 25;  // op-start windows: 64 - bases in the previous window, 6 bits
-
-template <int WARPS>
-struct CompareSmem {
-    OpEntry tab[WARPS][TILE_TAB];
-    uint32_t rec[WARPS][TILE_TAB];
-    uint32_t bm[WARPS][TILE_ITERS];
+struct WarpSmem {
+    OpEntry tab[TILE_TAB];
+    uint32_t rec[TILE_TAB];   // owning record, top bit: first op of the record
+    union {
+        uint64_t mask[MASK_PAD];
+        uint64_t list[LIST_CAP];
+    } u;
+    uint32_t bm[TILE_ITERS];  // bit p: an op starts at tile window p
 };
 
-// index of the op owning tile window `srel`, from the bitmap of op starts (bit p of bm: an op starts at window p)
-__device__ __forceinline__ uint32_t op_index(const uint32_t *bm, int it, unsigned lane, uint32_t &pre, unsigned adj, uint32_t &w) {
-    w = bm[it];
-    const uint32_t idx = pre + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
-    pre += __popc(w);
-    return idx;
+// ---- A: op table of one warp tile. Returns adj (1 when table entry 0 starts exactly at tile window 0) and
+// whether any op of the tile touches a non-ACGT word.
+__device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, int64_t tile, uint64_t s0, uint64_t tile_end,
+                                            unsigned lane, unsigned &adj, bool &any_exc) {
+    __syncwarp();
+    if (lane < TILE_ITERS) S.bm[lane] = 0;
+    __syncwarp();
+    const int64_t cur = P.tile_first_op[tile];
+    bool more = true, exc = false;
+    adj = 0;
+    for (int g = 0; more; g++) {
+        const int64_t k = cur + 32 * g + lane;
+        const bool valid = k < P.n_ops;
+        uint64_t wo = INF64, opw = 0, tpw = 0, qpw = 0;
+        uint32_t rec = 0;
+        if (valid) {
+            wo = __ldg(P.woff + k); opw = __ldg(P.ops + k); tpw = __ldg(P.tpos + k); qpw = __ldg(P.qpos + k);
+            rec = __ldg(P.op_rec + k);
+        }
+        const bool in = valid && wo < tile_end;
+        if (in) {
+            const int e = 32 * g + (int)lane;
+            OpEntry en;
+            if ((int)(opw >> 56) != OP_M) {
+                en.tw = (int32_t)(uint32_t)opw; en.qw = (int32_t)(uint32_t)(opw >> 32); en.rem = 0; en.misc = EF_PASS;
+            } else {
+                const int64_t back = WIN_BASES * (int64_t)(s0 - wo);  // op bases before tile window 0 (negative: op starts inside)
+                const bool rev = (qpw & QFLAG_REV) != 0;
+                const int64_t tb = (int64_t)(tpw & POS_MASK) + back;
+                // lowest query base of tile window 0's span: '+' walks up from it, '-' starts 63 below the top base
+                const int64_t qb = rev ? (int64_t)(qpw & POS_MASK) - back - (WIN_BASES - 1) : (int64_t)(qpw & POS_MASK) + back;
+                int64_t rem = (int64_t)(opw & LEN_MASK) - back;
+                if (rem > REM_CLAMP) rem = REM_CLAMP;
+                en.tw = (int32_t)(tb >> 5);
+                en.qw = (int32_t)(qb >> 5);
+                en.rem = (int32_t)rem;
+                en.misc = (uint32_t)(tb & 31) | ((uint32_t)(qb & 31) << 5) | (rev ? EF_REV : 0u) | ((qpw & QFLAG_EXC) ? EF_EXC : 0u);
+                exc |= (qpw & QFLAG_EXC) != 0;
+            }
+            S.tab[e] = en;
+            S.rec[e] = rec;
+            if (wo >= s0) atomicOr(&S.bm[(wo - s0) >> 5], 1u << ((wo - s0) & 31));
+        }
+        if (g == 0) adj = __shfl_sync(FULL, (unsigned)(wo == s0), 0);
+        more = __all_sync(FULL, in);
+    }
+    any_exc = __any_sync(FULL, exc);
+    __syncwarp();
 }
 
-template <int WARPS, int BATCH>
-__global__ void __launch_bounds__(32 * WARPS) compare_kernel(EncodeParams P) {
+// ---- B: compare. Striped windows; masks to shared memory; per-record mismatch tallies. Returns (lane 0) the
+// mismatch state of the base just before the tile when tile window 0 continues an op.
+template <int BATCH, bool EXC>
+__device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem &S, uint32_t n_act, unsigned lane, unsigned adj) {
     static_assert(TILE_ITERS % BATCH == 0, "BATCH must divide the iterations of a tile");
-    __shared__ CompareSmem<WARPS> S;
-    const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const uint64_t *__restrict__ gw = P.G.words;
-
-    for (int64_t tile = (int64_t)blockIdx.x * WARPS + wid; tile < P.n_tiles; tile += (int64_t)gridDim.x * WARPS) {
-        const uint64_t s0 = (uint64_t)tile * TILE_WIN;
-        const uint64_t tile_end = min(s0 + (uint64_t)TILE_WIN, P.n_win);
-        const uint32_t n_act = (uint32_t)(tile_end - s0);
-
-        // ---- op table: lane k of group g owns op cur + 32 g + k (all loads independent: one round trip)
-        unsigned adj = 0;
-        __syncwarp();
-        if (lane < TILE_ITERS) S.bm[wid][lane] = 0;
-        __syncwarp();
-        {
-            const int64_t cur = P.tile_first_op[tile];
-            bool more = true;
-            for (int g = 0; more; g++) {
-                const int64_t k = cur + 32 * g + lane;
-                const bool valid = k < P.n_ops;
-                uint64_t wo = INF64, opw = 0, tpw = 0, qpw = 0;
-                uint32_t rec = 0;
-                if (valid) {
-                    wo = __ldg(P.woff + k); opw = __ldg(P.ops + k); tpw = __ldg(P.tpos + k); qpw = __ldg(P.qpos + k);
-                    rec = __ldg(P.op_rec + k);
+    uint32_t pre = 0, pm0 = 0;
+    uint32_t acc_rec = INF32, acc_mm = 0;
+#pragma unroll
+    for (int hb = 0; hb < TILE_ITERS; hb += BATCH) {
+        // issue every sequence load of the batch (inactive and pass-through windows read arena word 0: no branches)
+        uint32_t IDX[BATCH];
+        uint64_t T0[BATCH], T1[BATCH], T2[BATCH], Q0[BATCH], Q1[BATCH], Q2[BATCH];
+        uint64_t pm_t = 0, pm_q = 0;  // lane 0, first window only: words holding the base before the window
+        uint32_t pm_k = 0;
+#pragma unroll
+        for (int b = 0; b < BATCH; b++) {
+            const int it = hb + b;
+            const uint32_t srel = 32u * it + lane;
+            const uint32_t w = S.bm[it];
+            uint32_t idx = pre + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
+            pre += __popc(w);
+            if (srel >= n_act) idx = 0;
+            IDX[b] = idx;
+            const OpEntry en = S.tab[idx];
+            const bool isM = srel < n_act && !(en.misc & EF_PASS);
+            const bool rev = (en.misc & EF_REV) != 0;
+            const int32_t tw = isM ? en.tw + 2 * (int32_t)srel : 0;
+            const int32_t qw = isM ? (rev ? en.qw - 2 * (int32_t)srel : en.qw + 2 * (int32_t)srel) : 0;
+            const uint64_t *tpn = gw + tw, *qpn = gw + qw;
+            T0[b] = ldg64(tpn); T1[b] = ldg64(tpn + 1); T2[b] = ldg64(tpn + 2);
+            Q0[b] = ldg64(qpn); Q1[b] = ldg64(qpn + 1); Q2[b] = ldg64(qpn + 2);
+            if (it == 0 && lane == 0 && isM && !(w & 1u)) {
+                // tile window 0 continues an op: mismatch state of the base just before the tile
+                const uint64_t tp = ((uint64_t)(uint32_t)tw << 5) + (en.misc & 31u);
+                const uint64_t qtop = ((uint64_t)(uint32_t)qw << 5) + ((en.misc >> 5) & 31u) + (rev ? WIN_BASES - 1 : 0);
+                const uint64_t qprev = rev ? qtop + 1 : qtop - 1;
+                if (EXC && (en.misc & EF_EXC)) {
+                    pm0 = slow_mismatch(P.G, tp - 1, qprev, rev) ? 0x80000000u : 0u;
+                } else {
+                    pm_t = ldg64(gw + ((tp - 1) >> 5));
+                    pm_q = ldg64(gw + (qprev >> 5));
+                    pm_k = (uint32_t)((tp - 1) & 31) | ((uint32_t)(qprev & 31) << 5) | (rev ? 1u << 10 : 0u) | (1u << 11);
                 }
-                const bool in = valid && wo < tile_end;
-                if (in) {
-                    const int e = 32 * g + (int)lane;
-                    const int64_t back = WIN_BASES * (int64_t)(s0 - wo);  // op bases before tile window 0 (negative: op starts inside)
-                    const bool rev = (qpw & QFLAG_REV) != 0, pass = (int)(opw >> 56) != OP_M;
-                    const int64_t tb = (int64_t)(tpw & POS_MASK) + back;
-                    // lowest query base of tile window 0's span: '+' walks up from it, '-' starts 63 below the top base
-                    const int64_t qb = rev ? (int64_t)(qpw & POS_MASK) - back - (WIN_BASES - 1) : (int64_t)(qpw & POS_MASK) + back;
-                    int64_t rem = (int64_t)(opw & LEN_MASK) - back;
-                    if (rem > (1ll << 30)) rem = 1ll << 30;
-                    OpEntry en;
-                    en.tw = (int32_t)(tb >> 5);
-                    en.qw = (int32_t)(qb >> 5);
-                    en.rem = (int32_t)rem;
-                    en.misc = (uint32_t)(tb & 31) | ((uint32_t)(qb & 31) << 5) | (pass ? EF_PASS : 0u) | (rev ? EF_REV : 0u) |
-                              ((qpw & QFLAG_EXC) ? EF_EXC : 0u);
-                    S.tab[wid][e] = en;
-                    S.rec[wid][e] = rec & 0x7fffffffu;  // top bit: first op of its record
-                    if (wo >= s0) atomicOr(&S.bm[wid][(wo - s0) >> 5], 1u << ((wo - s0) & 31));
-                }
-                if (g == 0) adj = __shfl_sync(FULL, (unsigned)(wo == s0), 0);
-                more = __all_sync(FULL, in);
             }
         }
-        __syncwarp();
-
-        uint32_t tile_count = 0, pre = 0;
-        uint32_t carry_m = 0;
-        uint32_t acc_rec = INF32, acc_mm = 0;
+        if (hb == 0 && (pm_k >> 11)) {  // lane 0 only; consumed after the batch's loads were issued
+            const unsigned kt = pm_k & 31u, kq = (pm_k >> 5) & 31u;
+            const unsigned tc = ((unsigned)(pm_t >> kt) & 1u) | (((unsigned)(pm_t >> (32 + kt)) & 1u) << 1);
+            unsigned qc = ((unsigned)(pm_q >> kq) & 1u) | (((unsigned)(pm_q >> (32 + kq)) & 1u) << 1);
+            if (pm_k & (1u << 10)) qc ^= 3u;
+            pm0 = tc != qc ? 0x80000000u : 0u;
+        }
+        // mismatch bits
 #pragma unroll
-        for (int hb = 0; hb < TILE_ITERS; hb += BATCH) {
-            // ---- phase A: window -> op, then issue every sequence load of the batch
-            uint32_t META[BATCH];
-            uint64_t T0[BATCH], T1[BATCH], T2[BATCH], Q0[BATCH], Q1[BATCH], Q2[BATCH];
-            uint64_t pm_t = 0, pm_q = 0;  // lane 0, first window only: words holding the base before the window
-#pragma unroll
-            for (int b = 0; b < BATCH; b++) {
-                const int it = hb + b;
-                const uint32_t srel = 32u * it + lane;
-                uint32_t w;
-                const uint32_t idx = op_index(S.bm[wid], it, lane, pre, adj, w);
-                uint32_t meta = 0;
-                T0[b] = T1[b] = T2[b] = Q0[b] = Q1[b] = Q2[b] = 0;
-                if (srel < n_act) {
-                    const OpEntry en = S.tab[wid][idx];
-                    meta = MB_ACTIVE | (idx << MS_IDX) | (((w >> lane) & 1u) ? MB_WI0 : 0u);
-                    if (en.misc & EF_PASS) {
-                        meta |= MB_PASS;
-                    } else {
-                        const bool rev = (en.misc & EF_REV) != 0;
-                        const int32_t rem = en.rem - WIN_BASES * (int32_t)srel;
-                        const uint32_t n = rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
-                        if (rev) meta |= MB_REV;
-                        const int32_t tw = en.tw + 2 * (int32_t)srel;
-                        const int32_t qw = rev ? en.qw - 2 * (int32_t)srel : en.qw + 2 * (int32_t)srel;
-                        bool slow = false;
-                        if (en.misc & EF_EXC) {
-                            const uint64_t tp = ((uint64_t)(uint32_t)tw << 5) + (en.misc & 31u);
-                            const uint64_t ql = ((uint64_t)(uint32_t)qw << 5) + ((en.misc >> 5) & 31u) + (rev ? WIN_BASES - n : 0u);
-                            slow = span_has_exception(P.G, tp, tp + n - 1) || span_has_exception(P.G, ql, ql + n - 1);
-                        }
-                        if (slow) meta |= MB_SLOW;
-                        meta |= n;
-                        const uint64_t *tpn = gw + tw, *qpn = gw + qw;
-                        T0[b] = ldg64(tpn); T1[b] = ldg64(tpn + 1); T2[b] = ldg64(tpn + 2);
-                        Q0[b] = ldg64(qpn); Q1[b] = ldg64(qpn + 1); Q2[b] = ldg64(qpn + 2);
-                        if (it == 0 && lane == 0 && !(meta & MB_WI0)) {
-                            // mismatch state of the base just before the tile (same op)
-                            const uint64_t tp = ((uint64_t)(uint32_t)tw << 5) + (en.misc & 31u);
-                            const uint64_t qtop = ((uint64_t)(uint32_t)qw << 5) + ((en.misc >> 5) & 31u) + (rev ? WIN_BASES - 1 : 0);
-                            const uint64_t qprev = rev ? qtop + 1 : qtop - 1;
-                            if (en.misc & EF_EXC) {
-                                if (slow_mismatch(P.G, tp - 1, qprev, rev)) meta |= MB_PM;
-                            } else {
-                                pm_t = ldg64(gw + ((tp - 1) >> 5));
-                                pm_q = ldg64(gw + (qprev >> 5));
-                            }
-                        }
-                    }
-                }
-                META[b] = meta;
+        for (int b = 0; b < BATCH; b++) {
+            const int it = hb + b;
+            const uint32_t srel = 32u * it + lane;
+            const uint32_t idx = IDX[b];
+            const OpEntry en = S.tab[idx];
+            const bool isM = srel < n_act && !(en.misc & EF_PASS);
+            const bool rev = (en.misc & EF_REV) != 0;
+            const int32_t rem = en.rem - WIN_BASES * (int32_t)srel;
+            const uint32_t n = !isM ? 0u : rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
+            const uint32_t misc = en.misc;
+            const unsigned sht = misc & 31u, shq = (misc >> 5) & 31u;
+            const uint32_t tl0 = __funnelshift_r((uint32_t)T0[b], (uint32_t)T1[b], sht);
+            const uint32_t tl1 = __funnelshift_r((uint32_t)T1[b], (uint32_t)T2[b], sht);
+            const uint32_t th0 = __funnelshift_r((uint32_t)(T0[b] >> 32), (uint32_t)(T1[b] >> 32), sht);
+            const uint32_t th1 = __funnelshift_r((uint32_t)(T1[b] >> 32), (uint32_t)(T2[b] >> 32), sht);
+            uint32_t ql0 = __funnelshift_r((uint32_t)Q0[b], (uint32_t)Q1[b], shq);
+            uint32_t ql1 = __funnelshift_r((uint32_t)Q1[b], (uint32_t)Q2[b], shq);
+            uint32_t qh0 = __funnelshift_r((uint32_t)(Q0[b] >> 32), (uint32_t)(Q1[b] >> 32), shq);
+            uint32_t qh1 = __funnelshift_r((uint32_t)(Q1[b] >> 32), (uint32_t)(Q2[b] >> 32), shq);
+            if (rev) {  // reverse the 64 bases (swap + BREV) and complement (NOT of both planes)
+                const uint32_t a = ~__brev(ql1), c = ~__brev(ql0), d = ~__brev(qh1), e = ~__brev(qh0);
+                ql0 = a; ql1 = c; qh0 = d; qh1 = e;
             }
-            // ---- phase B: mismatch bits (stored for emit_kernel), run-start count, per-record tallies
-#pragma unroll
-            for (int b = 0; b < BATCH; b++) {
-                const int it = hb + b;
-                uint32_t meta = META[b];
-                const uint32_t srel = 32u * it + lane;
-                const bool active = (meta & MB_ACTIVE) != 0;
-                const uint32_t idx = (meta >> MS_IDX) & 511u;
-                const uint32_t n = meta & MB_N;
-                const bool wi0 = (meta & MB_WI0) != 0;
-                const bool isM = active && !(meta & MB_PASS);
-                uint32_t m0 = 0, m1 = 0;
-                if (isM) {
-                    const uint32_t rec = S.rec[wid][idx];
-                    const bool rev = (meta & MB_REV) != 0;
-                    const uint32_t misc = S.tab[wid][idx].misc;
-                    if (!(meta & MB_SLOW)) {
-                        const unsigned sht = misc & 31u, shq = (misc >> 5) & 31u;
-                        const uint32_t tl0 = __funnelshift_r((uint32_t)T0[b], (uint32_t)T1[b], sht);
-                        const uint32_t tl1 = __funnelshift_r((uint32_t)T1[b], (uint32_t)T2[b], sht);
-                        const uint32_t th0 = __funnelshift_r((uint32_t)(T0[b] >> 32), (uint32_t)(T1[b] >> 32), sht);
-                        const uint32_t th1 = __funnelshift_r((uint32_t)(T1[b] >> 32), (uint32_t)(T2[b] >> 32), sht);
-                        uint32_t ql0 = __funnelshift_r((uint32_t)Q0[b], (uint32_t)Q1[b], shq);
-                        uint32_t ql1 = __funnelshift_r((uint32_t)Q1[b], (uint32_t)Q2[b], shq);
-                        uint32_t qh0 = __funnelshift_r((uint32_t)(Q0[b] >> 32), (uint32_t)(Q1[b] >> 32), shq);
-                        uint32_t qh1 = __funnelshift_r((uint32_t)(Q1[b] >> 32), (uint32_t)(Q2[b] >> 32), shq);
-                        if (rev) {  // reverse the 64 bases (swap + BREV) and complement (NOT of both planes)
-                            const uint32_t a = ~__brev(ql1), c = ~__brev(ql0), d = ~__brev(qh1), e = ~__brev(qh0);
-                            ql0 = a; ql1 = c; qh0 = d; qh1 = e;
-                        }
-                        m0 = (tl0 ^ ql0) | (th0 ^ qh0);
-                        m1 = (tl1 ^ ql1) | (th1 ^ qh1);
-                    } else {
-                        const OpEntry en = S.tab[wid][idx];
-                        const uint64_t tp = ((uint64_t)(uint32_t)(en.tw + 2 * (int32_t)srel) << 5) + (misc & 31u);
-                        const uint64_t qlo = ((uint64_t)(uint32_t)(rev ? en.qw - 2 * (int32_t)srel : en.qw + 2 * (int32_t)srel) << 5) + ((misc >> 5) & 31u);
-                        for (uint32_t k = 0; k < n; k++) {
-                            const unsigned mm = slow_mismatch(P.G, tp + k, rev ? qlo + (WIN_BASES - 1) - k : qlo + k, rev);
-                            if (k < 32) m0 |= mm << k; else m1 |= mm << (k - 32);
-                        }
+            uint32_t m0 = (tl0 ^ ql0) | (th0 ^ qh0);
+            uint32_t m1 = (tl1 ^ ql1) | (th1 ^ qh1);
+            if (EXC && isM && (misc & EF_EXC)) {
+                const uint64_t tp = ((uint64_t)(uint32_t)(en.tw + 2 * (int32_t)srel) << 5) + sht;
+                const uint64_t qlo = ((uint64_t)(uint32_t)(rev ? en.qw - 2 * (int32_t)srel : en.qw + 2 * (int32_t)srel) << 5) + shq;
+                const uint64_t ql = qlo + (rev ? WIN_BASES - n : 0u);
+                if (span_has_exception(P.G, tp, tp + n - 1) || span_has_exception(P.G, ql, ql + n - 1)) {
+                    m0 = m1 = 0;
+                    for (uint32_t k = 0; k < n; k++) {
+                        const unsigned mm = slow_mismatch(P.G, tp + k, rev ? qlo + (WIN_BASES - 1) - k : qlo + k, rev);
+                        if (k < 32) m0 |= mm << k; else m1 |= mm << (k - 32);
                     }
-                    // bases beyond the op's end do not exist
-                    const uint64_t valid = ~0ull >> (WIN_BASES - n);
-                    m0 &= (uint32_t)valid;
-                    m1 &= (uint32_t)(valid >> 32);
-                    P.masks[s0 + srel] = ((uint64_t)m1 << 32) | m0;
-                    if (it == 0 && lane == 0 && !wi0 && !(misc & EF_EXC)) {
-                        const OpEntry en = S.tab[wid][idx];
-                        const uint64_t tp = ((uint64_t)(uint32_t)en.tw << 5) + (misc & 31u);
-                        const uint64_t qtop = ((uint64_t)(uint32_t)en.qw << 5) + ((misc >> 5) & 31u) + (rev ? WIN_BASES - 1 : 0);
-                        const uint64_t qprev = rev ? qtop + 1 : qtop - 1;
-                        const unsigned kt = (unsigned)((tp - 1) & 31), kq = (unsigned)(qprev & 31);
-                        const unsigned tc = ((unsigned)(pm_t >> kt) & 1u) | (((unsigned)(pm_t >> (32 + kt)) & 1u) << 1);
-                        unsigned qc = ((unsigned)(pm_q >> kq) & 1u) | (((unsigned)(pm_q >> (32 + kq)) & 1u) << 1);
-                        if (rev) qc ^= 3u;
-                        if (tc != qc) meta |= MB_PM;
-                    }
-                    // per-record mismatch tally, flushed when the lane moves to another record
-                    if (rec != acc_rec && !(P.debug & 4)) {
-                        if (acc_mm) atomicAdd(P.rec_mism + acc_rec, (unsigned long long)acc_mm);
-                        acc_rec = rec;
-                        acc_mm = 0;
-                    }
-                    acc_mm += __popc(m0) + __popc(m1);
                 }
-                // mismatch state of the previous base: top bit of the previous window
-                uint32_t pm = __shfl_up_sync(FULL, m1, 1);
-                if (lane == 0) pm = it == 0 ? ((meta & MB_PM) ? 0x80000000u : 0u) : carry_m;
-                carry_m = __shfl_sync(FULL, m1, 31);
-                uint32_t cnt = active ? 1u : 0u;  // pass-through ops are one output each
-                if (isM) {
-                    const uint64_t valid = ~0ull >> (WIN_BASES - n);
-                    uint32_t d0 = (m0 ^ __funnelshift_l(pm, m0, 1)) & (uint32_t)valid;
-                    const uint32_t d1 = (m1 ^ __funnelshift_l(m0, m1, 1)) & (uint32_t)(valid >> 32);
-                    if (wi0) d0 |= 1u;
-                    cnt = __popc(d0) + __popc(d1);
+            }
+            // bases beyond the op's end do not exist
+            const uint64_t valid = n ? ~0ull >> (WIN_BASES - n) : 0ull;
+            m0 &= (uint32_t)valid;
+            m1 &= (uint32_t)(valid >> 32);
+            S.u.mask[srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
+            // per-record mismatch tally, flushed when the lane moves to another record
+            if (isM) {
+                const uint32_t rec = S.rec[idx] & 0x7fffffffu;
+                if (rec != acc_rec) {
+                    if (acc_mm) atomicAdd(P.rec_mism + acc_rec, (unsigned long long)acc_mm);
+                    acc_rec = rec;
+                    acc_mm = 0;
                 }
-                tile_count += cnt;
+                acc_mm += __popc(m0) + __popc(m1);
             }
         }
-#pragma unroll
-        for (int o = 16; o; o >>= 1) tile_count += __shfl_xor_sync(FULL, tile_count, o);
-        if (lane == 0) P.tile_count[tile] = tile_count;
+    }
+    // flush the tallies: one atomic per warp when the whole tile is one record
+    const uint32_t r0 = __shfl_sync(FULL, acc_rec, 0);
+    if (__all_sync(FULL, acc_rec == r0)) {
+        const uint32_t sum = __reduce_add_sync(FULL, acc_mm);
+        if (lane == 0 && sum && r0 != INF32) atomicAdd(P.rec_mism + r0, (unsigned long long)sum);
+    } else if (acc_mm && acc_rec != INF32) {
+        atomicAdd(P.rec_mism + acc_rec, (unsigned long long)acc_mm);
+    }
+    return pm0;
+}
 
-        // ---- per-record mismatch tallies
-        if (!(P.debug & 4)) {
-            const uint32_t r0 = __shfl_sync(FULL, acc_rec, 0);
-            if (__all_sync(FULL, acc_rec == r0)) {
-                const uint32_t sum = __reduce_add_sync(FULL, acc_mm);
-                if (lane == 0 && sum && r0 != INF32) atomicAdd(P.rec_mism + r0, (unsigned long long)sum);
-            } else if (acc_mm && acc_rec != INF32) {
-                atomicAdd(P.rec_mism + acc_rec, (unsigned long long)acc_mm);
+// ---- C / E: blocked walk. Lane owns tile windows 8 * lane .. 8 * lane + 7. An "event" is an output op: the
+// start of an =/X run or a pass-through op. Coordinates are tile-relative (64 * window + base).
+struct LaneWalk {
+    uint64_t MK[TILE_ITERS];  // masks of the lane's windows
+    uint32_t byte;            // op-start bits of the lane's windows
+    int cur0;                 // table index of the op owning the window before the lane's first
+    uint32_t pm;              // top bit: mismatch state of the base before the lane's first window
+    uint32_t n_win;           // active windows of the lane
+};
+
+__device__ __forceinline__ uint64_t run_starts(uint64_t m, uint32_t pm, bool op_start, uint32_t n) {
+    uint64_t d = m ^ ((m << 1) | (pm >> 31));
+    if (op_start) d |= 1ull;
+    return d & (~0ull >> (WIN_BASES - n));  // n >= 1 here
+}
+
+// C: events of the lane and the coordinate at which a run left open by an earlier lane closes (COORD_OPEN: none here)
+// end_closer (lane owning the tile's last active window): end of that window's M op if it ends inside the tile
+__device__ __forceinline__ void lane_count(const WarpSmem &S, const LaneWalk &W, unsigned lane, uint32_t &cnt, uint32_t &first_closer,
+                                           uint32_t &end_closer) {
+    cnt = 0;
+    first_closer = COORD_OPEN;
+    int cur = W.cur0;
+    OpEntry en = S.tab[cur < 0 ? 0 : cur];
+    uint32_t pm = W.pm;
+#pragma unroll
+    for (int j = 0; j < TILE_ITERS; j++) {
+        if ((uint32_t)j < W.n_win) {
+            const uint32_t p = 8u * lane + j;
+            const bool start = (W.byte >> j) & 1u;
+            if (start) {
+                // the previous op ends here: an M op at its end coordinate, a pass-through op at the window boundary
+                if (first_closer == COORD_OPEN) first_closer = (cur >= 0 && !(en.misc & EF_PASS)) ? (uint32_t)en.rem : WIN_BASES * p;
+                en = S.tab[++cur];
             }
+            if (en.misc & EF_PASS) {
+                cnt++;
+                pm = 0;
+            } else {
+                const int32_t rem = en.rem - WIN_BASES * (int32_t)p;
+                const uint32_t n = rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
+                const uint64_t d = run_starts(W.MK[j], pm, start, n);
+                if (d && first_closer == COORD_OPEN) first_closer = WIN_BASES * p + (__ffsll((long long)d) - 1);
+                cnt += __popcll(d);
+                pm = (uint32_t)(W.MK[j] >> 32);
+            }
+        }
+    }
+    end_closer = (!(en.misc & EF_PASS) && en.rem <= (int32_t)(WIN_BASES * (8u * lane + W.n_win))) ? (uint32_t)en.rem : COORD_OPEN;
+}
+
+// E: the lane's events as CigarRecord words into the staging list (entries base .. base + LIST_CAP - 1 of the tile).
+// ex = rank of the lane's first event inside the tile, closer = where a run still open at the lane's end closes.
+__device__ __forceinline__ void lane_emit(const EncodeParams &P, WarpSmem &S, const LaneWalk &W, unsigned lane, uint32_t ex, uint32_t base,
+                                          uint32_t closer, uint64_t s0, uint64_t tile_slot0, int64_t tile) {
+    uint64_t *L = S.u.list;
+    uint32_t rank = ex;
+    bool have = false;
+    uint32_t pstart = 0, prank = 0;
+    uint64_t ptyp = 0;
+    auto put = [&](uint32_t r, uint64_t word) {
+        const uint32_t k = r - base;
+        if (k < (uint32_t)LIST_CAP) L[k] = word;
+    };
+    int cur = W.cur0;
+    OpEntry en = S.tab[cur < 0 ? 0 : cur];
+    uint32_t pm = W.pm;
+#pragma unroll
+    for (int j = 0; j < TILE_ITERS; j++) {
+        if ((uint32_t)j < W.n_win) {
+            const uint32_t p = 8u * lane + j;
+            const bool start = (W.byte >> j) & 1u;
+            if (start) {
+                if (have) {  // the run ends with its op
+                    put(prank, ptyp | (uint64_t)((uint32_t)en.rem - pstart));
+                    have = false;
+                }
+                en = S.tab[++cur];
+                const uint32_t recw = S.rec[cur];
+                if ((recw >> 31) && rank - base < (uint32_t)LIST_CAP) P.rec_out_begin[recw & 0x7fffffffu] = (int64_t)(tile_slot0 + rank);
+            }
+            if (en.misc & EF_PASS) {
+                put(rank, ((uint64_t)(uint32_t)en.qw << 32) | (uint32_t)en.tw);
+                rank++;
+                pm = 0;
+            } else {
+                const int32_t rem = en.rem - WIN_BASES * (int32_t)p;
+                const uint32_t n = rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
+                const uint64_t m = W.MK[j];
+                uint64_t d = run_starts(m, pm, start, n);
+                while (d) {
+                    const uint32_t b = (uint32_t)__ffsll((long long)d) - 1u;
+                    d &= d - 1;
+                    const uint32_t c = WIN_BASES * p + b;
+                    if (have) put(prank, ptyp | (uint64_t)(c - pstart));
+                    pstart = c;
+                    ptyp = (uint64_t)(((m >> b) & 1ull) ? OP_X : OP_EQ) << 56;
+                    prank = rank++;
+                    have = true;
+                }
+                pm = (uint32_t)(m >> 32);
+            }
+        }
+    }
+    if (have) {
+        if (closer == COORD_OPEN) {
+            // provisional: absolute start, turned into a length by stitch_kernel
+            put(prank, ptyp | (WIN_BASES * s0 + pstart));
+            if (prank - base < (uint32_t)LIST_CAP) P.tile_open_slot[tile] = (int64_t)(tile_slot0 + prank);
+        } else {
+            put(prank, ptyp | (uint64_t)(closer - pstart));
         }
     }
 }
 
-// ---- emit_kernel ------------------------------------------------------------------------------------
-// list entry: bits 0-13 start coordinate inside the tile (64 * window + base), 14-19 gap back to the end of the
-// previous op (op-start entries only: 64 - bases in the previous window), 20 X run, 21 pass-through, 22-30 table index
-constexpr uint32_t LE_START = 0x3fffu, LE_X = 1u << 20, LE_PASS = 1u << 21;
-constexpr int LS_GAP = 14, LS_IDX = 22;
-constexpr uint32_t TERM_OPEN = 0xffffffffu;
-constexpr int LIST_CAP = 8 * 64 + 32;  // 8 lanes can start 512 runs in one iteration
-
-struct __align__(16) EmitEntry {
-    uint64_t opw;   // the op word (copied through when it is not an M op)
-    int32_t rem;    // M: op bases left at tile window 0, clamped to 2^30
-    uint32_t rec;   // record, top bit: first op of the record
-};
-
-template <int WARPS>
-struct EmitSmem {
-    EmitEntry tab[WARPS][TILE_TAB];
-    uint32_t list[WARPS][LIST_CAP];
-    uint32_t bm[WARPS][TILE_ITERS];
-    uint32_t itc[WARPS][TILE_ITERS];
-};
-
-template <int WARPS>
-__global__ void __launch_bounds__(32 * WARPS) emit_kernel(EncodeParams P) {
-    constexpr int ITERS = TILE_ITERS;
-    __shared__ EmitSmem<WARPS> S;
+template <int WARPS, int BATCH>
+__global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
+    __shared__ WarpSmem SM[WARPS];
+    __shared__ uint32_t s_wcount[WARPS];
+    __shared__ unsigned long long s_excl;
+    __shared__ int64_t s_ticket;
     const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    WarpSmem &S = SM[wid];
 
-    for (int64_t tile = (int64_t)blockIdx.x * WARPS + wid; tile < P.n_tiles; tile += (int64_t)gridDim.x * WARPS) {
+    for (;;) {
+        if (threadIdx.x == 0) s_ticket = (int64_t)atomicAdd(P.ticket, 1u);
+        __syncthreads();
+        const int64_t ct = s_ticket;
+        if (ct >= P.n_cta_tiles) break;
+        const int64_t tile = ct * WARPS + wid;
         const uint64_t s0 = (uint64_t)tile * TILE_WIN;
-        const uint64_t tile_end = min(s0 + (uint64_t)TILE_WIN, P.n_win);
-        const uint32_t n_act = (uint32_t)(tile_end - s0);
-        const uint64_t excl = __ldg(P.tile_excl + tile);
-        const uint32_t tile_count = __ldg(P.tile_count + tile);
+        const uint32_t n_act = s0 < P.n_win ? (uint32_t)min((uint64_t)TILE_WIN, P.n_win - s0) : 0u;
 
-        // the masks of the whole tile: independent loads, issued before anything else
-        uint64_t MK[ITERS];
+        LaneWalk W;
+        uint32_t cnt = 0, first_closer = COORD_OPEN, end_closer = COORD_OPEN, inc = 0;
+        if (n_act) {
+            unsigned adj;
+            bool any_exc;
+            build_table(P, S, tile, s0, s0 + n_act, lane, adj, any_exc);
+            uint32_t pm0 = any_exc ? compare_tile<BATCH, true>(P, S, n_act, lane, adj) : compare_tile<BATCH, false>(P, S, n_act, lane, adj);
+            __syncwarp();
+            // blocked view of the tile
+            W.byte = (S.bm[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
+            W.n_win = 8u * lane >= n_act ? 0u : min(8u, n_act - 8u * lane);
 #pragma unroll
-        for (int it = 0; it < ITERS; it++) MK[it] = 32u * it + lane < n_act ? __ldg(P.masks + s0 + 32u * it + lane) : 0ull;
-        uint32_t pm0 = 0;  // lane 0: top bit of the window before the tile
-        if (lane == 0 && s0 > 0) pm0 = (uint32_t)(__ldg(P.masks + s0 - 1) >> 32);
-
-        // ---- op table
-        unsigned adj = 0;
-        __syncwarp();
-        if (lane < ITERS) S.bm[wid][lane] = 0;
-        __syncwarp();
-        {
-            const int64_t cur = P.tile_first_op[tile];
-            bool more = true;
-            for (int g = 0; more; g++) {
-                const int64_t k = cur + 32 * g + lane;
-                const bool valid = k < P.n_ops;
-                uint64_t wo = INF64, opw = 0;
-                uint32_t rec = 0;
-                if (valid) { wo = __ldg(P.woff + k); opw = __ldg(P.ops + k); rec = __ldg(P.op_rec + k); }
-                const bool in = valid && wo < tile_end;
-                if (in) {
-                    const int e = 32 * g + (int)lane;
-                    int64_t rem = (int64_t)(opw & LEN_MASK) - WIN_BASES * (int64_t)(s0 - wo);
-                    if (rem > (1ll << 30)) rem = 1ll << 30;
-                    EmitEntry en;
-                    en.opw = opw; en.rem = (int32_t)rem; en.rec = rec;
-                    S.tab[wid][e] = en;
-                    if (wo >= s0) atomicOr(&S.bm[wid][(wo - s0) >> 5], 1u << ((wo - s0) & 31));
-                }
-                if (g == 0) adj = __shfl_sync(FULL, (unsigned)(wo == s0), 0);
-                more = __all_sync(FULL, in);
-            }
-        }
-        __syncwarp();
-
-        // ---- run starts and their ranks inside the tile
-        uint32_t D0[ITERS], D1[ITERS], EX[ITERS], META[ITERS];
-        uint32_t run = 0, pre = 0, term_local = TERM_OPEN;
-        uint32_t carry_m = 0, carry_n = WIN_BASES;
+            for (int j = 0; j < TILE_ITERS; j++) W.MK[j] = S.u.mask[9 * lane + j];
+            uint32_t oinc = __popc(W.byte);
+            const uint32_t oc = oinc;
 #pragma unroll
-        for (int it = 0; it < ITERS; it++) {
-            const uint32_t srel = 32u * it + lane;
-            const bool active = srel < n_act;
-            uint32_t w;
-            const uint32_t idx = op_index(S.bm[wid], it, lane, pre, adj, w);
-            const uint32_t m0 = (uint32_t)MK[it], m1 = (uint32_t)(MK[it] >> 32);
-            uint32_t meta = 0, n = WIN_BASES, d0 = 0, d1 = 0, cnt = 0;
-            bool isM = false;
-            if (active) {
-                const EmitEntry en = S.tab[wid][idx];
-                const bool wi0 = (w >> lane) & 1u;
-                meta = MB_ACTIVE | (idx << MS_IDX) | (wi0 ? MB_WI0 : 0u);
-                if ((int)(en.opw >> 56) != OP_M) {
-                    meta |= MB_PASS;
-                    cnt = 1;
-                } else {
-                    isM = true;
-                    const int32_t rem = en.rem - WIN_BASES * (int32_t)srel;
-                    n = rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
-                    if (rem <= WIN_BASES) {
-                        meta |= MB_LAST;
-                        if (srel == n_act - 1) term_local = WIN_BASES * srel + n;
-                    }
-                }
-                if (wi0 && (en.rec >> 31)) meta |= MB_HEAD;
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(FULL, oinc, o);
+                if (lane >= (unsigned)o) oinc += t;
             }
-            // neighbours: mismatch state of the previous base and size of the previous window
-            const uint32_t mm1 = isM ? m1 : 0u;
-            uint32_t pm = __shfl_up_sync(FULL, mm1, 1);
-            uint32_t pn = __shfl_up_sync(FULL, n, 1);
-            if (lane == 0) {
-                pm = it == 0 ? pm0 : carry_m;
-                pn = it == 0 ? (uint32_t)WIN_BASES : carry_n;
-            }
-            carry_m = __shfl_sync(FULL, mm1, 31);
-            carry_n = __shfl_sync(FULL, n, 31);
-            if (isM) {
-                const uint64_t valid = ~0ull >> (WIN_BASES - n);
-                d0 = (m0 ^ __funnelshift_l(pm, m0, 1)) & (uint32_t)valid;
-                d1 = (m1 ^ __funnelshift_l(m0, m1, 1)) & (uint32_t)(valid >> 32);
-                if (meta & MB_WI0) d0 |= 1u;
-                cnt = __popc(d0) + __popc(d1);
-            }
-            if (meta & MB_WI0) meta |= (WIN_BASES - pn) << MS_GAP;
-            uint32_t inc = cnt;
+            W.cur0 = (int)(oinc - oc) - (int)adj;
+            const uint32_t up = __shfl_up_sync(FULL, (uint32_t)(W.MK[TILE_ITERS - 1] >> 32), 1);
+            W.pm = lane ? up : pm0;
+            lane_count(S, W, lane, cnt, first_closer, end_closer);
+            inc = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const uint32_t t = __shfl_up_sync(FULL, inc, o);
                 if (lane >= (unsigned)o) inc += t;
             }
-            EX[it] = run + inc - cnt;
-            run += __shfl_sync(FULL, inc, 31);
-            if (lane == 0) S.itc[wid][it] = run;
-            if (meta & MB_HEAD) P.rec_out_begin[S.tab[wid][idx].rec & 0x7fffffffu] = (int64_t)(excl + EX[it]);
-            D0[it] = d0; D1[it] = d1; META[it] = meta;
         }
-        const uint32_t term = __shfl_sync(FULL, term_local, (n_act - 1) & 31);
-        if (lane == 0 && tile_count == 0) P.tile_first_closer[tile] = term == TERM_OPEN ? INF64 : WIN_BASES * s0 + term;
+        const uint32_t tile_count = __shfl_sync(FULL, inc, 31);
+        if (lane == 0) s_wcount[wid] = tile_count;
+        __syncthreads();
 
-        // ---- emission: scatter run starts into the list, then turn it into CigarRecord words (coalesced stores)
-        uint32_t *L = S.list[wid];
-        uint32_t flushed = 0;  // list entries already written out
-        auto flush = [&](uint32_t fill, bool final) {
-            __syncwarp();
-            const uint32_t n_emit = final ? fill : fill - 1;
-            for (uint32_t i = lane; i < n_emit; i += 32) {
-                const uint32_t e = L[i];
-                const uint64_t slot = excl + flushed + i;
-                uint64_t word;
-                if (e & LE_PASS) {
-                    word = S.tab[wid][(e >> LS_IDX) & 511u].opw;
-                } else {
-                    uint32_t close = term;
-                    if (i + 1 < fill) {
-                        const uint32_t nx = L[i + 1];
-                        close = (nx & LE_START) - ((nx >> LS_GAP) & 63u);
-                    }
-                    const uint64_t typ = (uint64_t)((e & LE_X) ? OP_X : OP_EQ) << 56;
-                    if (close == TERM_OPEN) {
-                        word = typ | (WIN_BASES * s0 + (e & LE_START));  // provisional: absolute start, fixed by stitch_kernel
-                        P.tile_open_slot[tile] = (int64_t)slot;
-                    } else {
-                        word = typ | (uint64_t)(close - (e & LE_START));
-                    }
-                }
-                P.out[slot] = word;
-                if (flushed + i == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + (e & LE_START) - ((e >> LS_GAP) & 63u);
-            }
-            __syncwarp();
-            if (!final) {
-                const uint32_t last = L[fill - 1];
-                __syncwarp();
-                if (lane == 0) L[0] = last;
-                flushed += fill - 1;
-            }
-        };
-        // one lane's run starts of one window -> list
-        auto scatter = [&](int it) {
-            const uint32_t meta = META[it];
-            if (!(meta & MB_ACTIVE)) return;
-            uint32_t r = EX[it] - flushed;
-            const uint32_t x0 = WIN_BASES * (32u * it + lane);
-            const uint32_t gap = ((meta >> MS_GAP) & 63u) << LS_GAP;
-            if (meta & MB_PASS) {
-                L[r] = x0 | gap | LE_PASS | (((meta >> MS_IDX) & 511u) << LS_IDX);
-                return;
-            }
-            const uint32_t m0 = (uint32_t)MK[it], m1 = (uint32_t)(MK[it] >> 32);
-            uint32_t d = D0[it];
-            bool first = true;
-            while (d) {
-                const uint32_t b = __ffs(d) - 1;
-                d &= d - 1;
-                L[r++] = (x0 + b) | (first ? gap : 0u) | (((m0 >> b) & 1u) ? LE_X : 0u);
-                first = false;
-            }
-            d = D1[it];
-            while (d) {
-                const uint32_t b = __ffs(d) - 1;
-                d &= d - 1;
-                L[r++] = (x0 + 32 + b) | (((m1 >> b) & 1u) ? LE_X : 0u);
-            }
-        };
+        // ---- D: decoupled look-back over CTA tiles (warp 0)
+        if (wid == 0) {
+            unsigned long long agg = 0;
 #pragma unroll
-        for (int it = 0; it < ITERS; it++) {
-            const uint32_t before = it ? S.itc[wid][it - 1] : 0u, after = S.itc[wid][it];
-            if (after - flushed <= (uint32_t)LIST_CAP) {
-                scatter(it);  // the usual case: the whole iteration fits behind what is already listed
-            } else {
-                // dense run starts: 8 lanes at a time (at most 512 entries), flushing in between
-#pragma unroll 1
-                for (int g = 0; g < 4; g++) {
-                    const uint32_t g_begin = __shfl_sync(FULL, EX[it], 8 * g);
-                    const uint32_t g_end = g < 3 ? __shfl_sync(FULL, EX[it], (8 * g + 8) & 31) : after;
-                    if (g_end - flushed > (uint32_t)LIST_CAP && g_begin > flushed) flush(g_begin - flushed, false);
-                    if ((lane >> 3) == (unsigned)g) scatter(it);
+            for (int w = 0; w < WARPS; w++) agg += s_wcount[w];
+            volatile unsigned long long *st = P.status;
+            if (lane == 0) st[ct] = (ct == 0 ? ST_INCL : ST_AGG) | agg;
+            unsigned long long excl = 0;
+            if (ct > 0) {
+                int64_t j = ct - 1 - (int64_t)lane;
+                for (;;) {
+                    unsigned long long v = j >= 0 ? st[j] : (2ull << 62);
+                    while (__any_sync(FULL, (v >> 62) == 0)) v = j >= 0 ? st[j] : (2ull << 62);
+                    const unsigned incl = __ballot_sync(FULL, (v >> 62) == 2);
+                    const unsigned upto = incl ? (unsigned)__ffs(incl) - 1u : 31u;  // nearest tile holding an inclusive prefix
+                    unsigned long long c = lane <= upto ? (v & ST_VAL) : 0ull;
+#pragma unroll
+                    for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(FULL, c, o);
+                    excl += c;
+                    if (incl) break;
+                    j -= 32;
+                }
+                if (lane == 0) st[ct] = ST_INCL | (excl + agg);
+            }
+            if (lane == 0) {
+                s_excl = excl;
+                if (ct == P.n_cta_tiles - 1) *P.total_out = excl + agg;
+            }
+        }
+        __syncthreads();
+
+        // ---- E: emit
+        if (n_act) {
+            unsigned long long slot0 = s_excl;
+#pragma unroll
+            for (int w = 0; w < WARPS; w++) slot0 += (unsigned)w < wid ? s_wcount[w] : 0u;
+            // where a run left open at the end of a lane closes: first closer of the later lanes, else the tile's end
+            const uint32_t term = __shfl_sync(FULL, end_closer, (n_act - 1) >> 3);
+            uint32_t suf = first_closer;  // inclusive suffix-min
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_down_sync(FULL, suf, o);
+                if (lane + o < 32) suf = min(suf, t);
+            }
+            uint32_t closer = __shfl_down_sync(FULL, suf, 1);
+            if (lane == 31) closer = COORD_OPEN;
+            closer = min(closer, term);
+            if (lane == 0) {
+                const uint32_t fc = min(suf, term);
+                P.tile_first_closer[tile] = fc == COORD_OPEN ? INF64 : WIN_BASES * s0 + fc;
+            }
+            const uint32_t ex = inc - cnt;
+            for (uint32_t base = 0; base < tile_count; base += LIST_CAP) {
+                __syncwarp();
+                if (cnt && ex < base + LIST_CAP && ex + cnt > base) lane_emit(P, S, W, lane, ex, base, closer, s0, slot0, tile);
+                __syncwarp();
+                const uint32_t n_emit = min((uint32_t)LIST_CAP, tile_count - base);
+                for (uint32_t i = lane; i < n_emit; i += 32) {
+                    const unsigned long long slot = slot0 + base + i;
+                    if (slot < (unsigned long long)P.out_cap) P.out[slot] = S.u.list[i];
                 }
             }
-            (void)before;
         }
-        if (tile_count > flushed) flush(tile_count - flushed, true);
     }
 }
 
-// A run left open at the end of tile t closes at the first run start / op end of a later tile.
+// A run left open at the end of warp tile t closes at the first run start / op end of a later tile.
 __global__ void stitch_kernel(int64_t n_tiles, const int64_t *tile_open_slot, const uint64_t *tile_first_closer,
                               uint64_t *out, int64_t out_cap) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

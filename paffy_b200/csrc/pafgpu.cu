@@ -76,7 +76,7 @@ struct GenomeStore {
 struct pafgpu_ctx {
     int device = 0;
     int sm_count = 148;
-    int cmp_ctas_per_sm = 4, emit_ctas_per_sm = 4;
+    int enc_ctas_per_sm = 4;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[8] = {};
     std::string err;
@@ -88,7 +88,7 @@ struct pafgpu_ctx {
     // staging for host batches
     DevBuf in_op_begin, in_ops, in_qc, in_tc, in_qs, in_qe, in_ts, in_strand, in_seq;
     // per-batch work buffers
-    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, tile_count, masks, tile_excl, tile_first_closer, tile_open_slot;
+    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, status, tile_first_closer, tile_open_slot;
     DevBuf out, rec_out_begin, rec_mism, scalars;
     // serialiser
     DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
@@ -96,7 +96,7 @@ struct pafgpu_ctx {
 
     // last batch
     bool have_batch = false;
-    int64_t n_records = 0, n_ops = 0, n_out = 0, n_tiles = 0;
+    int64_t n_records = 0, n_ops = 0, n_out = 0, n_tiles = 0, aligned = 0, retried = 0;
     uint64_t n_win = 0;
     EncodeParams last{};
 };
@@ -105,7 +105,7 @@ namespace {
 
 constexpr int ITERS = 8;
 constexpr uint32_t TILE_WINDOWS = 32u * ITERS;
-enum { SC_BAD = 0, SC_ALIGNED = 1, SC_SPARE = 2, SC_TOTAL = 3, SC_NWIN = 4, SC_TMP = 5, SC_COUNT = 8 };
+enum { SC_BAD = 0, SC_ALIGNED = 1, SC_TOTAL = 2, SC_TICKET = 3, SC_NWIN = 4, SC_TMP = 5, SC_COUNT = 8 };
 
 int fail(pafgpu_ctx *c, int code, const std::string &msg) {
     if (c) c->err = msg; else g_create_error = msg;
@@ -223,36 +223,45 @@ int genome_sync_table(pafgpu_ctx *c, GenomeStore &g) {
 
 constexpr int ENC_WARPS = 4, CMP_BATCH = 4;
 
-// (re)launch compare -> scan -> emit -> stitch for c->last; leaves the output op count in c->n_out
-int launch_encode(pafgpu_ctx *c) {
+// one pass of encode_kernel + stitch_kernel for c->last; leaves the output op count in c->n_out
+int launch_encode_once(pafgpu_ctx *c) {
     EncodeParams &P = c->last;
     uint64_t *sc = c->scalars.as<uint64_t>();
-    const int64_t T = c->n_tiles;
+    const int64_t T = c->n_tiles, CT = P.n_cta_tiles;
     CU(cudaMemsetAsync(c->tile_open_slot.p, 0xff, (size_t)std::max<int64_t>(T, 1) * 8, c->stream));
     CU(cudaMemsetAsync(c->rec_mism.p, 0, (size_t)std::max<int64_t>(c->n_records, 1) * 8, c->stream));
-    CU(cudaEventRecord(c->ev[4], c->stream));
-    if (T > 0) {
-        const unsigned grid = (unsigned)std::min<int64_t>((T + ENC_WARPS - 1) / ENC_WARPS, (int64_t)c->sm_count * c->cmp_ctas_per_sm);
-        compare_kernel<ENC_WARPS, CMP_BATCH><<<grid, 32 * ENC_WARPS, 0, c->stream>>>(P);
-    }
-    CU(cudaEventRecord(c->ev[5], c->stream));
-    if (int rc = scan_u32(c, c->tile_count.as<uint32_t>(), T, c->tile_excl.as<uint64_t>(), sc + SC_TOTAL)) return rc;
-    CU(cudaMemcpyAsync(&c->host_total, sc + SC_TOTAL, 8, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
-    const int64_t total = (int64_t)c->host_total;
-    CU(c->out.ensure((size_t)std::max<int64_t>(total, 1) * 8));
+    CU(cudaMemsetAsync(c->status.p, 0, (size_t)std::max<int64_t>(CT, 1) * 8, c->stream));
+    CU(cudaMemsetAsync(sc + SC_TOTAL, 0, 16, c->stream));  // SC_TOTAL and SC_TICKET
     P.out = c->out.as<uint64_t>();
     P.out_cap = (int64_t)(c->out.cap / 8);
-    CU(cudaEventRecord(c->ev[6], c->stream));
-    if (T > 0) {
-        const unsigned grid = (unsigned)std::min<int64_t>((T + ENC_WARPS - 1) / ENC_WARPS, (int64_t)c->sm_count * c->emit_ctas_per_sm);
-        emit_kernel<ENC_WARPS><<<grid, 32 * ENC_WARPS, 0, c->stream>>>(P);
-        stitch_kernel<<<blocks_for(T, 256), 256, 0, c->stream>>>(T, P.tile_open_slot, P.tile_first_closer, P.out, P.out_cap);
+    CU(cudaEventRecord(c->ev[4], c->stream));
+    if (CT > 0) {
+        const unsigned grid = (unsigned)std::min<int64_t>(CT, (int64_t)c->sm_count * c->enc_ctas_per_sm);
+        encode_kernel<ENC_WARPS, CMP_BATCH><<<grid, 32 * ENC_WARPS, 0, c->stream>>>(P);
     }
+    CU(cudaEventRecord(c->ev[5], c->stream));
+    if (T > 0) stitch_kernel<<<blocks_for(T, 256), 256, 0, c->stream>>>(T, P.tile_open_slot, P.tile_first_closer, P.out, P.out_cap);
     CU(cudaMemcpyAsync(P.rec_out_begin + c->n_records, sc + SC_TOTAL, 8, cudaMemcpyDeviceToDevice, c->stream));
+    CU(cudaMemcpyAsync(&c->host_total, sc + SC_TOTAL, 8, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaEventRecord(c->ev[7], c->stream));
+    CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
-    c->n_out = total;
+    c->n_out = (int64_t)c->host_total;
+    return 0;
+}
+
+// The number of output ops is only known after the pass: the buffer is sized from a guess (or the last batch) and,
+// when the guess was too small, grown to the exact size and the pass repeated (stores beyond capacity are dropped).
+int launch_encode(pafgpu_ctx *c, int64_t aligned) {
+    const int64_t guess = c->n_ops + aligned / 32 + 1024;
+    CU(c->out.ensure((size_t)guess * 8));
+    c->retried = 0;
+    if (int rc = launch_encode_once(c)) return rc;
+    if (c->n_out > (int64_t)(c->out.cap / 8)) {
+        CU(c->out.ensure((size_t)c->n_out * 8));
+        c->retried = 1;
+        if (int rc = launch_encode_once(c)) return rc;
+    }
     return 0;
 }
 
@@ -302,9 +311,8 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     const int64_t aligned = (int64_t)host_sc[SC_ALIGNED];
     const int64_t n_tiles = (int64_t)((n_win + TILE_WINDOWS - 1) / TILE_WINDOWS);
     CU(c->tile_first_op.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 4));
-    CU(c->tile_count.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 4));
-    CU(c->tile_excl.ensure((size_t)(n_tiles + 1) * 8));
-    CU(c->masks.ensure((size_t)std::max<uint64_t>(n_win, 1) * 8));
+    const int64_t n_cta_tiles = (n_tiles + ENC_WARPS - 1) / ENC_WARPS;
+    CU(c->status.ensure((size_t)std::max<int64_t>(n_cta_tiles, 1) * 8));
     CU(c->tile_first_closer.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
     CU(c->tile_open_slot.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
     if (N > 0)
@@ -318,10 +326,10 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     P.op_rec = c->op_rec.as<uint32_t>(); P.tile_first_op = c->tile_first_op.as<uint32_t>();
     P.n_ops = N; P.n_win = n_win; P.n_tiles = n_tiles;
     P.out = c->out.as<uint64_t>(); P.out_cap = (int64_t)(c->out.cap / 8);
-    P.masks = c->masks.as<uint64_t>();
-    P.tile_count = c->tile_count.as<uint32_t>();
-    P.tile_excl = c->tile_excl.as<uint64_t>();
-    P.debug = getenv("PAFGPU_DEBUG") ? atoi(getenv("PAFGPU_DEBUG")) : 0;
+    P.n_cta_tiles = n_cta_tiles;
+    P.status = c->status.as<unsigned long long>();
+    P.ticket = (unsigned int *)(sc + SC_TICKET);
+    P.total_out = (unsigned long long *)(sc + SC_TOTAL);
     P.tile_first_closer = c->tile_first_closer.as<uint64_t>();
     P.tile_open_slot = c->tile_open_slot.as<int64_t>();
     P.rec_out_begin = c->rec_out_begin.as<int64_t>();
@@ -329,7 +337,8 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     c->n_records = R; c->n_ops = N; c->n_tiles = n_tiles; c->n_win = n_win;
 
     CU(cudaEventRecord(c->ev[2], c->stream));
-    if (int rc = launch_encode(c)) return rc;
+    c->aligned = aligned;
+    if (int rc = launch_encode(c, aligned)) return rc;
     CU(cudaEventRecord(c->ev[3], c->stream));
     CU(cudaStreamSynchronize(c->stream));
     c->have_batch = true;
@@ -339,11 +348,11 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
         res->aligned_bases = aligned;
         res->n_windows = (int64_t)n_win;
         res->n_tiles = n_tiles;
-        res->retried = 0;
+        res->retried = c->retried;
         cudaEventElapsedTime(&res->ms_ingest, c->ev[0], c->ev[1]);
         cudaEventElapsedTime(&res->ms_encode, c->ev[2], c->ev[3]);
         cudaEventElapsedTime(&res->ms_kernel, c->ev[4], c->ev[5]);
-        cudaEventElapsedTime(&res->ms_emit, c->ev[6], c->ev[7]);
+        cudaEventElapsedTime(&res->ms_emit, c->ev[5], c->ev[7]);
     }
     return 0;
 }
@@ -421,10 +430,8 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
     {
         int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, compare_kernel<ENC_WARPS, CMP_BATCH>, 32 * ENC_WARPS, 0) == cudaSuccess && per_sm > 0)
-            ctx->cmp_ctas_per_sm = per_sm;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, emit_kernel<ENC_WARPS>, 32 * ENC_WARPS, 0) == cudaSuccess && per_sm > 0)
-            ctx->emit_ctas_per_sm = per_sm;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<ENC_WARPS, CMP_BATCH>, 32 * ENC_WARPS, 0) == cudaSuccess && per_sm > 0)
+            ctx->enc_ctas_per_sm = per_sm;
     }
     ctx->scalars.ensure(SC_COUNT * 8);
     *out = ctx;
@@ -439,7 +446,7 @@ void pafgpu_destroy(pafgpu_ctx *c) {
     c->scratch.release();
     DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
                       &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
-                      &c->tile_count, &c->masks, &c->tile_excl, &c->tile_first_closer, &c->tile_open_slot, &c->out, &c->rec_out_begin, &c->rec_mism,
+                      &c->status, &c->tile_first_closer, &c->tile_open_slot, &c->out, &c->rec_out_begin, &c->rec_mism,
                       &c->scalars, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
                       &c->ser_text};
     for (DevBuf *b : bufs) b->release();
@@ -605,7 +612,7 @@ int pafgpu_time_encode(pafgpu_ctx *c, int reps, float *ms_stage, float *ms_kerne
     double sum = 0, ksum = 0;
     for (int i = 0; i < reps; i++) {
         CU(cudaEventRecord(c->ev[2], c->stream));
-        if (int rc = launch_encode(c)) return rc;
+        if (int rc = launch_encode(c, c->aligned)) return rc;
         CU(cudaEventRecord(c->ev[3], c->stream));
         CU(cudaStreamSynchronize(c->stream));
         float ms = 0;
