@@ -40,7 +40,8 @@ struct EncodeParams {
     unsigned int *ticket;           // pre-set to 0
     unsigned long long *total_out;  // number of output ops of the whole batch
     uint64_t *tile_first_closer;    // absolute window-axis coordinate (64 * window + base) of the warp tile's first run start / op end
-    int64_t *tile_open_slot;        // output slot of a run left open, -1 if none (pre-set)
+    int32_t *tile_open_rank;        // rank inside the warp tile of a run left open, -1 if none (pre-set)
+    uint64_t *tile_slot0;           // output slot of the warp tile's first event
     int64_t *rec_out_begin;
     unsigned long long *rec_mism;
 };
@@ -50,7 +51,7 @@ constexpr int TILE_ITERS = 8;                 // windows per lane per warp tile
 constexpr int TILE_WIN = 32 * TILE_ITERS;     // windows per warp tile
 constexpr int TILE_TAB = TILE_WIN + 2;        // a tile overlaps at most TILE_WIN + 1 ops
 constexpr int MASK_PAD = TILE_WIN + TILE_WIN / 8;  // mask of window p sits at p + (p >> 3): conflict-free blocked reads
-constexpr int LIST_CAP = 512;                 // staged output words per round
+constexpr int LIST_CAP = 1024;                // events converted per round
 constexpr uint32_t COORD_OPEN = 0xffffffffu;
 constexpr unsigned long long ST_AGG = 1ull << 62, ST_INCL = 2ull << 62, ST_VAL = (1ull << 62) - 1;
 
@@ -78,7 +79,7 @@ struct WarpSmem {
     uint32_t rec[TILE_TAB];   // owning record, top bit: first op of the record
     union {
         uint64_t mask[MASK_PAD];
-        uint64_t list[LIST_CAP];
+        uint32_t list[LIST_CAP + 2];   // 32-bit event entries of one round (+ successor of the last)
     } u;
     uint32_t bm[TILE_ITERS];  // bit p: an op starts at tile window p
 };
@@ -255,6 +256,15 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
 
 // ---- C / E: blocked walk. Lane owns tile windows 8 * lane .. 8 * lane + 7. An "event" is an output op: the
 // start of an =/X run or a pass-through op. Coordinates are tile-relative (64 * window + base).
+// Events are first listed as 32-bit entries in tile order:
+//   bits 0-13  run start coordinate (pass-through op: its table index)
+//   bits 14-28 coordinate at which the run before this event closes: the event's own coordinate inside an op,
+//              the previous op's end at an op start
+//   bit 29 X run, bit 30 pass-through op
+// so that entry i's length is close(entry i + 1) - start(entry i), computed by any lane.
+constexpr uint32_t LE_START = 0x3fffu, LE_CLOSE = 0x7fffu, LE_X = 1u << 29, LE_PASS = 1u << 30;
+constexpr int LS_CLOSE = 14;
+
 struct LaneWalk {
     uint64_t MK[TILE_ITERS];  // masks of the lane's windows
     uint32_t byte;            // op-start bits of the lane's windows
@@ -263,18 +273,20 @@ struct LaneWalk {
     uint32_t n_win;           // active windows of the lane
 };
 
-__device__ __forceinline__ uint64_t run_starts(uint64_t m, uint32_t pm, bool op_start, uint32_t n) {
-    uint64_t d = m ^ ((m << 1) | (pm >> 31));
-    if (op_start) d |= 1ull;
-    return d & (~0ull >> (WIN_BASES - n));  // n >= 1 here
+// run-start bits of one M window (n >= 1 bases); the op-start bit is handled by the caller
+__device__ __forceinline__ void run_starts(uint32_t m0, uint32_t m1, uint32_t pm, uint32_t n, uint32_t &d0, uint32_t &d1) {
+    d0 = m0 ^ ((m0 << 1) | (pm >> 31));
+    d1 = m1 ^ __funnelshift_l(m0, m1, 1);
+    const uint32_t v0 = n >= 32 ? 0xffffffffu : (1u << n) - 1u;
+    const uint32_t v1 = n > 32 ? 0xffffffffu >> (64 - n) : 0u;
+    d0 &= v0;
+    d1 &= v1;
 }
 
-// C: events of the lane and the coordinate at which a run left open by an earlier lane closes (COORD_OPEN: none here)
-// end_closer (lane owning the tile's last active window): end of that window's M op if it ends inside the tile
-__device__ __forceinline__ void lane_count(const WarpSmem &S, const LaneWalk &W, unsigned lane, uint32_t &cnt, uint32_t &first_closer,
-                                           uint32_t &end_closer) {
+// C: number of events of the lane; end_closer (meaningful on the lane owning the tile's last active window): end
+// of that window's M op when it ends inside the tile, else COORD_OPEN
+__device__ __forceinline__ void lane_count(const WarpSmem &S, const LaneWalk &W, unsigned lane, uint32_t &cnt, uint32_t &end_closer) {
     cnt = 0;
-    first_closer = COORD_OPEN;
     int cur = W.cur0;
     OpEntry en = S.tab[cur < 0 ? 0 : cur];
     uint32_t pm = W.pm;
@@ -283,40 +295,31 @@ __device__ __forceinline__ void lane_count(const WarpSmem &S, const LaneWalk &W,
         if ((uint32_t)j < W.n_win) {
             const uint32_t p = 8u * lane + j;
             const bool start = (W.byte >> j) & 1u;
-            if (start) {
-                // the previous op ends here: an M op at its end coordinate, a pass-through op at the window boundary
-                if (first_closer == COORD_OPEN) first_closer = (cur >= 0 && !(en.misc & EF_PASS)) ? (uint32_t)en.rem : WIN_BASES * p;
-                en = S.tab[++cur];
-            }
+            if (start) en = S.tab[++cur];
             if (en.misc & EF_PASS) {
                 cnt++;
                 pm = 0;
             } else {
                 const int32_t rem = en.rem - WIN_BASES * (int32_t)p;
                 const uint32_t n = rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
-                const uint64_t d = run_starts(W.MK[j], pm, start, n);
-                if (d && first_closer == COORD_OPEN) first_closer = WIN_BASES * p + (__ffsll((long long)d) - 1);
-                cnt += __popcll(d);
-                pm = (uint32_t)(W.MK[j] >> 32);
+                const uint32_t m0 = (uint32_t)W.MK[j], m1 = (uint32_t)(W.MK[j] >> 32);
+                uint32_t d0, d1;
+                run_starts(m0, m1, pm, n, d0, d1);
+                if (start) d0 |= 1u;
+                cnt += __popc(d0) + __popc(d1);
+                pm = m1;
             }
         }
     }
     end_closer = (!(en.misc & EF_PASS) && en.rem <= (int32_t)(WIN_BASES * (8u * lane + W.n_win))) ? (uint32_t)en.rem : COORD_OPEN;
 }
 
-// E: the lane's events as CigarRecord words into the staging list (entries base .. base + LIST_CAP - 1 of the tile).
-// ex = rank of the lane's first event inside the tile, closer = where a run still open at the lane's end closes.
-__device__ __forceinline__ void lane_emit(const EncodeParams &P, WarpSmem &S, const LaneWalk &W, unsigned lane, uint32_t ex, uint32_t base,
-                                          uint32_t closer, uint64_t s0, uint64_t tile_slot0, int64_t tile) {
-    uint64_t *L = S.u.list;
-    uint32_t rank = ex;
-    bool have = false;
-    uint32_t pstart = 0, prank = 0;
-    uint64_t ptyp = 0;
-    auto put = [&](uint32_t r, uint64_t word) {
-        const uint32_t k = r - base;
-        if (k < (uint32_t)LIST_CAP) L[k] = word;
-    };
+// E1: list the lane's events, entries base .. base + LIST_CAP of the tile (one more than a round converts, so the
+// last converted entry sees its successor). ex = rank of the lane's first event inside the tile. Also leaves the
+// tile-relative output rank of every record's first op in rec_out_begin (rec_begin_kernel adds the tile's slot).
+__device__ __forceinline__ void lane_scatter(const EncodeParams &P, WarpSmem &S, const LaneWalk &W, unsigned lane, uint32_t ex, uint32_t base) {
+    uint32_t *L = S.u.list;
+    uint32_t r = ex - base;  // wraps for events before the round; comes back to 0 exactly at entry `base`
     int cur = W.cur0;
     OpEntry en = S.tab[cur < 0 ? 0 : cur];
     uint32_t pm = W.pm;
@@ -324,46 +327,45 @@ __device__ __forceinline__ void lane_emit(const EncodeParams &P, WarpSmem &S, co
     for (int j = 0; j < TILE_ITERS; j++) {
         if ((uint32_t)j < W.n_win) {
             const uint32_t p = 8u * lane + j;
+            const uint32_t x0 = WIN_BASES * p;
             const bool start = (W.byte >> j) & 1u;
+            uint32_t close0 = x0;
             if (start) {
-                if (have) {  // the run ends with its op
-                    put(prank, ptyp | (uint64_t)((uint32_t)en.rem - pstart));
-                    have = false;
-                }
+                // the previous op ends here: an M op at its end coordinate, a pass-through op at the window boundary
+                if (cur >= 0 && !(en.misc & EF_PASS)) close0 = (uint32_t)en.rem;
                 en = S.tab[++cur];
                 const uint32_t recw = S.rec[cur];
-                if ((recw >> 31) && rank - base < (uint32_t)LIST_CAP) P.rec_out_begin[recw & 0x7fffffffu] = (int64_t)(tile_slot0 + rank);
+                if ((recw >> 31) && r <= (uint32_t)LIST_CAP) P.rec_out_begin[recw & 0x7fffffffu] = (int64_t)(r + base);
             }
             if (en.misc & EF_PASS) {
-                put(rank, ((uint64_t)(uint32_t)en.qw << 32) | (uint32_t)en.tw);
-                rank++;
+                if (r <= (uint32_t)LIST_CAP) L[r] = (uint32_t)cur | (close0 << LS_CLOSE) | LE_PASS;
+                r++;
                 pm = 0;
             } else {
                 const int32_t rem = en.rem - WIN_BASES * (int32_t)p;
                 const uint32_t n = rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
-                const uint64_t m = W.MK[j];
-                uint64_t d = run_starts(m, pm, start, n);
-                while (d) {
-                    const uint32_t b = (uint32_t)__ffsll((long long)d) - 1u;
-                    d &= d - 1;
-                    const uint32_t c = WIN_BASES * p + b;
-                    if (have) put(prank, ptyp | (uint64_t)(c - pstart));
-                    pstart = c;
-                    ptyp = (uint64_t)(((m >> b) & 1ull) ? OP_X : OP_EQ) << 56;
-                    prank = rank++;
-                    have = true;
+                const uint32_t m0 = (uint32_t)W.MK[j], m1 = (uint32_t)(W.MK[j] >> 32);
+                uint32_t d0, d1;
+                run_starts(m0, m1, pm, n, d0, d1);
+                if (start) {
+                    if (r <= (uint32_t)LIST_CAP) L[r] = x0 | (close0 << LS_CLOSE) | ((m0 & 1u) ? LE_X : 0u);
+                    r++;
+                    d0 &= ~1u;
                 }
-                pm = (uint32_t)(m >> 32);
+                while (d0) {
+                    const uint32_t b = (uint32_t)__ffs((int)d0) - 1u;
+                    d0 &= d0 - 1u;
+                    if (r <= (uint32_t)LIST_CAP) L[r] = (x0 + b) * ((1u << LS_CLOSE) + 1u) | (((m0 >> b) & 1u) ? LE_X : 0u);
+                    r++;
+                }
+                while (d1) {
+                    const uint32_t b = (uint32_t)__ffs((int)d1) - 1u;
+                    d1 &= d1 - 1u;
+                    if (r <= (uint32_t)LIST_CAP) L[r] = (x0 + 32u + b) * ((1u << LS_CLOSE) + 1u) | (((m1 >> b) & 1u) ? LE_X : 0u);
+                    r++;
+                }
+                pm = m1;
             }
-        }
-    }
-    if (have) {
-        if (closer == COORD_OPEN) {
-            // provisional: absolute start, turned into a length by stitch_kernel
-            put(prank, ptyp | (WIN_BASES * s0 + pstart));
-            if (prank - base < (uint32_t)LIST_CAP) P.tile_open_slot[tile] = (int64_t)(tile_slot0 + prank);
-        } else {
-            put(prank, ptyp | (uint64_t)(closer - pstart));
         }
     }
 }
@@ -387,7 +389,7 @@ __global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
         const uint32_t n_act = s0 < P.n_win ? (uint32_t)min((uint64_t)TILE_WIN, P.n_win - s0) : 0u;
 
         LaneWalk W;
-        uint32_t cnt = 0, first_closer = COORD_OPEN, end_closer = COORD_OPEN, inc = 0;
+        uint32_t cnt = 0, end_closer = COORD_OPEN, inc = 0;
         if (n_act) {
             unsigned adj;
             bool any_exc;
@@ -409,7 +411,7 @@ __global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
             W.cur0 = (int)(oinc - oc) - (int)adj;
             const uint32_t up = __shfl_up_sync(FULL, (uint32_t)(W.MK[TILE_ITERS - 1] >> 32), 1);
             W.pm = lane ? up : pm0;
-            lane_count(S, W, lane, cnt, first_closer, end_closer);
+            lane_count(S, W, lane, cnt, end_closer);
             inc = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -418,22 +420,35 @@ __global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
             }
         }
         const uint32_t tile_count = __shfl_sync(FULL, inc, 31);
+        const uint32_t ex = inc - cnt;
         if (lane == 0) s_wcount[wid] = tile_count;
         __syncthreads();
 
-        // ---- D: decoupled look-back over CTA tiles (warp 0)
+        // ---- D (first half): publish the CTA tile's number of events, then list round 0 before anybody waits
+        volatile unsigned long long *st = P.status;
+        unsigned long long agg = 0;
         if (wid == 0) {
-            unsigned long long agg = 0;
 #pragma unroll
             for (int w = 0; w < WARPS; w++) agg += s_wcount[w];
-            volatile unsigned long long *st = P.status;
             if (lane == 0) st[ct] = (ct == 0 ? ST_INCL : ST_AGG) | agg;
+        }
+        const uint32_t term = n_act ? __shfl_sync(FULL, end_closer, (n_act - 1) >> 3) : COORD_OPEN;
+        if (n_act) {
+            __syncwarp();  // every lane holds its masks in registers: the list may overwrite them
+            if (cnt && ex <= (uint32_t)LIST_CAP) lane_scatter(P, S, W, lane, ex, 0u);
+            if (lane == 0 && tile_count <= (uint32_t)LIST_CAP) S.u.list[tile_count] = (term & LE_CLOSE) << LS_CLOSE;
+        }
+        // ---- D (second half): decoupled look-back over CTA tiles (warp 0)
+        if (wid == 0) {
             unsigned long long excl = 0;
             if (ct > 0) {
                 int64_t j = ct - 1 - (int64_t)lane;
                 for (;;) {
                     unsigned long long v = j >= 0 ? st[j] : (2ull << 62);
-                    while (__any_sync(FULL, (v >> 62) == 0)) v = j >= 0 ? st[j] : (2ull << 62);
+                    while (__any_sync(FULL, (v >> 62) == 0)) {
+                        __nanosleep(64);
+                        v = j >= 0 ? st[j] : (2ull << 62);
+                    }
                     const unsigned incl = __ballot_sync(FULL, (v >> 62) == 2);
                     const unsigned upto = incl ? (unsigned)__ffs(incl) - 1u : 31u;  // nearest tile holding an inclusive prefix
                     unsigned long long c = lane <= upto ? (v & ST_VAL) : 0ull;
@@ -452,35 +467,43 @@ __global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
         }
         __syncthreads();
 
-        // ---- E: emit
+        // ---- E2: entries -> CigarRecord words, coalesced stores
         if (n_act) {
             unsigned long long slot0 = s_excl;
 #pragma unroll
             for (int w = 0; w < WARPS; w++) slot0 += (unsigned)w < wid ? s_wcount[w] : 0u;
-            // where a run left open at the end of a lane closes: first closer of the later lanes, else the tile's end
-            const uint32_t term = __shfl_sync(FULL, end_closer, (n_act - 1) >> 3);
-            uint32_t suf = first_closer;  // inclusive suffix-min
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t t = __shfl_down_sync(FULL, suf, o);
-                if (lane + o < 32) suf = min(suf, t);
-            }
-            uint32_t closer = __shfl_down_sync(FULL, suf, 1);
-            if (lane == 31) closer = COORD_OPEN;
-            closer = min(closer, term);
             if (lane == 0) {
-                const uint32_t fc = min(suf, term);
-                P.tile_first_closer[tile] = fc == COORD_OPEN ? INF64 : WIN_BASES * s0 + fc;
+                P.tile_slot0[tile] = slot0;
+                P.tile_first_closer[tile] = tile_count ? WIN_BASES * s0 + ((S.u.list[0] >> LS_CLOSE) & LE_CLOSE)
+                                                       : (term == COORD_OPEN ? INF64 : WIN_BASES * s0 + term);
             }
-            const uint32_t ex = inc - cnt;
             for (uint32_t base = 0; base < tile_count; base += LIST_CAP) {
+                if (base) {  // dense tiles: further rounds
+                    __syncwarp();
+                    if (cnt && ex <= base + LIST_CAP && ex + cnt > base) lane_scatter(P, S, W, lane, ex, base);
+                    if (lane == 0 && tile_count - base <= (uint32_t)LIST_CAP) S.u.list[tile_count - base] = (term & LE_CLOSE) << LS_CLOSE;
+                }
                 __syncwarp();
-                if (cnt && ex < base + LIST_CAP && ex + cnt > base) lane_emit(P, S, W, lane, ex, base, closer, s0, slot0, tile);
-                __syncwarp();
-                const uint32_t n_emit = min((uint32_t)LIST_CAP, tile_count - base);
-                for (uint32_t i = lane; i < n_emit; i += 32) {
+                const uint32_t n_round = min((uint32_t)LIST_CAP, tile_count - base);
+                for (uint32_t i = lane; i < n_round; i += 32) {
+                    const uint32_t e = S.u.list[i], nx = S.u.list[i + 1];
+                    uint32_t lo, hi;
+                    if (e & LE_PASS) {
+                        const OpEntry en = S.tab[e & 0x1ffu];
+                        lo = (uint32_t)en.tw; hi = (uint32_t)en.qw;
+                    } else {
+                        const uint32_t start = e & LE_START;
+                        hi = (uint32_t)((e & LE_X) ? OP_X : OP_EQ) << 24;
+                        lo = ((nx >> LS_CLOSE) & LE_CLOSE) - start;
+                        if (base + i == tile_count - 1 && term == COORD_OPEN) {
+                            // run still open at the tile's end: provisional absolute start, turned into a length by stitch_kernel
+                            const uint64_t abs_start = WIN_BASES * s0 + start;
+                            lo = (uint32_t)abs_start; hi |= (uint32_t)(abs_start >> 32);
+                            P.tile_open_rank[tile] = (int32_t)(base + i);
+                        }
+                    }
                     const unsigned long long slot = slot0 + base + i;
-                    if (slot < (unsigned long long)P.out_cap) P.out[slot] = S.u.list[i];
+                    if (slot < (unsigned long long)P.out_cap) P.out[slot] = ((uint64_t)hi << 32) | lo;
                 }
             }
         }
@@ -488,17 +511,28 @@ __global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
 }
 
 // A run left open at the end of warp tile t closes at the first run start / op end of a later tile.
-__global__ void stitch_kernel(int64_t n_tiles, const int64_t *tile_open_slot, const uint64_t *tile_first_closer,
+__global__ void stitch_kernel(int64_t n_tiles, const int32_t *tile_open_rank, const uint64_t *tile_slot0, const uint64_t *tile_first_closer,
                               uint64_t *out, int64_t out_cap) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_tiles) return;
-    const int64_t slot = tile_open_slot[t];
-    if (slot < 0 || slot >= out_cap) return;
+    const int32_t rank = tile_open_rank[t];
+    if (rank < 0) return;
+    const int64_t slot = (int64_t)tile_slot0[t] + rank;
+    if (slot >= out_cap) return;
     int64_t u = t + 1;
     while (u < n_tiles && tile_first_closer[u] == INF64) u++;
     if (u >= n_tiles) return;  // cannot happen: the op's end is always a closer
     const uint64_t rec = out[slot];
     out[slot] = (tile_first_closer[u] - (rec & LEN_MASK)) | (rec & ~LEN_MASK);
+}
+
+// rec_out_begin[r] holds the rank of the record's first output op inside its warp tile: add the tile's first slot.
+__global__ void rec_begin_kernel(int64_t n_records, const int64_t *op_begin, const uint64_t *woff, const uint64_t *tile_slot0,
+                                 int64_t *rec_out_begin) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_records) return;
+    const uint64_t tile = woff[op_begin[r]] / TILE_WIN;
+    rec_out_begin[r] += (int64_t)tile_slot0[tile];
 }
 
 }  // namespace pafgpu

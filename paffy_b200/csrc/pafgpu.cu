@@ -88,7 +88,7 @@ struct pafgpu_ctx {
     // staging for host batches
     DevBuf in_op_begin, in_ops, in_qc, in_tc, in_qs, in_qe, in_ts, in_strand, in_seq;
     // per-batch work buffers
-    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, status, tile_first_closer, tile_open_slot;
+    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, status, tile_first_closer, tile_open_rank, tile_slot0;
     DevBuf out, rec_out_begin, rec_mism, scalars;
     // serialiser
     DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
@@ -99,6 +99,7 @@ struct pafgpu_ctx {
     int64_t n_records = 0, n_ops = 0, n_out = 0, n_tiles = 0, aligned = 0, retried = 0;
     uint64_t n_win = 0;
     EncodeParams last{};
+    const int64_t *last_op_begin = nullptr;
 };
 
 namespace {
@@ -228,7 +229,7 @@ int launch_encode_once(pafgpu_ctx *c) {
     EncodeParams &P = c->last;
     uint64_t *sc = c->scalars.as<uint64_t>();
     const int64_t T = c->n_tiles, CT = P.n_cta_tiles;
-    CU(cudaMemsetAsync(c->tile_open_slot.p, 0xff, (size_t)std::max<int64_t>(T, 1) * 8, c->stream));
+    CU(cudaMemsetAsync(c->tile_open_rank.p, 0xff, (size_t)std::max<int64_t>(T, 1) * 4, c->stream));
     CU(cudaMemsetAsync(c->rec_mism.p, 0, (size_t)std::max<int64_t>(c->n_records, 1) * 8, c->stream));
     CU(cudaMemsetAsync(c->status.p, 0, (size_t)std::max<int64_t>(CT, 1) * 8, c->stream));
     CU(cudaMemsetAsync(sc + SC_TOTAL, 0, 16, c->stream));  // SC_TOTAL and SC_TICKET
@@ -240,7 +241,11 @@ int launch_encode_once(pafgpu_ctx *c) {
         encode_kernel<ENC_WARPS, CMP_BATCH><<<grid, 32 * ENC_WARPS, 0, c->stream>>>(P);
     }
     CU(cudaEventRecord(c->ev[5], c->stream));
-    if (T > 0) stitch_kernel<<<blocks_for(T, 256), 256, 0, c->stream>>>(T, P.tile_open_slot, P.tile_first_closer, P.out, P.out_cap);
+    if (T > 0) {
+        stitch_kernel<<<blocks_for(T, 256), 256, 0, c->stream>>>(T, P.tile_open_rank, P.tile_slot0, P.tile_first_closer, P.out, P.out_cap);
+        rec_begin_kernel<<<blocks_for(c->n_records, 256), 256, 0, c->stream>>>(c->n_records, c->last_op_begin, P.woff, P.tile_slot0,
+                                                                              P.rec_out_begin);
+    }
     CU(cudaMemcpyAsync(P.rec_out_begin + c->n_records, sc + SC_TOTAL, 8, cudaMemcpyDeviceToDevice, c->stream));
     CU(cudaMemcpyAsync(&c->host_total, sc + SC_TOTAL, 8, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaEventRecord(c->ev[7], c->stream));
@@ -314,7 +319,8 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     const int64_t n_cta_tiles = (n_tiles + ENC_WARPS - 1) / ENC_WARPS;
     CU(c->status.ensure((size_t)std::max<int64_t>(n_cta_tiles, 1) * 8));
     CU(c->tile_first_closer.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
-    CU(c->tile_open_slot.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
+    CU(c->tile_open_rank.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 4));
+    CU(c->tile_slot0.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
     if (N > 0)
         tile_first_op_kernel<<<blocks_for(N, 256), 256, 0, c->stream>>>(c->woff.as<uint64_t>(), N, TILE_WINDOWS,
                                                                         c->tile_first_op.as<uint32_t>());
@@ -331,7 +337,9 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     P.ticket = (unsigned int *)(sc + SC_TICKET);
     P.total_out = (unsigned long long *)(sc + SC_TOTAL);
     P.tile_first_closer = c->tile_first_closer.as<uint64_t>();
-    P.tile_open_slot = c->tile_open_slot.as<int64_t>();
+    P.tile_open_rank = c->tile_open_rank.as<int32_t>();
+    P.tile_slot0 = c->tile_slot0.as<uint64_t>();
+    c->last_op_begin = b->op_begin;
     P.rec_out_begin = c->rec_out_begin.as<int64_t>();
     P.rec_mism = c->rec_mism.as<unsigned long long>();
     c->n_records = R; c->n_ops = N; c->n_tiles = n_tiles; c->n_win = n_win;
@@ -446,7 +454,7 @@ void pafgpu_destroy(pafgpu_ctx *c) {
     c->scratch.release();
     DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
                       &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
-                      &c->status, &c->tile_first_closer, &c->tile_open_slot, &c->out, &c->rec_out_begin, &c->rec_mism,
+                      &c->status, &c->tile_first_closer, &c->tile_open_rank, &c->tile_slot0, &c->out, &c->rec_out_begin, &c->rec_mism,
                       &c->scalars, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
                       &c->ser_text};
     for (DevBuf *b : bufs) b->release();
