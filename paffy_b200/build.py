@@ -33,6 +33,7 @@ def build(force=False, verbose=False):
         return LIB
     srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
     flags = [f for f in NVCC_FLAGS if f != "--use_fast_math=false"]
+    flags = flags + os.environ.get("PAFGPU_NVCC_DEFS", "").split()  # experiments only (e.g. -DENC_MINB=5)
     cmd = [nvcc()] + flags + ["-I", os.path.join(HERE, "..", "include"), "-x", "cu"] + srcs + ["-o", LIB]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or r.returncode:

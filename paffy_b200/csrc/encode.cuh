@@ -40,8 +40,7 @@ struct EncodeParams {
     unsigned int *ticket;           // pre-set to 0
     unsigned long long *total_out;  // number of output ops of the whole batch
     uint64_t *tile_first_closer;    // absolute window-axis coordinate (64 * window + base) of the warp tile's first run start / op end
-    int32_t *tile_open_rank;        // rank inside the warp tile of a run left open, -1 if none (pre-set)
-    uint64_t *tile_slot0;           // output slot of the warp tile's first event
+    int64_t *tile_open_slot;        // output slot of a run left open, -1 if none (pre-set)
     int64_t *rec_out_begin;
     unsigned long long *rec_mism;
 };
@@ -51,7 +50,7 @@ constexpr int TILE_ITERS = 8;                 // windows per lane per warp tile
 constexpr int TILE_WIN = 32 * TILE_ITERS;     // windows per warp tile
 constexpr int TILE_TAB = TILE_WIN + 2;        // a tile overlaps at most TILE_WIN + 1 ops
 constexpr int MASK_PAD = TILE_WIN + TILE_WIN / 8;  // mask of window p sits at p + (p >> 3): conflict-free blocked reads
-constexpr int LIST_CAP = 1024;                // events converted per round
+constexpr int LIST_CAP = 512;                 // events converted per round
 constexpr uint32_t COORD_OPEN = 0xffffffffu;
 constexpr unsigned long long ST_AGG = 1ull << 62, ST_INCL = 2ull << 62, ST_VAL = (1ull << 62) - 1;
 
@@ -76,12 +75,11 @@ constexpr int32_t REM_CLAMP = 1 << 30;
 
 struct WarpSmem {
     OpEntry tab[TILE_TAB];
-    uint32_t rec[TILE_TAB];   // owning record, top bit: first op of the record
-    union {
-        uint64_t mask[MASK_PAD];
-        uint32_t list[LIST_CAP + 2];   // 32-bit event entries of one round (+ successor of the last)
-    } u;
-    uint32_t bm[TILE_ITERS];  // bit p: an op starts at tile window p
+    uint32_t rec[TILE_TAB];           // owning record, top bit: first op of the record
+    uint64_t mask[MASK_PAD];          // mismatch bits of window p at p + (p >> 3)
+    uint16_t list[LIST_CAP + 2];      // event coordinates of one round (+ successor of the last), bit 15: X run
+    uint32_t bm[TILE_ITERS];          // bit p: an op starts at tile window p
+    uint32_t bmpre[TILE_ITERS];       // op starts before word k of bm
 };
 
 // ---- A: op table of one warp tile. Returns adj (1 when table entry 0 starts exactly at tile window 0) and
@@ -131,6 +129,12 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
         more = __all_sync(FULL, in);
     }
     any_exc = __any_sync(FULL, exc);
+    __syncwarp();
+    if (lane < TILE_ITERS) {
+        uint32_t pre = 0;
+        for (unsigned q = 0; q < lane; q++) pre += __popc(S.bm[q]);
+        S.bmpre[lane] = pre;
+    }
     __syncwarp();
 }
 
@@ -226,11 +230,16 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
                     }
                 }
             }
-            // bases beyond the op's end do not exist
-            const uint64_t valid = n ? ~0ull >> (WIN_BASES - n) : 0ull;
-            m0 &= (uint32_t)valid;
-            m1 &= (uint32_t)(valid >> 32);
-            S.u.mask[srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
+            // bases beyond the op's end do not exist: they are tallied as matches and then take the value of the
+            // op's last base, so that no run appears to start behind the end (the next window starts another op)
+            const uint32_t v0 = n >= 32 ? 0xffffffffu : (1u << n) - 1u;
+            const uint32_t v1 = n > 32 ? 0xffffffffu >> (64 - n) : 0u;
+            m0 &= v0;
+            m1 &= v1;
+            const uint32_t mm_count = __popc(m0) + __popc(m1);
+            const bool last_set = n > 32 ? (m1 >> (n - 33)) & 1u : n ? (m0 >> (n - 1)) & 1u : false;
+            if (last_set) { m0 |= ~v0; m1 |= ~v1; }
+            S.mask[srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
             // per-record mismatch tally, flushed when the lane moves to another record
             if (isM) {
                 const uint32_t rec = S.rec[idx] & 0x7fffffffu;
@@ -239,7 +248,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
                     acc_rec = rec;
                     acc_mm = 0;
                 }
-                acc_mm += __popc(m0) + __popc(m1);
+                acc_mm += mm_count;
             }
         }
     }
@@ -254,124 +263,68 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
     return pm0;
 }
 
-// ---- C / E: blocked walk. Lane owns tile windows 8 * lane .. 8 * lane + 7. An "event" is an output op: the
-// start of an =/X run or a pass-through op. Coordinates are tile-relative (64 * window + base).
-// Events are first listed as 32-bit entries in tile order:
-//   bits 0-13  run start coordinate (pass-through op: its table index)
-//   bits 14-28 coordinate at which the run before this event closes: the event's own coordinate inside an op,
-//              the previous op's end at an op start
-//   bit 29 X run, bit 30 pass-through op
-// so that entry i's length is close(entry i + 1) - start(entry i), computed by any lane.
-constexpr uint32_t LE_START = 0x3fffu, LE_CLOSE = 0x7fffu, LE_X = 1u << 29, LE_PASS = 1u << 30;
-constexpr int LS_CLOSE = 14;
+// ---- C / E: blocked view. Lane owns tile windows 8 * lane .. 8 * lane + 7 = 16 half-window words of 32 bases.
+// An "event" is an output op: the start of an =/X run, or a pass-through op (its window holds no mismatch bits and
+// starts an op, so it shows up as one forced start bit). Coordinates are tile-relative (64 * window + base).
 
-struct LaneWalk {
-    uint64_t MK[TILE_ITERS];  // masks of the lane's windows
-    uint32_t byte;            // op-start bits of the lane's windows
-    int cur0;                 // table index of the op owning the window before the lane's first
-    uint32_t pm;              // top bit: mismatch state of the base before the lane's first window
-    uint32_t n_win;           // active windows of the lane
-};
-
-// run-start bits of one M window (n >= 1 bases); the op-start bit is handled by the caller
-__device__ __forceinline__ void run_starts(uint32_t m0, uint32_t m1, uint32_t pm, uint32_t n, uint32_t &d0, uint32_t &d1) {
-    d0 = m0 ^ ((m0 << 1) | (pm >> 31));
-    d1 = m1 ^ __funnelshift_l(m0, m1, 1);
-    const uint32_t v0 = n >= 32 ? 0xffffffffu : (1u << n) - 1u;
-    const uint32_t v1 = n > 32 ? 0xffffffffu >> (64 - n) : 0u;
-    d0 &= v0;
-    d1 &= v1;
+// run-start bits of one 32-base word: m = its mismatch bits, prev = the word before it (top bit used), forced = an op
+// starts at bit 0
+__device__ __forceinline__ uint32_t start_bits(uint32_t m, uint32_t prev, bool forced) {
+    return (m ^ ((m << 1) | (prev >> 31))) | (forced ? 1u : 0u);
 }
 
-// C: number of events of the lane; end_closer (meaningful on the lane owning the tile's last active window): end
-// of that window's M op when it ends inside the tile, else COORD_OPEN
-__device__ __forceinline__ void lane_count(const WarpSmem &S, const LaneWalk &W, unsigned lane, uint32_t &cnt, uint32_t &end_closer) {
+// table index of the op owning tile window w
+__device__ __forceinline__ uint32_t window_op(const WarpSmem &S, uint32_t w, unsigned adj) {
+    return S.bmpre[w >> 5] + __popc(S.bm[w >> 5] & (0xffffffffu >> (31 - (w & 31)))) - adj;
+}
+
+// C: events of the lane and the bitmap of its words that hold any
+__device__ __forceinline__ void lane_count(const WarpSmem &S, unsigned lane, uint32_t n_win, uint32_t byte, uint32_t pm, uint32_t &cnt,
+                                           uint32_t &nz) {
+    const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 18 * lane;
     cnt = 0;
-    int cur = W.cur0;
-    OpEntry en = S.tab[cur < 0 ? 0 : cur];
-    uint32_t pm = W.pm;
+    nz = 0;
+    uint32_t prev = pm;
 #pragma unroll
     for (int j = 0; j < TILE_ITERS; j++) {
-        if ((uint32_t)j < W.n_win) {
-            const uint32_t p = 8u * lane + j;
-            const bool start = (W.byte >> j) & 1u;
-            if (start) en = S.tab[++cur];
-            if (en.misc & EF_PASS) {
-                cnt++;
-                pm = 0;
-            } else {
-                const int32_t rem = en.rem - WIN_BASES * (int32_t)p;
-                const uint32_t n = rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
-                const uint32_t m0 = (uint32_t)W.MK[j], m1 = (uint32_t)(W.MK[j] >> 32);
-                uint32_t d0, d1;
-                run_starts(m0, m1, pm, n, d0, d1);
-                if (start) d0 |= 1u;
-                cnt += __popc(d0) + __popc(d1);
-                pm = m1;
-            }
+        const uint2 m = *reinterpret_cast<const uint2 *>(M + 2 * j);
+        if ((uint32_t)j < n_win) {
+            const uint32_t d0 = start_bits(m.x, prev, (byte >> j) & 1u), d1 = start_bits(m.y, m.x, false);
+            cnt += __popc(d0) + __popc(d1);
+            nz |= (d0 ? 1u : 0u) << (2 * j) | (d1 ? 2u : 0u) << (2 * j);
         }
+        prev = m.y;
     }
-    end_closer = (!(en.misc & EF_PASS) && en.rem <= (int32_t)(WIN_BASES * (8u * lane + W.n_win))) ? (uint32_t)en.rem : COORD_OPEN;
 }
 
-// E1: list the lane's events, entries base .. base + LIST_CAP of the tile (one more than a round converts, so the
-// last converted entry sees its successor). ex = rank of the lane's first event inside the tile. Also leaves the
-// tile-relative output rank of every record's first op in rec_out_begin (rec_begin_kernel adds the tile's slot).
-__device__ __forceinline__ void lane_scatter(const EncodeParams &P, WarpSmem &S, const LaneWalk &W, unsigned lane, uint32_t ex, uint32_t base) {
-    uint32_t *L = S.u.list;
+// E1: coordinates of the lane's events, ranks base .. base + LIST_CAP of the tile, into the list (bit 15: X run).
+// One event per trip whatever word it comes from, so lanes stay busy as long as they have events left.
+__device__ __forceinline__ void lane_list(WarpSmem &S, unsigned lane, uint32_t byte, uint32_t pm, uint32_t nz, uint32_t ex, uint32_t base) {
+    const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 18 * lane;
     uint32_t r = ex - base;  // wraps for events before the round; comes back to 0 exactly at entry `base`
-    int cur = W.cur0;
-    OpEntry en = S.tab[cur < 0 ? 0 : cur];
-    uint32_t pm = W.pm;
-#pragma unroll
-    for (int j = 0; j < TILE_ITERS; j++) {
-        if ((uint32_t)j < W.n_win) {
-            const uint32_t p = 8u * lane + j;
-            const uint32_t x0 = WIN_BASES * p;
-            const bool start = (W.byte >> j) & 1u;
-            uint32_t close0 = x0;
-            if (start) {
-                // the previous op ends here: an M op at its end coordinate, a pass-through op at the window boundary
-                if (cur >= 0 && !(en.misc & EF_PASS)) close0 = (uint32_t)en.rem;
-                en = S.tab[++cur];
-                const uint32_t recw = S.rec[cur];
-                if ((recw >> 31) && r <= (uint32_t)LIST_CAP) P.rec_out_begin[recw & 0x7fffffffu] = (int64_t)(r + base);
-            }
-            if (en.misc & EF_PASS) {
-                if (r <= (uint32_t)LIST_CAP) L[r] = (uint32_t)cur | (close0 << LS_CLOSE) | LE_PASS;
-                r++;
-                pm = 0;
-            } else {
-                const int32_t rem = en.rem - WIN_BASES * (int32_t)p;
-                const uint32_t n = rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
-                const uint32_t m0 = (uint32_t)W.MK[j], m1 = (uint32_t)(W.MK[j] >> 32);
-                uint32_t d0, d1;
-                run_starts(m0, m1, pm, n, d0, d1);
-                if (start) {
-                    if (r <= (uint32_t)LIST_CAP) L[r] = x0 | (close0 << LS_CLOSE) | ((m0 & 1u) ? LE_X : 0u);
-                    r++;
-                    d0 &= ~1u;
-                }
-                while (d0) {
-                    const uint32_t b = (uint32_t)__ffs((int)d0) - 1u;
-                    d0 &= d0 - 1u;
-                    if (r <= (uint32_t)LIST_CAP) L[r] = (x0 + b) * ((1u << LS_CLOSE) + 1u) | (((m0 >> b) & 1u) ? LE_X : 0u);
-                    r++;
-                }
-                while (d1) {
-                    const uint32_t b = (uint32_t)__ffs((int)d1) - 1u;
-                    d1 &= d1 - 1u;
-                    if (r <= (uint32_t)LIST_CAP) L[r] = (x0 + 32u + b) * ((1u << LS_CLOSE) + 1u) | (((m1 >> b) & 1u) ? LE_X : 0u);
-                    r++;
-                }
-                pm = m1;
-            }
+    uint32_t d = 0, m = 0, c0 = 0;
+    for (;;) {
+        if (d == 0) {
+            if (nz == 0) break;
+            const uint32_t w = (uint32_t)__ffs((int)nz) - 1u;
+            nz &= nz - 1u;
+            m = M[w];
+            const uint32_t prev = w ? M[w - 1] : pm;
+            d = start_bits(m, prev, !(w & 1u) && ((byte >> (w >> 1)) & 1u));
+            c0 = 512u * lane + 32u * w;
         }
+        const uint32_t b = (uint32_t)__ffs((int)d) - 1u;
+        d &= d - 1u;
+        if (r <= (uint32_t)LIST_CAP) S.list[r] = (uint16_t)((c0 + b) | (((m >> b) & 1u) << 15));
+        r++;
     }
 }
 
+#ifndef ENC_MINB
+#define ENC_MINB 6
+#endif
 template <int WARPS, int BATCH>
-__global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
+__global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kernel(EncodeParams P) {
     __shared__ WarpSmem SM[WARPS];
     __shared__ uint32_t s_wcount[WARPS];
     __shared__ unsigned long long s_excl;
@@ -388,36 +341,27 @@ __global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
         const uint64_t s0 = (uint64_t)tile * TILE_WIN;
         const uint32_t n_act = s0 < P.n_win ? (uint32_t)min((uint64_t)TILE_WIN, P.n_win - s0) : 0u;
 
-        LaneWalk W;
-        uint32_t cnt = 0, end_closer = COORD_OPEN, inc = 0;
+        unsigned adj = 0;
+        uint32_t cnt = 0, nz = 0, inc = 0, byte = 0, pm = 0, term = COORD_OPEN;
         if (n_act) {
-            unsigned adj;
             bool any_exc;
             build_table(P, S, tile, s0, s0 + n_act, lane, adj, any_exc);
-            uint32_t pm0 = any_exc ? compare_tile<BATCH, true>(P, S, n_act, lane, adj) : compare_tile<BATCH, false>(P, S, n_act, lane, adj);
+            const uint32_t pm0 = any_exc ? compare_tile<BATCH, true>(P, S, n_act, lane, adj) : compare_tile<BATCH, false>(P, S, n_act, lane, adj);
             __syncwarp();
             // blocked view of the tile
-            W.byte = (S.bm[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
-            W.n_win = 8u * lane >= n_act ? 0u : min(8u, n_act - 8u * lane);
-#pragma unroll
-            for (int j = 0; j < TILE_ITERS; j++) W.MK[j] = S.u.mask[9 * lane + j];
-            uint32_t oinc = __popc(W.byte);
-            const uint32_t oc = oinc;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t t = __shfl_up_sync(FULL, oinc, o);
-                if (lane >= (unsigned)o) oinc += t;
-            }
-            W.cur0 = (int)(oinc - oc) - (int)adj;
-            const uint32_t up = __shfl_up_sync(FULL, (uint32_t)(W.MK[TILE_ITERS - 1] >> 32), 1);
-            W.pm = lane ? up : pm0;
-            lane_count(S, W, lane, cnt, end_closer);
+            byte = (S.bm[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
+            const uint32_t n_win = 8u * lane >= n_act ? 0u : min(8u, n_act - 8u * lane);
+            pm = lane ? reinterpret_cast<const uint32_t *>(S.mask)[18 * lane - 3] : pm0;
+            lane_count(S, lane, n_win, byte, pm, cnt, nz);
             inc = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const uint32_t t = __shfl_up_sync(FULL, inc, o);
                 if (lane >= (unsigned)o) inc += t;
             }
+            // where a run still open at the tile's last window closes: the end of that window's op if it lies inside the tile
+            const OpEntry en = S.tab[window_op(S, n_act - 1, adj)];
+            term = (en.misc & EF_PASS) ? WIN_BASES * n_act : en.rem <= (int32_t)(WIN_BASES * n_act) ? (uint32_t)en.rem : COORD_OPEN;
         }
         const uint32_t tile_count = __shfl_sync(FULL, inc, 31);
         const uint32_t ex = inc - cnt;
@@ -432,12 +376,7 @@ __global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
             for (int w = 0; w < WARPS; w++) agg += s_wcount[w];
             if (lane == 0) st[ct] = (ct == 0 ? ST_INCL : ST_AGG) | agg;
         }
-        const uint32_t term = n_act ? __shfl_sync(FULL, end_closer, (n_act - 1) >> 3) : COORD_OPEN;
-        if (n_act) {
-            __syncwarp();  // every lane holds its masks in registers: the list may overwrite them
-            if (cnt && ex <= (uint32_t)LIST_CAP) lane_scatter(P, S, W, lane, ex, 0u);
-            if (lane == 0 && tile_count <= (uint32_t)LIST_CAP) S.u.list[tile_count] = (term & LE_CLOSE) << LS_CLOSE;
-        }
+        if (cnt && ex <= (uint32_t)LIST_CAP) lane_list(S, lane, byte, pm, nz, ex, 0u);
         // ---- D (second half): decoupled look-back over CTA tiles (warp 0)
         if (wid == 0) {
             unsigned long long excl = 0;
@@ -467,43 +406,54 @@ __global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
         }
         __syncthreads();
 
-        // ---- E2: entries -> CigarRecord words, coalesced stores
+        // ---- E2: events -> CigarRecord words, coalesced stores; 31 events per step, lane 31 looks one ahead
         if (n_act) {
             unsigned long long slot0 = s_excl;
 #pragma unroll
             for (int w = 0; w < WARPS; w++) slot0 += (unsigned)w < wid ? s_wcount[w] : 0u;
-            if (lane == 0) {
-                P.tile_slot0[tile] = slot0;
-                P.tile_first_closer[tile] = tile_count ? WIN_BASES * s0 + ((S.u.list[0] >> LS_CLOSE) & LE_CLOSE)
-                                                       : (term == COORD_OPEN ? INF64 : WIN_BASES * s0 + term);
-            }
+            if (lane == 0 && tile_count == 0) P.tile_first_closer[tile] = term == COORD_OPEN ? INF64 : WIN_BASES * s0 + term;
             for (uint32_t base = 0; base < tile_count; base += LIST_CAP) {
                 if (base) {  // dense tiles: further rounds
                     __syncwarp();
-                    if (cnt && ex <= base + LIST_CAP && ex + cnt > base) lane_scatter(P, S, W, lane, ex, base);
-                    if (lane == 0 && tile_count - base <= (uint32_t)LIST_CAP) S.u.list[tile_count - base] = (term & LE_CLOSE) << LS_CLOSE;
+                    if (cnt && ex <= base + LIST_CAP && ex + cnt > base) lane_list(S, lane, byte, pm, nz, ex, base);
                 }
                 __syncwarp();
-                const uint32_t n_round = min((uint32_t)LIST_CAP, tile_count - base);
-                for (uint32_t i = lane; i < n_round; i += 32) {
-                    const uint32_t e = S.u.list[i], nx = S.u.list[i + 1];
-                    uint32_t lo, hi;
-                    if (e & LE_PASS) {
-                        const OpEntry en = S.tab[e & 0x1ffu];
-                        lo = (uint32_t)en.tw; hi = (uint32_t)en.qw;
-                    } else {
-                        const uint32_t start = e & LE_START;
-                        hi = (uint32_t)((e & LE_X) ? OP_X : OP_EQ) << 24;
-                        lo = ((nx >> LS_CLOSE) & LE_CLOSE) - start;
-                        if (base + i == tile_count - 1 && term == COORD_OPEN) {
-                            // run still open at the tile's end: provisional absolute start, turned into a length by stitch_kernel
-                            const uint64_t abs_start = WIN_BASES * s0 + start;
-                            lo = (uint32_t)abs_start; hi |= (uint32_t)(abs_start >> 32);
-                            P.tile_open_rank[tile] = (int32_t)(base + i);
+                const uint32_t round_end = min(base + (uint32_t)LIST_CAP, tile_count);
+                for (uint32_t i0 = base; i0 < round_end; i0 += 31) {
+                    const uint32_t i = i0 + lane;
+                    const bool have = i < tile_count && i <= round_end;
+                    const uint32_t e = have ? S.list[i - base] : 0u;
+                    const uint32_t c = e & 0x3fffu, w = c >> 6;
+                    uint32_t close = c, lo = 0, hi = (uint32_t)((e >> 15) ? OP_X : OP_EQ) << 24;
+                    bool pass = false;
+                    if (have && (c & 63u) == 0 && ((S.bm[w >> 5] >> (w & 31)) & 1u)) {
+                        // an op starts here: the run before it ends with the previous op
+                        const uint32_t idx = window_op(S, w, adj);
+                        const OpEntry en = S.tab[idx];
+                        if (idx >= 1) {
+                            const OpEntry pe = S.tab[idx - 1];
+                            if (!(pe.misc & EF_PASS)) close = (uint32_t)pe.rem;
                         }
+                        if (en.misc & EF_PASS) { pass = true; lo = (uint32_t)en.tw; hi = (uint32_t)en.qw; }
+                        const uint32_t recw = S.rec[idx];
+                        if ((recw >> 31) && lane < 31) P.rec_out_begin[recw & 0x7fffffffu] = (int64_t)(slot0 + i);
                     }
-                    const unsigned long long slot = slot0 + base + i;
-                    if (slot < (unsigned long long)P.out_cap) P.out[slot] = ((uint64_t)hi << 32) | lo;
+                    if (i == tile_count) close = term;
+                    if (i == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + close;
+                    const uint32_t nclose = __shfl_down_sync(FULL, close, 1);
+                    if (lane < 31 && i < round_end) {
+                        if (!pass) {
+                            lo = nclose - c;
+                            if (i == tile_count - 1 && term == COORD_OPEN) {
+                                // run still open at the tile's end: provisional absolute start, turned into a length by stitch_kernel
+                                const uint64_t abs_start = WIN_BASES * s0 + c;
+                                lo = (uint32_t)abs_start; hi |= (uint32_t)(abs_start >> 32);
+                                P.tile_open_slot[tile] = (int64_t)(slot0 + i);
+                            }
+                        }
+                        const unsigned long long slot = slot0 + i;
+                        if (slot < (unsigned long long)P.out_cap) P.out[slot] = ((uint64_t)hi << 32) | lo;
+                    }
                 }
             }
         }
@@ -511,28 +461,17 @@ __global__ void __launch_bounds__(32 * WARPS) encode_kernel(EncodeParams P) {
 }
 
 // A run left open at the end of warp tile t closes at the first run start / op end of a later tile.
-__global__ void stitch_kernel(int64_t n_tiles, const int32_t *tile_open_rank, const uint64_t *tile_slot0, const uint64_t *tile_first_closer,
-                              uint64_t *out, int64_t out_cap) {
+__global__ void stitch_kernel(int64_t n_tiles, const int64_t *tile_open_slot, const uint64_t *tile_first_closer, uint64_t *out,
+                              int64_t out_cap) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_tiles) return;
-    const int32_t rank = tile_open_rank[t];
-    if (rank < 0) return;
-    const int64_t slot = (int64_t)tile_slot0[t] + rank;
-    if (slot >= out_cap) return;
+    const int64_t slot = tile_open_slot[t];
+    if (slot < 0 || slot >= out_cap) return;
     int64_t u = t + 1;
     while (u < n_tiles && tile_first_closer[u] == INF64) u++;
     if (u >= n_tiles) return;  // cannot happen: the op's end is always a closer
     const uint64_t rec = out[slot];
     out[slot] = (tile_first_closer[u] - (rec & LEN_MASK)) | (rec & ~LEN_MASK);
-}
-
-// rec_out_begin[r] holds the rank of the record's first output op inside its warp tile: add the tile's first slot.
-__global__ void rec_begin_kernel(int64_t n_records, const int64_t *op_begin, const uint64_t *woff, const uint64_t *tile_slot0,
-                                 int64_t *rec_out_begin) {
-    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n_records) return;
-    const uint64_t tile = woff[op_begin[r]] / TILE_WIN;
-    rec_out_begin[r] += (int64_t)tile_slot0[tile];
 }
 
 }  // namespace pafgpu

@@ -76,7 +76,7 @@ struct GenomeStore {
 struct pafgpu_ctx {
     int device = 0;
     int sm_count = 148;
-    int enc_ctas_per_sm = 4;
+    int enc_ctas_per_sm = 4, enc_warps = 4;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[8] = {};
     std::string err;
@@ -88,7 +88,7 @@ struct pafgpu_ctx {
     // staging for host batches
     DevBuf in_op_begin, in_ops, in_qc, in_tc, in_qs, in_qe, in_ts, in_strand, in_seq;
     // per-batch work buffers
-    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, status, tile_first_closer, tile_open_rank, tile_slot0;
+    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, status, tile_first_closer, tile_open_slot;
     DevBuf out, rec_out_begin, rec_mism, scalars;
     // serialiser
     DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
@@ -99,7 +99,6 @@ struct pafgpu_ctx {
     int64_t n_records = 0, n_ops = 0, n_out = 0, n_tiles = 0, aligned = 0, retried = 0;
     uint64_t n_win = 0;
     EncodeParams last{};
-    const int64_t *last_op_begin = nullptr;
 };
 
 namespace {
@@ -222,14 +221,20 @@ int genome_sync_table(pafgpu_ctx *c, GenomeStore &g) {
     return 0;
 }
 
-constexpr int ENC_WARPS = 4, CMP_BATCH = 4;
+#ifndef ENC_BATCH
+#define ENC_BATCH 4
+#endif
+constexpr int ENC_WARPS = 4, CMP_BATCH = ENC_BATCH;
 
 // one pass of encode_kernel + stitch_kernel for c->last; leaves the output op count in c->n_out
 int launch_encode_once(pafgpu_ctx *c) {
     EncodeParams &P = c->last;
     uint64_t *sc = c->scalars.as<uint64_t>();
-    const int64_t T = c->n_tiles, CT = P.n_cta_tiles;
-    CU(cudaMemsetAsync(c->tile_open_rank.p, 0xff, (size_t)std::max<int64_t>(T, 1) * 4, c->stream));
+    const int64_t T = c->n_tiles;
+    const int W = c->enc_warps;
+    P.n_cta_tiles = (T + W - 1) / W;
+    const int64_t CT = P.n_cta_tiles;
+    CU(cudaMemsetAsync(c->tile_open_slot.p, 0xff, (size_t)std::max<int64_t>(T, 1) * 8, c->stream));
     CU(cudaMemsetAsync(c->rec_mism.p, 0, (size_t)std::max<int64_t>(c->n_records, 1) * 8, c->stream));
     CU(cudaMemsetAsync(c->status.p, 0, (size_t)std::max<int64_t>(CT, 1) * 8, c->stream));
     CU(cudaMemsetAsync(sc + SC_TOTAL, 0, 16, c->stream));  // SC_TOTAL and SC_TICKET
@@ -238,14 +243,12 @@ int launch_encode_once(pafgpu_ctx *c) {
     CU(cudaEventRecord(c->ev[4], c->stream));
     if (CT > 0) {
         const unsigned grid = (unsigned)std::min<int64_t>(CT, (int64_t)c->sm_count * c->enc_ctas_per_sm);
-        encode_kernel<ENC_WARPS, CMP_BATCH><<<grid, 32 * ENC_WARPS, 0, c->stream>>>(P);
+        if (W == 1) encode_kernel<1, CMP_BATCH><<<grid, 32, 0, c->stream>>>(P);
+        else if (W == 2) encode_kernel<2, CMP_BATCH><<<grid, 64, 0, c->stream>>>(P);
+        else encode_kernel<4, CMP_BATCH><<<grid, 128, 0, c->stream>>>(P);
     }
     CU(cudaEventRecord(c->ev[5], c->stream));
-    if (T > 0) {
-        stitch_kernel<<<blocks_for(T, 256), 256, 0, c->stream>>>(T, P.tile_open_rank, P.tile_slot0, P.tile_first_closer, P.out, P.out_cap);
-        rec_begin_kernel<<<blocks_for(c->n_records, 256), 256, 0, c->stream>>>(c->n_records, c->last_op_begin, P.woff, P.tile_slot0,
-                                                                              P.rec_out_begin);
-    }
+    if (T > 0) stitch_kernel<<<blocks_for(T, 256), 256, 0, c->stream>>>(T, P.tile_open_slot, P.tile_first_closer, P.out, P.out_cap);
     CU(cudaMemcpyAsync(P.rec_out_begin + c->n_records, sc + SC_TOTAL, 8, cudaMemcpyDeviceToDevice, c->stream));
     CU(cudaMemcpyAsync(&c->host_total, sc + SC_TOTAL, 8, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaEventRecord(c->ev[7], c->stream));
@@ -316,11 +319,9 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     const int64_t aligned = (int64_t)host_sc[SC_ALIGNED];
     const int64_t n_tiles = (int64_t)((n_win + TILE_WINDOWS - 1) / TILE_WINDOWS);
     CU(c->tile_first_op.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 4));
-    const int64_t n_cta_tiles = (n_tiles + ENC_WARPS - 1) / ENC_WARPS;
-    CU(c->status.ensure((size_t)std::max<int64_t>(n_cta_tiles, 1) * 8));
+    CU(c->status.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));  // one word per CTA tile; a CTA tile is >= 1 warp tile
     CU(c->tile_first_closer.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
-    CU(c->tile_open_rank.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 4));
-    CU(c->tile_slot0.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
+    CU(c->tile_open_slot.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
     if (N > 0)
         tile_first_op_kernel<<<blocks_for(N, 256), 256, 0, c->stream>>>(c->woff.as<uint64_t>(), N, TILE_WINDOWS,
                                                                         c->tile_first_op.as<uint32_t>());
@@ -332,14 +333,11 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     P.op_rec = c->op_rec.as<uint32_t>(); P.tile_first_op = c->tile_first_op.as<uint32_t>();
     P.n_ops = N; P.n_win = n_win; P.n_tiles = n_tiles;
     P.out = c->out.as<uint64_t>(); P.out_cap = (int64_t)(c->out.cap / 8);
-    P.n_cta_tiles = n_cta_tiles;
     P.status = c->status.as<unsigned long long>();
     P.ticket = (unsigned int *)(sc + SC_TICKET);
     P.total_out = (unsigned long long *)(sc + SC_TOTAL);
     P.tile_first_closer = c->tile_first_closer.as<uint64_t>();
-    P.tile_open_rank = c->tile_open_rank.as<int32_t>();
-    P.tile_slot0 = c->tile_slot0.as<uint64_t>();
-    c->last_op_begin = b->op_begin;
+    P.tile_open_slot = c->tile_open_slot.as<int64_t>();
     P.rec_out_begin = c->rec_out_begin.as<int64_t>();
     P.rec_mism = c->rec_mism.as<unsigned long long>();
     c->n_records = R; c->n_ops = N; c->n_tiles = n_tiles; c->n_win = n_win;
@@ -438,8 +436,11 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
     {
         int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<ENC_WARPS, CMP_BATCH>, 32 * ENC_WARPS, 0) == cudaSuccess && per_sm > 0)
-            ctx->enc_ctas_per_sm = per_sm;
+        if (const char *e = getenv("PAFGPU_WARPS")) ctx->enc_warps = atoi(e) == 1 ? 1 : atoi(e) == 2 ? 2 : 4;
+        cudaError_t oe = ctx->enc_warps == 1   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<1, CMP_BATCH>, 32, 0)
+                         : ctx->enc_warps == 2 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<2, CMP_BATCH>, 64, 0)
+                                               : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<4, CMP_BATCH>, 128, 0);
+        if (oe == cudaSuccess && per_sm > 0) ctx->enc_ctas_per_sm = per_sm;
     }
     ctx->scalars.ensure(SC_COUNT * 8);
     *out = ctx;
@@ -454,7 +455,7 @@ void pafgpu_destroy(pafgpu_ctx *c) {
     c->scratch.release();
     DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
                       &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
-                      &c->status, &c->tile_first_closer, &c->tile_open_rank, &c->tile_slot0, &c->out, &c->rec_out_begin, &c->rec_mism,
+                      &c->status, &c->tile_first_closer, &c->tile_open_slot, &c->out, &c->rec_out_begin, &c->rec_mism,
                       &c->scalars, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
                       &c->ser_text};
     for (DevBuf *b : bufs) b->release();
