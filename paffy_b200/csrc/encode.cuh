@@ -50,7 +50,7 @@ constexpr int TILE_ITERS = 8;                 // windows per lane per warp tile
 constexpr int TILE_WIN = 32 * TILE_ITERS;     // windows per warp tile
 constexpr int TILE_TAB = TILE_WIN + 2;        // a tile overlaps at most TILE_WIN + 1 ops
 constexpr int MASK_PAD = TILE_WIN + TILE_WIN / 8;  // mask of window p sits at p + (p >> 3): conflict-free blocked reads
-constexpr int LIST_CAP = 512;                 // events converted per round
+constexpr int LIST_CAP = 448;                 // events converted per round
 constexpr uint32_t COORD_OPEN = 0xffffffffu;
 constexpr unsigned long long ST_AGG = 1ull << 62, ST_INCL = 2ull << 62, ST_VAL = (1ull << 62) - 1;
 
@@ -68,30 +68,39 @@ __device__ __forceinline__ unsigned slow_mismatch(const Genome &G, uint64_t tp, 
 //   any other op:  tw / qw = low / high half of the op word (copied through)
 struct __align__(16) OpEntry {
     int32_t tw, qw, rem;
-    uint32_t misc;   // bits 0-4 target phase, 5-9 query phase, then flags
+    uint32_t misc;   // bits 0-4 target phase, 5-9 query phase, then EF_* flags and ES_* fields
 };
 constexpr uint32_t EF_PASS = 1u << 11, EF_REV = 1u << 12, EF_EXC = 1u << 13;
+// ops that start inside the tile: bits 14-21 the tile window they start at, 22-27 bases between the previous M op's
+// end and that window boundary (64 - bases in its last window), 28 first op of its record
+constexpr int ES_WIN = 14, ES_GAP = 22;
+constexpr uint32_t EF_HEAD = 1u << 28;
 constexpr int32_t REM_CLAMP = 1 << 30;
 
 struct WarpSmem {
     OpEntry tab[TILE_TAB];
-    uint32_t rec[TILE_TAB];           // owning record, top bit: first op of the record
+    uint16_t rec[TILE_TAB];           // owning record, relative to the record of table entry 0
     uint64_t mask[MASK_PAD];          // mismatch bits of window p at p + (p >> 3)
-    uint16_t list[LIST_CAP + 2];      // event coordinates of one round (+ successor of the last), bit 15: X run
+    uint32_t list[LIST_CAP + 2];      // events of one round (+ successor of the last), see LE_*
+    uint16_t prel[TILE_WIN];          // events of the owning lane before window p
+    uint16_t lanex[32];               // events of the tile before lane l
     uint32_t bm[TILE_ITERS];          // bit p: an op starts at tile window p
     uint32_t bmpre[TILE_ITERS];       // op starts before word k of bm
 };
 
-// ---- A: op table of one warp tile. Returns adj (1 when table entry 0 starts exactly at tile window 0) and
-// whether any op of the tile touches a non-ACGT word.
+// ---- A: op table of one warp tile. adj = 1 when table entry 0 starts exactly at tile window 0; n_tab = entries;
+// rec_first = record of entry 0; any_exc = some op of the tile touches a non-ACGT word.
 __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, int64_t tile, uint64_t s0, uint64_t tile_end,
-                                            unsigned lane, unsigned &adj, bool &any_exc) {
+                                            unsigned lane, unsigned &adj, uint32_t &n_tab, uint32_t &rec_first, bool &any_exc) {
     __syncwarp();
     if (lane < TILE_ITERS) S.bm[lane] = 0;
     __syncwarp();
     const int64_t cur = P.tile_first_op[tile];
     bool more = true, exc = false;
     adj = 0;
+    n_tab = 0;
+    rec_first = 0;
+    uint32_t carry_end = 0;  // end coordinate of the last op of the previous group if it is an M op, else 0
     for (int g = 0; more; g++) {
         const int64_t k = cur + 32 * g + lane;
         const bool valid = k < P.n_ops;
@@ -102,11 +111,17 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
             rec = __ldg(P.op_rec + k);
         }
         const bool in = valid && wo < tile_end;
+        if (g == 0) {
+            adj = __shfl_sync(FULL, (unsigned)(wo == s0), 0);
+            rec_first = __shfl_sync(FULL, rec, 0) & 0x7fffffffu;
+        }
+        OpEntry en;
+        en.tw = en.qw = en.rem = 0;
+        en.misc = EF_PASS;
+        uint32_t my_end = 0;
         if (in) {
-            const int e = 32 * g + (int)lane;
-            OpEntry en;
             if ((int)(opw >> 56) != OP_M) {
-                en.tw = (int32_t)(uint32_t)opw; en.qw = (int32_t)(uint32_t)(opw >> 32); en.rem = 0; en.misc = EF_PASS;
+                en.tw = (int32_t)(uint32_t)opw; en.qw = (int32_t)(uint32_t)(opw >> 32);
             } else {
                 const int64_t back = WIN_BASES * (int64_t)(s0 - wo);  // op bases before tile window 0 (negative: op starts inside)
                 const bool rev = (qpw & QFLAG_REV) != 0;
@@ -120,13 +135,27 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
                 en.rem = (int32_t)rem;
                 en.misc = (uint32_t)(tb & 31) | ((uint32_t)(qb & 31) << 5) | (rev ? EF_REV : 0u) | ((qpw & QFLAG_EXC) ? EF_EXC : 0u);
                 exc |= (qpw & QFLAG_EXC) != 0;
+                my_end = (uint32_t)rem;
             }
-            S.tab[e] = en;
-            S.rec[e] = rec;
-            if (wo >= s0) atomicOr(&S.bm[(wo - s0) >> 5], 1u << ((wo - s0) & 31));
         }
-        if (g == 0) adj = __shfl_sync(FULL, (unsigned)(wo == s0), 0);
-        more = __all_sync(FULL, in);
+        // end of the op before mine (0: none in the table, or a pass-through op)
+        uint32_t prev_end = __shfl_up_sync(FULL, my_end, 1);
+        if (lane == 0) prev_end = carry_end;
+        carry_end = __shfl_sync(FULL, my_end, 31);
+        if (in) {
+            if (wo >= s0) {
+                const uint32_t w = (uint32_t)(wo - s0);
+                const uint32_t gap = prev_end ? WIN_BASES * w - prev_end : 0u;
+                en.misc |= (w << ES_WIN) | ((gap & 63u) << ES_GAP) | ((rec >> 31) ? EF_HEAD : 0u);
+                atomicOr(&S.bm[w >> 5], 1u << (w & 31));
+            }
+            const int e = 32 * g + (int)lane;
+            S.tab[e] = en;
+            S.rec[e] = (uint16_t)((rec & 0x7fffffffu) - rec_first);
+        }
+        const unsigned inb = __ballot_sync(FULL, in);
+        n_tab += __popc(inb);
+        more = inb == FULL;
     }
     any_exc = __any_sync(FULL, exc);
     __syncwarp();
@@ -141,7 +170,7 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
 // ---- B: compare. Striped windows; masks to shared memory; per-record mismatch tallies. Returns (lane 0) the
 // mismatch state of the base just before the tile when tile window 0 continues an op.
 template <int BATCH, bool EXC>
-__device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem &S, uint32_t n_act, unsigned lane, unsigned adj) {
+__device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem &S, uint32_t n_act, unsigned lane, unsigned adj, uint32_t rec_first) {
     static_assert(TILE_ITERS % BATCH == 0, "BATCH must divide the iterations of a tile");
     const uint64_t *__restrict__ gw = P.G.words;
     uint32_t pre = 0, pm0 = 0;
@@ -242,9 +271,9 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             S.mask[srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
             // per-record mismatch tally, flushed when the lane moves to another record
             if (isM) {
-                const uint32_t rec = S.rec[idx] & 0x7fffffffu;
+                const uint32_t rec = S.rec[idx];
                 if (rec != acc_rec) {
-                    if (acc_mm) atomicAdd(P.rec_mism + acc_rec, (unsigned long long)acc_mm);
+                    if (acc_mm) atomicAdd(P.rec_mism + rec_first + acc_rec, (unsigned long long)acc_mm);
                     acc_rec = rec;
                     acc_mm = 0;
                 }
@@ -256,9 +285,9 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
     const uint32_t r0 = __shfl_sync(FULL, acc_rec, 0);
     if (__all_sync(FULL, acc_rec == r0)) {
         const uint32_t sum = __reduce_add_sync(FULL, acc_mm);
-        if (lane == 0 && sum && r0 != INF32) atomicAdd(P.rec_mism + r0, (unsigned long long)sum);
+        if (lane == 0 && sum && r0 != INF32) atomicAdd(P.rec_mism + rec_first + r0, (unsigned long long)sum);
     } else if (acc_mm && acc_rec != INF32) {
-        atomicAdd(P.rec_mism + acc_rec, (unsigned long long)acc_mm);
+        atomicAdd(P.rec_mism + rec_first + acc_rec, (unsigned long long)acc_mm);
     }
     return pm0;
 }
@@ -266,6 +295,14 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
 // ---- C / E: blocked view. Lane owns tile windows 8 * lane .. 8 * lane + 7 = 16 half-window words of 32 bases.
 // An "event" is an output op: the start of an =/X run, or a pass-through op (its window holds no mismatch bits and
 // starts an op, so it shows up as one forced start bit). Coordinates are tile-relative (64 * window + base).
+// List entry of an event (32 bits):
+//   bits 0-13 coordinate of the run start, bit 15 X run            (pass-through op: bits 0-8 its table index)
+//   bits 16-30 coordinate at which the run BEFORE the event closes: the event's own coordinate inside an op, the end
+//              of the previous op at an op start (patched in by the op pass)
+//   bit 31 pass-through op
+// so that an event's length is close(next entry) - its own coordinate, computed by any lane.
+constexpr uint32_t LE_COORD = 0x3fffu, LE_X = 1u << 15, LE_CLOSE = 0x7fffu, LE_PASS = 1u << 31;
+constexpr int LS_CLOSE = 16;
 
 // run-start bits of one 32-base word: m = its mismatch bits, prev = the word before it (top bit used), forced = an op
 // starts at bit 0
@@ -278,8 +315,8 @@ __device__ __forceinline__ uint32_t window_op(const WarpSmem &S, uint32_t w, uns
     return S.bmpre[w >> 5] + __popc(S.bm[w >> 5] & (0xffffffffu >> (31 - (w & 31)))) - adj;
 }
 
-// C: events of the lane and the bitmap of its words that hold any
-__device__ __forceinline__ void lane_count(const WarpSmem &S, unsigned lane, uint32_t n_win, uint32_t byte, uint32_t pm, uint32_t &cnt,
+// C: events of the lane, the bitmap of its words that hold any, and the lane-relative event prefix of its windows
+__device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t n_win, uint32_t byte, uint32_t pm, uint32_t &cnt,
                                            uint32_t &nz) {
     const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 18 * lane;
     cnt = 0;
@@ -288,6 +325,7 @@ __device__ __forceinline__ void lane_count(const WarpSmem &S, unsigned lane, uin
 #pragma unroll
     for (int j = 0; j < TILE_ITERS; j++) {
         const uint2 m = *reinterpret_cast<const uint2 *>(M + 2 * j);
+        S.prel[8 * lane + j] = (uint16_t)cnt;
         if ((uint32_t)j < n_win) {
             const uint32_t d0 = start_bits(m.x, prev, (byte >> j) & 1u), d1 = start_bits(m.y, m.x, false);
             cnt += __popc(d0) + __popc(d1);
@@ -297,8 +335,8 @@ __device__ __forceinline__ void lane_count(const WarpSmem &S, unsigned lane, uin
     }
 }
 
-// E1: coordinates of the lane's events, ranks base .. base + LIST_CAP of the tile, into the list (bit 15: X run).
-// One event per trip whatever word it comes from, so lanes stay busy as long as they have events left.
+// E1: the lane's events, ranks base .. base + LIST_CAP of the tile, into the list. One event per trip whatever word
+// it comes from, so lanes stay busy as long as they have events left.
 __device__ __forceinline__ void lane_list(WarpSmem &S, unsigned lane, uint32_t byte, uint32_t pm, uint32_t nz, uint32_t ex, uint32_t base) {
     const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 18 * lane;
     uint32_t r = ex - base;  // wraps for events before the round; comes back to 0 exactly at entry `base`
@@ -315,8 +353,26 @@ __device__ __forceinline__ void lane_list(WarpSmem &S, unsigned lane, uint32_t b
         }
         const uint32_t b = (uint32_t)__ffs((int)d) - 1u;
         d &= d - 1u;
-        if (r <= (uint32_t)LIST_CAP) S.list[r] = (uint16_t)((c0 + b) | (((m >> b) & 1u) << 15));
+        if (r <= (uint32_t)LIST_CAP) S.list[r] = (c0 + b) * 0x10001u | (((m >> b) & 1u) << 15);
         r++;
+    }
+}
+
+// E1': op pass. Every op that starts inside the tile patches its event: the run before it closes at the previous op's
+// end, a pass-through op is copied through, the first op of a record leaves the record's first output slot.
+__device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, unsigned lane, unsigned adj, uint32_t n_tab, uint32_t rec_first,
+                                        uint32_t base, unsigned long long slot0) {
+    for (uint32_t e = lane + (adj ? 0u : 1u); e < n_tab; e += 32) {
+        const uint32_t misc = S.tab[e].misc;
+        const uint32_t w = (misc >> ES_WIN) & 0xffu;
+        const uint32_t r = (uint32_t)S.lanex[w >> 3] + S.prel[w];
+        const uint32_t k = r - base;
+        if (k <= (uint32_t)LIST_CAP) {
+            const uint32_t close0 = WIN_BASES * w - ((misc >> ES_GAP) & 63u);
+            if (misc & EF_PASS) S.list[k] = e | (close0 << LS_CLOSE) | LE_PASS;
+            else reinterpret_cast<uint16_t *>(S.list)[2 * k + 1] = (uint16_t)close0;
+            if ((misc & EF_HEAD) && k < (uint32_t)LIST_CAP) P.rec_out_begin[rec_first + S.rec[e]] = (int64_t)(slot0 + r);
+        }
     }
 }
 
@@ -342,11 +398,12 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         const uint32_t n_act = s0 < P.n_win ? (uint32_t)min((uint64_t)TILE_WIN, P.n_win - s0) : 0u;
 
         unsigned adj = 0;
-        uint32_t cnt = 0, nz = 0, inc = 0, byte = 0, pm = 0, term = COORD_OPEN;
+        uint32_t cnt = 0, nz = 0, inc = 0, byte = 0, pm = 0, term = COORD_OPEN, n_tab = 0, rec_first = 0;
         if (n_act) {
             bool any_exc;
-            build_table(P, S, tile, s0, s0 + n_act, lane, adj, any_exc);
-            const uint32_t pm0 = any_exc ? compare_tile<BATCH, true>(P, S, n_act, lane, adj) : compare_tile<BATCH, false>(P, S, n_act, lane, adj);
+            build_table(P, S, tile, s0, s0 + n_act, lane, adj, n_tab, rec_first, any_exc);
+            const uint32_t pm0 = any_exc ? compare_tile<BATCH, true>(P, S, n_act, lane, adj, rec_first)
+                                         : compare_tile<BATCH, false>(P, S, n_act, lane, adj, rec_first);
             __syncwarp();
             // blocked view of the tile
             byte = (S.bm[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
@@ -359,6 +416,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                 const uint32_t t = __shfl_up_sync(FULL, inc, o);
                 if (lane >= (unsigned)o) inc += t;
             }
+            S.lanex[lane] = (uint16_t)(inc - cnt);
             // where a run still open at the tile's last window closes: the end of that window's op if it lies inside the tile
             const OpEntry en = S.tab[window_op(S, n_act - 1, adj)];
             term = (en.misc & EF_PASS) ? WIN_BASES * n_act : en.rem <= (int32_t)(WIN_BASES * n_act) ? (uint32_t)en.rem : COORD_OPEN;
@@ -413,37 +471,27 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             for (int w = 0; w < WARPS; w++) slot0 += (unsigned)w < wid ? s_wcount[w] : 0u;
             if (lane == 0 && tile_count == 0) P.tile_first_closer[tile] = term == COORD_OPEN ? INF64 : WIN_BASES * s0 + term;
             for (uint32_t base = 0; base < tile_count; base += LIST_CAP) {
-                if (base) {  // dense tiles: further rounds
-                    __syncwarp();
-                    if (cnt && ex <= base + LIST_CAP && ex + cnt > base) lane_list(S, lane, byte, pm, nz, ex, base);
-                }
+                __syncwarp();
+                if (base && cnt && ex <= base + LIST_CAP && ex + cnt > base) lane_list(S, lane, byte, pm, nz, ex, base);  // dense tiles
+                __syncwarp();
+                op_pass(P, S, lane, adj, n_tab, rec_first, base, slot0);
                 __syncwarp();
                 const uint32_t round_end = min(base + (uint32_t)LIST_CAP, tile_count);
                 for (uint32_t i0 = base; i0 < round_end; i0 += 31) {
                     const uint32_t i = i0 + lane;
-                    const bool have = i < tile_count && i <= round_end;
-                    const uint32_t e = have ? S.list[i - base] : 0u;
-                    const uint32_t c = e & 0x3fffu, w = c >> 6;
-                    uint32_t close = c, lo = 0, hi = (uint32_t)((e >> 15) ? OP_X : OP_EQ) << 24;
-                    bool pass = false;
-                    if (have && (c & 63u) == 0 && ((S.bm[w >> 5] >> (w & 31)) & 1u)) {
-                        // an op starts here: the run before it ends with the previous op
-                        const uint32_t idx = window_op(S, w, adj);
-                        const OpEntry en = S.tab[idx];
-                        if (idx >= 1) {
-                            const OpEntry pe = S.tab[idx - 1];
-                            if (!(pe.misc & EF_PASS)) close = (uint32_t)pe.rem;
-                        }
-                        if (en.misc & EF_PASS) { pass = true; lo = (uint32_t)en.tw; hi = (uint32_t)en.qw; }
-                        const uint32_t recw = S.rec[idx];
-                        if ((recw >> 31) && lane < 31) P.rec_out_begin[recw & 0x7fffffffu] = (int64_t)(slot0 + i);
-                    }
-                    if (i == tile_count) close = term;
-                    if (i == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + close;
-                    const uint32_t nclose = __shfl_down_sync(FULL, close, 1);
+                    uint32_t e = (i < tile_count && i <= round_end) ? S.list[i - base] : 0u;
+                    if (i == tile_count) e = (term & LE_CLOSE) << LS_CLOSE;  // virtual event closing the tile's last run
+                    if (i == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + ((e >> LS_CLOSE) & LE_CLOSE);
+                    const uint32_t nx = __shfl_down_sync(FULL, e, 1);
                     if (lane < 31 && i < round_end) {
-                        if (!pass) {
-                            lo = nclose - c;
+                        uint32_t lo, hi;
+                        if (e & LE_PASS) {
+                            const OpEntry en = S.tab[e & 0x1ffu];
+                            lo = (uint32_t)en.tw; hi = (uint32_t)en.qw;
+                        } else {
+                            const uint32_t c = e & LE_COORD;
+                            hi = (uint32_t)((e & LE_X) ? OP_X : OP_EQ) << 24;
+                            lo = ((nx >> LS_CLOSE) & LE_CLOSE) - c;
                             if (i == tile_count - 1 && term == COORD_OPEN) {
                                 // run still open at the tile's end: provisional absolute start, turned into a length by stitch_kernel
                                 const uint64_t abs_start = WIN_BASES * s0 + c;
