@@ -132,6 +132,51 @@ int pafgpu_encode_one(pafgpu_ctx *ctx, const uint64_t *ops, int64_t n_ops, int s
  * ms_kernel: mean CUDA-event ms of the base-comparison kernel alone. */
 int pafgpu_time_encode(pafgpu_ctx *ctx, int reps, float *ms_stage, float *ms_kernel);
 
+/* Index (within the batch) of the record that made the last encode call fail with PAFGPU_EBOUNDS, else -1. */
+int64_t pafgpu_last_bad_record(const pafgpu_ctx *ctx);
+
+/* Pinned host memory for batch arrays and fetched text (cudaHostAlloc / cudaFreeHost): the _host entry points copy
+ * at full PCIe/C2C speed only from such memory. */
+void *pafgpu_host_alloc(int64_t bytes);
+void pafgpu_host_free(void *p);
+
+/* ---- whole-file filter: replaces the record loop of paffy_add_mismatches_main (impl/paf_add_mismatches.c:106-140)
+ *      and, for mode 2, the loop of paffy_trim_main behind it (impl/paf_trim.c:113-127). Reads PAF text, runs every M
+ *      op through the CUDA kernels in batches, writes PAF text in input order. A record that the reference would
+ *      abort on (unknown contig, paf_check failure, bad strand / CIGAR letter) ends the run: every record before it
+ *      has been written, the reference's message is printed to stderr and kept in pafgpu_last_error, and 1 is
+ *      returned (the reference's exit code). Negative returns are library errors. ------------------------------- */
+enum { PAFGPU_MODE_ADD = 0, PAFGPU_MODE_REMOVE = 1, PAFGPU_MODE_ADD_TRIM = 2 };
+typedef struct {
+    int mode;                  /* PAFGPU_MODE_*: add_mismatches, add_mismatches -a, add_mismatches | trim */
+    float trim_score_fraction; /* paffy trim -r (reference default 0.05) */
+    float trim_max_fraction;   /* paffy trim -t (reference default 1.0) */
+    int threads;               /* host threads for parsing / rendering, 0 = all */
+    int64_t batch_bases;       /* aligned bases per GPU batch, 0 = default */
+} pafgpu_file_opts;
+typedef struct {
+    int64_t records;           /* records written */
+    int64_t aligned_bases;     /* sum of input M lengths of the written records */
+    int64_t batches;
+    int64_t failed_record;     /* input index of the record that ended the run, -1 if none */
+    int64_t stats[7];          /* paf_stats_calc totals over the encoded records + record count, as `paffy view -s`
+                                  accumulates them (impl/paf_view.c:176-178): matches, mismatches, query_inserts,
+                                  query_deletes, query_insert_bases, query_delete_bases, records */
+    double s_read, s_parse, s_gpu, s_host, s_write; /* wall seconds per stage */
+} pafgpu_file_report;
+/* in_path / out_path NULL = stdin / stdout. */
+int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char *out_path, const pafgpu_file_opts *opts,
+                               pafgpu_file_report *report);
+
+/* Drop-in for the reference's subcommand entry point (impl/paf_add_mismatches.c:26; paffy_main.c:52-77 dispatches to
+ * it by name): same options (-i/--inputFile, -o/--outputFile, -a/--removeMismatches, -l/--logLevel, -h/--help,
+ * FASTA files as positionals), same exit codes. Uses CUDA device $PAFFY_B200_DEVICE (default 0). */
+int paffy_add_mismatches_main(int argc, char *argv[]);
+
+/* ---- multi-GPU sharding: cut n input-ordered records with the given weights (aligned bases) into
+ *      `parts` contiguous ranges of near-equal weight. cuts has parts + 1 entries, cuts[0] = 0, cuts[parts] = n. */
+int pafgpu_partition(const int64_t *weights, int64_t n, int parts, int64_t *cuts);
+
 #ifdef __cplusplus
 }
 #endif

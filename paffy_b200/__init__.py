@@ -3,6 +3,8 @@
 The product is the CUDA library libpaffy_b200.so (C ABI in include/paffy_b200.h); this package is
 the thin Python plumbing over it (ctypes), mirroring the reference's interface for the path.
 """
-from .lib import Batch, Context, PafGpuError, Result, load, ABI_SYMBOLS  # noqa: F401
+from .lib import (ABI_SYMBOLS, REFERENCE_SYMBOLS, Batch, Context, FileOpts, FileReport, PafGpuError, Result, load, partition,  # noqa: F401
+                  remove_mismatches_file)
 
-__all__ = ["Context", "PafGpuError", "Batch", "Result", "load", "ABI_SYMBOLS"]
+__all__ = ["Context", "PafGpuError", "Batch", "Result", "FileOpts", "FileReport", "load", "partition", "remove_mismatches_file", "ABI_SYMBOLS",
+           "REFERENCE_SYMBOLS"]

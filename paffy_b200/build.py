@@ -6,8 +6,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpaffy_b200.so")
-SOURCES = ["pafgpu.cu", "paf_host.cpp"]
-HEADERS = ["kernels.cuh", "serialise.cuh", "paf_compat.h", os.path.join("..", "..", "include", "paffy_b200.h")]
+SOURCES = ["pafgpu.cu", "paf_host.cpp", "paf_compat.cpp"]
+CLI = os.path.join(HERE, "paffy_b200_cli")
+HEADERS = ["kernels.cuh", "encode.cuh", "serialise.cuh", "internal.h", "paffy_main.c", os.path.join("..", "..", "include", "paf_b200_compat.h"), os.path.join("..", "..", "include", "paffy_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--use_fast_math=false",
               "-Xcompiler", "-fPIC,-O3,-Wall,-fvisibility=default", "-Xptxas", "-v", "-shared", "-cudart", "shared",
               "-Xlinker", "-Bsymbolic"]
@@ -42,6 +43,12 @@ def build(force=False, verbose=False):
         raise RuntimeError("nvcc failed")
     with open(os.path.join(HERE, "build_ptxas.log"), "w") as fh:
         fh.write(r.stdout + r.stderr)
+    # the command line front end (C, links the library by relative rpath)
+    r = subprocess.run(["gcc", "-O2", "-o", CLI, os.path.join(CSRC, "paffy_main.c"), "-L", HERE, "-lpaffy_b200",
+                        "-Wl,-rpath,$ORIGIN"], capture_output=True, text=True)
+    if r.returncode:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("building the CLI failed")
     return LIB
 
 

@@ -15,6 +15,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <strings.h>
 #include <string>
 #include <thread>
 #include <vector>
@@ -343,3 +344,507 @@ void parallel_for(int64_t n, int threads, F f) {  // f(begin, end, thread)
 
 }  // namespace
 
+#include "internal.h"
+
+#include <chrono>
+#include <getopt.h>
+
+namespace {
+
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+// paf_remove_mismatches (impl/paf.c:786-809): consecutive M / = / X ops become one M, across original op boundaries.
+// Compacts ops[lo, hi) in place and returns the new hi.
+int64_t merge_matches(uint64_t *ops, int64_t lo, int64_t hi) {
+    int64_t w = lo;
+    for (int64_t k = lo; k < hi; k++) {
+        const int c = op_code(ops[k]);
+        const bool diag = c == OPM || c == OPEQ || c == OPX;
+        if (diag && w > lo && op_code(ops[w - 1]) == OPM) ops[w - 1] = mk_op(op_len(ops[w - 1]) + op_len(ops[k]), OPM);
+        else ops[w++] = diag ? mk_op(op_len(ops[k]), OPM) : ops[k];
+    }
+    return w;
+}
+
+// the whole line of a record as paf_write_to_buffer prints it
+void render_line(const Rec &r, const uint64_t *ops, int64_t n, std::string &out) {
+    render_prefix(r, out);
+    if (r.has_cigar) render_ops(ops, n, out);
+    out.push_back('\n');
+}
+
+std::string parse_error(const Rec &r) {
+    char buf[128];
+    switch (r.bad) {
+        case 2: snprintf(buf, sizeof buf, "Got an unexpected strand character (%c) in a paf string", r.bad_char); break;
+        case 3: snprintf(buf, sizeof buf, "Got an unexpected character paf cigar string: %c", r.bad_char ? r.bad_char : ' '); break;
+        case 4: snprintf(buf, sizeof buf, "Got an unexpected tp value in a paf string"); break;
+        default: snprintf(buf, sizeof buf, "Too few fields in a paf line"); break;
+    }
+    return buf;
+}
+
+struct Pinned {  // pinned host buffer that only grows
+    void *p = nullptr;
+    int64_t cap = 0;
+    bool ensure(int64_t bytes) {
+        if (bytes <= cap) return true;
+        if (p) pafgpu_host_free(p);
+        cap = bytes + bytes / 4 + 4096;
+        p = pafgpu_host_alloc(cap);
+        if (!p) cap = 0;
+        return p != nullptr;
+    }
+    ~Pinned() { if (p) pafgpu_host_free(p); }
+    template <class T> T *as() { return static_cast<T *>(p); }
+};
+
+bool write_all(FILE *fh, const char *p, size_t n) { return n == 0 || fwrite(p, 1, n, fh) == n; }
+
+}  // namespace
+
+// ================================================================================================
+// The file filter. Everything the reference does per record around paf_encode_mismatches, done per batch.
+namespace {
+
+struct Filter {
+    pafgpu_ctx *ctx;
+    pafgpu_file_opts o;
+    pafgpu_file_report rep{};
+    int threads = 1;
+    FILE *out = nullptr;
+    Parsed in;
+    std::string err;           // message of the record that ended the run
+    // per-record
+    std::vector<int32_t> qc, tc;
+    // batch staging (pinned)
+    Pinned p_ops, p_begin, p_qc, p_tc, p_qs, p_qe, p_ts, p_st, p_prefix, p_text, p_out_ops;
+    std::vector<int64_t> prefix_begin, line_begin, out_begin, mism;
+    std::vector<int64_t> map;  // batch record -> input record
+
+    // records [a, b) -> one GPU batch. Returns 0, 1 (bad record: b is moved to it) or a negative library error.
+    int run_batch(int64_t a, int64_t &b);
+    int finish_add(int64_t a, int64_t b);
+    int finish_trim(int64_t a, int64_t b);
+};
+
+int Filter::run_batch(int64_t a, int64_t &b) {
+    std::vector<Rec> &R = in.recs;
+    for (;;) {
+        // SoA of the records that carry aligned work; the others are printed by the host as they are
+        map.clear();
+        int64_t n_ops = 0;
+        for (int64_t i = a; i < b; i++) {
+            if (!R[i].has_cigar) continue;
+            int64_t kept = 0;
+            for (int64_t k = R[i].op_begin; k < R[i].op_end; k++) kept += !(op_code(in.ops[k]) == OPM && op_len(in.ops[k]) == 0);
+            if (!kept) continue;
+            map.push_back(i);
+            n_ops += kept;
+        }
+        const int64_t nb = (int64_t)map.size();
+        if (nb == 0) return 0;
+        if (!p_ops.ensure(n_ops * 8) || !p_begin.ensure((nb + 1) * 8) || !p_qc.ensure(nb * 4) || !p_tc.ensure(nb * 4) ||
+            !p_qs.ensure(nb * 8) || !p_qe.ensure(nb * 8) || !p_ts.ensure(nb * 8) || !p_st.ensure(nb))
+            return pafgpu_internal_fail(ctx, PAFGPU_ENODEVICE, "pinned host allocation failed");
+        int64_t *begin = p_begin.as<int64_t>();
+        begin[0] = 0;
+        for (int64_t j = 0; j < nb; j++) {
+            const Rec &r = R[map[j]];
+            int64_t kept = 0;
+            for (int64_t k = r.op_begin; k < r.op_end; k++) kept += !(op_code(in.ops[k]) == OPM && op_len(in.ops[k]) == 0);
+            begin[j + 1] = begin[j] + kept;
+        }
+        uint64_t *ops = p_ops.as<uint64_t>();
+        parallel_for(nb, threads, [&](int64_t j0, int64_t j1, int) {
+            for (int64_t j = j0; j < j1; j++) {
+                const Rec &r = R[map[j]];
+                uint64_t *w = ops + begin[j];
+                for (int64_t k = r.op_begin; k < r.op_end; k++)
+                    if (!(op_code(in.ops[k]) == OPM && op_len(in.ops[k]) == 0)) *w++ = in.ops[k];
+                p_qc.as<int32_t>()[j] = qc[map[j]]; p_tc.as<int32_t>()[j] = tc[map[j]];
+                p_qs.as<int64_t>()[j] = r.qs; p_qe.as<int64_t>()[j] = r.qe; p_ts.as<int64_t>()[j] = r.ts;
+                p_st.as<uint8_t>()[j] = r.same_strand ? 1 : 0;
+            }
+        });
+        pafgpu_batch B{nb, n_ops, begin, ops, p_qc.as<int32_t>(), p_tc.as<int32_t>(), p_qs.as<int64_t>(), p_qe.as<int64_t>(),
+                       p_ts.as<int64_t>(), p_st.as<uint8_t>()};
+        pafgpu_result res;
+        const int rc = pafgpu_encode_batch_host(ctx, &B, &res);
+        if (rc == 0) {
+            rep.aligned_bases += res.aligned_bases;
+            return 0;
+        }
+        if (rc != PAFGPU_EBOUNDS) return rc;
+        // the reference would read outside the sequence here (undefined behaviour); the run ends at that record
+        const int64_t bad = pafgpu_last_bad_record(ctx);
+        if (bad < 0 || bad >= nb) return rc;
+        b = map[bad];
+        err = std::string("ERROR: ") + pafgpu_last_error(ctx);
+        if (b == a) return 1;
+        const int again = run_batch(a, b);
+        return again ? again : 1;
+    }
+}
+
+// stats of records [a, b) as paf_stats_calc sees their encoded CIGARs (impl/paf.c:236-260): input ops + the mismatch
+// counts the kernel tallied per record
+static void add_stats(Filter &F, int64_t a, int64_t b) {
+    int64_t *s = F.rep.stats;
+    size_t j = 0;
+    for (int64_t i = a; i < b; i++) {
+        const Rec &r = F.in.recs[i];
+        int64_t m = 0;
+        for (int64_t k = r.op_begin; k < r.op_end; k++) {
+            const int c = op_code(F.in.ops[k]);
+            const int64_t n = op_len(F.in.ops[k]);
+            if (c == OPM) m += n;
+            else if (c == OPEQ) s[0] += n;
+            else if (c == OPX) s[1] += n;
+            else if (c == OPI) { s[2]++; s[4] += n; }
+            else if (c == OPD) { s[3]++; s[5] += n; }
+        }
+        int64_t mm = 0;
+        if (j < F.map.size() && F.map[j] == i) mm = F.mism[j++];
+        s[0] += m - mm;
+        s[1] += mm;
+        s[6]++;
+    }
+}
+
+int Filter::finish_add(int64_t a, int64_t b) {
+    std::vector<Rec> &R = in.recs;
+    const int64_t nb = (int64_t)map.size();
+    double t0 = now_s();
+    mism.assign((size_t)nb, 0);
+    line_begin.assign((size_t)nb + 1, 0);
+    int64_t text_bytes = 0;
+    if (nb) {
+        // text before the CIGAR, rendered on the host threads; the device appends <len><op>... and '\n'
+        std::vector<std::string> part((size_t)threads);
+        std::vector<int64_t> plen((size_t)nb);
+        parallel_for(nb, threads, [&](int64_t j0, int64_t j1, int t) {
+            std::string &s = part[(size_t)t];
+            for (int64_t j = j0; j < j1; j++) {
+                const size_t before = s.size();
+                render_prefix(R[map[j]], s);
+                plen[(size_t)j] = (int64_t)(s.size() - before);
+            }
+        });
+        prefix_begin.assign((size_t)nb + 1, 0);
+        for (int64_t j = 0; j < nb; j++) prefix_begin[(size_t)j + 1] = prefix_begin[(size_t)j] + plen[(size_t)j];
+        if (!p_prefix.ensure(prefix_begin[(size_t)nb] + 8)) return pafgpu_internal_fail(ctx, PAFGPU_ENODEVICE, "pinned host allocation failed");
+        {
+            char *w = p_prefix.as<char>();
+            for (auto &s : part) { memcpy(w, s.data(), s.size()); w += s.size(); }
+        }
+        rep.s_host += now_s() - t0;
+        t0 = now_s();
+        int rc = pafgpu_serialise(ctx, p_prefix.as<char>(), prefix_begin.data(), &text_bytes, nullptr);
+        if (rc) return rc;
+        if (!p_text.ensure(text_bytes + 8)) return pafgpu_internal_fail(ctx, PAFGPU_ENODEVICE, "pinned host allocation failed");
+        if ((rc = pafgpu_fetch_text(ctx, p_text.as<char>(), line_begin.data()))) return rc;
+        if ((rc = pafgpu_fetch_ops(ctx, nullptr, nullptr, mism.data()))) return rc;
+        rep.s_gpu += now_s() - t0;
+        t0 = now_s();
+    }
+    add_stats(*this, a, b);
+    // write in input order: device text for the batch records, host text for the records without aligned work
+    const char *text = p_text.as<char>();
+    bool ok = true;
+    if (nb == b - a) {
+        ok = write_all(out, text, (size_t)text_bytes);
+    } else {
+        std::string plain;
+        int64_t j = 0, run_from = 0;
+        for (int64_t i = a; i < b && ok; i++) {
+            if (j < nb && map[(size_t)j] == i) { j++; continue; }
+            ok = write_all(out, text + line_begin[(size_t)run_from], (size_t)(line_begin[(size_t)j] - line_begin[(size_t)run_from]));
+            run_from = j;
+            plain.clear();
+            render_line(R[i], nullptr, 0, plain);
+            ok = ok && write_all(out, plain.data(), plain.size());
+        }
+        ok = ok && write_all(out, text + line_begin[(size_t)run_from], (size_t)(line_begin[(size_t)nb] - line_begin[(size_t)run_from]));
+    }
+    rep.s_write += now_s() - t0;
+    return ok ? 0 : pafgpu_internal_fail(ctx, PAFGPU_EIO, "write failed");
+}
+
+// add_mismatches | trim: the encoded ops come back to the host, where the float32 identity walk of
+// paf_trim_unreliable_tails (impl/paf.c:811-953) runs per record on all threads, then paf_check and printing.
+int Filter::finish_trim(int64_t a, int64_t b) {
+    std::vector<Rec> &R = in.recs;
+    const int64_t nb = (int64_t)map.size();
+    double t0 = now_s();
+    mism.assign((size_t)nb, 0);
+    out_begin.assign((size_t)nb + 1, 0);
+    uint64_t *enc = nullptr;
+    if (nb) {
+        int rc = pafgpu_fetch_ops(ctx, nullptr, out_begin.data(), mism.data());
+        if (rc) return rc;
+        if (!p_out_ops.ensure(out_begin[(size_t)nb] * 8 + 8)) return pafgpu_internal_fail(ctx, PAFGPU_ENODEVICE, "pinned host allocation failed");
+        enc = p_out_ops.as<uint64_t>();
+        if ((rc = pafgpu_fetch_ops(ctx, enc, nullptr, nullptr))) return rc;
+    }
+    rep.s_gpu += now_s() - t0;
+    t0 = now_s();
+    add_stats(*this, a, b);
+    // batch slot of every record of [a, b) (-1: no aligned work)
+    std::vector<int64_t> slot((size_t)(b - a), -1);
+    for (int64_t j = 0; j < nb; j++) slot[(size_t)(map[(size_t)j] - a)] = j;
+    std::vector<std::string> part((size_t)threads);
+    std::vector<int64_t> bad((size_t)threads, -1);
+    std::vector<std::string> bad_msg((size_t)threads);
+    parallel_for(b - a, threads, [&](int64_t i0, int64_t i1, int t) {
+        std::string &s = part[(size_t)t];
+        for (int64_t i = a + i0; i < a + i1; i++) {
+            Rec r = R[(size_t)i];
+            const int64_t j = slot[(size_t)(i - a)];
+            uint64_t *ops = j >= 0 ? enc + out_begin[(size_t)j] : nullptr;
+            int64_t lo = 0, hi = j >= 0 ? out_begin[(size_t)j + 1] - out_begin[(size_t)j] : 0;
+            if (r.has_cigar && hi > lo) {
+                const bool fine = trim_unreliable_tails(r, ops, lo, hi, o.trim_score_fraction, o.trim_max_fraction);
+                std::string msg;
+                if (!fine || check_record(r, ops + lo, hi - lo, &msg)) {
+                    bad[(size_t)t] = i;
+                    if (!fine) msg = "trimmed alignment identity fell below the untrimmed identity (reference assert)";
+                    std::string line;
+                    render_line(r, ops + lo, hi - lo, line);
+                    bad_msg[(size_t)t] = "ERROR: " + msg + " " + line;
+                    return;
+                }
+            }
+            render_line(r, ops ? ops + lo : nullptr, hi - lo, s);
+        }
+    });
+    rep.s_host += now_s() - t0;
+    t0 = now_s();
+    bool ok = true;
+    int rc = 0;
+    for (size_t t = 0; t < part.size() && ok; t++) {
+        ok = write_all(out, part[t].data(), part[t].size());
+        if (bad[t] >= 0) {  // records of later threads come after the failing one: not written
+            err = bad_msg[t];
+            rep.failed_record = bad[t];
+            rc = 1;
+            break;
+        }
+    }
+    rep.s_write += now_s() - t0;
+    if (!ok) return pafgpu_internal_fail(ctx, PAFGPU_EIO, "write failed");
+    return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pafgpu_partition(const int64_t *weights, int64_t n, int parts, int64_t *cuts) {
+    if (n < 0 || parts < 1 || !cuts || (n && !weights)) return PAFGPU_EINVAL;
+    long double total = 0;
+    for (int64_t i = 0; i < n; i++) total += (long double)std::max<int64_t>(weights[i], 0);
+    cuts[0] = 0;
+    long double acc = 0;
+    int64_t i = 0;
+    for (int p = 1; p < parts; p++) {
+        // first record index at which the running weight reaches p / parts of the total
+        const long double want = total * p / parts;
+        while (i < n && acc + (long double)std::max<int64_t>(weights[i], 0) / 2 < want) acc += (long double)std::max<int64_t>(weights[i++], 0);
+        cuts[p] = i;
+    }
+    cuts[parts] = n;
+    return 0;
+}
+
+int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char *out_path, const pafgpu_file_opts *opts,
+                               pafgpu_file_report *report) {
+    if (!ctx && !(opts && opts->mode == PAFGPU_MODE_REMOVE)) return PAFGPU_EINVAL;  // -a is host-only text work
+    Filter F;
+    F.ctx = ctx;
+    F.o = opts ? *opts : pafgpu_file_opts{PAFGPU_MODE_ADD, 0.05f, 1.0f, 0, 0};
+    if (F.o.mode < 0 || F.o.mode > 2) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "bad mode");
+    F.threads = F.o.threads > 0 ? F.o.threads : hw_threads();
+    const int64_t batch_bases = F.o.batch_bases > 0 ? F.o.batch_bases : (int64_t)1 << 34;
+    const int64_t batch_ops = (int64_t)1 << 30;
+    F.rep.failed_record = -1;
+
+    double t0 = now_s();
+    FILE *fin = in_path ? fopen(in_path, "rb") : stdin;
+    if (!fin) return pafgpu_internal_fail(ctx, PAFGPU_EIO, (std::string("cannot open ") + in_path).c_str());
+    std::string text;
+    const bool read_ok = slurp(fin, text);
+    if (in_path) fclose(fin);
+    if (!read_ok) return pafgpu_internal_fail(ctx, PAFGPU_EIO, "read failed");
+    text.erase(std::remove(text.begin(), text.end(), '\r'), text.end());  // the line reader drops '\r' (sonLibFile.c:49-51)
+    F.rep.s_read = now_s() - t0;
+    t0 = now_s();
+    parse_all(text, F.threads, F.in);
+    F.rep.s_parse = now_s() - t0;
+    F.out = out_path ? fopen(out_path, "wb") : stdout;
+    if (!F.out) return pafgpu_internal_fail(ctx, PAFGPU_EIO, (std::string("cannot open ") + out_path).c_str());
+
+    std::vector<Rec> &R = F.in.recs;
+    const int64_t n = (int64_t)R.size();
+    int rc = 0;
+    // ---- the record that ends the run, found in input order before anything is computed: parse failures, unknown
+    // contigs (impl/paf_add_mismatches.c:116-127) and paf_check (impl/paf.c:427-461; encoding keeps every sum it tests)
+    t0 = now_s();
+    int64_t stop = n;
+    F.qc.assign((size_t)n, -1);
+    F.tc.assign((size_t)n, -1);
+    for (int64_t i = 0; i < n; i++) {
+        Rec &r = R[(size_t)i];
+        std::string msg;
+        if (r.bad) {
+            msg = "ERROR: " + parse_error(r);
+        } else {
+            if (F.o.mode != PAFGPU_MODE_REMOVE) {
+                const std::string qn(r.qname, r.qname_len), tn(r.tname, r.tname_len);
+                const int64_t q = pafgpu_genome_find(ctx, qn.c_str());
+                const int64_t t = q >= 0 ? pafgpu_genome_find(ctx, tn.c_str()) : -1;
+                if (q < 0) msg = "No query sequence named: " + qn + " found";
+                else if (t < 0) msg = "No target sequence named: " + tn + " found";
+                F.qc[(size_t)i] = (int32_t)q;
+                F.tc[(size_t)i] = (int32_t)t;
+            }
+            if (msg.empty()) {
+                if (F.o.mode == PAFGPU_MODE_REMOVE && r.has_cigar) r.op_end = merge_matches(F.in.ops.data(), r.op_begin, r.op_end);
+                std::string why;
+                if (check_record(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, &why)) {
+                    // (the reference prints the record as it stands after encoding; this message shows its input CIGAR)
+                    std::string line;
+                    render_line(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, line);
+                    msg = "ERROR: " + why + " " + line;
+                }
+            }
+        }
+        if (!msg.empty()) {
+            stop = i;
+            F.err = msg;
+            F.rep.failed_record = i;
+            rc = 1;
+            break;
+        }
+    }
+    F.rep.s_host += now_s() - t0;
+
+    // ---- batches
+    int64_t a = 0;
+    while (a < stop) {
+        int64_t b = a, bases = 0, nops = 0;
+        if (F.o.mode == PAFGPU_MODE_REMOVE) {
+            b = std::min<int64_t>(stop, a + (1 << 20));
+        } else {
+            while (b < stop && (b == a || (bases < batch_bases && nops + (R[(size_t)b].op_end - R[(size_t)b].op_begin) < batch_ops))) {
+                for (int64_t k = R[(size_t)b].op_begin; k < R[(size_t)b].op_end; k++)
+                    if (op_code(F.in.ops[(size_t)k]) == OPM) bases += op_len(F.in.ops[(size_t)k]);
+                nops += R[(size_t)b].op_end - R[(size_t)b].op_begin;
+                b++;
+            }
+        }
+        int brc = 0;
+        if (F.o.mode == PAFGPU_MODE_REMOVE) {
+            t0 = now_s();
+            std::vector<std::string> part((size_t)F.threads);
+            parallel_for(b - a, F.threads, [&](int64_t i0, int64_t i1, int t) {
+                for (int64_t i = a + i0; i < a + i1; i++)
+                    render_line(R[(size_t)i], F.in.ops.data() + R[(size_t)i].op_begin, R[(size_t)i].op_end - R[(size_t)i].op_begin, part[(size_t)t]);
+            });
+            F.rep.s_host += now_s() - t0;
+            for (auto &s : part)
+                if (!write_all(F.out, s.data(), s.size())) brc = pafgpu_internal_fail(ctx, PAFGPU_EIO, "write failed");
+        } else {
+            t0 = now_s();
+            int64_t b2 = b;
+            brc = F.run_batch(a, b2);
+            F.rep.s_gpu += now_s() - t0;
+            if (brc == 1) {  // a record walks outside its contig: the records before it are still written
+                if (b2 > a) {
+                    const int frc = F.o.mode == PAFGPU_MODE_ADD ? F.finish_add(a, b2) : F.finish_trim(a, b2);
+                    if (frc < 0) brc = frc;
+                    if (frc == 1) { b2 = F.rep.failed_record; }
+                }
+                if (brc == 1 && F.rep.failed_record < 0) F.rep.failed_record = b2;
+                F.rep.records += std::max<int64_t>(0, (F.rep.failed_record >= 0 ? F.rep.failed_record : b2) - a);
+            } else if (brc == 0) {
+                brc = F.o.mode == PAFGPU_MODE_ADD ? F.finish_add(a, b) : F.finish_trim(a, b);
+                if (brc == 1) F.rep.records += F.rep.failed_record - a;
+            }
+        }
+        if (brc) { rc = brc; break; }
+        F.rep.records += b - a;
+        F.rep.batches++;
+        a = b;
+    }
+    if (out_path) fclose(F.out); else fflush(F.out);
+    if (rc == 1) {
+        fprintf(stderr, "%s\n", F.err.c_str());
+        pafgpu_internal_fail(ctx, 1, F.err.c_str());
+    }
+    if (report) *report = F.rep;
+    return rc;
+}
+
+}  // extern "C"
+
+// ================================================================================================
+// Drop-in subcommand entry point (impl/paf_add_mismatches.c:26-160).
+namespace {
+void add_mismatches_usage() {
+    fprintf(stderr, "paffy add_mismatches [fasta_file]xN [options], version 0.1 (paffy_b200: CUDA sm_100a path)\n");
+    fprintf(stderr, "Replace Ms with =/Xs in PAF cigar string\n");
+    fprintf(stderr, "-i --inputFile : Input paf file. If not specified reads from stdin\n");
+    fprintf(stderr, "-o --outputFile : Output paf file. If not specified outputs to stdout\n");
+    fprintf(stderr, "-a : Remove mismatches, removing X and = encoding and replacing with M\n");
+    fprintf(stderr, "-l --logLevel : Set the log level\n");
+    fprintf(stderr, "-h --help : Print this help message\n");
+}
+}  // namespace
+
+extern "C" int paffy_add_mismatches_main(int argc, char *argv[]) {
+    const char *input = nullptr, *output = nullptr, *log_level = nullptr;
+    bool remove = false;
+    static struct option long_options[] = {{"logLevel", required_argument, 0, 'l'},   {"inputFile", required_argument, 0, 'i'},
+                                           {"outputFile", required_argument, 0, 'o'}, {"removeMismatches", no_argument, 0, 'a'},
+                                           {"help", no_argument, 0, 'h'},             {0, 0, 0, 0}};
+    optind = 1;
+    for (;;) {
+        int idx = 0;
+        const int key = getopt_long(argc, argv, "l:i:o:ha", long_options, &idx);
+        if (key == -1) break;
+        switch (key) {
+            case 'l': log_level = optarg; break;
+            case 'i': input = optarg; break;
+            case 'o': output = optarg; break;
+            case 'a': remove = true; break;
+            case 'h': add_mismatches_usage(); return 0;
+            default: add_mismatches_usage(); return 1;
+        }
+    }
+    const bool verbose = log_level && (!strcasecmp(log_level, "INFO") || !strcasecmp(log_level, "DEBUG"));
+    const double t0 = now_s();
+    pafgpu_ctx *ctx = nullptr;
+    const char *dev = getenv("PAFFY_B200_DEVICE");
+    if (!remove && pafgpu_create(dev ? atoi(dev) : 0, &ctx)) {
+        fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(nullptr));
+        exit(1);
+    }
+    while (optind < argc) {
+        const char *fa = argv[optind++];
+        if (verbose) fprintf(stderr, "Parsing sequence file : %s\n", fa);
+        if (ctx && pafgpu_genome_load_fasta(ctx, fa)) {
+            fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
+            exit(1);
+        }
+    }
+    if (verbose && ctx) fprintf(stderr, "Read %i sequences from sequence files\n", (int)pafgpu_genome_num_contigs(ctx));
+    pafgpu_file_opts o{remove ? PAFGPU_MODE_REMOVE : PAFGPU_MODE_ADD, 0.05f, 1.0f, 0, 0};
+    pafgpu_file_report rep;
+    const int rc = pafgpu_add_mismatches_file(ctx, input, output, &o, &rep);
+    if (rc < 0) fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
+    pafgpu_destroy(ctx);
+    if (rc) exit(1);  // st_errAbort / exit(1) in the reference
+    if (verbose) fprintf(stderr, "Paffy add_mismatches is done!, %lld seconds have elapsed\n", (long long)(now_s() - t0));
+    return 0;
+}

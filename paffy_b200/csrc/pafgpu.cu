@@ -4,6 +4,7 @@
 #include "kernels.cuh"
 #include "encode.cuh"
 #include "serialise.cuh"
+#include "internal.h"
 
 #include <algorithm>
 #include <cctype>
@@ -96,6 +97,7 @@ struct pafgpu_ctx {
 
     // last batch
     bool have_batch = false;
+    int64_t bad_record = -1;
     int64_t n_records = 0, n_ops = 0, n_out = 0, n_tiles = 0, aligned = 0, retried = 0;
     uint64_t n_win = 0;
     EncodeParams last{};
@@ -279,6 +281,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     if (b->n_ops >= (1ll << 32) || b->n_records >= (1ll << 31)) return fail(c, PAFGPU_EINVAL, "batch too large: split it");
     if (int rc = genome_sync_table(c, g)) return rc;
     c->have_batch = false;
+    c->bad_record = -1;
     const int64_t R = b->n_records, N = b->n_ops;
     CU(c->scalars.ensure(SC_COUNT * 8));
     CU(c->tpos.ensure((size_t)std::max<int64_t>(N, 1) * 8));
@@ -313,6 +316,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
         char msg[160];
         snprintf(msg, sizeof msg, "record %llu: CIGAR/coordinates walk outside the contig (or unknown contig id)",
                  (unsigned long long)host_sc[SC_BAD]);
+        c->bad_record = (int64_t)host_sc[SC_BAD];
         return fail(c, PAFGPU_EBOUNDS, msg);
     }
     const uint64_t n_win = host_sc[SC_NWIN];
@@ -465,6 +469,15 @@ void pafgpu_destroy(pafgpu_ctx *c) {
 }
 
 const char *pafgpu_last_error(const pafgpu_ctx *c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+int64_t pafgpu_last_bad_record(const pafgpu_ctx *c) { return c ? c->bad_record : -1; }
+
+void *pafgpu_host_alloc(int64_t bytes) {
+    void *p = nullptr;
+    if (bytes <= 0 || cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void pafgpu_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 // ---- genome store ------------------------------------------------------------------------------
 int pafgpu_genome_reserve(pafgpu_ctx *c, int64_t total_bases) {
@@ -737,3 +750,5 @@ int pafgpu_fetch_text(pafgpu_ctx *c, char *text, int64_t *line_begin) {
 }
 
 }  // extern "C"
+
+int pafgpu_internal_fail(pafgpu_ctx *c, int code, const char *msg) { return fail(c, code, msg ? msg : ""); }

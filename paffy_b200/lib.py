@@ -20,7 +20,10 @@ ABI_SYMBOLS = [
     "pafgpu_genome_find", "pafgpu_genome_contig_length", "pafgpu_genome_num_contigs", "pafgpu_genome_fetch",
     "pafgpu_encode_batch_host", "pafgpu_encode_batch_device", "pafgpu_fetch_ops", "pafgpu_result_device_ptrs",
     "pafgpu_serialise", "pafgpu_fetch_text", "pafgpu_encode_one", "pafgpu_time_encode",
+    "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition",
 ]
+# reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
+REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
 
 
 class PafGpuError(RuntimeError):
@@ -33,6 +36,17 @@ class Batch(C.Structure):
     _fields_ = [("n_records", C.c_int64), ("n_ops", C.c_int64), ("op_begin", C.c_void_p), ("ops", C.c_void_p),
                 ("q_contig", C.c_void_p), ("t_contig", C.c_void_p), ("q_start", C.c_void_p), ("q_end", C.c_void_p),
                 ("t_start", C.c_void_p), ("same_strand", C.c_void_p)]
+
+
+class FileOpts(C.Structure):
+    _fields_ = [("mode", C.c_int), ("trim_score_fraction", C.c_float), ("trim_max_fraction", C.c_float), ("threads", C.c_int),
+                ("batch_bases", C.c_int64)]
+
+
+class FileReport(C.Structure):
+    _fields_ = [("records", C.c_int64), ("aligned_bases", C.c_int64), ("batches", C.c_int64), ("failed_record", C.c_int64),
+                ("stats", C.c_int64 * 7), ("s_read", C.c_double), ("s_parse", C.c_double), ("s_gpu", C.c_double),
+                ("s_host", C.c_double), ("s_write", C.c_double)]
 
 
 class Result(C.Structure):
@@ -81,8 +95,34 @@ def load():
     L.pafgpu_fetch_text.argtypes = [vp, vp, vp]
     L.pafgpu_encode_one.argtypes = [vp, vp, i64, C.c_int, i64, i64, i64, vp, vp, C.POINTER(vp), i64p, i64p]
     L.pafgpu_time_encode.argtypes = [vp, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    L.pafgpu_last_bad_record.argtypes = [vp]
+    L.pafgpu_last_bad_record.restype = i64
+    L.pafgpu_host_alloc.argtypes = [i64]
+    L.pafgpu_host_alloc.restype = vp
+    L.pafgpu_host_free.argtypes = [vp]
+    L.pafgpu_host_free.restype = None
+    L.pafgpu_add_mismatches_file.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(FileOpts), C.POINTER(FileReport)]
+    L.pafgpu_partition.argtypes = [vp, i64, C.c_int, vp]
     _lib = L
     return L
+
+
+def partition(weights, parts):
+    """Contiguous near-equal-weight cuts of input-ordered records (multi-GPU sharding, no device needed)."""
+    w = np.ascontiguousarray(weights, dtype=np.int64)
+    cuts = np.zeros(parts + 1, dtype=np.int64)
+    rc = load().pafgpu_partition(w.ctypes.data, w.size, parts, cuts.ctypes.data)
+    if rc:
+        raise PafGpuError(rc, "pafgpu_partition: bad arguments")
+    return cuts
+
+
+def remove_mismatches_file(in_path, out_path, threads=0):
+    """`paffy add_mismatches -a` (host-only text work: no CUDA device needed). -> (rc, FileReport)"""
+    o = FileOpts(1, 0.05, 1.0, threads, 0)
+    rep = FileReport()
+    rc = load().pafgpu_add_mismatches_file(None, in_path.encode(), out_path.encode(), C.byref(o), C.byref(rep))
+    return rc, rep
 
 
 def _ptr(a):
@@ -201,6 +241,19 @@ class Context:
         lines = np.empty(self.n_records + 1, dtype=np.int64)
         self._check(self.L.pafgpu_fetch_text(self.h, _ptr(buf), lines.ctypes.data))
         return buf, lines
+
+    def add_mismatches_file(self, in_path, out_path, mode=0, trim_r=0.05, trim_t=1.0, threads=0, batch_bases=0):
+        """The whole-file filter (paffy add_mismatches / -a / | trim). -> (rc, FileReport); rc 1 = a record ended the
+        run the way the reference exits 1 (message in self.last_error())."""
+        o = FileOpts(mode, trim_r, trim_t, threads, batch_bases)
+        rep = FileReport()
+        rc = self.L.pafgpu_add_mismatches_file(self.h, in_path.encode(), out_path.encode(), C.byref(o), C.byref(rep))
+        if rc < 0:
+            self._check(rc)
+        return rc, rep
+
+    def last_error(self):
+        return self.L.pafgpu_last_error(self.h).decode()
 
     def encode_one(self, ops, same_strand, q_start, q_end, t_start, query_seq, target_seq):
         """paf_encode_mismatches on one record with whole-contig host strings -> (uint64 ops, mismatches)."""

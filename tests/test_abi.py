@@ -29,9 +29,19 @@ def test_library_exports_every_declared_symbol():
     assert lib.pafgpu_abi_version() == 1
 
 
+def test_reference_named_entry_points_are_exported():
+    lib = paffy_b200.load()
+    for name in L.REFERENCE_SYMBOLS:
+        assert hasattr(lib, name), name
+    text = open(os.path.join(ROOT, "include", "paf_b200_compat.h")).read() + open(os.path.join(ROOT, "include", "paffy_b200.h")).read()
+    for name in L.REFERENCE_SYMBOLS:
+        assert re.search(r"\b" + name + r"\s*\(", text), f"{name} is not declared in include/"
+
+
 def test_result_struct_layout_matches_header():
     # 5 x int64 + 4 x float, padded to 8
     assert C.sizeof(L.Result) == 56 and C.sizeof(L.Batch) == 80
+    assert C.sizeof(L.FileOpts) == 24 and C.sizeof(L.FileReport) == 128
 
 
 def test_no_cpu_fallback():

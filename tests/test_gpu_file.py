@@ -1,0 +1,154 @@
+"""GPU parity of the host layer above the C ABI: PAF text in -> CUDA kernels -> PAF text out, byte-compared with the
+committed outputs of the unmodified reference CLI (tests/golden, written by tests/golden/make_golden.py)."""
+import ctypes as C
+import gzip
+import hashlib
+import json
+import os
+import subprocess
+
+import pytest
+
+import paffy_b200
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+SETS = ["edge", "rand101", "rand102", "rand103"]
+
+
+@pytest.fixture()
+def fresh():
+    c = paffy_b200.Context(0)
+    yield c
+    c.close()
+
+
+def golden(name):
+    return open(os.path.join(G, name), "rb").read()
+
+
+@pytest.mark.parametrize("stem", SETS)
+@pytest.mark.parametrize("batch_bases", [0, 3000])
+def test_add_mismatches_file_matches_reference(fresh, stem, batch_bases, tmp_path):
+    fresh.load_fasta(os.path.join(G, stem + ".fa"))
+    out = tmp_path / "out.paf"
+    rc, rep = fresh.add_mismatches_file(os.path.join(G, stem + ".paf"), str(out), batch_bases=batch_bases)
+    assert rc == 0
+    assert out.read_bytes() == golden(stem + ".add.paf")
+    assert util.view_summary(list(rep.stats)).encode() == golden(stem + ".view.txt")
+    if batch_bases:
+        assert rep.batches > 1
+
+
+@pytest.mark.parametrize("stem", SETS[1:])
+def test_add_then_trim_file_matches_reference(fresh, stem, tmp_path):
+    fresh.load_fasta(os.path.join(G, stem + ".fa"))
+    out = tmp_path / "out.paf"
+    rc, rep = fresh.add_mismatches_file(os.path.join(G, stem + ".paf"), str(out), mode=2)
+    assert rc == 0
+    assert out.read_bytes() == golden(stem + ".trim.paf")
+
+
+def test_error_paths_match_reference(fresh, tmp_path):
+    """Exit code 1, the records before the failing one written, the reference's message (tests/golden/errors.json)."""
+    errs = json.load(open(os.path.join(G, "errors.json")))
+    fresh.load_fasta(os.path.join(G, "edge.fa"))
+    for name, e in errs.items():
+        inp, out = tmp_path / f"{name}.paf", tmp_path / f"{name}.out"
+        inp.write_text("\n".join(e["input"]) + "\n")
+        rc, rep = fresh.add_mismatches_file(str(inp), str(out))
+        assert rc == 1 and e["exit"] == 1, name
+        assert out.read_text() == e["stdout"], name
+        assert rep.failed_record == 1
+        msg = fresh.last_error()
+        assert e["stderr_message"].split(" q\t")[0].replace("ERROR: ", "") in msg, (name, msg)
+
+
+def test_record_outside_contig_ends_run(fresh, tmp_path):
+    """Declared lengths larger than the FASTA: the reference reads past the string (UB); here the run ends at that
+    record with exit code 1 after the earlier records were written."""
+    fresh.load_fasta(os.path.join(G, "edge.fa"))
+    good = "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:25M"
+    bad = "q\t100\t50\t75\t+\tt\t100\t50\t75\t0\t25\t60\tcg:Z:25M"
+    inp, out = tmp_path / "in.paf", tmp_path / "out.paf"
+    inp.write_text("\n".join([good, good, bad, good]) + "\n")
+    rc, rep = fresh.add_mismatches_file(str(inp), str(out))
+    assert rc == 1 and rep.failed_record == 2
+    assert out.read_text().count("\n") == 2
+
+
+def test_c1_fixture_matches_reference(fresh, tmp_path):
+    """Config C1: the reference's own 207-record fixture over the seeded synthetic chr10 (124 949 228 aligned bp)."""
+    info = json.load(open(os.path.join(G, "c1.json")))
+    raw = gzip.open(os.path.join(G, "c1_human_chimp.paf.gz")).read()
+    inp, out = tmp_path / "c1.paf", tmp_path / "c1.out"
+    inp.write_bytes(raw)
+    fresh.add_contig("chr10", util.c1_genome())
+    rc, rep = fresh.add_mismatches_file(str(inp), str(out))
+    got = out.read_bytes()
+    assert rc == 0 and rep.aligned_bases == 124949228 and rep.records == 207
+    assert len(got) == info["add_bytes"] and hashlib.md5(got).hexdigest() == info["add_md5"]
+    assert util.view_summary(list(rep.stats)) == info["view_summary"]
+    rc, rep = fresh.add_mismatches_file(str(inp), str(out), mode=2)
+    got = out.read_bytes()
+    assert rc == 0 and len(got) == info["trim_bytes"] and hashlib.md5(got).hexdigest() == info["trim_md5"]
+
+
+def test_cli_drop_in(tmp_path):
+    """`paffy_b200_cli add_mismatches` takes the reference's arguments and prints the reference's bytes."""
+    exe = os.path.join(os.path.dirname(paffy_b200.lib.LIB_PATH), "paffy_b200_cli")
+    r = subprocess.run([exe, "add_mismatches", os.path.join(G, "rand101.fa"), "-i", os.path.join(G, "rand101.paf")], capture_output=True)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout == golden("rand101.add.paf")
+    out = tmp_path / "o.paf"
+    r = subprocess.run([exe, "add_mismatches", "-a", "-i", os.path.join(G, "rand101.add.paf"), "-o", str(out)], capture_output=True)
+    assert r.returncode == 0 and out.read_bytes() == golden("rand101.remove.paf")
+    r = subprocess.run([exe, "add_mismatches", os.path.join(G, "edge.fa"), "-i", "/dev/stdin"], capture_output=True,
+                       input=b"nope\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:25M\n")
+    assert r.returncode == 1 and b"No query sequence named: nope found" in r.stderr
+
+
+class Cigar(C.Structure):
+    _fields_ = [("recs", C.POINTER(C.c_uint64)), ("length", C.c_int64), ("start", C.c_int64), ("capacity", C.c_int64)]
+
+
+class Paf(C.Structure):
+    _fields_ = [("query_name", C.c_char_p), ("query_length", C.c_int64), ("query_start", C.c_int64), ("query_end", C.c_int64),
+                ("target_name", C.c_char_p), ("target_length", C.c_int64), ("target_start", C.c_int64), ("target_end", C.c_int64),
+                ("cigar", C.POINTER(Cigar)), ("cigar_string", C.c_char_p), ("score", C.c_int64), ("mapping_quality", C.c_int64),
+                ("num_matches", C.c_int64), ("num_bases", C.c_int64), ("tile_level", C.c_int64), ("chain_id", C.c_int64),
+                ("chain_score", C.c_int64), ("same_strand", C.c_bool), ("type", C.c_char)]
+
+
+def test_paf_encode_mismatches_symbol():
+    """The reference-named entry point on the reference's struct layout (inc/paf.h:61-109), incl. cigar->start and
+    ownership (recs replaced by a malloc'd array)."""
+    assert C.sizeof(Paf) == 144 and C.sizeof(Cigar) == 32
+    lib = paffy_b200.load()
+    libc = C.CDLL(None)
+    libc.malloc.restype = C.c_void_p
+    libc.malloc.argtypes = [C.c_size_t]
+    q, t = b"ACGTNnacgtMRWSYKVHDBXACGT", b"ACGTNNACGTKYWSRMBDHVXACGA"
+    ops = util.words([(7, "I"), (25, "M")])  # start = 1 skips the first op, like a prefix-trimmed cigar
+    mem = libc.malloc(16)
+    C.memmove(mem, ops.ctypes.data, 16)
+    cg = Cigar(C.cast(mem, C.POINTER(C.c_uint64)), 1, 1, 2)
+    p = Paf(b"q", 25, 0, 25, b"t", 25, 0, 25, C.pointer(cg), None, 0, 60, 0, 0, -1, -1, -1, True, b"P")
+    lib.paf_encode_mismatches.argtypes = [C.POINTER(Paf), C.c_char_p, C.c_char_p]
+    lib.paf_encode_mismatches.restype = None
+    lib.paf_encode_mismatches(C.byref(p), q, t)
+    got = util.pairs_of([cg.recs[i] for i in range(cg.length)])
+    from oracle import pyoracle as O
+    assert cg.start == 0 and O.cigar_str(got) == "10=2X2=6X4=1X"
+    p.same_strand = False
+    C.memmove(mem := libc.malloc(8), util.words([(25, "M")]).ctypes.data, 8)
+    cg2 = Cigar(C.cast(mem, C.POINTER(C.c_uint64)), 1, 0, 1)
+    p.cigar = C.pointer(cg2)
+    lib.pafgpu_paf_encode_mismatches.argtypes = [C.POINTER(Paf), C.c_char_p, C.c_char_p]
+    lib.pafgpu_paf_encode_mismatches.restype = C.c_int64
+    mm = lib.pafgpu_paf_encode_mismatches(C.byref(p), q, t)
+    want = O.encode([(25, "M")], False, 0, 25, 0, q, t)
+    assert util.pairs_of([cg2.recs[i] for i in range(cg2.length)]) == want
+    assert mm == sum(n for n, c in want if c == "X")

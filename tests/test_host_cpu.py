@@ -1,0 +1,70 @@
+"""CPU-only checks of the host logic that needs no base comparison: `add_mismatches -a` (text in, merged M ops out,
+byte-compared with the reference CLI's committed output), record partitioning for multi-GPU sharding (single process
+and world_size-2 gloo)."""
+import os
+
+import numpy as np
+import pytest
+
+import paffy_b200
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.mark.parametrize("stem", ["edge", "rand101", "rand102", "rand103"])
+def test_remove_mismatches_file_matches_reference(stem, tmp_path):
+    out = tmp_path / "o.paf"
+    rc, rep = paffy_b200.remove_mismatches_file(os.path.join(G, stem + ".add.paf"), str(out))
+    assert rc == 0
+    assert out.read_bytes() == open(os.path.join(G, stem + ".remove.paf"), "rb").read()
+
+
+def test_remove_mismatches_bad_record_ends_run(tmp_path):
+    good = "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:10=2X13="
+    bad = "q\t25\t0\t10\t+\tt\t25\t0\t9\t0\t0\t60\tcg:Z:9="
+    inp, out = tmp_path / "i.paf", tmp_path / "o.paf"
+    inp.write_text("\n".join([good, bad, good]) + "\n")
+    rc, rep = paffy_b200.remove_mismatches_file(str(inp), str(out))
+    assert rc == 1 and rep.failed_record == 1
+    assert out.read_text() == "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tAS:i:0\tcg:Z:25M\n"
+
+
+def test_partition_properties():
+    rng = np.random.default_rng(3)
+    for parts in (1, 2, 3, 8):
+        w = rng.integers(1, 5_000_000, 5000)
+        cuts = paffy_b200.partition(w, parts)
+        assert cuts[0] == 0 and cuts[-1] == len(w) and (np.diff(cuts) >= 0).all()
+        loads = np.add.reduceat(w, cuts[:-1])[: parts] if parts > 1 else np.array([w.sum()])
+        assert abs(loads - w.sum() / parts).max() <= w.max()  # imbalance bounded by one record
+    assert list(paffy_b200.partition([], 3)) == [0, 0, 0, 0]
+    assert list(paffy_b200.partition([7], 4)) in ([0, 0, 0, 0, 1], [0, 0, 0, 1, 1], [0, 0, 1, 1, 1], [0, 1, 1, 1, 1])
+
+
+def _rank_main(rank, world, port, q):
+    import torch.distributed as dist
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    from paffy_b200 import shard
+    rng = np.random.default_rng(11)
+    weights = rng.integers(100, 100000, 1000)
+    lo, hi = shard.my_range(weights, rank, world)
+    mine = np.arange(lo, hi, dtype=np.int64)
+    gathered = shard.gather_in_order(mine.tobytes(), rank, world)
+    if rank == 0:
+        q.put((np.frombuffer(gathered, dtype=np.int64).tolist() == list(range(1000)), int(weights[lo:hi].sum()), int(weights.sum())))
+    dist.destroy_process_group()
+
+
+def test_sharding_world_size_2_gloo():
+    """Two ranks take contiguous base-balanced ranges; rank 0 gathers the outputs in input order (no data-path
+    collective: a gather of finished bytes only)."""
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_rank_main, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in ps]
+    ok, mine, total = q.get(timeout=120)
+    [p.join(60) for p in ps]
+    assert ok and abs(mine - total / 2) < 100000
