@@ -259,15 +259,15 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
                     }
                 }
             }
-            // bases beyond the op's end do not exist: they are tallied as matches and then take the value of the
-            // op's last base, so that no run appears to start behind the end (the next window starts another op)
-            const uint32_t v0 = n >= 32 ? 0xffffffffu : (1u << n) - 1u;
-            const uint32_t v1 = n > 32 ? 0xffffffffu >> (64 - n) : 0u;
-            m0 &= v0;
-            m1 &= v1;
-            const uint32_t mm_count = __popc(m0) + __popc(m1);
-            const bool last_set = n > 32 ? (m1 >> (n - 33)) & 1u : n ? (m0 >> (n - 1)) & 1u : false;
-            if (last_set) { m0 |= ~v0; m1 |= ~v1; }
+            // bases beyond the op's end do not exist: shifting them out leaves the op's last base on top, the tally
+            // counts what is left, and the arithmetic shift back copies that last base over the tail, so that no run
+            // appears to start behind the end (the next window starts another op)
+            const unsigned sh = isM ? WIN_BASES - n : 0u;
+            const uint64_t up = (isM ? ((uint64_t)m1 << 32) | m0 : 0ull) << sh;
+            const uint32_t mm_count = __popcll(up);
+            const uint64_t mx = (uint64_t)((int64_t)up >> sh);
+            m0 = (uint32_t)mx;
+            m1 = (uint32_t)(mx >> 32);
             S.mask[srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
             // per-record mismatch tally, flushed when the lane moves to another record
             if (isM) {

@@ -233,63 +233,71 @@ struct IngestParams {
     uint32_t *op_rec, *nwin;
     unsigned long long *bad_record;  // min index of a record that fails validation (init ~0)
     unsigned long long *aligned;     // sum of M lengths
+    int has_exceptions;              // 0: the genome holds only ACGT, no op can touch the exception plane
 };
 
+// G lanes per record (8, 16 or 32, chosen by the host from the mean ops per record) so that short CIGARs do not leave
+// most of a warp idle; every lane stays in the loop until the longest record of the warp is done (the scans shuffle).
+template <int G>
 __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
-    const unsigned lane = threadIdx.x & 31;
-    const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (r >= P.n_records) return;
-    const int64_t j0 = P.op_begin[r], j1 = P.op_begin[r + 1];
-    const int64_t qc = P.q_contig[r], tc = P.t_contig[r];
-    const bool rev = P.same_strand[r] == 0;
-    const int64_t qs = P.q_start[r], qe = P.q_end[r], ts = P.t_start[r];
-    bool ok = qc >= 0 && qc < P.n_contigs && tc >= 0 && tc < P.n_contigs && j1 > j0 && qs >= 0 && ts >= 0 && qs <= qe;
+    __shared__ unsigned long long block_aligned;
+    if (threadIdx.x == 0) block_aligned = 0;
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31, gl = lane & (G - 1);
+    const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
+    const bool live = r < P.n_records;
+    int64_t j0 = 0, j1 = 0, qc = -1, tc = -1, qs = 0, qe = 0, ts = 0;
+    bool rev = false;
+    if (live) {
+        j0 = P.op_begin[r]; j1 = P.op_begin[r + 1];
+        qc = P.q_contig[r]; tc = P.t_contig[r];
+        rev = P.same_strand[r] == 0;
+        qs = P.q_start[r]; qe = P.q_end[r]; ts = P.t_start[r];
+    }
+    bool ok = live && qc >= 0 && qc < P.n_contigs && tc >= 0 && tc < P.n_contigs && j1 > j0 && qs >= 0 && ts >= 0 && qs <= qe;
     int64_t q_len = 0, t_len = 0, q_off = 0, t_off = 0;
     if (ok) {
         q_len = P.contig_len[qc]; t_len = P.contig_len[tc];
         q_off = P.contig_off[qc]; t_off = P.contig_off[tc];
         ok = qe <= q_len && ts <= t_len;
     }
-    if (!ok) {
-        if (lane == 0) atomicMin(P.bad_record, (unsigned long long)r);
-        // still give every op a harmless window so downstream kernels stay in bounds
-        for (int64_t j = j0 + lane; j < j1; j += 32) {
-            P.tpos[j] = (j == j0 ? TFLAG_HEAD : 0) | (uint64_t)ARENA_ALIGN / 2;
-            P.qpos[j] = (uint64_t)ARENA_ALIGN / 2;
-            P.op_rec[j] = (uint32_t)r | (j == j0 ? 0x80000000u : 0u);
-            P.nwin[j] = 1;
-        }
-        return;
-    }
     const uint64_t t_base = (uint64_t)(t_off + ts);
     const uint64_t q_base = (uint64_t)(rev ? q_off + qe - 1 : q_off + qs);
     uint64_t t_used = 0, q_used = 0, m_sum = 0;
     bool overflow = false;
-    for (int64_t base = j0; base < j1; base += 32) {
-        const int64_t j = base + lane;
+    for (int64_t base = j0; __any_sync(FULL, base < j1); base += G) {
+        const int64_t j = base + gl;
         const bool have = j < j1;
         const uint64_t w = have ? P.ops[j] : 0;
         const int code = (int)(w >> 56);
         const uint64_t len = w & LEN_MASK;
         if (have && ((len >> 47) || (code == OP_M && len == 0))) overflow = true;  // negative / absurd length, or a 0M (callers drop those)
         const uint64_t tl = (have && code != OP_I) ? len : 0, ql = (have && code != OP_D) ? len : 0;
-        const uint64_t t_inc = warp_incl_scan(tl, lane), q_inc = warp_incl_scan(ql, lane);
+        uint64_t t_inc = tl, q_inc = ql;
+#pragma unroll
+        for (int o = 1; o < G; o <<= 1) {
+            const uint64_t a = __shfl_up_sync(FULL, t_inc, o, G), b = __shfl_up_sync(FULL, q_inc, o, G);
+            if (gl >= (unsigned)o) { t_inc += a; q_inc += b; }
+        }
         if (have) {
-            const uint64_t tp = t_base + t_used + (t_inc - tl);
-            const uint64_t qd = q_used + (q_inc - ql);
-            const uint64_t qp = rev ? q_base - qd : q_base + qd;
-            uint64_t qflags = rev ? QFLAG_REV : 0;
+            uint64_t tp = (uint64_t)ARENA_ALIGN / 2, qp = (uint64_t)ARENA_ALIGN / 2, qflags = 0;
             uint32_t nw = 1;
-            if (code == OP_M) {
-                nw = (uint32_t)((len + 63) >> 6);
-                m_sum += len;
-                // bounds of this op decide whether its spans may be dereferenced at all
-                const bool inside = (ts + (int64_t)(t_used + t_inc) <= t_len) &&
-                                    (rev ? (qe - (int64_t)(qd + len) >= 0) : (qs + (int64_t)(qd + len) <= q_len));
-                if (len > 0 && inside && !overflow) {
-                    const uint64_t qlo = rev ? qp - (len - 1) : qp;
-                    if (span_has_exception(P.G, tp, tp + len - 1) || span_has_exception(P.G, qlo, qlo + len - 1))
-                        qflags |= QFLAG_EXC;
+            if (ok) {  // a record that fails validation still gets one harmless window per op so downstream kernels stay in bounds
+                tp = t_base + t_used + (t_inc - tl);
+                const uint64_t qd = q_used + (q_inc - ql);
+                qp = rev ? q_base - qd : q_base + qd;
+                qflags = rev ? QFLAG_REV : 0;
+                if (code == OP_M) {
+                    nw = (uint32_t)((len + 63) >> 6);
+                    m_sum += len;
+                    // bounds of this op decide whether its spans may be dereferenced at all
+                    const bool inside = (ts + (int64_t)(t_used + t_inc) <= t_len) &&
+                                        (rev ? (qe - (int64_t)(qd + len) >= 0) : (qs + (int64_t)(qd + len) <= q_len));
+                    if (P.has_exceptions && len > 0 && inside && !overflow) {
+                        const uint64_t qlo = rev ? qp - (len - 1) : qp;
+                        if (span_has_exception(P.G, tp, tp + len - 1) || span_has_exception(P.G, qlo, qlo + len - 1))
+                            qflags |= QFLAG_EXC;
+                    }
                 }
             }
             P.tpos[j] = (tp & POS_MASK) | (j == j0 ? TFLAG_HEAD : 0);
@@ -297,17 +305,20 @@ __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
             P.op_rec[j] = (uint32_t)r | (j == j0 ? 0x80000000u : 0u);  // top bit: first op of the record
             P.nwin[j] = nw;
         }
-        t_used += __shfl_sync(FULL, t_inc, 31);
-        q_used += __shfl_sync(FULL, q_inc, 31);
+        t_used += __shfl_sync(FULL, t_inc, G - 1, G);
+        q_used += __shfl_sync(FULL, q_inc, G - 1, G);
     }
-    overflow = __any_sync(FULL, overflow);
     // memory safety: the walk must stay inside both contigs (the reference has UB here, a1-edge vii)
-    const bool inside = !overflow && ts + (int64_t)t_used <= t_len &&
-                        (rev ? qe - (int64_t)q_used >= 0 : qs + (int64_t)q_used <= q_len);
-    if (!inside && lane == 0) atomicMin(P.bad_record, (unsigned long long)r);
+    const unsigned group_mask = G == 32 ? FULL : ((1u << G) - 1u) << (lane & ~(unsigned)(G - 1));
+    overflow = (__ballot_sync(FULL, overflow) & group_mask) != 0;
+    const bool inside = ok && !overflow && ts + (int64_t)t_used <= t_len && (rev ? qe - (int64_t)q_used >= 0 : qs + (int64_t)q_used <= q_len);
+    if (live && !inside && gl == 0) atomicMin(P.bad_record, (unsigned long long)r);
+    if (!inside) m_sum = 0;
 #pragma unroll
     for (int o = 16; o; o >>= 1) m_sum += __shfl_xor_sync(FULL, m_sum, o);
-    if (lane == 0 && m_sum) atomicAdd(P.aligned, (unsigned long long)m_sum);
+    if (lane == 0 && m_sum) atomicAdd(&block_aligned, (unsigned long long)m_sum);
+    __syncthreads();
+    if (threadIdx.x == 0 && block_aligned) atomicAdd(P.aligned, block_aligned);  // one global atomic per block, not per record
 }
 
 // first op of each warp tile: op j owns windows [woff[j], woff[j+1])

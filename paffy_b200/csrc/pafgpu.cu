@@ -303,11 +303,17 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     I.q_start = b->q_start; I.q_end = b->q_end; I.t_start = b->t_start; I.same_strand = b->same_strand;
     I.contig_off = g.d_off.as<int64_t>(); I.contig_len = g.d_len.as<int64_t>(); I.n_contigs = (int64_t)g.off.size();
     I.G = g.view();
+    I.has_exceptions = g.exc_total > 0;
     I.tpos = c->tpos.as<uint64_t>(); I.qpos = c->qpos.as<uint64_t>();
     I.op_rec = c->op_rec.as<uint32_t>(); I.nwin = c->nwin.as<uint32_t>();
     I.bad_record = (unsigned long long *)(sc + SC_BAD);
     I.aligned = (unsigned long long *)(sc + SC_ALIGNED);
-    if (R > 0) ingest_kernel<<<blocks_for(R * 32, 256), 256, 0, c->stream>>>(I);
+    if (R > 0) {
+        const int64_t mean_ops = N / R;
+        if (mean_ops <= 10) ingest_kernel<8><<<blocks_for(R * 8, 256), 256, 0, c->stream>>>(I);
+        else if (mean_ops <= 24) ingest_kernel<16><<<blocks_for(R * 16, 256), 256, 0, c->stream>>>(I);
+        else ingest_kernel<32><<<blocks_for(R * 32, 256), 256, 0, c->stream>>>(I);
+    }
     if (int rc = scan_u32(c, c->nwin.as<uint32_t>(), N, c->woff.as<uint64_t>(), sc + SC_NWIN)) return rc;
     uint64_t host_sc[SC_COUNT];
     CU(cudaMemcpyAsync(host_sc, sc, sizeof host_sc, cudaMemcpyDeviceToHost, c->stream));
