@@ -9,8 +9,8 @@
 //                   shared memory (word index + bit phase of target and query, bases left, flags) plus a
 //                   bitmap of the windows at which an op starts, so a window finds its op with a popcount.
 //   B  compare      striped (window = 32 * iteration + lane, coalesced): every lane issues the 6 x 64-bit
-//                   loads of several windows at once, funnel-shifts the bit planes into phase, BREV + NOT
-//                   the query on '-' strands, one LOP3 per plane -> one mismatch bit per base. The 64-bit
+//                   loads of several windows at once, funnel-shifts the bit planes into phase ('-' strand
+//                   queries are read from the reverse-complement copy of the contig), one LOP3 per plane -> one mismatch bit per base. The 64-bit
 //                   mask of every window goes to shared memory; mismatches are tallied per record.
 //   C  count        blocked (lane owns 8 consecutive windows): run starts per lane, warp scan.
 //   D  look-back    the CTA publishes its number of output ops and obtains the number before it with a
@@ -55,11 +55,8 @@ constexpr uint32_t COORD_OPEN = 0xffffffffu;
 constexpr unsigned long long ST_AGG = 1ull << 62, ST_INCL = 2ull << 62, ST_VAL = (1ull << 62) - 1;
 
 // mismatch bit of one aligned base of an op, through the byte plane (slow, exact)
-__device__ __forceinline__ unsigned slow_mismatch(const Genome &G, uint64_t tp, uint64_t qp, bool rev) {
-    const uint8_t t = byte_at(G, tp);
-    uint8_t q = byte_at(G, qp);
-    if (rev) q = complement_upper(q);
-    return t != q;
+__device__ __forceinline__ unsigned slow_mismatch(const Genome &G, uint64_t tp, uint64_t qp) {
+    return byte_at(G, tp) != byte_at(G, qp);  // '-' strand queries live reverse-complemented in the arena
 }
 
 // per-op table entry (16 bytes, read with one LDS.128)
@@ -70,7 +67,7 @@ struct __align__(16) OpEntry {
     int32_t tw, qw, rem;
     uint32_t misc;   // bits 0-4 target phase, 5-9 query phase, then EF_* flags and ES_* fields
 };
-constexpr uint32_t EF_PASS = 1u << 11, EF_REV = 1u << 12, EF_EXC = 1u << 13;
+constexpr uint32_t EF_PASS = 1u << 11, EF_EXC = 1u << 13;
 // ops that start inside the tile: bits 14-21 the tile window they start at, 22-27 bases between the previous M op's
 // end and that window boundary (64 - bases in its last window), 28 first op of its record
 constexpr int ES_WIN = 14, ES_GAP = 22;
@@ -124,16 +121,14 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
                 en.tw = (int32_t)(uint32_t)opw; en.qw = (int32_t)(uint32_t)(opw >> 32);
             } else {
                 const int64_t back = WIN_BASES * (int64_t)(s0 - wo);  // op bases before tile window 0 (negative: op starts inside)
-                const bool rev = (qpw & QFLAG_REV) != 0;
                 const int64_t tb = (int64_t)(tpw & POS_MASK) + back;
-                // lowest query base of tile window 0's span: '+' walks up from it, '-' starts 63 below the top base
-                const int64_t qb = rev ? (int64_t)(qpw & POS_MASK) - back - (WIN_BASES - 1) : (int64_t)(qpw & POS_MASK) + back;
+                const int64_t qb = (int64_t)(qpw & POS_MASK) + back;
                 int64_t rem = (int64_t)(opw & LEN_MASK) - back;
                 if (rem > REM_CLAMP) rem = REM_CLAMP;
                 en.tw = (int32_t)(tb >> 5);
                 en.qw = (int32_t)(qb >> 5);
                 en.rem = (int32_t)rem;
-                en.misc = (uint32_t)(tb & 31) | ((uint32_t)(qb & 31) << 5) | (rev ? EF_REV : 0u) | ((qpw & QFLAG_EXC) ? EF_EXC : 0u);
+                en.misc = (uint32_t)(tb & 31) | ((uint32_t)(qb & 31) << 5) | ((qpw & QFLAG_EXC) ? EF_EXC : 0u);
                 exc |= (qpw & QFLAG_EXC) != 0;
                 my_end = (uint32_t)rem;
             }
@@ -193,31 +188,28 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             IDX[b] = idx;
             const OpEntry en = S.tab[idx];
             const bool isM = srel < n_act && !(en.misc & EF_PASS);
-            const bool rev = (en.misc & EF_REV) != 0;
             const int32_t tw = isM ? en.tw + 2 * (int32_t)srel : 0;
-            const int32_t qw = isM ? (rev ? en.qw - 2 * (int32_t)srel : en.qw + 2 * (int32_t)srel) : 0;
+            const int32_t qw = isM ? en.qw + 2 * (int32_t)srel : 0;
             const uint64_t *tpn = gw + tw, *qpn = gw + qw;
             T0[b] = ldg64(tpn); T1[b] = ldg64(tpn + 1); T2[b] = ldg64(tpn + 2);
             Q0[b] = ldg64(qpn); Q1[b] = ldg64(qpn + 1); Q2[b] = ldg64(qpn + 2);
             if (it == 0 && lane == 0 && isM && !(w & 1u)) {
                 // tile window 0 continues an op: mismatch state of the base just before the tile
                 const uint64_t tp = ((uint64_t)(uint32_t)tw << 5) + (en.misc & 31u);
-                const uint64_t qtop = ((uint64_t)(uint32_t)qw << 5) + ((en.misc >> 5) & 31u) + (rev ? WIN_BASES - 1 : 0);
-                const uint64_t qprev = rev ? qtop + 1 : qtop - 1;
+                const uint64_t qprev = ((uint64_t)(uint32_t)qw << 5) + ((en.misc >> 5) & 31u) - 1;
                 if (EXC && (en.misc & EF_EXC)) {
-                    pm0 = slow_mismatch(P.G, tp - 1, qprev, rev) ? 0x80000000u : 0u;
+                    pm0 = slow_mismatch(P.G, tp - 1, qprev) ? 0x80000000u : 0u;
                 } else {
                     pm_t = ldg64(gw + ((tp - 1) >> 5));
                     pm_q = ldg64(gw + (qprev >> 5));
-                    pm_k = (uint32_t)((tp - 1) & 31) | ((uint32_t)(qprev & 31) << 5) | (rev ? 1u << 10 : 0u) | (1u << 11);
+                    pm_k = (uint32_t)((tp - 1) & 31) | ((uint32_t)(qprev & 31) << 5) | (1u << 11);
                 }
             }
         }
         if (hb == 0 && (pm_k >> 11)) {  // lane 0 only; consumed after the batch's loads were issued
             const unsigned kt = pm_k & 31u, kq = (pm_k >> 5) & 31u;
             const unsigned tc = ((unsigned)(pm_t >> kt) & 1u) | (((unsigned)(pm_t >> (32 + kt)) & 1u) << 1);
-            unsigned qc = ((unsigned)(pm_q >> kq) & 1u) | (((unsigned)(pm_q >> (32 + kq)) & 1u) << 1);
-            if (pm_k & (1u << 10)) qc ^= 3u;
+            const unsigned qc = ((unsigned)(pm_q >> kq) & 1u) | (((unsigned)(pm_q >> (32 + kq)) & 1u) << 1);
             pm0 = tc != qc ? 0x80000000u : 0u;
         }
         // mismatch bits
@@ -228,7 +220,6 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const uint32_t idx = IDX[b];
             const OpEntry en = S.tab[idx];
             const bool isM = srel < n_act && !(en.misc & EF_PASS);
-            const bool rev = (en.misc & EF_REV) != 0;
             const int32_t rem = en.rem - WIN_BASES * (int32_t)srel;
             const uint32_t n = !isM ? 0u : rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
             const uint32_t misc = en.misc;
@@ -237,24 +228,19 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const uint32_t tl1 = __funnelshift_r((uint32_t)T1[b], (uint32_t)T2[b], sht);
             const uint32_t th0 = __funnelshift_r((uint32_t)(T0[b] >> 32), (uint32_t)(T1[b] >> 32), sht);
             const uint32_t th1 = __funnelshift_r((uint32_t)(T1[b] >> 32), (uint32_t)(T2[b] >> 32), sht);
-            uint32_t ql0 = __funnelshift_r((uint32_t)Q0[b], (uint32_t)Q1[b], shq);
-            uint32_t ql1 = __funnelshift_r((uint32_t)Q1[b], (uint32_t)Q2[b], shq);
-            uint32_t qh0 = __funnelshift_r((uint32_t)(Q0[b] >> 32), (uint32_t)(Q1[b] >> 32), shq);
-            uint32_t qh1 = __funnelshift_r((uint32_t)(Q1[b] >> 32), (uint32_t)(Q2[b] >> 32), shq);
-            if (rev) {  // reverse the 64 bases (swap + BREV) and complement (NOT of both planes)
-                const uint32_t a = ~__brev(ql1), c = ~__brev(ql0), d = ~__brev(qh1), e = ~__brev(qh0);
-                ql0 = a; ql1 = c; qh0 = d; qh1 = e;
-            }
+            const uint32_t ql0 = __funnelshift_r((uint32_t)Q0[b], (uint32_t)Q1[b], shq);
+            const uint32_t ql1 = __funnelshift_r((uint32_t)Q1[b], (uint32_t)Q2[b], shq);
+            const uint32_t qh0 = __funnelshift_r((uint32_t)(Q0[b] >> 32), (uint32_t)(Q1[b] >> 32), shq);
+            const uint32_t qh1 = __funnelshift_r((uint32_t)(Q1[b] >> 32), (uint32_t)(Q2[b] >> 32), shq);
             uint32_t m0 = (tl0 ^ ql0) | (th0 ^ qh0);
             uint32_t m1 = (tl1 ^ ql1) | (th1 ^ qh1);
             if (EXC && isM && (misc & EF_EXC)) {
                 const uint64_t tp = ((uint64_t)(uint32_t)(en.tw + 2 * (int32_t)srel) << 5) + sht;
-                const uint64_t qlo = ((uint64_t)(uint32_t)(rev ? en.qw - 2 * (int32_t)srel : en.qw + 2 * (int32_t)srel) << 5) + shq;
-                const uint64_t ql = qlo + (rev ? WIN_BASES - n : 0u);
-                if (span_has_exception(P.G, tp, tp + n - 1) || span_has_exception(P.G, ql, ql + n - 1)) {
+                const uint64_t qlo = ((uint64_t)(uint32_t)(en.qw + 2 * (int32_t)srel) << 5) + shq;
+                if (span_has_exception(P.G, tp, tp + n - 1) || span_has_exception(P.G, qlo, qlo + n - 1)) {
                     m0 = m1 = 0;
                     for (uint32_t k = 0; k < n; k++) {
-                        const unsigned mm = slow_mismatch(P.G, tp + k, rev ? qlo + (WIN_BASES - 1) - k : qlo + k, rev);
+                        const unsigned mm = slow_mismatch(P.G, tp + k, qlo + k);
                         if (k < 32) m0 |= mm << k; else m1 |= mm << (k - 32);
                     }
                 }

@@ -11,7 +11,6 @@ namespace pafgpu {
 
 constexpr uint64_t LEN_MASK = (1ull << 56) - 1;
 constexpr uint64_t POS_MASK = (1ull << 48) - 1;
-constexpr uint64_t QFLAG_REV = 1ull << 63;   // qpos: '-' strand, query walks downwards
 constexpr uint64_t QFLAG_EXC = 1ull << 62;   // qpos: the op's target or query span touches a non-ACGT word
 constexpr uint64_t TFLAG_HEAD = 1ull << 63;  // tpos: first op of a record
 constexpr uint64_t EVEN_BITS = 0x5555555555555555ull;
@@ -69,28 +68,35 @@ __device__ __forceinline__ uint8_t complement_upper(uint8_t c) {
 }
 __device__ __forceinline__ uint8_t upper(uint8_t c) { return (c >= 'a' && c <= 'z') ? c - 32 : c; }
 
-// ---- pack: ASCII -> 2-bit words + flag bits. One thread per word, one warp per flag word. --------
+// ---- pack: ASCII -> 2-bit words + flag bits. One thread per word, one warp per flag word. ------------
+// rc = true packs the reverse complement of the contig (base i = complement of source base len-1-i), so that '-'
+// strand alignments read the query ascending like '+' ones: no reversal or complement is left in the hot kernel.
+__device__ __forceinline__ uint8_t source_byte(const uint8_t *__restrict__ src, int64_t len, int64_t i, bool rc) {
+    if (i >= len) return (uint8_t)'A';
+    const uint8_t u = upper(__ldg(src + (rc ? len - 1 - i : i)));
+    return rc ? complement_upper(u) : u;
+}
 __global__ void pack_kernel(const uint8_t *__restrict__ src, int64_t len, uint64_t word0, uint64_t *words,
-                            uint32_t *flags, int64_t n_words /* multiple of 32 */) {
+                            uint32_t *flags, int64_t n_words /* multiple of 32 */, bool rc) {
     const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= n_words) return;
     const int64_t b0 = w * 32;
     uint64_t packed = 0;
     bool exc = false;
     uint8_t c[32];
-    if (b0 + 32 <= len && ((uintptr_t)(src + b0) & 15) == 0) {
+    if (!rc && b0 + 32 <= len && ((uintptr_t)(src + b0) & 15) == 0) {
         const uint4 a = __ldg(reinterpret_cast<const uint4 *>(src + b0));
         const uint4 b = __ldg(reinterpret_cast<const uint4 *>(src + b0) + 1);
         const uint32_t v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
 #pragma unroll
-        for (int k = 0; k < 32; k++) c[k] = (uint8_t)(v[k >> 2] >> ((k & 3) * 8));
+        for (int k = 0; k < 32; k++) c[k] = upper((uint8_t)(v[k >> 2] >> ((k & 3) * 8)));
     } else {
 #pragma unroll
-        for (int k = 0; k < 32; k++) c[k] = (b0 + k < len) ? __ldg(src + b0 + k) : (uint8_t)'A';
+        for (int k = 0; k < 32; k++) c[k] = source_byte(src, len, b0 + k, rc);
     }
 #pragma unroll
     for (int k = 0; k < 32; k++) {
-        const uint8_t u = upper(c[k]);
+        const uint8_t u = c[k];
         const bool acgt = (u == 'A') | (u == 'C') | (u == 'G') | (u == 'T');
         exc |= !acgt;
         const uint64_t code = acgt ? (uint64_t)(((u >> 1) ^ (u >> 2)) & 3u) : 0ull;
@@ -113,7 +119,7 @@ __global__ void rank_fill_kernel(const uint64_t *scanned, int64_t n, uint32_t ba
 }
 // store the 32 upper-cased bytes of every flagged word
 __global__ void exc_fill_kernel(const uint8_t *__restrict__ src, int64_t len, uint64_t word0, const uint32_t *flags,
-                                const uint32_t *rank, uint8_t *exc, int64_t n_words) {
+                                const uint32_t *rank, uint8_t *exc, int64_t n_words, bool rc) {
     const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= n_words) return;
     const uint64_t gw = word0 + w;
@@ -122,7 +128,7 @@ __global__ void exc_fill_kernel(const uint8_t *__restrict__ src, int64_t len, ui
     const uint64_t r = rank[gw >> 5] + __popc(f & ((1u << (gw & 31)) - 1u));
     for (int k = 0; k < 32; k++) {
         const int64_t b = w * 32 + k;
-        exc[r * 32 + k] = b < len ? upper(src[b]) : (uint8_t)'A';
+        exc[r * 32 + k] = source_byte(src, len, b, rc);
     }
 }
 // read back bases as the bytes the comparison sees (tests / pafgpu_genome_fetch)
@@ -226,7 +232,7 @@ struct IngestParams {
     const int32_t *q_contig, *t_contig;
     const int64_t *q_start, *q_end, *t_start;
     const uint8_t *same_strand;
-    const int64_t *contig_off, *contig_len;
+    const int64_t *contig_off, *contig_off_rc, *contig_len;  // forward copy, reverse-complement copy, length
     int64_t n_contigs;
     Genome G;
     uint64_t *tpos, *qpos;
@@ -258,11 +264,12 @@ __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
     int64_t q_len = 0, t_len = 0, q_off = 0, t_off = 0;
     if (ok) {
         q_len = P.contig_len[qc]; t_len = P.contig_len[tc];
-        q_off = P.contig_off[qc]; t_off = P.contig_off[tc];
+        q_off = rev ? P.contig_off_rc[qc] : P.contig_off[qc]; t_off = P.contig_off[tc];
         ok = qe <= q_len && ts <= t_len;
     }
     const uint64_t t_base = (uint64_t)(t_off + ts);
-    const uint64_t q_base = (uint64_t)(rev ? q_off + qe - 1 : q_off + qs);
+    // '-' strand: the query walks down from query_end - 1, i.e. up from q_len - query_end in the reverse-complement copy
+    const uint64_t q_base = (uint64_t)(rev ? q_off + (q_len - qe) : q_off + qs);
     uint64_t t_used = 0, q_used = 0, m_sum = 0;
     bool overflow = false;
     for (int64_t base = j0; __any_sync(FULL, base < j1); base += G) {
@@ -285,8 +292,7 @@ __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
             if (ok) {  // a record that fails validation still gets one harmless window per op so downstream kernels stay in bounds
                 tp = t_base + t_used + (t_inc - tl);
                 const uint64_t qd = q_used + (q_inc - ql);
-                qp = rev ? q_base - qd : q_base + qd;
-                qflags = rev ? QFLAG_REV : 0;
+                qp = q_base + qd;
                 if (code == OP_M) {
                     nw = (uint32_t)((len + 63) >> 6);
                     m_sum += len;
@@ -294,8 +300,7 @@ __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
                     const bool inside = (ts + (int64_t)(t_used + t_inc) <= t_len) &&
                                         (rev ? (qe - (int64_t)(qd + len) >= 0) : (qs + (int64_t)(qd + len) <= q_len));
                     if (P.has_exceptions && len > 0 && inside && !overflow) {
-                        const uint64_t qlo = rev ? qp - (len - 1) : qp;
-                        if (span_has_exception(P.G, tp, tp + len - 1) || span_has_exception(P.G, qlo, qlo + len - 1))
+                        if (span_has_exception(P.G, tp, tp + len - 1) || span_has_exception(P.G, qp, qp + len - 1))
                             qflags |= QFLAG_EXC;
                     }
                 }

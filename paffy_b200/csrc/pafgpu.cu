@@ -57,19 +57,19 @@ struct GenomeStore {
     int64_t next_off = ARENA_ALIGN;       // first free arena position (front pad of one block)
     uint32_t exc_total = 0;               // flagged words so far
     std::vector<std::string> names;
-    std::vector<int64_t> off, len;
+    std::vector<int64_t> off, off_rc, len;  // arena offset of the forward copy, of the reverse-complement copy, length
     std::unordered_map<std::string, int64_t> index;
-    DevBuf d_off, d_len;
+    DevBuf d_off, d_off_rc, d_len;
     bool table_dirty = true;
 
     Genome view() const { return Genome{words.as<uint64_t>(), flags.as<uint32_t>(), rank.as<uint32_t>(), exc.as<uint8_t>()}; }
     void reset() {
         next_off = ARENA_ALIGN;
         exc_total = 0;
-        names.clear(); off.clear(); len.clear(); index.clear();
+        names.clear(); off.clear(); off_rc.clear(); len.clear(); index.clear();
         table_dirty = true;
     }
-    void release() { words.release(); flags.release(); rank.release(); exc.release(); d_off.release(); d_len.release(); }
+    void release() { words.release(); flags.release(); rank.release(); exc.release(); d_off.release(); d_off_rc.release(); d_len.release(); }
 };
 
 }  // namespace
@@ -154,23 +154,19 @@ int genome_grow(pafgpu_ctx *c, GenomeStore &g, int64_t need_bases) {
     return 0;
 }
 
-// pack `len` ASCII bytes at device pointer src as a new contig
-int64_t genome_add_device(pafgpu_ctx *c, GenomeStore &g, const char *name, const uint8_t *src, int64_t len) {
-    if (len < 0 || !name) return fail(c, PAFGPU_EINVAL, "bad contig");
-    const int64_t off = g.next_off;
-    const int64_t span = align_up(len, ARENA_ALIGN) + ARENA_ALIGN;  // contig + trailing pad block
-    if (int rc = genome_grow(c, g, off + span + ARENA_ALIGN)) return rc;
+// pack one copy (forward or reverse complement) of `len` ASCII bytes at device pointer src at arena offset `off`
+int genome_pack_copy(pafgpu_ctx *c, GenomeStore &g, const uint8_t *src, int64_t len, int64_t off, int64_t span, bool rc) {
     const int64_t n_words = span / 32, n_groups = span / 1024;
     if (len > 0) {
         pack_kernel<<<blocks_for(n_words, 256), 256, 0, c->stream>>>(src, len, (uint64_t)off / 32, g.words.as<uint64_t>(),
-                                                                      g.flags.as<uint32_t>(), n_words);
+                                                                      g.flags.as<uint32_t>(), n_words, rc);
     }
     // rank directory for the new groups
     CU(c->nwin.ensure((size_t)n_groups * 4));
     CU(c->woff.ensure((size_t)(n_groups + 1) * 8));
     flag_popc_kernel<<<blocks_for(n_groups, 256), 256, 0, c->stream>>>(g.flags.as<uint32_t>() + off / 1024, n_groups,
                                                                         c->nwin.as<uint32_t>());
-    if (int rc = scan_u32(c, c->nwin.as<uint32_t>(), n_groups, c->woff.as<uint64_t>(), nullptr)) return rc;
+    if (int rc2 = scan_u32(c, c->nwin.as<uint32_t>(), n_groups, c->woff.as<uint64_t>(), nullptr)) return rc2;
     rank_fill_kernel<<<blocks_for(n_groups, 256), 256, 0, c->stream>>>(c->woff.as<uint64_t>(), n_groups, g.exc_total,
                                                                         g.rank.as<uint32_t>() + off / 1024);
     uint64_t n_exc = 0;
@@ -179,12 +175,12 @@ int64_t genome_add_device(pafgpu_ctx *c, GenomeStore &g, const char *name, const
     if (n_exc) {
         CU(g.exc.ensure((size_t)(g.exc_total + n_exc) * 32, (size_t)g.exc_total * 32));
         exc_fill_kernel<<<blocks_for(n_words, 256), 256, 0, c->stream>>>(src, len, (uint64_t)off / 32, g.flags.as<uint32_t>(),
-                                                                          g.rank.as<uint32_t>(), g.exc.as<uint8_t>(), n_words);
+                                                                          g.rank.as<uint32_t>(), g.exc.as<uint8_t>(), n_words, rc);
         g.exc_total += (uint32_t)n_exc;
     } else if (!g.exc.p) {
         CU(g.exc.ensure(32));
     }
-    // groups after this contig (up to capacity) must report the new running total
+    // groups after this copy (up to capacity) must report the new running total
     {
         const int64_t g0 = (off + span) / 1024, g1 = g.cap_bases / 1024 + 2;
         std::vector<uint32_t> fill((size_t)std::min<int64_t>(g1 - g0, 4), g.exc_total);
@@ -193,12 +189,24 @@ int64_t genome_add_device(pafgpu_ctx *c, GenomeStore &g, const char *name, const
         CU(cudaStreamSynchronize(c->stream));
     }
     CU(cudaGetLastError());
+    return 0;
+}
+
+// pack `len` ASCII bytes at device pointer src as a new contig: forward copy, then its reverse complement
+int64_t genome_add_device(pafgpu_ctx *c, GenomeStore &g, const char *name, const uint8_t *src, int64_t len) {
+    if (len < 0 || !name) return fail(c, PAFGPU_EINVAL, "bad contig");
+    const int64_t off = g.next_off;
+    const int64_t span = align_up(len, ARENA_ALIGN) + ARENA_ALIGN;  // contig + trailing pad block
+    if (int rc = genome_grow(c, g, off + 2 * span + ARENA_ALIGN)) return rc;
+    if (int rc = genome_pack_copy(c, g, src, len, off, span, false)) return rc;
+    if (int rc = genome_pack_copy(c, g, src, len, off + span, span, true)) return rc;
     const int64_t id = (int64_t)g.names.size();
     g.names.emplace_back(name);
     g.off.push_back(off);
+    g.off_rc.push_back(off + span);
     g.len.push_back(len);
     g.index[g.names.back()] = id;  // a repeated name points at the newest contig (sonLibHash.c:68-73)
-    g.next_off = off + span;
+    g.next_off = off + 2 * span;
     g.table_dirty = true;
     return id;
 }
@@ -214,8 +222,10 @@ int genome_sync_table(pafgpu_ctx *c, GenomeStore &g) {
     const size_t n = g.off.size();
     CU(g.d_off.ensure(std::max<size_t>(n, 1) * 8));
     CU(g.d_len.ensure(std::max<size_t>(n, 1) * 8));
+    CU(g.d_off_rc.ensure(std::max<size_t>(n, 1) * 8));
     if (n) {
         CU(cudaMemcpyAsync(g.d_off.p, g.off.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(g.d_off_rc.p, g.off_rc.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemcpyAsync(g.d_len.p, g.len.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
         CU(cudaStreamSynchronize(c->stream));
     }
@@ -301,7 +311,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     I.op_begin = b->op_begin; I.ops = b->ops;
     I.q_contig = b->q_contig; I.t_contig = b->t_contig;
     I.q_start = b->q_start; I.q_end = b->q_end; I.t_start = b->t_start; I.same_strand = b->same_strand;
-    I.contig_off = g.d_off.as<int64_t>(); I.contig_len = g.d_len.as<int64_t>(); I.n_contigs = (int64_t)g.off.size();
+    I.contig_off = g.d_off.as<int64_t>(); I.contig_off_rc = g.d_off_rc.as<int64_t>(); I.contig_len = g.d_len.as<int64_t>(); I.n_contigs = (int64_t)g.off.size();
     I.G = g.view();
     I.has_exceptions = g.exc_total > 0;
     I.tpos = c->tpos.as<uint64_t>(); I.qpos = c->qpos.as<uint64_t>();
@@ -490,7 +500,7 @@ int pafgpu_genome_reserve(pafgpu_ctx *c, int64_t total_bases) {
     if (!c) return PAFGPU_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
-    return genome_grow(c, c->genome, c->genome.next_off + total_bases + 2 * ARENA_ALIGN);
+    return genome_grow(c, c->genome, c->genome.next_off + 2 * total_bases + 4 * ARENA_ALIGN);  // forward + reverse-complement copies
 }
 
 int64_t pafgpu_genome_add_contig(pafgpu_ctx *c, const char *name, const char *seq, int64_t len) {
