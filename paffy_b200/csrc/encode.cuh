@@ -206,6 +206,28 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
                 }
             }
         }
+        if (hb == 0) {
+            // the first batch's loads are in flight: pull the sequence of every later window of the tile into L2 now, so
+            // that only this first batch waits for DRAM
+            uint32_t pre2 = pre;
+#pragma unroll
+            for (int it = BATCH; it < TILE_ITERS; it++) {
+                const uint32_t srel = 32u * it + lane;
+                const uint32_t w = S.bm[it];
+                const uint32_t idx = pre2 + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
+                pre2 += __popc(w);
+                if (srel < n_act) {
+                    const OpEntry en = S.tab[idx];
+                    if (!(en.misc & EF_PASS)) {
+                        const uint64_t *tpn = gw + (en.tw + 2 * (int32_t)srel), *qpn = gw + (en.qw + 2 * (int32_t)srel);
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(tpn));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(tpn + 2));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(qpn));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(qpn + 2));
+                    }
+                }
+            }
+        }
         if (hb == 0 && (pm_k >> 11)) {  // lane 0 only; consumed after the batch's loads were issued
             const unsigned kt = pm_k & 31u, kq = (pm_k >> 5) & 31u;
             const unsigned tc = ((unsigned)(pm_t >> kt) & 1u) | (((unsigned)(pm_t >> (32 + kt)) & 1u) << 1);

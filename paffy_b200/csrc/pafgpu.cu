@@ -234,7 +234,7 @@ int genome_sync_table(pafgpu_ctx *c, GenomeStore &g) {
 }
 
 #ifndef ENC_BATCH
-#define ENC_BATCH 4
+#define ENC_BATCH 2
 #endif
 constexpr int ENC_WARPS = 4, CMP_BATCH = ENC_BATCH;
 
