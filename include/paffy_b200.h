@@ -120,6 +120,15 @@ int pafgpu_serialise(pafgpu_ctx *ctx, const char *prefix_bytes, const int64_t *p
 /* Copy the serialised text (text_bytes_out bytes) and optionally per-record line offsets (n_records+1). */
 int pafgpu_fetch_text(pafgpu_ctx *ctx, char *text, int64_t *line_begin);
 
+/* ---- device trim: replaces paf_trim_unreliable_tails (inc/paf.h:269, impl/paf.c:906-953) for the whole batch, on the
+ *      encoded ops still resident on the device. score_fraction / max_fraction are `paffy trim -r / -t`. t_end: host
+ *      array of Paf.target_end per record. coords receives 4 * n_records values: query_start[], query_end[],
+ *      target_start[], target_end[] after trimming. kept_ops (optional): ops left per record. failed (optional):
+ *      1 where the reference's final assert (impl/paf.c:952) would fire. A following pafgpu_serialise prints only the
+ *      kept ops; pafgpu_fetch_ops still returns all of them. ------------------------------------------------------- */
+int pafgpu_trim(pafgpu_ctx *ctx, float score_fraction, float max_fraction, const int64_t *t_end, int64_t *coords,
+                int64_t *kept_ops, uint8_t *failed);
+
 /* ---- one-record convenience used by the paf.h-compatible paf_encode_mismatches
  *      (impl/paf.c:739-784): sequences are whole-contig host strings, indexed by absolute coordinate.
  *      Packs only the spans the record touches. out_ops is malloc'd (caller frees). ----------------- */

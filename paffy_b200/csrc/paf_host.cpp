@@ -5,7 +5,7 @@
 // look the contigs up, encode (on the GPU, as one batch), paf_check, write - with the reference's record
 // order, tag normalisation, failure ordering (records before a bad one are still written) and exit codes.
 // Parsing restates paf_parse / cigar_parse (impl/paf.c:70-111, 137-209) and printing restates
-// paf_write_to_buffer (impl/paf.c:317-389); the trim pass restates impl/paf.c:811-953. Nothing is copied.
+// paf_write_to_buffer (impl/paf.c:317-389); the trim pass (impl/paf.c:811-953) runs on the device (trim.cuh). Nothing is copied.
 // There is no CPU implementation of the base comparison here: every M op goes through the CUDA kernels.
 #include "../../include/paffy_b200.h"
 
@@ -187,89 +187,6 @@ int check_record(const Rec &r, const uint64_t *ops, int64_t n, std::string *msg)
         }
     }
     return 0;
-}
-
-// ---- trim (impl/paf.c:811-953). An alignment view: the record's coordinates plus a window [lo, hi) of its ops,
-// so dropping ops at either end is O(1) like the reference's cigar->start. -------------------------------------
-struct Aln {
-    Rec *r;
-    uint64_t *ops;
-    int64_t lo, hi;
-    bool flipped;  // inverted view: query/target swapped, I/D swapped, op order reversed on '-' strands
-};
-inline bool is_match_code(int c) { return c == OPM || c == OPEQ; }
-// identity as the reference computes it: float32 quotient of a float32-rounded numerator, widened to double
-inline double ident32(int64_t m, int64_t mm) { return (double)((float)m / (float)(m + mm)); }
-
-// k-th op of the view in walking order, with I/D swapped when flipped
-inline uint64_t view_op(const Aln &a, int64_t k) {
-    const bool backwards = a.flipped && !a.r->same_strand;
-    const uint64_t w = a.ops[backwards ? a.hi - 1 - k : a.lo + k];
-    if (!a.flipped) return w;
-    const int c = op_code(w);
-    return c == OPI ? mk_op(op_len(w), OPD) : c == OPD ? mk_op(op_len(w), OPI) : w;
-}
-
-// drop the first `count` ops of the view, moving the start coordinates (impl/paf.c:842-861)
-void drop_front(Aln &a, int64_t count) {
-    Rec &r = *a.r;
-    for (int64_t k = 0; k < count; k++) {
-        const uint64_t w = view_op(a, k);
-        const int c = op_code(w);
-        const int64_t n = op_len(w);
-        // in the flipped view "target" is the record's query and vice versa
-        if (!a.flipped) {
-            if (c != OPI) r.ts += n;
-            if (c != OPD) { if (r.same_strand) r.qs += n; else r.qe -= n; }
-        } else {
-            if (c != OPI) r.qs += n;                                          // flipped target = query
-            if (c != OPD) { if (r.same_strand) r.ts += n; else r.te -= n; }   // flipped query = target
-        }
-    }
-    if (a.flipped && !r.same_strand) a.hi -= count; else a.lo += count;
-}
-
-// impl/paf.c:863-904 with the scan of :811-840
-void trim_prefix(Aln &a, float threshold_f, float identity_f, int64_t max_trim) {
-    const double threshold = threshold_f, identity = identity_f;
-    const int64_t n = a.hi - a.lo;
-    int64_t m = 0, mm = 0, last_low = -1;
-    for (int64_t k = 0; k < n; k++) {
-        const uint64_t w = view_op(a, k);
-        if (is_match_code(op_code(w))) m += op_len(w); else mm += op_len(w);
-        if (max_trim >= 0 && m + mm > max_trim) break;
-        if (ident32(m, mm) < threshold) last_low = k;
-    }
-    if (last_low < 0) return;
-    int64_t sm = 0, smm = 0, keep_from = -1;
-    for (int64_t k = last_low; k >= 0; k--) {
-        const uint64_t w = view_op(a, k);
-        if (is_match_code(op_code(w))) sm += op_len(w); else smm += op_len(w);
-        if (ident32(sm, smm) >= identity) keep_from = k;
-    }
-    const int64_t count = keep_from >= 0 ? keep_from : last_low + 1;
-    if (count > 0) drop_front(a, count);
-}
-
-// paf_trim_unreliable_tails (impl/paf.c:906-953). Returns false where the reference's final assert would fire.
-bool trim_unreliable_tails(Rec &r, uint64_t *ops, int64_t &lo, int64_t &hi, float score_fraction, float max_fraction) {
-    int64_t m = 0, mm = 0;
-    for (int64_t k = lo; k < hi; k++) {
-        if (is_match_code(op_code(ops[k]))) m += op_len(ops[k]); else mm += op_len(ops[k]);
-    }
-    const double identity = ident32(m, mm);
-    const double threshold = identity - (identity * score_fraction);
-    const int64_t max_trim = (int64_t)((m + mm) * max_fraction);
-    Aln a{&r, ops, lo, hi, false};
-    trim_prefix(a, (float)threshold, (float)identity, max_trim);
-    a.flipped = true;
-    trim_prefix(a, (float)threshold, (float)identity, max_trim);
-    lo = a.lo; hi = a.hi;
-    int64_t fm = 0, fmm = 0;
-    for (int64_t k = lo; k < hi; k++) {
-        if (is_match_code(op_code(ops[k]))) fm += op_len(ops[k]); else fmm += op_len(ops[k]);
-    }
-    return ident32(fm, fmm) >= identity;
 }
 
 // ---- reading: the whole input, split into lines the way the reference's line reader does (sonLibFile.c:42-71:
@@ -571,69 +488,92 @@ int Filter::finish_add(int64_t a, int64_t b) {
     return ok ? 0 : pafgpu_internal_fail(ctx, PAFGPU_EIO, "write failed");
 }
 
-// add_mismatches | trim: the encoded ops come back to the host, where the float32 identity walk of
-// paf_trim_unreliable_tails (impl/paf.c:811-953) runs per record on all threads, then paf_check and printing.
+// add_mismatches | trim: paf_trim_unreliable_tails (impl/paf.c:811-953) runs on the device over the encoded ops
+// (pafgpu_trim, one thread per record, the reference's float32 arithmetic); only the moved coordinates come back. The
+// host re-renders the text before each CIGAR with them, the device serialiser prints the kept ops.
 int Filter::finish_trim(int64_t a, int64_t b) {
     std::vector<Rec> &R = in.recs;
     const int64_t nb = (int64_t)map.size();
     double t0 = now_s();
     mism.assign((size_t)nb, 0);
-    out_begin.assign((size_t)nb + 1, 0);
-    uint64_t *enc = nullptr;
-    if (nb) {
-        int rc = pafgpu_fetch_ops(ctx, nullptr, out_begin.data(), mism.data());
-        if (rc) return rc;
-        if (!p_out_ops.ensure(out_begin[(size_t)nb] * 8 + 8)) return pafgpu_internal_fail(ctx, PAFGPU_ENODEVICE, "pinned host allocation failed");
-        enc = p_out_ops.as<uint64_t>();
-        if ((rc = pafgpu_fetch_ops(ctx, enc, nullptr, nullptr))) return rc;
-    }
-    rep.s_gpu += now_s() - t0;
-    t0 = now_s();
-    add_stats(*this, a, b);
-    // batch slot of every record of [a, b) (-1: no aligned work)
-    std::vector<int64_t> slot((size_t)(b - a), -1);
-    for (int64_t j = 0; j < nb; j++) slot[(size_t)(map[(size_t)j] - a)] = j;
-    std::vector<std::string> part((size_t)threads);
-    std::vector<int64_t> bad((size_t)threads, -1);
-    std::vector<std::string> bad_msg((size_t)threads);
-    parallel_for(b - a, threads, [&](int64_t i0, int64_t i1, int t) {
-        std::string &s = part[(size_t)t];
-        for (int64_t i = a + i0; i < a + i1; i++) {
-            Rec r = R[(size_t)i];
-            const int64_t j = slot[(size_t)(i - a)];
-            uint64_t *ops = j >= 0 ? enc + out_begin[(size_t)j] : nullptr;
-            int64_t lo = 0, hi = j >= 0 ? out_begin[(size_t)j + 1] - out_begin[(size_t)j] : 0;
-            if (r.has_cigar && hi > lo) {
-                const bool fine = trim_unreliable_tails(r, ops, lo, hi, o.trim_score_fraction, o.trim_max_fraction);
-                std::string msg;
-                if (!fine || check_record(r, ops + lo, hi - lo, &msg)) {
-                    bad[(size_t)t] = i;
-                    if (!fine) msg = "trimmed alignment identity fell below the untrimmed identity (reference assert)";
-                    std::string line;
-                    render_line(r, ops + lo, hi - lo, line);
-                    bad_msg[(size_t)t] = "ERROR: " + msg + " " + line;
-                    return;
-                }
-            }
-            render_line(r, ops ? ops + lo : nullptr, hi - lo, s);
-        }
-    });
-    rep.s_host += now_s() - t0;
-    t0 = now_s();
-    bool ok = true;
+    line_begin.assign((size_t)nb + 1, 0);
+    int64_t text_bytes = 0;
     int rc = 0;
-    for (size_t t = 0; t < part.size() && ok; t++) {
-        ok = write_all(out, part[t].data(), part[t].size());
-        if (bad[t] >= 0) {  // records of later threads come after the failing one: not written
-            err = bad_msg[t];
-            rep.failed_record = bad[t];
-            rc = 1;
-            break;
+    int64_t stop = b;  // first record that fails after trimming
+    std::vector<Rec> trimmed;
+    if (nb) {
+        std::vector<int64_t> t_end((size_t)nb), coords((size_t)nb * 4);
+        std::vector<uint8_t> failed((size_t)nb);
+        for (int64_t j = 0; j < nb; j++) t_end[(size_t)j] = R[(size_t)map[(size_t)j]].te;
+        if ((rc = pafgpu_trim(ctx, o.trim_score_fraction, o.trim_max_fraction, t_end.data(), coords.data(), nullptr, failed.data()))) return rc;
+        if ((rc = pafgpu_fetch_ops(ctx, nullptr, nullptr, mism.data()))) return rc;
+        rep.s_gpu += now_s() - t0;
+        t0 = now_s();
+        trimmed.resize((size_t)nb);
+        for (int64_t j = 0; j < nb; j++) {
+            Rec r = R[(size_t)map[(size_t)j]];
+            r.qs = coords[(size_t)j]; r.qe = coords[(size_t)(nb + j)]; r.ts = coords[(size_t)(2 * nb + j)]; r.te = coords[(size_t)(3 * nb + j)];
+            trimmed[(size_t)j] = r;
+            // paf_check after the trim (impl/paf_trim.c:124): the coordinate tests; the op sums follow the coordinates
+            // by construction of the trim. The reference's final assert (impl/paf.c:952) aborts as well.
+            std::string why;
+            Rec coords_only = r;
+            coords_only.has_cigar = false;
+            if (stop == b && (failed[(size_t)j] || check_record(coords_only, nullptr, 0, &why))) {
+                stop = map[(size_t)j];
+                if (failed[(size_t)j]) why = "trimmed alignment identity fell below the untrimmed identity (reference assert)";
+                std::string line;
+                render_prefix(r, line);
+                err = "ERROR: " + why + " " + line;
+            }
         }
+        std::vector<std::string> part((size_t)threads);
+        std::vector<int64_t> plen((size_t)nb);
+        parallel_for(nb, threads, [&](int64_t j0, int64_t j1, int t) {
+            std::string &s = part[(size_t)t];
+            for (int64_t j = j0; j < j1; j++) {
+                const size_t before = s.size();
+                render_prefix(trimmed[(size_t)j], s);
+                plen[(size_t)j] = (int64_t)(s.size() - before);
+            }
+        });
+        prefix_begin.assign((size_t)nb + 1, 0);
+        for (int64_t j = 0; j < nb; j++) prefix_begin[(size_t)j + 1] = prefix_begin[(size_t)j] + plen[(size_t)j];
+        if (!p_prefix.ensure(prefix_begin[(size_t)nb] + 8)) return pafgpu_internal_fail(ctx, PAFGPU_ENODEVICE, "pinned host allocation failed");
+        {
+            char *w = p_prefix.as<char>();
+            for (auto &s : part) { memcpy(w, s.data(), s.size()); w += s.size(); }
+        }
+        rep.s_host += now_s() - t0;
+        t0 = now_s();
+        if ((rc = pafgpu_serialise(ctx, p_prefix.as<char>(), prefix_begin.data(), &text_bytes, nullptr))) return rc;
+        if (!p_text.ensure(text_bytes + 8)) return pafgpu_internal_fail(ctx, PAFGPU_ENODEVICE, "pinned host allocation failed");
+        if ((rc = pafgpu_fetch_text(ctx, p_text.as<char>(), line_begin.data()))) return rc;
+        rep.s_gpu += now_s() - t0;
+        t0 = now_s();
     }
+    add_stats(*this, a, b);
+    // write in input order up to the first failing record
+    const char *text = p_text.as<char>();
+    bool ok = true;
+    std::string plain;
+    int64_t j = 0, run_from = 0;
+    for (int64_t i = a; i < stop && ok; i++) {
+        if (j < nb && map[(size_t)j] == i) { j++; continue; }
+        ok = write_all(out, text + line_begin[(size_t)run_from], (size_t)(line_begin[(size_t)j] - line_begin[(size_t)run_from]));
+        run_from = j;
+        plain.clear();
+        render_line(R[(size_t)i], nullptr, 0, plain);
+        ok = ok && write_all(out, plain.data(), plain.size());
+    }
+    ok = ok && write_all(out, text + line_begin[(size_t)run_from], (size_t)(line_begin[(size_t)j] - line_begin[(size_t)run_from]));
     rep.s_write += now_s() - t0;
     if (!ok) return pafgpu_internal_fail(ctx, PAFGPU_EIO, "write failed");
-    return rc;
+    if (stop < b) {
+        rep.failed_record = stop;
+        return 1;
+    }
+    return 0;
 }
 
 }  // namespace

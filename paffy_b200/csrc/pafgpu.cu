@@ -4,6 +4,7 @@
 #include "kernels.cuh"
 #include "encode.cuh"
 #include "serialise.cuh"
+#include "trim.cuh"
 #include "internal.h"
 
 #include <algorithm>
@@ -93,6 +94,11 @@ struct pafgpu_ctx {
     DevBuf out, rec_out_begin, rec_mism, scalars;
     // serialiser
     DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
+    // trim
+    DevBuf trim_coords, trim_lo, trim_hi, trim_failed;
+    bool trimmed = false;
+    const uint8_t *last_strand = nullptr;
+    const int64_t *last_qs = nullptr, *last_qe = nullptr, *last_ts = nullptr;
     int64_t ser_text_bytes = 0;
 
     // last batch
@@ -291,6 +297,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     if (b->n_ops >= (1ll << 32) || b->n_records >= (1ll << 31)) return fail(c, PAFGPU_EINVAL, "batch too large: split it");
     if (int rc = genome_sync_table(c, g)) return rc;
     c->have_batch = false;
+    c->trimmed = false;
     c->bad_record = -1;
     const int64_t R = b->n_records, N = b->n_ops;
     CU(c->scalars.ensure(SC_COUNT * 8));
@@ -358,6 +365,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     P.total_out = (unsigned long long *)(sc + SC_TOTAL);
     P.tile_first_closer = c->tile_first_closer.as<uint64_t>();
     P.tile_open_slot = c->tile_open_slot.as<int64_t>();
+    c->last_strand = b->same_strand; c->last_qs = b->q_start; c->last_qe = b->q_end; c->last_ts = b->t_start;
     P.rec_out_begin = c->rec_out_begin.as<int64_t>();
     P.rec_mism = c->rec_mism.as<unsigned long long>();
     c->n_records = R; c->n_ops = N; c->n_tiles = n_tiles; c->n_win = n_win;
@@ -476,7 +484,7 @@ void pafgpu_destroy(pafgpu_ctx *c) {
     DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
                       &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
                       &c->status, &c->tile_first_closer, &c->tile_open_slot, &c->out, &c->rec_out_begin, &c->rec_mism,
-                      &c->scalars, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
+                      &c->scalars, &c->trim_coords, &c->trim_lo, &c->trim_hi, &c->trim_failed, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
                       &c->ser_text};
     for (DevBuf *b : bufs) b->release();
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -710,6 +718,47 @@ int pafgpu_encode_one(pafgpu_ctx *c, const uint64_t *ops, int64_t n_ops, int sam
     return 0;
 }
 
+// ---- device trim (paf_trim_unreliable_tails, impl/paf.c:906-953) -------------------------------------
+int pafgpu_trim(pafgpu_ctx *c, float score_fraction, float max_fraction, const int64_t *t_end, int64_t *coords, int64_t *kept_ops,
+                uint8_t *failed) {
+    if (!c || !t_end || !coords) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!c->have_batch) return fail(c, PAFGPU_ESTATE, "no batch has been encoded");
+    CU(cudaSetDevice(c->device));
+    const int64_t R = c->n_records;
+    const size_t rb = (size_t)std::max<int64_t>(R, 1) * 8;
+    CU(c->trim_coords.ensure(4 * rb));
+    CU(c->trim_lo.ensure(rb));
+    CU(c->trim_hi.ensure(rb));
+    CU(c->trim_failed.ensure((size_t)std::max<int64_t>(R, 1)));
+    int64_t *co = c->trim_coords.as<int64_t>();
+    // the batch arrays live in c->in_* (host batches) or in the caller's device memory (device batches)
+    CU(cudaMemcpyAsync(co, c->last_qs, (size_t)R * 8, cudaMemcpyDeviceToDevice, c->stream));
+    CU(cudaMemcpyAsync(co + R, c->last_qe, (size_t)R * 8, cudaMemcpyDeviceToDevice, c->stream));
+    CU(cudaMemcpyAsync(co + 2 * R, c->last_ts, (size_t)R * 8, cudaMemcpyDeviceToDevice, c->stream));
+    CU(cudaMemcpyAsync(co + 3 * R, t_end, (size_t)R * 8, cudaMemcpyHostToDevice, c->stream));
+    TrimParams T{};
+    T.n_records = R; T.out = c->out.as<uint64_t>(); T.rec_out_begin = c->rec_out_begin.as<int64_t>();
+    T.same_strand = c->last_strand;
+    T.qs = co; T.qe = co + R; T.ts = co + 2 * R; T.te = co + 3 * R;
+    T.lo = c->trim_lo.as<int64_t>(); T.hi = c->trim_hi.as<int64_t>(); T.failed = c->trim_failed.as<uint8_t>();
+    T.score_fraction = score_fraction; T.max_fraction = max_fraction;
+    if (R > 0) trim_kernel<<<blocks_for(R, 128), 128, 0, c->stream>>>(T);
+    CU(cudaMemcpyAsync(coords, co, 4 * (size_t)R * 8, cudaMemcpyDeviceToHost, c->stream));
+    if (failed) CU(cudaMemcpyAsync(failed, T.failed, (size_t)R, cudaMemcpyDeviceToHost, c->stream));
+    std::vector<int64_t> lo, hi;
+    if (kept_ops) {
+        lo.resize((size_t)R); hi.resize((size_t)R);
+        CU(cudaMemcpyAsync(lo.data(), T.lo, (size_t)R * 8, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(hi.data(), T.hi, (size_t)R * 8, cudaMemcpyDeviceToHost, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    if (kept_ops) for (int64_t i = 0; i < R; i++) kept_ops[i] = hi[(size_t)i] - lo[(size_t)i];
+    c->trimmed = true;
+    return 0;
+}
+
 // ---- device serialiser ---------------------------------------------------------------------------
 int pafgpu_serialise(pafgpu_ctx *c, const char *prefix_bytes, const int64_t *prefix_begin, int64_t *text_bytes_out, float *ms_out) {
     if (!c || !prefix_bytes || !prefix_begin) return PAFGPU_EINVAL;
@@ -726,7 +775,10 @@ int pafgpu_serialise(pafgpu_ctx *c, const char *prefix_bytes, const int64_t *pre
     CU(c->ser_optoff.ensure((size_t)(K + 1) * 8));
     CU(c->ser_line_begin.ensure((size_t)(R + 1) * 8));
     CU(cudaEventRecord(c->ev[0], c->stream));
-    if (K > 0) op_text_len_kernel<<<blocks_for(K, 256), 256, 0, c->stream>>>(c->out.as<uint64_t>(), K, c->ser_oplen.as<uint32_t>());
+    if (K > 0)
+        op_text_len_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(
+            c->out.as<uint64_t>(), K, c->ser_oplen.as<uint32_t>(), c->rec_out_begin.as<int64_t>(), R,
+            c->trimmed ? c->trim_lo.as<int64_t>() : nullptr, c->trimmed ? c->trim_hi.as<int64_t>() : nullptr);
     if (int rc = scan_u32(c, c->ser_oplen.as<uint32_t>(), K, c->ser_optoff.as<uint64_t>(), nullptr)) return rc;
     // line_begin[r] = prefix_begin[r] + optoff[rec_out_begin[r]] + r   (prefixes + cigar text + newlines before r)
     line_begin_kernel<<<blocks_for(R + 1, 256), 256, 0, c->stream>>>(R, c->ser_prefix_begin.as<int64_t>(), c->rec_out_begin.as<int64_t>(),

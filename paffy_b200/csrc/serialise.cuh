@@ -32,14 +32,37 @@ __device__ __forceinline__ uint32_t dec_digits(uint64_t v) {
     return n;
 }
 
-__global__ void op_text_len_kernel(const uint64_t *__restrict__ out, int64_t n, uint32_t *__restrict__ tl) {
-    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    const int64_t len = op_signed_len(out[k]);
-    const uint64_t mag = len < 0 ? 0 - (uint64_t)len : (uint64_t)len;
-    uint32_t d = dec_digits(mag);
-    if (mag >= 10000000000000000ull) d = 17;  // dec_digits folds at most 8+4+2+1 extra digits
-    tl[k] = d + (len < 0) + 1;
+// largest r in [lo, hi) with rec_out_begin[r] <= k
+__device__ __forceinline__ int64_t record_of_op(const int64_t *__restrict__ rec_out_begin, int64_t lo, int64_t hi, int64_t k) {
+    while (hi - lo > 1) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (__ldg(rec_out_begin + mid) <= k) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// text bytes of every op; ops outside their record's kept window [keep_lo[r], keep_hi[r]) (set by trim_kernel; null =
+// keep everything) get length 0 and so vanish from the line
+__global__ void __launch_bounds__(SER_THREADS) op_text_len_kernel(const uint64_t *__restrict__ out, int64_t n, uint32_t *__restrict__ tl,
+                                                                  const int64_t *__restrict__ rec_out_begin, int64_t n_records,
+                                                                  const int64_t *__restrict__ keep_lo, const int64_t *__restrict__ keep_hi) {
+    __shared__ int64_t r_range[2];
+    const int64_t k0 = (int64_t)blockIdx.x * SER_OPS_PER_BLOCK;
+    const int64_t k1 = min(k0 + (int64_t)SER_OPS_PER_BLOCK, n);
+    if (keep_lo && threadIdx.x < 2) r_range[threadIdx.x] = record_of_op(rec_out_begin, 0, n_records, threadIdx.x == 0 ? k0 : k1 - 1);
+    __syncthreads();
+    for (int64_t k = k0 + threadIdx.x; k < k1; k += SER_THREADS) {
+        const int64_t len = op_signed_len(out[k]);
+        const uint64_t mag = len < 0 ? 0 - (uint64_t)len : (uint64_t)len;
+        uint32_t d = dec_digits(mag);
+        if (mag >= 10000000000000000ull) d = 17;  // dec_digits folds at most 8+4+2+1 extra digits
+        uint32_t bytes = d + (len < 0) + 1;
+        if (keep_lo) {
+            const int64_t r = record_of_op(rec_out_begin, r_range[0], r_range[1] + 1, k);
+            if (k < __ldg(keep_lo + r) || k >= __ldg(keep_hi + r)) bytes = 0;
+        }
+        tl[k] = bytes;
+    }
 }
 
 // line_begin[r] = bytes of all earlier prefixes + earlier CIGAR text + one newline per earlier record
@@ -65,28 +88,17 @@ __global__ void __launch_bounds__(SER_THREADS) op_text_kernel(SerialiseParams S)
     __shared__ int64_t r_range[2];
     const int64_t k0 = (int64_t)blockIdx.x * SER_OPS_PER_BLOCK;
     const int64_t k1 = min(k0 + (int64_t)SER_OPS_PER_BLOCK, S.n_out);
-    if (threadIdx.x < 2) {
-        const int64_t key = threadIdx.x == 0 ? k0 : k1 - 1;
-        int64_t lo = 0, hi = S.n_records;  // largest r with rec_out_begin[r] <= key
-        while (hi - lo > 1) {
-            const int64_t mid = (lo + hi) >> 1;
-            if (S.rec_out_begin[mid] <= key) lo = mid; else hi = mid;
-        }
-        r_range[threadIdx.x] = lo;
-    }
+    if (threadIdx.x < 2) r_range[threadIdx.x] = record_of_op(S.rec_out_begin, 0, S.n_records, threadIdx.x == 0 ? k0 : k1 - 1);
     __syncthreads();
     for (int64_t k = k0 + threadIdx.x; k < k1; k += SER_THREADS) {
-        int64_t lo = r_range[0], hi = r_range[1] + 1;
-        while (hi - lo > 1) {
-            const int64_t mid = (lo + hi) >> 1;
-            if (__ldg(S.rec_out_begin + mid) <= k) lo = mid; else hi = mid;
-        }
-        const int64_t r = lo;
+        const uint64_t t0 = __ldg(S.op_toff + k), t1 = __ldg(S.op_toff + k + 1);
+        if (t1 == t0) continue;  // trimmed away
+        const int64_t r = record_of_op(S.rec_out_begin, r_range[0], r_range[1] + 1, k);
         const uint64_t w = __ldg(S.out + k);
         const int64_t len = op_signed_len(w);
         uint64_t mag = len < 0 ? 0 - (uint64_t)len : (uint64_t)len;
-        char *p = S.text + (int64_t)__ldg(S.op_toff + k) + __ldg(S.prefix_begin + r + 1) + r;
-        char *e = S.text + (int64_t)__ldg(S.op_toff + k + 1) + __ldg(S.prefix_begin + r + 1) + r;
+        char *p = S.text + (int64_t)t0 + __ldg(S.prefix_begin + r + 1) + r;
+        char *e = S.text + (int64_t)t1 + __ldg(S.prefix_begin + r + 1) + r;
         const unsigned code = (unsigned)(w >> 56);
         *--e = code <= 4 ? "MID=X"[code] : 'N';
         do { *--e = (char)('0' + mag % 10); mag /= 10; } while (mag);

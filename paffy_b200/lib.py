@@ -20,7 +20,7 @@ ABI_SYMBOLS = [
     "pafgpu_genome_find", "pafgpu_genome_contig_length", "pafgpu_genome_num_contigs", "pafgpu_genome_fetch",
     "pafgpu_encode_batch_host", "pafgpu_encode_batch_device", "pafgpu_fetch_ops", "pafgpu_result_device_ptrs",
     "pafgpu_serialise", "pafgpu_fetch_text", "pafgpu_encode_one", "pafgpu_time_encode",
-    "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition",
+    "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition", "pafgpu_trim",
 ]
 # reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
 REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
@@ -103,6 +103,7 @@ def load():
     L.pafgpu_host_free.restype = None
     L.pafgpu_add_mismatches_file.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(FileOpts), C.POINTER(FileReport)]
     L.pafgpu_partition.argtypes = [vp, i64, C.c_int, vp]
+    L.pafgpu_trim.argtypes = [vp, C.c_float, C.c_float, vp, vp, vp, vp]
     _lib = L
     return L
 
@@ -241,6 +242,17 @@ class Context:
         lines = np.empty(self.n_records + 1, dtype=np.int64)
         self._check(self.L.pafgpu_fetch_text(self.h, _ptr(buf), lines.ctypes.data))
         return buf, lines
+
+    def trim(self, t_end, score_fraction=0.05, max_fraction=1.0):
+        """paf_trim_unreliable_tails on the encoded batch (device). -> (coords int64[4, R] = qs, qe, ts, te; kept ops; failed)"""
+        R = self.n_records
+        t_end = np.ascontiguousarray(t_end, dtype=np.int64)
+        coords = np.empty((4, R), dtype=np.int64)
+        kept = np.empty(R, dtype=np.int64)
+        failed = np.empty(R, dtype=np.uint8)
+        self._check(self.L.pafgpu_trim(self.h, score_fraction, max_fraction, t_end.ctypes.data, coords.ctypes.data, kept.ctypes.data,
+                                       failed.ctypes.data))
+        return coords, kept, failed
 
     def add_mismatches_file(self, in_path, out_path, mode=0, trim_r=0.05, trim_t=1.0, threads=0, batch_bases=0):
         """The whole-file filter (paffy add_mismatches / -a / | trim). -> (rc, FileReport); rc 1 = a record ended the

@@ -152,3 +152,25 @@ def test_paf_encode_mismatches_symbol():
     want = O.encode([(25, "M")], False, 0, 25, 0, q, t)
     assert util.pairs_of([cg2.recs[i] for i in range(cg2.length)]) == want
     assert mm == sum(n for n, c in want if c == "X")
+
+
+@pytest.mark.parametrize("seed", [71, 72, 73])
+def test_device_trim_matches_oracle(ctx, seed):
+    """pafgpu_trim (one thread per record, float32 identity walk) vs the oracle's paf_trim_unreliable_tails: moved
+    coordinates and kept op counts, both strands, several -r / -t settings."""
+    import numpy as np
+    from oracle import pyoracle as O
+    case = util.random_case(seed, n_records=80, contig_len=30000, n_ops=14, max_len=900, p_main=0.97)
+    case["records"] = [r for r in case["records"] if any(c == "M" and n for n, c in r["ops"])]
+    got, res = util.gpu_encode(ctx, case)
+    lines = util.case_lines(case)
+    t_end = np.array([r["ts"] + sum(n for n, c in r["ops"] if c != "I") for r in case["records"]], dtype=np.int64)
+    for sf, mf in [(0.05, 1.0), (0.3, 0.5), (0.01, 0.2)]:
+        coords, kept, failed = ctx.trim(t_end, sf, mf)
+        for i, (line, (enc, _)) in enumerate(zip(lines, got)):
+            rc, p = O.parse(line.split("\tcg:Z:")[0] + "\tcg:Z:" + O.cigar_str(enc))
+            assert rc == 0
+            O.lib().oracle_trim_unreliable_tails(C.byref(p), sf, mf)
+            want = [p.query_start, p.query_end, p.target_start, p.target_end]
+            assert [int(coords[k][i]) for k in range(4)] == want, (i, sf, mf)
+            assert int(kept[i]) == p.n_ops and not failed[i]
