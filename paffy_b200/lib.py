@@ -230,17 +230,19 @@ class Context:
         return stage.value, kernel.value
 
     def serialise(self, prefix_bytes, prefix_begin):
-        prefix_begin = np.ascontiguousarray(prefix_begin, dtype=np.int64)
+        if isinstance(prefix_begin, np.ndarray):
+            prefix_begin = np.ascontiguousarray(prefix_begin, dtype=np.int64)
         pb = np.frombuffer(prefix_bytes, dtype=np.uint8) if isinstance(prefix_bytes, (bytes, bytearray)) else prefix_bytes
         n, ms = C.c_int64(), C.c_float()
-        self._check(self.L.pafgpu_serialise(self.h, _ptr(pb), prefix_begin.ctypes.data, C.byref(n), C.byref(ms)))
+        self._check(self.L.pafgpu_serialise(self.h, _ptr(pb), _ptr(prefix_begin), C.byref(n), C.byref(ms)))
         self.text_bytes = n.value
         return n.value, ms.value
 
-    def fetch_text(self, pinned=None):
+    def fetch_text(self, pinned=None, want_lines=True):
+        """-> (text uint8[text_bytes], line offsets int64[R+1] or None). pinned: caller's (pinned) destination buffer."""
         buf = np.empty(self.text_bytes, dtype=np.uint8) if pinned is None else pinned
-        lines = np.empty(self.n_records + 1, dtype=np.int64)
-        self._check(self.L.pafgpu_fetch_text(self.h, _ptr(buf), lines.ctypes.data))
+        lines = np.empty(self.n_records + 1, dtype=np.int64) if want_lines else None
+        self._check(self.L.pafgpu_fetch_text(self.h, _ptr(buf), _ptr(lines)))
         return buf, lines
 
     def trim(self, t_end, score_fraction=0.05, max_fraction=1.0):
