@@ -396,11 +396,12 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
     const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     WarpSmem &S = SM[wid];
 
-    for (;;) {
-        if (threadIdx.x == 0) s_ticket = (int64_t)atomicAdd(P.ticket, 1u);
-        __syncthreads();
-        const int64_t ct = s_ticket;
-        if (ct >= P.n_cta_tiles) break;
+    // the ticket of the next CTA tile is taken while the current one is finished (its latency hides behind the
+    // conversion pass and the barrier that publishes the look-back result also publishes it)
+    if (threadIdx.x == 0) s_ticket = (int64_t)atomicAdd(P.ticket, 1u);
+    __syncthreads();
+    int64_t ct = s_ticket;
+    while (ct < P.n_cta_tiles) {
         const int64_t tile = ct * WARPS + wid;
         const uint64_t s0 = (uint64_t)tile * TILE_WIN;
         const uint32_t n_act = s0 < P.n_win ? (uint32_t)min((uint64_t)TILE_WIN, P.n_win - s0) : 0u;
@@ -468,9 +469,11 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             if (lane == 0) {
                 s_excl = excl;
                 if (ct == P.n_cta_tiles - 1) *P.total_out = excl + agg;
+                s_ticket = (int64_t)atomicAdd(P.ticket, 1u);
             }
         }
         __syncthreads();
+        const int64_t next_ct = s_ticket;
 
         // ---- E2: events -> CigarRecord words, coalesced stores; 31 events per step, lane 31 looks one ahead
         if (n_act) {
@@ -513,6 +516,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                 }
             }
         }
+        ct = next_ct;
     }
 }
 
