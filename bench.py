@@ -122,6 +122,33 @@ def run_reference(fa, paf, threads, reps):
     return json.loads(r.stdout)
 
 
+def run_reference_cli(fa, paf, workdir):
+    """The reference CLI end to end on the sample, as BASELINE.json asks: `paffy add_mismatches` single process, then
+    one process per `paffy split_file` shard (one shard per target contig) run concurrently; wall = slowest."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "paffy")
+    if not os.access(exe, os.X_OK):
+        return None
+    out = {}
+    t0 = time.perf_counter()
+    r = subprocess.run([exe, "add_mismatches", fa, "-i", paf, "-o", os.path.join(workdir, "single.out")], capture_output=True)
+    if r.returncode:
+        return None
+    out["single_process_s"] = time.perf_counter() - t0
+    prefix = os.path.join(workdir, "shard_")
+    t0 = time.perf_counter()
+    if subprocess.run([exe, "split_file", "-i", paf, "-p", prefix], capture_output=True).returncode:
+        return out
+    out["split_file_s"] = time.perf_counter() - t0
+    shards = sorted(f for f in os.listdir(workdir) if f.startswith("shard_") and f.endswith(".paf"))
+    t0 = time.perf_counter()
+    procs = [subprocess.Popen([exe, "add_mismatches", fa, "-i", os.path.join(workdir, f), "-o", os.path.join(workdir, f + ".out")],
+                              stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL) for f in shards]
+    ok = all(p.wait() == 0 for p in procs)
+    out["parallel_processes"] = len(shards)
+    out["parallel_wall_s"] = time.perf_counter() - t0 if ok else None
+    return out
+
+
 def reference_arm(args, rank):
     """The reference's own CPU implementation (oracle/_ref/ref_bench: unmodified paf_encode_mismatches on all
     host threads) on a bounded sample of the same workload. Rank 0 only."""
@@ -359,6 +386,15 @@ def main():
                    "sample": f"{r['records']} records of {args.workload}'s generator on contig pairs t1/q1 (+) and t2/q2 (-), {r['aligned_bp']} aligned bp; "
                              f"unmodified paf_encode_mismatches on {cores} pthreads, FASTA load ({out['load_s']:.1f} s) and PAF parse ({r['parse_s']:.2f} s) excluded",
                    "single_thread_value": one["aligned_bp"] / one["encode_s"], "fasta_load_s": out["load_s"], "parse_s": r["parse_s"]}
+            cli = run_reference_cli(fa, paf, d)
+            if cli:
+                cli["aligned_bp"] = r["aligned_bp"]
+                cli["single_process_bp_per_s_end_to_end"] = r["aligned_bp"] / cli["single_process_s"]
+                if cli.get("parallel_wall_s"):
+                    cli["parallel_bp_per_s_end_to_end"] = r["aligned_bp"] / cli["parallel_wall_s"]
+                cli["what"] = ("reference CLI `paffy add_mismatches` file to file on the same sample (FASTA load, parse, encode, print): one process, "
+                               "then one process per `paffy split_file` shard (per target contig) run concurrently")
+                cpu["reference_cli"] = cli
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

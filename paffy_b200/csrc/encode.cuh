@@ -481,18 +481,23 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
 #pragma unroll
             for (int w = 0; w < WARPS; w++) slot0 += (unsigned)w < wid ? s_wcount[w] : 0u;
             if (lane == 0 && tile_count == 0) P.tile_first_closer[tile] = term == COORD_OPEN ? INF64 : WIN_BASES * s0 + term;
+            uint64_t *outp = P.out + slot0;
+            // events that may be stored (the host re-runs the pass with a larger buffer when some were dropped)
+            const uint32_t storable = (unsigned long long)P.out_cap > slot0 ? (uint32_t)min((unsigned long long)tile_count, (unsigned long long)P.out_cap - slot0) : 0u;
+            const uint32_t open_i = term == COORD_OPEN ? tile_count - 1 : 0xffffffffu;  // a run still open at the tile's end
             for (uint32_t base = 0; base < tile_count; base += LIST_CAP) {
                 __syncwarp();
                 if (base && cnt && ex <= base + LIST_CAP && ex + cnt > base) lane_list(S, lane, byte, pm, nz, ex, base);  // dense tiles
                 __syncwarp();
                 op_pass(P, S, lane, adj, n_tab, rec_first, base, slot0);
-                __syncwarp();
                 const uint32_t round_end = min(base + (uint32_t)LIST_CAP, tile_count);
+                // virtual event closing the tile's last run
+                if (lane == 0 && round_end == tile_count) S.list[tile_count - base] = (term & LE_CLOSE) << LS_CLOSE;
+                __syncwarp();
+                if (lane == 0 && base == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + ((S.list[0] >> LS_CLOSE) & LE_CLOSE);
                 for (uint32_t i0 = base; i0 < round_end; i0 += 31) {
                     const uint32_t i = i0 + lane;
-                    uint32_t e = (i < tile_count && i <= round_end) ? S.list[i - base] : 0u;
-                    if (i == tile_count) e = (term & LE_CLOSE) << LS_CLOSE;  // virtual event closing the tile's last run
-                    if (i == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + ((e >> LS_CLOSE) & LE_CLOSE);
+                    const uint32_t e = i <= round_end ? S.list[i - base] : 0u;
                     const uint32_t nx = __shfl_down_sync(FULL, e, 1);
                     if (lane < 31 && i < round_end) {
                         uint32_t lo, hi;
@@ -503,15 +508,14 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                             const uint32_t c = e & LE_COORD;
                             hi = (uint32_t)((e & LE_X) ? OP_X : OP_EQ) << 24;
                             lo = ((nx >> LS_CLOSE) & LE_CLOSE) - c;
-                            if (i == tile_count - 1 && term == COORD_OPEN) {
-                                // run still open at the tile's end: provisional absolute start, turned into a length by stitch_kernel
+                            if (i == open_i) {
+                                // provisional absolute start, turned into a length by stitch_kernel
                                 const uint64_t abs_start = WIN_BASES * s0 + c;
                                 lo = (uint32_t)abs_start; hi |= (uint32_t)(abs_start >> 32);
                                 P.tile_open_slot[tile] = (int64_t)(slot0 + i);
                             }
                         }
-                        const unsigned long long slot = slot0 + i;
-                        if (slot < (unsigned long long)P.out_cap) P.out[slot] = ((uint64_t)hi << 32) | lo;
+                        if (i < storable) outp[i] = ((uint64_t)hi << 32) | lo;
                     }
                 }
             }
