@@ -87,12 +87,11 @@ struct WarpSmem {
 
 // ---- A: op table of one warp tile. adj = 1 when table entry 0 starts exactly at tile window 0; n_tab = entries;
 // rec_first = record of entry 0; any_exc = some op of the tile touches a non-ACGT word.
-__device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, int64_t tile, uint64_t s0, uint64_t tile_end,
+__device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, int64_t cur, uint64_t s0, uint64_t tile_end,
                                             unsigned lane, unsigned &adj, uint32_t &n_tab, uint32_t &rec_first, bool &any_exc) {
     __syncwarp();
     if (lane < TILE_ITERS) S.bm[lane] = 0;
     __syncwarp();
-    const int64_t cur = P.tile_first_op[tile];
     bool more = true, exc = false;
     adj = 0;
     n_tab = 0;
@@ -401,6 +400,9 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
     if (threadIdx.x == 0) s_ticket = (int64_t)atomicAdd(P.ticket, 1u);
     __syncthreads();
     int64_t ct = s_ticket;
+    // first op of this warp's tile; for every later tile it is fetched (and the tile's op arrays pulled into L2) while
+    // the previous tile is converted, so a tile does not start with a chain of DRAM round trips
+    uint32_t first_op = ct * WARPS + wid < P.n_tiles ? __ldg(P.tile_first_op + ct * WARPS + wid) : 0u;
     while (ct < P.n_cta_tiles) {
         const int64_t tile = ct * WARPS + wid;
         const uint64_t s0 = (uint64_t)tile * TILE_WIN;
@@ -410,7 +412,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         uint32_t cnt = 0, nz = 0, inc = 0, byte = 0, pm = 0, term = COORD_OPEN, n_tab = 0, rec_first = 0;
         if (n_act) {
             bool any_exc;
-            build_table(P, S, tile, s0, s0 + n_act, lane, adj, n_tab, rec_first, any_exc);
+            build_table(P, S, (int64_t)first_op, s0, s0 + n_act, lane, adj, n_tab, rec_first, any_exc);
             const uint32_t pm0 = any_exc ? compare_tile<BATCH, true>(P, S, n_act, lane, adj, rec_first)
                                          : compare_tile<BATCH, false>(P, S, n_act, lane, adj, rec_first);
             __syncwarp();
@@ -474,6 +476,8 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         }
         __syncthreads();
         const int64_t next_ct = s_ticket;
+        const int64_t next_tile = next_ct * WARPS + wid;
+        const uint32_t next_first_op = next_tile < P.n_tiles ? __ldg(P.tile_first_op + next_tile) : 0u;
 
         // ---- E2: events -> CigarRecord words, coalesced stores; 31 events per step, lane 31 looks one ahead
         if (n_act) {
@@ -520,6 +524,17 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                 }
             }
         }
+        if (next_tile < P.n_tiles) {
+            const int64_t k = (int64_t)next_first_op + lane;
+            if (k < P.n_ops) {
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.woff + k));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.ops + k));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.tpos + k));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.qpos + k));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.op_rec + k));
+            }
+        }
+        first_op = next_first_op;
         ct = next_ct;
     }
 }
