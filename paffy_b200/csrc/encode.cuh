@@ -43,12 +43,15 @@ struct EncodeParams {
     int64_t *tile_open_slot;        // output slot of a run left open, -1 if none (pre-set)
     int64_t *rec_out_begin;
     unsigned long long *rec_mism;
+    struct OpEntry *tab_overflow;   // TILE_TAB entries per resident warp: table entries TAB_SMEM.. of tiles with many short ops
+    uint16_t *rec_overflow;
 };
 
 constexpr int WIN_BASES = 64;
 constexpr int TILE_ITERS = 8;                 // windows per lane per warp tile
 constexpr int TILE_WIN = 32 * TILE_ITERS;     // windows per warp tile
 constexpr int TILE_TAB = TILE_WIN + 2;        // a tile overlaps at most TILE_WIN + 1 ops
+constexpr int TAB_SMEM = 112;                 // table entries kept in shared memory; denser tiles spill the rest to HBM
 constexpr int MASK_PAD = TILE_WIN + TILE_WIN / 8;  // mask of window p sits at p + (p >> 3): conflict-free blocked reads
 constexpr int LIST_CAP = 448;                 // events converted per round
 constexpr uint32_t COORD_OPEN = 0xffffffffu;
@@ -75,8 +78,8 @@ constexpr uint32_t EF_HEAD = 1u << 28;
 constexpr int32_t REM_CLAMP = 1 << 30;
 
 struct WarpSmem {
-    OpEntry tab[TILE_TAB];
-    uint16_t rec[TILE_TAB];           // owning record, relative to the record of table entry 0
+    OpEntry tab[TAB_SMEM];
+    uint16_t rec[TAB_SMEM];           // owning record, relative to the record of table entry 0
     uint64_t mask[MASK_PAD];          // mismatch bits of window p at p + (p >> 3)
     uint32_t list[LIST_CAP + 2];      // events of one round (+ successor of the last), see LE_*
     uint16_t prel[TILE_WIN];          // events of the owning lane before window p
@@ -85,9 +88,31 @@ struct WarpSmem {
     uint32_t bmpre[TILE_ITERS];       // op starts before word k of bm
 };
 
+// table entry i of the warp's tile: shared memory, or the warp's overflow area in HBM for the rare tile with more
+// than TAB_SMEM ops (written and read by the same warp, L1 bypassed)
+struct TileTab {
+    WarpSmem &S;
+    OpEntry *otab;
+    uint16_t *orec;
+    __device__ __forceinline__ OpEntry get(uint32_t i) const {
+        if (i < (uint32_t)TAB_SMEM) return S.tab[i];
+        const int4 v = __ldcg(reinterpret_cast<const int4 *>(otab + i));
+        OpEntry en;
+        en.tw = v.x; en.qw = v.y; en.rem = v.z; en.misc = (uint32_t)v.w;
+        return en;
+    }
+    __device__ __forceinline__ uint32_t rec(uint32_t i) const {
+        return i < (uint32_t)TAB_SMEM ? (uint32_t)S.rec[i] : (uint32_t)__ldcg(orec + i);
+    }
+    __device__ __forceinline__ void put(uint32_t i, const OpEntry &en, uint16_t r) const {
+        if (i < (uint32_t)TAB_SMEM) { S.tab[i] = en; S.rec[i] = r; }
+        else { otab[i] = en; orec[i] = r; }
+    }
+};
+
 // ---- A: op table of one warp tile. adj = 1 when table entry 0 starts exactly at tile window 0; n_tab = entries;
 // rec_first = record of entry 0; any_exc = some op of the tile touches a non-ACGT word.
-__device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, int64_t cur, uint64_t s0, uint64_t tile_end,
+__device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, const TileTab &T, int64_t cur, uint64_t s0, uint64_t tile_end,
                                             unsigned lane, unsigned &adj, uint32_t &n_tab, uint32_t &rec_first, bool &any_exc) {
     __syncwarp();
     if (lane < TILE_ITERS) S.bm[lane] = 0;
@@ -143,9 +168,7 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
                 en.misc |= (w << ES_WIN) | ((gap & 63u) << ES_GAP) | ((rec >> 31) ? EF_HEAD : 0u);
                 atomicOr(&S.bm[w >> 5], 1u << (w & 31));
             }
-            const int e = 32 * g + (int)lane;
-            S.tab[e] = en;
-            S.rec[e] = (uint16_t)((rec & 0x7fffffffu) - rec_first);
+            T.put(32u * g + lane, en, (uint16_t)((rec & 0x7fffffffu) - rec_first));
         }
         const unsigned inb = __ballot_sync(FULL, in);
         n_tab += __popc(inb);
@@ -164,7 +187,7 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
 // ---- B: compare. Striped windows; masks to shared memory; per-record mismatch tallies. Returns (lane 0) the
 // mismatch state of the base just before the tile when tile window 0 continues an op.
 template <int BATCH, bool EXC>
-__device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem &S, uint32_t n_act, unsigned lane, unsigned adj, uint32_t rec_first) {
+__device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem &S, const TileTab &T, uint32_t n_act, unsigned lane, unsigned adj, uint32_t rec_first) {
     static_assert(TILE_ITERS % BATCH == 0, "BATCH must divide the iterations of a tile");
     const uint64_t *__restrict__ gw = P.G.words;
     uint32_t pre = 0, pm0 = 0;
@@ -185,7 +208,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             pre += __popc(w);
             if (srel >= n_act) idx = 0;
             IDX[b] = idx;
-            const OpEntry en = S.tab[idx];
+            const OpEntry en = T.get(idx);
             const bool isM = srel < n_act && !(en.misc & EF_PASS);
             const int32_t tw = isM ? en.tw + 2 * (int32_t)srel : 0;
             const int32_t qw = isM ? en.qw + 2 * (int32_t)srel : 0;
@@ -216,7 +239,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
                 const uint32_t idx = pre2 + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
                 pre2 += __popc(w);
                 if (srel < n_act) {
-                    const OpEntry en = S.tab[idx];
+                    const OpEntry en = T.get(idx);
                     if (!(en.misc & EF_PASS)) {
                         const uint64_t *tpn = gw + (en.tw + 2 * (int32_t)srel), *qpn = gw + (en.qw + 2 * (int32_t)srel);
                         asm volatile("prefetch.global.L2 [%0];" ::"l"(tpn));
@@ -239,7 +262,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const int it = hb + b;
             const uint32_t srel = 32u * it + lane;
             const uint32_t idx = IDX[b];
-            const OpEntry en = S.tab[idx];
+            const OpEntry en = T.get(idx);
             const bool isM = srel < n_act && !(en.misc & EF_PASS);
             const int32_t rem = en.rem - WIN_BASES * (int32_t)srel;
             const uint32_t n = !isM ? 0u : rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
@@ -278,7 +301,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             S.mask[srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
             // per-record mismatch tally, flushed when the lane moves to another record
             if (isM) {
-                const uint32_t rec = S.rec[idx];
+                const uint32_t rec = T.rec(idx);
                 if (rec != acc_rec) {
                     if (acc_mm) atomicAdd(P.rec_mism + rec_first + acc_rec, (unsigned long long)acc_mm);
                     acc_rec = rec;
@@ -367,10 +390,10 @@ __device__ __forceinline__ void lane_list(WarpSmem &S, unsigned lane, uint32_t b
 
 // E1': op pass. Every op that starts inside the tile patches its event: the run before it closes at the previous op's
 // end, a pass-through op is copied through, the first op of a record leaves the record's first output slot.
-__device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, unsigned lane, unsigned adj, uint32_t n_tab, uint32_t rec_first,
+__device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, const TileTab &T, unsigned lane, unsigned adj, uint32_t n_tab, uint32_t rec_first,
                                         uint32_t base, unsigned long long slot0) {
     for (uint32_t e = lane + (adj ? 0u : 1u); e < n_tab; e += 32) {
-        const uint32_t misc = S.tab[e].misc;
+        const uint32_t misc = T.get(e).misc;
         const uint32_t w = (misc >> ES_WIN) & 0xffu;
         const uint32_t r = (uint32_t)S.lanex[w >> 3] + S.prel[w];
         const uint32_t k = r - base;
@@ -378,13 +401,13 @@ __device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, unsi
             const uint32_t close0 = WIN_BASES * w - ((misc >> ES_GAP) & 63u);
             if (misc & EF_PASS) S.list[k] = e | (close0 << LS_CLOSE) | LE_PASS;
             else reinterpret_cast<uint16_t *>(S.list)[2 * k + 1] = (uint16_t)close0;
-            if ((misc & EF_HEAD) && k < (uint32_t)LIST_CAP) P.rec_out_begin[rec_first + S.rec[e]] = (int64_t)(slot0 + r);
+            if ((misc & EF_HEAD) && k < (uint32_t)LIST_CAP) P.rec_out_begin[rec_first + T.rec(e)] = (int64_t)(slot0 + r);
         }
     }
 }
 
 #ifndef ENC_MINB
-#define ENC_MINB 6
+#define ENC_MINB 8
 #endif
 template <int WARPS, int BATCH>
 __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kernel(EncodeParams P) {
@@ -394,6 +417,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
     __shared__ int64_t s_ticket;
     const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     WarpSmem &S = SM[wid];
+    const TileTab T{S, P.tab_overflow + ((size_t)blockIdx.x * WARPS + wid) * TILE_TAB, P.rec_overflow + ((size_t)blockIdx.x * WARPS + wid) * TILE_TAB};
 
     // the ticket of the next CTA tile is taken while the current one is finished (its latency hides behind the
     // conversion pass and the barrier that publishes the look-back result also publishes it)
@@ -412,9 +436,9 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         uint32_t cnt = 0, nz = 0, inc = 0, byte = 0, pm = 0, term = COORD_OPEN, n_tab = 0, rec_first = 0;
         if (n_act) {
             bool any_exc;
-            build_table(P, S, (int64_t)first_op, s0, s0 + n_act, lane, adj, n_tab, rec_first, any_exc);
-            const uint32_t pm0 = any_exc ? compare_tile<BATCH, true>(P, S, n_act, lane, adj, rec_first)
-                                         : compare_tile<BATCH, false>(P, S, n_act, lane, adj, rec_first);
+            build_table(P, S, T, (int64_t)first_op, s0, s0 + n_act, lane, adj, n_tab, rec_first, any_exc);
+            const uint32_t pm0 = any_exc ? compare_tile<BATCH, true>(P, S, T, n_act, lane, adj, rec_first)
+                                         : compare_tile<BATCH, false>(P, S, T, n_act, lane, adj, rec_first);
             __syncwarp();
             // blocked view of the tile
             byte = (S.bm[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
@@ -429,7 +453,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             }
             S.lanex[lane] = (uint16_t)(inc - cnt);
             // where a run still open at the tile's last window closes: the end of that window's op if it lies inside the tile
-            const OpEntry en = S.tab[window_op(S, n_act - 1, adj)];
+            const OpEntry en = T.get(window_op(S, n_act - 1, adj));
             term = (en.misc & EF_PASS) ? WIN_BASES * n_act : en.rem <= (int32_t)(WIN_BASES * n_act) ? (uint32_t)en.rem : COORD_OPEN;
         }
         const uint32_t tile_count = __shfl_sync(FULL, inc, 31);
@@ -493,7 +517,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                 __syncwarp();
                 if (base && cnt && ex <= base + LIST_CAP && ex + cnt > base) lane_list(S, lane, byte, pm, nz, ex, base);  // dense tiles
                 __syncwarp();
-                op_pass(P, S, lane, adj, n_tab, rec_first, base, slot0);
+                op_pass(P, S, T, lane, adj, n_tab, rec_first, base, slot0);
                 const uint32_t round_end = min(base + (uint32_t)LIST_CAP, tile_count);
                 // virtual event closing the tile's last run
                 if (lane == 0 && round_end == tile_count) S.list[tile_count - base] = (term & LE_CLOSE) << LS_CLOSE;
@@ -506,7 +530,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                     if (lane < 31 && i < round_end) {
                         uint32_t lo, hi;
                         if (e & LE_PASS) {
-                            const OpEntry en = S.tab[e & 0x1ffu];
+                            const OpEntry en = T.get(e & 0x1ffu);
                             lo = (uint32_t)en.tw; hi = (uint32_t)en.qw;
                         } else {
                             const uint32_t c = e & LE_COORD;
