@@ -27,8 +27,8 @@ import torch  # noqa: E402
 
 METRIC = "add_mismatches aligned bp/sec"
 UNIT = "aligned bp/s"
-KERNELS_PER_STEP = 7       # ingest, 3x scan, tile_first_op, encode, stitch
-KERNELS_PER_E2E_STEP = 14  # + op_text_len, 3x scan, line_begin, prefix_copy, op_text
+KERNELS_PER_STEP = 6       # ingest, 3x scan (the last also writes tile_first_op), encode, stitch
+KERNELS_PER_E2E_STEP = 13  # + op_text_len, 3x scan, line_begin, prefix_copy, op_text
 
 
 def peaks():

@@ -197,9 +197,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_spine_kernel(uint64_t *bloc
     }
     if (threadIdx.x == 0) *out_total = carry;
 }
+// tile_first_op (optional): in[] are windows per op; every warp tile of tile_windows windows learns the op that owns
+// its first window (op j owns windows [out[j], out[j + 1]))
 __global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(const uint32_t *__restrict__ in, int64_t n,
                                                                    const uint64_t *__restrict__ block_sums,
-                                                                   uint64_t *__restrict__ out) {
+                                                                   uint64_t *__restrict__ out, uint32_t *__restrict__ tile_first_op,
+                                                                   uint32_t tile_windows, uint64_t tile_cap) {
     // thread t owns SCAN_ITEMS consecutive items so the block scan runs once
     const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
     uint32_t v[SCAN_ITEMS];
@@ -213,7 +216,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(const uint32_t
     uint64_t run = block_incl_scan(s, &tot) - s + block_sums[blockIdx.x];
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
-        if (base + k < n) out[base + k] = run;
+        if (base + k < n) {
+            out[base + k] = run;
+            if (tile_first_op && v[k])
+                for (uint64_t t = (run + tile_windows - 1) / tile_windows; t * tile_windows < run + v[k] && t < tile_cap; t++)
+                    tile_first_op[t] = (uint32_t)(base + k);
+        }
         run += v[k];
     }
     if (base <= n - 1 && n - 1 < base + SCAN_ITEMS) out[n] = block_sums[blockIdx.x] + tot;

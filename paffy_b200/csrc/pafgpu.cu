@@ -130,7 +130,8 @@ inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 inline unsigned blocks_for(int64_t n, int per) { return (unsigned)std::max<int64_t>(1, (n + per - 1) / per); }
 
 // exclusive scan of n u32 values into out[0..n] (u64); total also lands in *total_dev if non-null
-int scan_u32(pafgpu_ctx *c, const uint32_t *in, int64_t n, uint64_t *out, uint64_t *total_dev) {
+int scan_u32(pafgpu_ctx *c, const uint32_t *in, int64_t n, uint64_t *out, uint64_t *total_dev, uint32_t *tile_first_op = nullptr,
+             uint32_t tile_windows = 1, int64_t tile_cap = 0) {
     if (n == 0) {
         CU(cudaMemsetAsync(out, 0, sizeof(uint64_t), c->stream));
         if (total_dev) CU(cudaMemsetAsync(total_dev, 0, sizeof(uint64_t), c->stream));
@@ -141,7 +142,7 @@ int scan_u32(pafgpu_ctx *c, const uint32_t *in, int64_t n, uint64_t *out, uint64
     uint64_t *tot = total_dev ? total_dev : c->scalars.as<uint64_t>() + SC_TMP;
     scan_sums_kernel<<<(unsigned)nb, SCAN_THREADS, 0, c->stream>>>(in, n, c->scan_sums.as<uint64_t>());
     scan_spine_kernel<<<1, SCAN_THREADS, 0, c->stream>>>(c->scan_sums.as<uint64_t>(), nb, tot);
-    scan_apply_kernel<<<(unsigned)nb, SCAN_THREADS, 0, c->stream>>>(in, n, c->scan_sums.as<uint64_t>(), out);
+    scan_apply_kernel<<<(unsigned)nb, SCAN_THREADS, 0, c->stream>>>(in, n, c->scan_sums.as<uint64_t>(), out, tile_first_op, tile_windows, (uint64_t)tile_cap);
     CU(cudaGetLastError());
     return 0;
 }
@@ -333,12 +334,23 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     I.bad_record = (unsigned long long *)(sc + SC_BAD);
     I.aligned = (unsigned long long *)(sc + SC_ALIGNED);
     if (R > 0) {
-        const int64_t mean_ops = N / R;
-        if (mean_ops <= 10) ingest_kernel<8><<<blocks_for(R * 8, 256), 256, 0, c->stream>>>(I);
-        else if (mean_ops <= 24) ingest_kernel<16><<<blocks_for(R * 16, 256), 256, 0, c->stream>>>(I);
+        // lanes per record: fewer lanes = more records in flight per SM, which hides the chain of dependent loads
+        // per record better than finishing a record in one stride (measured at C2, 20 ops per record: 4 lanes 0.53 ms,
+        // 8 lanes 0.58 ms, 16 lanes 0.69 ms, 32 lanes 0.90 ms for the ingest stage)
+        int64_t mean_ops = N / R;
+        if (const char *e = getenv("PAFGPU_INGEST_G")) mean_ops = atoi(e) <= 4 ? 1 : atoi(e) == 8 ? 100 : atoi(e) == 16 ? 1000 : 100000;  // experiments
+        if (mean_ops <= 64) ingest_kernel<4><<<blocks_for(R * 4, 256), 256, 0, c->stream>>>(I);
+        else if (mean_ops <= 256) ingest_kernel<8><<<blocks_for(R * 8, 256), 256, 0, c->stream>>>(I);
+        else if (mean_ops <= 2048) ingest_kernel<16><<<blocks_for(R * 16, 256), 256, 0, c->stream>>>(I);
         else ingest_kernel<32><<<blocks_for(R * 32, 256), 256, 0, c->stream>>>(I);
     }
-    if (int rc = scan_u32(c, c->nwin.as<uint32_t>(), N, c->woff.as<uint64_t>(), sc + SC_NWIN)) return rc;
+    // the scan of the windows per op also leaves the first op of every warp tile; the tile count is only known after it,
+    // so the array is sized from a guess and the separate kernel runs in the rare case that was too small
+    CU(c->tile_first_op.ensure((size_t)std::max<int64_t>(std::max<int64_t>(c->n_tiles + c->n_tiles / 2, N / 8), 1024) * 4));
+    const int64_t tfo_cap = (int64_t)(c->tile_first_op.cap / 4);
+    if (int rc = scan_u32(c, c->nwin.as<uint32_t>(), N, c->woff.as<uint64_t>(), sc + SC_NWIN, c->tile_first_op.as<uint32_t>(), TILE_WINDOWS,
+                          tfo_cap))
+        return rc;
     uint64_t host_sc[SC_COUNT];
     CU(cudaMemcpyAsync(host_sc, sc, sizeof host_sc, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
@@ -352,11 +364,12 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     const uint64_t n_win = host_sc[SC_NWIN];
     const int64_t aligned = (int64_t)host_sc[SC_ALIGNED];
     const int64_t n_tiles = (int64_t)((n_win + TILE_WINDOWS - 1) / TILE_WINDOWS);
+    const bool tfo_done = n_tiles <= tfo_cap;
     CU(c->tile_first_op.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 4));
     CU(c->status.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));  // one word per CTA tile; a CTA tile is >= 1 warp tile
     CU(c->tile_first_closer.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
     CU(c->tile_open_slot.ensure((size_t)std::max<int64_t>(n_tiles, 1) * 8));
-    if (N > 0)
+    if (N > 0 && !tfo_done)
         tile_first_op_kernel<<<blocks_for(N, 256), 256, 0, c->stream>>>(c->woff.as<uint64_t>(), N, TILE_WINDOWS,
                                                                         c->tile_first_op.as<uint32_t>());
     CU(cudaEventRecord(c->ev[1], c->stream));
