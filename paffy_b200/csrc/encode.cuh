@@ -44,7 +44,6 @@ struct EncodeParams {
     int64_t *rec_out_begin;
     unsigned long long *rec_mism;
     struct OpEntry *tab_overflow;   // TILE_TAB entries per resident warp: table entries TAB_SMEM.. of tiles with many short ops
-    uint16_t *rec_overflow;
 };
 
 constexpr int WIN_BASES = 64;
@@ -64,7 +63,9 @@ __device__ __forceinline__ unsigned slow_mismatch(const Genome &G, uint64_t tp, 
 
 // per-op table entry (16 bytes, read with one LDS.128)
 //   M op:          tw / qw = word index of the target base / lowest query base under tile window 0,
-//                  rem = op bases left at tile window 0 = tile-relative coordinate of the op's end
+//                  rem (low 16 bits) = op bases left at tile window 0 = tile-relative coordinate of the op's end,
+//                  clamped to 0xffff (anything beyond the tile's 16 384 bases only has to stay "beyond")
+//   every op:      rem (high 16 bits) = owning record, relative to the record of table entry 0
 //   any other op:  tw / qw = low / high half of the op word (copied through)
 struct __align__(16) OpEntry {
     int32_t tw, qw, rem;
@@ -75,11 +76,15 @@ constexpr uint32_t EF_PASS = 1u << 11, EF_EXC = 1u << 13;
 // end and that window boundary (64 - bases in its last window), 28 first op of its record
 constexpr int ES_WIN = 14, ES_GAP = 22;
 constexpr uint32_t EF_HEAD = 1u << 28;
-constexpr int32_t REM_CLAMP = 1 << 30;
+constexpr int32_t REM_CLAMP = 0xffff;
+__device__ __forceinline__ int32_t entry_rem(const struct OpEntry &en);
+__device__ __forceinline__ uint32_t entry_rec(const struct OpEntry &en);
+
+__device__ __forceinline__ int32_t entry_rem(const OpEntry &en) { return en.rem & 0xffff; }
+__device__ __forceinline__ uint32_t entry_rec(const OpEntry &en) { return (uint32_t)en.rem >> 16; }
 
 struct WarpSmem {
     OpEntry tab[TAB_SMEM];
-    uint16_t rec[TAB_SMEM];           // owning record, relative to the record of table entry 0
     uint64_t mask[MASK_PAD];          // mismatch bits of window p at p + (p >> 3)
     uint32_t list[LIST_CAP + 2];      // events of one round (+ successor of the last), see LE_*
     uint16_t prel[TILE_WIN];          // events of the owning lane before window p
@@ -93,7 +98,6 @@ struct WarpSmem {
 struct TileTab {
     WarpSmem &S;
     OpEntry *otab;
-    uint16_t *orec;
     __device__ __forceinline__ OpEntry get(uint32_t i) const {
         if (i < (uint32_t)TAB_SMEM) return S.tab[i];
         const int4 v = __ldcg(reinterpret_cast<const int4 *>(otab + i));
@@ -101,12 +105,9 @@ struct TileTab {
         en.tw = v.x; en.qw = v.y; en.rem = v.z; en.misc = (uint32_t)v.w;
         return en;
     }
-    __device__ __forceinline__ uint32_t rec(uint32_t i) const {
-        return i < (uint32_t)TAB_SMEM ? (uint32_t)S.rec[i] : (uint32_t)__ldcg(orec + i);
-    }
-    __device__ __forceinline__ void put(uint32_t i, const OpEntry &en, uint16_t r) const {
-        if (i < (uint32_t)TAB_SMEM) { S.tab[i] = en; S.rec[i] = r; }
-        else { otab[i] = en; orec[i] = r; }
+    __device__ __forceinline__ void put(uint32_t i, const OpEntry &en) const {
+        if (i < (uint32_t)TAB_SMEM) S.tab[i] = en;
+        else otab[i] = en;
     }
 };
 
@@ -168,7 +169,8 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
                 en.misc |= (w << ES_WIN) | ((gap & 63u) << ES_GAP) | ((rec >> 31) ? EF_HEAD : 0u);
                 atomicOr(&S.bm[w >> 5], 1u << (w & 31));
             }
-            T.put(32u * g + lane, en, (uint16_t)((rec & 0x7fffffffu) - rec_first));
+            en.rem |= (int32_t)(((rec & 0x7fffffffu) - rec_first) << 16);
+            T.put(32u * g + lane, en);
         }
         const unsigned inb = __ballot_sync(FULL, in);
         n_tab += __popc(inb);
@@ -206,7 +208,6 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const uint32_t w = S.bm[it];
             uint32_t idx = pre + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
             pre += __popc(w);
-            if (srel >= n_act) idx = 0;
             IDX[b] = idx;
             const OpEntry en = T.get(idx);
             const bool isM = srel < n_act && !(en.misc & EF_PASS);
@@ -242,10 +243,10 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
                     const OpEntry en = T.get(idx);
                     if (!(en.misc & EF_PASS)) {
                         const uint64_t *tpn = gw + (en.tw + 2 * (int32_t)srel), *qpn = gw + (en.qw + 2 * (int32_t)srel);
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(tpn));
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(tpn + 2));
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(qpn));
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(qpn + 2));
+                        // a window spans 3 words, the next lane's window starts 2 words on: the middle word of every
+                        // window touches every 32-byte sector of the op's span
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(tpn + 1));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(qpn + 1));
                     }
                 }
             }
@@ -264,7 +265,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const uint32_t idx = IDX[b];
             const OpEntry en = T.get(idx);
             const bool isM = srel < n_act && !(en.misc & EF_PASS);
-            const int32_t rem = en.rem - WIN_BASES * (int32_t)srel;
+            const int32_t rem = entry_rem(en) - WIN_BASES * (int32_t)srel;
             const uint32_t n = !isM ? 0u : rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
             const uint32_t misc = en.misc;
             const unsigned sht = misc & 31u, shq = (misc >> 5) & 31u;
@@ -301,7 +302,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             S.mask[srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
             // per-record mismatch tally, flushed when the lane moves to another record
             if (isM) {
-                const uint32_t rec = T.rec(idx);
+                const uint32_t rec = entry_rec(en);
                 if (rec != acc_rec) {
                     if (acc_mm) atomicAdd(P.rec_mism + rec_first + acc_rec, (unsigned long long)acc_mm);
                     acc_rec = rec;
@@ -393,7 +394,8 @@ __device__ __forceinline__ void lane_list(WarpSmem &S, unsigned lane, uint32_t b
 __device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, const TileTab &T, unsigned lane, unsigned adj, uint32_t n_tab, uint32_t rec_first,
                                         uint32_t base, unsigned long long slot0) {
     for (uint32_t e = lane + (adj ? 0u : 1u); e < n_tab; e += 32) {
-        const uint32_t misc = T.get(e).misc;
+        const OpEntry en = T.get(e);
+        const uint32_t misc = en.misc;
         const uint32_t w = (misc >> ES_WIN) & 0xffu;
         const uint32_t r = (uint32_t)S.lanex[w >> 3] + S.prel[w];
         const uint32_t k = r - base;
@@ -401,7 +403,7 @@ __device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, cons
             const uint32_t close0 = WIN_BASES * w - ((misc >> ES_GAP) & 63u);
             if (misc & EF_PASS) S.list[k] = e | (close0 << LS_CLOSE) | LE_PASS;
             else reinterpret_cast<uint16_t *>(S.list)[2 * k + 1] = (uint16_t)close0;
-            if ((misc & EF_HEAD) && k < (uint32_t)LIST_CAP) P.rec_out_begin[rec_first + T.rec(e)] = (int64_t)(slot0 + r);
+            if ((misc & EF_HEAD) && k < (uint32_t)LIST_CAP) P.rec_out_begin[rec_first + entry_rec(en)] = (int64_t)(slot0 + r);
         }
     }
 }
@@ -417,7 +419,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
     __shared__ int64_t s_ticket;
     const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     WarpSmem &S = SM[wid];
-    const TileTab T{S, P.tab_overflow + ((size_t)blockIdx.x * WARPS + wid) * TILE_TAB, P.rec_overflow + ((size_t)blockIdx.x * WARPS + wid) * TILE_TAB};
+    const TileTab T{S, P.tab_overflow + ((size_t)blockIdx.x * WARPS + wid) * TILE_TAB};
 
     // the ticket of the next CTA tile is taken while the current one is finished (its latency hides behind the
     // conversion pass and the barrier that publishes the look-back result also publishes it)
@@ -454,7 +456,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             S.lanex[lane] = (uint16_t)(inc - cnt);
             // where a run still open at the tile's last window closes: the end of that window's op if it lies inside the tile
             const OpEntry en = T.get(window_op(S, n_act - 1, adj));
-            term = (en.misc & EF_PASS) ? WIN_BASES * n_act : en.rem <= (int32_t)(WIN_BASES * n_act) ? (uint32_t)en.rem : COORD_OPEN;
+            term = (en.misc & EF_PASS) ? WIN_BASES * n_act : entry_rem(en) <= (int32_t)(WIN_BASES * n_act) ? (uint32_t)entry_rem(en) : COORD_OPEN;
         }
         const uint32_t tile_count = __shfl_sync(FULL, inc, 31);
         const uint32_t ex = inc - cnt;

@@ -90,7 +90,7 @@ struct pafgpu_ctx {
     // staging for host batches
     DevBuf in_op_begin, in_ops, in_qc, in_tc, in_qs, in_qe, in_ts, in_strand, in_seq;
     // per-batch work buffers
-    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, status, tile_first_closer, tile_open_slot, tab_overflow, rec_overflow;
+    DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, status, tile_first_closer, tile_open_slot, tab_overflow;
     DevBuf out, rec_out_begin, rec_mism, scalars;
     // serialiser
     DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
@@ -262,9 +262,7 @@ int launch_encode_once(pafgpu_ctx *c) {
     {
         const size_t warps = (size_t)c->sm_count * c->enc_ctas_per_sm * W;
         CU(c->tab_overflow.ensure(warps * TILE_TAB * sizeof(OpEntry)));
-        CU(c->rec_overflow.ensure(warps * TILE_TAB * sizeof(uint16_t)));
         P.tab_overflow = c->tab_overflow.as<OpEntry>();
-        P.rec_overflow = c->rec_overflow.as<uint16_t>();
     }
     CU(cudaEventRecord(c->ev[4], c->stream));
     if (CT > 0) {
@@ -503,7 +501,7 @@ void pafgpu_destroy(pafgpu_ctx *c) {
     c->scratch.release();
     DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
                       &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
-                      &c->status, &c->tile_first_closer, &c->tile_open_slot, &c->tab_overflow, &c->rec_overflow, &c->out, &c->rec_out_begin, &c->rec_mism,
+                      &c->status, &c->tile_first_closer, &c->tile_open_slot, &c->tab_overflow, &c->out, &c->rec_out_begin, &c->rec_mism,
                       &c->scalars, &c->trim_coords, &c->trim_lo, &c->trim_hi, &c->trim_failed, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
                       &c->ser_text};
     for (DevBuf *b : bufs) b->release();
