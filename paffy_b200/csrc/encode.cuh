@@ -411,6 +411,12 @@ __device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, cons
 #ifndef ENC_MINB
 #define ENC_MINB 8
 #endif
+#ifndef ENC_SLEEP
+#define ENC_SLEEP 64
+#endif
+#ifndef ENC_WAIT_ALL
+#define ENC_WAIT_ALL 0
+#endif
 template <int WARPS, int BATCH>
 __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kernel(EncodeParams P) {
     __shared__ WarpSmem SM[WARPS];
@@ -479,11 +485,19 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                 int64_t j = ct - 1 - (int64_t)lane;
                 for (;;) {
                     unsigned long long v = j >= 0 ? st[j] : (2ull << 62);
-                    while (__any_sync(FULL, (v >> 62) == 0)) {
-                        __nanosleep(64);
+                    unsigned incl;
+                    for (;;) {
+                        incl = __ballot_sync(FULL, (v >> 62) == 2);
+#if ENC_WAIT_ALL
+                        const unsigned need = FULL;
+#else
+                        // only the tiles back to the nearest inclusive prefix have to be published
+                        const unsigned need = incl ? incl ^ (incl - 1u) : FULL;
+#endif
+                        if (!(__ballot_sync(FULL, (v >> 62) == 0) & need)) break;
+                        __nanosleep(ENC_SLEEP);
                         v = j >= 0 ? st[j] : (2ull << 62);
                     }
-                    const unsigned incl = __ballot_sync(FULL, (v >> 62) == 2);
                     const unsigned upto = incl ? (unsigned)__ffs(incl) - 1u : 31u;  // nearest tile holding an inclusive prefix
                     unsigned long long c = lane <= upto ? (v & ST_VAL) : 0ull;
 #pragma unroll
