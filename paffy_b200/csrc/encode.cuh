@@ -85,8 +85,9 @@ __device__ __forceinline__ uint32_t entry_rec(const OpEntry &en) { return (uint3
 
 struct WarpSmem {
     OpEntry tab[TAB_SMEM];
-    uint64_t mask[MASK_PAD];          // mismatch bits of window p at p + (p >> 3)
-    uint32_t list[LIST_CAP + 2];      // events of one round (+ successor of the last), see LE_*
+    uint64_t mask[MASK_PAD + 1];      // mismatch bits of window p at 1 + p + (p >> 3); the pad word before a lane's 8
+                                      // windows holds the half-window before them
+    uint32_t list[LIST_CAP + 32];     // events of one round (+ successor of the last, + sink, + read-ahead), see LE_*
     uint16_t prel[TILE_WIN];          // events of the owning lane before window p
     uint16_t lanex[32];               // events of the tile before lane l
     uint32_t bm[TILE_ITERS];          // bit p: an op starts at tile window p
@@ -299,7 +300,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const uint64_t mx = (uint64_t)((int64_t)up >> sh);
             m0 = (uint32_t)mx;
             m1 = (uint32_t)(mx >> 32);
-            S.mask[srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
+            S.mask[1 + srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
             // per-record mismatch tally, flushed when the lane moves to another record
             if (isM) {
                 const uint32_t rec = entry_rec(en);
@@ -327,18 +328,19 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
 // An "event" is an output op: the start of an =/X run, or a pass-through op (its window holds no mismatch bits and
 // starts an op, so it shows up as one forced start bit). Coordinates are tile-relative (64 * window + base).
 // List entry of an event (32 bits):
-//   bits 0-13 coordinate of the run start, bit 15 X run            (pass-through op: bits 0-8 its table index)
+//   bits 0-13 coordinate of the run start, bit 15 X run            (pass-through op: bit 15 set: bits 12-14 its op
+//              code, 0-11 its length; bit 15 clear: bits 0-8 its table index)
 //   bits 16-30 coordinate at which the run BEFORE the event closes: the event's own coordinate inside an op, the end
 //              of the previous op at an op start (patched in by the op pass)
 //   bit 31 pass-through op
 // so that an event's length is close(next entry) - its own coordinate, computed by any lane.
-constexpr uint32_t LE_COORD = 0x3fffu, LE_X = 1u << 15, LE_CLOSE = 0x7fffu, LE_PASS = 1u << 31;
+constexpr uint32_t LE_COORD = 0x3fffu, LE_X = 1u << 15, LE_CLOSE = 0x7fffu, LE_PASS = 1u << 31, LE_INLINE = 1u << 15;
 constexpr int LS_CLOSE = 16;
 
 // run-start bits of one 32-base word: m = its mismatch bits, prev = the word before it (top bit used), forced = an op
 // starts at bit 0
-__device__ __forceinline__ uint32_t start_bits(uint32_t m, uint32_t prev, bool forced) {
-    return (m ^ ((m << 1) | (prev >> 31))) | (forced ? 1u : 0u);
+__device__ __forceinline__ uint32_t start_bits(uint32_t m, uint32_t prev, uint32_t forced) {
+    return (m ^ ((m << 1) | (prev >> 31))) | forced;
 }
 
 // table index of the op owning tile window w
@@ -349,7 +351,8 @@ __device__ __forceinline__ uint32_t window_op(const WarpSmem &S, uint32_t w, uns
 // C: events of the lane, the bitmap of its words that hold any, and the lane-relative event prefix of its windows
 __device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t n_win, uint32_t byte, uint32_t pm, uint32_t &cnt,
                                            uint32_t &nz) {
-    const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 18 * lane;
+    uint32_t *M = reinterpret_cast<uint32_t *>(S.mask) + 2 + 18 * lane;
+    M[-1] = pm;  // lane_list reads "the word before" without a special case
     cnt = 0;
     nz = 0;
     uint32_t prev = pm;
@@ -358,7 +361,7 @@ __device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t 
         const uint2 m = *reinterpret_cast<const uint2 *>(M + 2 * j);
         S.prel[8 * lane + j] = (uint16_t)cnt;
         if ((uint32_t)j < n_win) {
-            const uint32_t d0 = start_bits(m.x, prev, (byte >> j) & 1u), d1 = start_bits(m.y, m.x, false);
+            const uint32_t d0 = start_bits(m.x, prev, (byte >> j) & 1u), d1 = start_bits(m.y, m.x, 0u);
             cnt += __popc(d0) + __popc(d1);
             nz |= (d0 ? 1u : 0u) << (2 * j) | (d1 ? 2u : 0u) << (2 * j);
         }
@@ -366,26 +369,37 @@ __device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t 
     }
 }
 
-// E1: the lane's events, ranks base .. base + LIST_CAP of the tile, into the list. One event per trip whatever word
-// it comes from, so lanes stay busy as long as they have events left.
-__device__ __forceinline__ void lane_list(WarpSmem &S, unsigned lane, uint32_t byte, uint32_t pm, uint32_t nz, uint32_t ex, uint32_t base) {
-    const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 18 * lane;
-    uint32_t r = ex - base;  // wraps for events before the round; comes back to 0 exactly at entry `base`
+// bit j of byte -> bit 2j: the lane's op-start windows as a bitmap over its 16 half-window words
+__device__ __forceinline__ uint32_t spread_bits(uint32_t byte) {
+    uint32_t x = byte;
+    x = (x | (x << 4)) & 0x0f0fu;
+    x = (x | (x << 2)) & 0x3333u;
+    x = (x | (x << 1)) & 0x5555u;
+    return x;
+}
+
+static_assert(OP_X == OP_EQ + 1, "the X flag of an event is added to OP_EQ");
+constexpr uint32_t LIST_SINK = LIST_CAP + 1;  // entry nobody reads: events outside the round land there
+
+// E1: the lane's events, ranks base .. base + LIST_CAP of the tile, into the list, last event first. One event per
+// trip whatever word it comes from, so lanes stay busy as long as they have events left.
+__device__ __forceinline__ void lane_list(WarpSmem &S, unsigned lane, uint32_t fbits, uint32_t nz, uint32_t ex, uint32_t cnt, uint32_t base) {
+    const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 2 + 18 * lane;
+    uint32_t r = ex + cnt - 1u - base;  // wraps for events before the round: those go to the sink like the ones behind it
     uint32_t d = 0, m = 0, c0 = 0;
     for (;;) {
         if (d == 0) {
             if (nz == 0) break;
-            const uint32_t w = (uint32_t)__ffs((int)nz) - 1u;
-            nz &= nz - 1u;
+            const uint32_t w = 31u - (uint32_t)__clz((int)nz);
+            nz ^= 1u << w;
             m = M[w];
-            const uint32_t prev = w ? M[w - 1] : pm;
-            d = start_bits(m, prev, !(w & 1u) && ((byte >> (w >> 1)) & 1u));
+            d = start_bits(m, M[(int)w - 1], (fbits >> w) & 1u);
             c0 = 512u * lane + 32u * w;
         }
-        const uint32_t b = (uint32_t)__ffs((int)d) - 1u;
-        d &= d - 1u;
-        if (r <= (uint32_t)LIST_CAP) S.list[r] = (c0 + b) * 0x10001u | (((m >> b) & 1u) << 15);
-        r++;
+        const uint32_t b = 31u - (uint32_t)__clz((int)d);
+        d ^= 1u << b;
+        S.list[min(r, LIST_SINK)] = (c0 + b) * 0x10001u | (((m >> b) & 1u) << 15);
+        r--;
     }
 }
 
@@ -401,7 +415,12 @@ __device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, cons
         const uint32_t k = r - base;
         if (k <= (uint32_t)LIST_CAP) {
             const uint32_t close0 = WIN_BASES * w - ((misc >> ES_GAP) & 63u);
-            if (misc & EF_PASS) S.list[k] = e | (close0 << LS_CLOSE) | LE_PASS;
+            if (misc & EF_PASS) {
+                // a short op travels in the event itself, any other is fetched from the table by the conversion pass
+                const uint32_t len = (uint32_t)en.tw, top = (uint32_t)en.qw;
+                const uint32_t payload = (len < 4096u && !(top & 0xf8ffffffu)) ? LE_INLINE | ((top >> 24) << 12) | len : e;
+                S.list[k] = payload | (close0 << LS_CLOSE) | LE_PASS;
+            }
             else reinterpret_cast<uint16_t *>(S.list)[2 * k + 1] = (uint16_t)close0;
             if ((misc & EF_HEAD) && k < (uint32_t)LIST_CAP) P.rec_out_begin[rec_first + entry_rec(en)] = (int64_t)(slot0 + r);
         }
@@ -410,6 +429,9 @@ __device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, cons
 
 #ifndef ENC_MINB
 #define ENC_MINB 8
+#endif
+#ifndef ENC_DIAG
+#define ENC_DIAG 0  // experiments only: bit 0 no conversion pass, 1 no listing, 3 no compare, 4 no table, 5 no look-back
 #endif
 #ifndef ENC_SLEEP
 #define ENC_SLEEP 64
@@ -444,14 +466,17 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         uint32_t cnt = 0, nz = 0, inc = 0, byte = 0, pm = 0, term = COORD_OPEN, n_tab = 0, rec_first = 0;
         if (n_act) {
             bool any_exc;
-            build_table(P, S, T, (int64_t)first_op, s0, s0 + n_act, lane, adj, n_tab, rec_first, any_exc);
-            const uint32_t pm0 = any_exc ? compare_tile<BATCH, true>(P, S, T, n_act, lane, adj, rec_first)
+            if (!(ENC_DIAG & 16)) build_table(P, S, T, (int64_t)first_op, s0, s0 + n_act, lane, adj, n_tab, rec_first, any_exc);
+            else { any_exc = false; if (lane < TILE_ITERS) S.bm[lane] = S.bmpre[lane] = 0; }
+            uint32_t pm0 = 0;
+            if (ENC_DIAG & 24) { for (int q = lane; q < MASK_PAD + 1; q += 32) S.mask[q] = 0x0000100000000100ull * (q & 3); }
+            else pm0 = any_exc ? compare_tile<BATCH, true>(P, S, T, n_act, lane, adj, rec_first)
                                          : compare_tile<BATCH, false>(P, S, T, n_act, lane, adj, rec_first);
             __syncwarp();
             // blocked view of the tile
             byte = (S.bm[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
             const uint32_t n_win = 8u * lane >= n_act ? 0u : min(8u, n_act - 8u * lane);
-            pm = lane ? reinterpret_cast<const uint32_t *>(S.mask)[18 * lane - 3] : pm0;
+            pm = lane ? reinterpret_cast<const uint32_t *>(S.mask)[18 * lane - 1] : pm0;
             lane_count(S, lane, n_win, byte, pm, cnt, nz);
             inc = cnt;
 #pragma unroll
@@ -477,11 +502,12 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             for (int w = 0; w < WARPS; w++) agg += s_wcount[w];
             if (lane == 0) st[ct] = (ct == 0 ? ST_INCL : ST_AGG) | agg;
         }
-        if (cnt && ex <= (uint32_t)LIST_CAP) lane_list(S, lane, byte, pm, nz, ex, 0u);
+        const uint32_t fbits = spread_bits(byte);
+        if (!(ENC_DIAG & 2) && cnt && ex <= (uint32_t)LIST_CAP) lane_list(S, lane, fbits, nz, ex, cnt, 0u);
         // ---- D (second half): decoupled look-back over CTA tiles (warp 0)
         if (wid == 0) {
             unsigned long long excl = 0;
-            if (ct > 0) {
+            if (ct > 0 && !(ENC_DIAG & 32)) {
                 int64_t j = ct - 1 - (int64_t)lane;
                 for (;;) {
                     unsigned long long v = j >= 0 ? st[j] : (2ull << 62);
@@ -520,18 +546,18 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         const uint32_t next_first_op = next_tile < P.n_tiles ? __ldg(P.tile_first_op + next_tile) : 0u;
 
         // ---- E2: events -> CigarRecord words, coalesced stores; 31 events per step, lane 31 looks one ahead
-        if (n_act) {
+        if (n_act && !(ENC_DIAG & 1)) {
             unsigned long long slot0 = s_excl;
 #pragma unroll
             for (int w = 0; w < WARPS; w++) slot0 += (unsigned)w < wid ? s_wcount[w] : 0u;
             if (lane == 0 && tile_count == 0) P.tile_first_closer[tile] = term == COORD_OPEN ? INF64 : WIN_BASES * s0 + term;
-            uint64_t *outp = P.out + slot0;
             // events that may be stored (the host re-runs the pass with a larger buffer when some were dropped)
-            const uint32_t storable = (unsigned long long)P.out_cap > slot0 ? (uint32_t)min((unsigned long long)tile_count, (unsigned long long)P.out_cap - slot0) : 0u;
+            uint32_t storable = (unsigned long long)P.out_cap > slot0 ? (uint32_t)min((unsigned long long)tile_count, (unsigned long long)P.out_cap - slot0) : 0u;
+            asm volatile("" : "+r"(storable));  // keep the loop's bound check 32 bits wide
             const uint32_t open_i = term == COORD_OPEN ? tile_count - 1 : 0xffffffffu;  // a run still open at the tile's end
             for (uint32_t base = 0; base < tile_count; base += LIST_CAP) {
                 __syncwarp();
-                if (base && cnt && ex <= base + LIST_CAP && ex + cnt > base) lane_list(S, lane, byte, pm, nz, ex, base);  // dense tiles
+                if (base && cnt && ex <= base + LIST_CAP && ex + cnt > base) lane_list(S, lane, fbits, nz, ex, cnt, base);  // dense tiles
                 __syncwarp();
                 op_pass(P, S, T, lane, adj, n_tab, rec_first, base, slot0);
                 const uint32_t round_end = min(base + (uint32_t)LIST_CAP, tile_count);
@@ -539,27 +565,28 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                 if (lane == 0 && round_end == tile_count) S.list[tile_count - base] = (term & LE_CLOSE) << LS_CLOSE;
                 __syncwarp();
                 if (lane == 0 && base == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + ((S.list[0] >> LS_CLOSE) & LE_CLOSE);
-                for (uint32_t i0 = base; i0 < round_end; i0 += 31) {
-                    const uint32_t i = i0 + lane;
-                    const uint32_t e = i <= round_end ? S.list[i - base] : 0u;
+                const uint32_t lim = lane < 31 ? min(round_end, storable) : 0u;
+                const uint32_t *lp = S.list + lane;
+                uint64_t *po = P.out + slot0 + base + lane;
+                for (uint32_t i = base + lane; i - lane < round_end; i += 31, lp += 31, po += 31) {
+                    const uint32_t e = *lp;  // reads up to 31 entries past the round: never used
                     const uint32_t nx = __shfl_down_sync(FULL, e, 1);
-                    if (lane < 31 && i < round_end) {
-                        uint32_t lo, hi;
-                        if (e & LE_PASS) {
+                    if (i < lim) {
+                        const bool pass = (int32_t)e < 0;
+                        const uint32_t c = e & LE_COORD;
+                        uint32_t lo = pass ? e & 0xfffu : ((nx >> LS_CLOSE) & LE_CLOSE) - c;
+                        uint32_t hi = (pass ? (e >> 12) & 7u : (uint32_t)OP_EQ + ((e >> 15) & 1u)) << 24;
+                        if (pass && !(e & LE_INLINE)) {
                             const OpEntry en = T.get(e & 0x1ffu);
                             lo = (uint32_t)en.tw; hi = (uint32_t)en.qw;
-                        } else {
-                            const uint32_t c = e & LE_COORD;
-                            hi = (uint32_t)((e & LE_X) ? OP_X : OP_EQ) << 24;
-                            lo = ((nx >> LS_CLOSE) & LE_CLOSE) - c;
-                            if (i == open_i) {
-                                // provisional absolute start, turned into a length by stitch_kernel
-                                const uint64_t abs_start = WIN_BASES * s0 + c;
-                                lo = (uint32_t)abs_start; hi |= (uint32_t)(abs_start >> 32);
-                                P.tile_open_slot[tile] = (int64_t)(slot0 + i);
-                            }
                         }
-                        if (i < storable) outp[i] = ((uint64_t)hi << 32) | lo;
+                        if (i == open_i) {
+                            // provisional absolute start, turned into a length by stitch_kernel
+                            const uint64_t abs_start = WIN_BASES * s0 + c;
+                            lo = (uint32_t)abs_start; hi |= (uint32_t)(abs_start >> 32);
+                            P.tile_open_slot[tile] = (int64_t)(slot0 + i);
+                        }
+                        *po = ((uint64_t)hi << 32) | lo;
                     }
                 }
             }

@@ -6,7 +6,7 @@ i=0
 for d in "$@"; do
   i=$((i+1))
   PAFGPU_NVCC_DEFS="$d" python -m paffy_b200.build --force > $out/build_$i.log 2>&1 || { echo "build failed: $d"; tail -5 $out/build_$i.log; continue; }
-  timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > $out/bench_$i.json 2> $out/bench_$i.err
+  PAFGPU_DEBUG=1 timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > $out/bench_$i.json 2> $out/bench_$i.err
   python - <<PY
 import json
 try:
