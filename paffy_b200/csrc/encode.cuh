@@ -87,7 +87,7 @@ struct WarpSmem {
     OpEntry tab[TAB_SMEM];
     uint64_t mask[MASK_PAD + 1];      // mismatch bits of window p at 1 + p + (p >> 3); the pad word before a lane's 8
                                       // windows holds the half-window before them
-    uint32_t list[LIST_CAP + 32];     // events of one round (+ successor of the last, + sink, + read-ahead), see LE_*
+    uint32_t list[LIST_CAP + 1];      // events of one round (+ sink), see LE_*
     uint16_t prel[TILE_WIN];          // events of the owning lane before window p
     uint16_t lanex[32];               // events of the tile before lane l
     uint32_t bm[TILE_ITERS];          // bit p: an op starts at tile window p
@@ -327,15 +327,13 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
 // ---- C / E: blocked view. Lane owns tile windows 8 * lane .. 8 * lane + 7 = 16 half-window words of 32 bases.
 // An "event" is an output op: the start of an =/X run, or a pass-through op (its window holds no mismatch bits and
 // starts an op, so it shows up as one forced start bit). Coordinates are tile-relative (64 * window + base).
-// List entry of an event (32 bits):
-//   bits 0-13 coordinate of the run start, bit 15 X run            (pass-through op: bit 15 set: bits 12-14 its op
-//              code, 0-11 its length; bit 15 clear: bits 0-8 its table index)
-//   bits 16-30 coordinate at which the run BEFORE the event closes: the event's own coordinate inside an op, the end
-//              of the previous op at an op start (patched in by the op pass)
-//   bit 31 pass-through op
-// so that an event's length is close(next entry) - its own coordinate, computed by any lane.
-constexpr uint32_t LE_COORD = 0x3fffu, LE_X = 1u << 15, LE_CLOSE = 0x7fffu, LE_PASS = 1u << 31, LE_INLINE = 1u << 15;
-constexpr int LS_CLOSE = 16;
+// List entry of an event (32 bits) = its output word squeezed: bits 24-31 the op code, bits 0-23 the length. A run's
+// length is the distance to the next event, known to the lane that walks its events last to first (the last event of
+// a lane closes at the first event of the next lane that has any, or where the tile's last op ends); the op pass
+// shortens the run before an op start by the bases between the previous op's end and the window boundary, and writes
+// pass-through ops in (code LE_ESCAPE + table index when the length does not fit).
+constexpr uint32_t LE_LEN = 0xffffffu, LE_ESCAPE = 0xffu;
+constexpr uint32_t COORD_END = 64u * 256u;  // stand-in closing coordinate of a run left open at the tile's end
 
 // run-start bits of one 32-base word: m = its mismatch bits, prev = the word before it (top bit used), forced = an op
 // starts at bit 0
@@ -379,50 +377,73 @@ __device__ __forceinline__ uint32_t spread_bits(uint32_t byte) {
 }
 
 static_assert(OP_X == OP_EQ + 1, "the X flag of an event is added to OP_EQ");
-constexpr uint32_t LIST_SINK = LIST_CAP + 1;  // entry nobody reads: events outside the round land there
+constexpr uint32_t LIST_SINK = LIST_CAP;  // entry nobody reads: events outside the round land there
 
-// E1: the lane's events, ranks base .. base + LIST_CAP of the tile, into the list, last event first. One event per
-// trip whatever word it comes from, so lanes stay busy as long as they have events left.
-__device__ __forceinline__ void lane_list(WarpSmem &S, unsigned lane, uint32_t fbits, uint32_t nz, uint32_t ex, uint32_t cnt, uint32_t base) {
+__device__ __forceinline__ uint32_t top_bit(uint32_t x) {
+    uint32_t r;
+    asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(x));
+    return r;
+}
+
+// coordinate of the lane's first event (cnt > 0)
+__device__ __forceinline__ uint32_t first_event(const WarpSmem &S, unsigned lane, uint32_t fbits, uint32_t nz) {
+    const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 2 + 18 * lane;
+    const uint32_t w = (uint32_t)__ffs((int)nz) - 1u;
+    const uint32_t d = start_bits(M[w], M[(int)w - 1], (fbits >> w) & 1u);
+    return 512u * lane + 32u * w + (uint32_t)__ffs((int)d) - 1u;
+}
+
+// E1: the lane's events, ranks base .. base + LIST_CAP - 1 of the tile, into the list, last event first (next_c = where
+// the lane's last run closes). One event per trip whatever word it comes from, so lanes stay busy as long as they
+// have events left.
+__device__ __forceinline__ void lane_list(WarpSmem &S, unsigned lane, uint32_t fbits, uint32_t nz, uint32_t ex, uint32_t cnt, uint32_t base,
+                                          uint32_t next_c) {
     const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 2 + 18 * lane;
     uint32_t r = ex + cnt - 1u - base;  // wraps for events before the round: those go to the sink like the ones behind it
     uint32_t d = 0, m = 0, c0 = 0;
     for (;;) {
         if (d == 0) {
             if (nz == 0) break;
-            const uint32_t w = 31u - (uint32_t)__clz((int)nz);
+            const uint32_t w = top_bit(nz);
             nz ^= 1u << w;
             m = M[w];
             d = start_bits(m, M[(int)w - 1], (fbits >> w) & 1u);
             c0 = 512u * lane + 32u * w;
         }
-        const uint32_t b = 31u - (uint32_t)__clz((int)d);
+        const uint32_t b = top_bit(d);
         d ^= 1u << b;
-        S.list[min(r, LIST_SINK)] = (c0 + b) * 0x10001u | (((m >> b) & 1u) << 15);
+        const uint32_t c = c0 + b;
+        S.list[min(r, LIST_SINK)] = (((m >> b) & 1u) << 24) + (next_c - c + ((uint32_t)OP_EQ << 24));
+        next_c = c;
         r--;
     }
 }
 
-// E1': op pass. Every op that starts inside the tile patches its event: the run before it closes at the previous op's
+// E1': op pass. Every op that starts inside the tile patches the list: the run before it closes at the previous op's
 // end, a pass-through op is copied through, the first op of a record leaves the record's first output slot.
 __device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, const TileTab &T, unsigned lane, unsigned adj, uint32_t n_tab, uint32_t rec_first,
-                                        uint32_t base, unsigned long long slot0) {
+                                        uint32_t base, unsigned long long slot0, int64_t tile, uint64_t s0) {
     for (uint32_t e = lane + (adj ? 0u : 1u); e < n_tab; e += 32) {
         const OpEntry en = T.get(e);
         const uint32_t misc = en.misc;
         const uint32_t w = (misc >> ES_WIN) & 0xffu;
         const uint32_t r = (uint32_t)S.lanex[w >> 3] + S.prel[w];
         const uint32_t k = r - base;
-        if (k <= (uint32_t)LIST_CAP) {
-            const uint32_t close0 = WIN_BASES * w - ((misc >> ES_GAP) & 63u);
+        const uint32_t gap = (misc >> ES_GAP) & 63u;
+        if (k == 0) {
+            // the run before this op lives in an earlier round (already stored) or an earlier tile (stitch_kernel)
+            if (base == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + WIN_BASES * w - gap;
+            else if (gap && slot0 + r - 1 < (unsigned long long)P.out_cap) P.out[slot0 + r - 1] -= gap;
+        } else if (k < (uint32_t)LIST_CAP && gap) {  // k == LIST_CAP: first event of the next round, patched there
+            S.list[k - 1] -= gap;
+        }
+        if (k < (uint32_t)LIST_CAP) {
             if (misc & EF_PASS) {
-                // a short op travels in the event itself, any other is fetched from the table by the conversion pass
                 const uint32_t len = (uint32_t)en.tw, top = (uint32_t)en.qw;
-                const uint32_t payload = (len < 4096u && !(top & 0xf8ffffffu)) ? LE_INLINE | ((top >> 24) << 12) | len : e;
-                S.list[k] = payload | (close0 << LS_CLOSE) | LE_PASS;
+                const bool fits = len <= LE_LEN && !(top & LE_LEN) && (top >> 24) != LE_ESCAPE;
+                S.list[k] = fits ? top | len : (LE_ESCAPE << 24) | e;
             }
-            else reinterpret_cast<uint16_t *>(S.list)[2 * k + 1] = (uint16_t)close0;
-            if ((misc & EF_HEAD) && k < (uint32_t)LIST_CAP) P.rec_out_begin[rec_first + entry_rec(en)] = (int64_t)(slot0 + r);
+            if (misc & EF_HEAD) P.rec_out_begin[rec_first + entry_rec(en)] = (int64_t)(slot0 + r);
         }
     }
 }
@@ -503,7 +524,20 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             if (lane == 0) st[ct] = (ct == 0 ? ST_INCL : ST_AGG) | agg;
         }
         const uint32_t fbits = spread_bits(byte);
-        if (!(ENC_DIAG & 2) && cnt && ex <= (uint32_t)LIST_CAP) lane_list(S, lane, fbits, nz, ex, cnt, 0u);
+        // where the lane's last run closes: at the first event of the next lane that has any, else where the tile's
+        // last op ends (COORD_END when that is beyond the tile: the run stays open)
+        uint32_t next_c;
+        {
+            const unsigned nonempty = __ballot_sync(FULL, cnt != 0);
+            const uint32_t fc = cnt ? first_event(S, lane, fbits, nz) : 0u;
+            const unsigned above = lane < 31 ? nonempty >> (lane + 1) : 0u;
+            const uint32_t nfc = __shfl_sync(FULL, fc, above ? lane + (unsigned)__ffs((int)above) : lane);
+            next_c = above ? nfc : term == COORD_OPEN ? COORD_END : term;
+            // a run left open by an earlier tile closes at this tile's first event (the op pass corrects it when that
+            // event is an op start)
+            if (cnt && !(nonempty & ((1u << lane) - 1u))) P.tile_first_closer[tile] = WIN_BASES * s0 + fc;
+        }
+        if (!(ENC_DIAG & 2) && cnt && ex < (uint32_t)LIST_CAP) lane_list(S, lane, fbits, nz, ex, cnt, 0u, next_c);
         // ---- D (second half): decoupled look-back over CTA tiles (warp 0)
         if (wid == 0) {
             unsigned long long excl = 0;
@@ -545,7 +579,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         const int64_t next_tile = next_ct * WARPS + wid;
         const uint32_t next_first_op = next_tile < P.n_tiles ? __ldg(P.tile_first_op + next_tile) : 0u;
 
-        // ---- E2: events -> CigarRecord words, coalesced stores; 31 events per step, lane 31 looks one ahead
+        // ---- E2: op pass, then the list goes out as CigarRecord words with coalesced stores
         if (n_act && !(ENC_DIAG & 1)) {
             unsigned long long slot0 = s_excl;
 #pragma unroll
@@ -554,39 +588,33 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             // events that may be stored (the host re-runs the pass with a larger buffer when some were dropped)
             uint32_t storable = (unsigned long long)P.out_cap > slot0 ? (uint32_t)min((unsigned long long)tile_count, (unsigned long long)P.out_cap - slot0) : 0u;
             asm volatile("" : "+r"(storable));  // keep the loop's bound check 32 bits wide
-            const uint32_t open_i = term == COORD_OPEN ? tile_count - 1 : 0xffffffffu;  // a run still open at the tile's end
             for (uint32_t base = 0; base < tile_count; base += LIST_CAP) {
                 __syncwarp();
-                if (base && cnt && ex <= base + LIST_CAP && ex + cnt > base) lane_list(S, lane, fbits, nz, ex, cnt, base);  // dense tiles
+                if (base && cnt && ex < base + LIST_CAP && ex + cnt > base) lane_list(S, lane, fbits, nz, ex, cnt, base, next_c);  // dense tiles
                 __syncwarp();
-                op_pass(P, S, T, lane, adj, n_tab, rec_first, base, slot0);
+                op_pass(P, S, T, lane, adj, n_tab, rec_first, base, slot0, tile, s0);
+                __syncwarp();
                 const uint32_t round_end = min(base + (uint32_t)LIST_CAP, tile_count);
-                // virtual event closing the tile's last run
-                if (lane == 0 && round_end == tile_count) S.list[tile_count - base] = (term & LE_CLOSE) << LS_CLOSE;
-                __syncwarp();
-                if (lane == 0 && base == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + ((S.list[0] >> LS_CLOSE) & LE_CLOSE);
-                const uint32_t lim = lane < 31 ? min(round_end, storable) : 0u;
+                const uint32_t lim = min(round_end, storable);
                 const uint32_t *lp = S.list + lane;
                 uint64_t *po = P.out + slot0 + base + lane;
-                for (uint32_t i = base + lane; i - lane < round_end; i += 31, lp += 31, po += 31) {
-                    const uint32_t e = *lp;  // reads up to 31 entries past the round: never used
-                    const uint32_t nx = __shfl_down_sync(FULL, e, 1);
-                    if (i < lim) {
-                        const bool pass = (int32_t)e < 0;
-                        const uint32_t c = e & LE_COORD;
-                        uint32_t lo = pass ? e & 0xfffu : ((nx >> LS_CLOSE) & LE_CLOSE) - c;
-                        uint32_t hi = (pass ? (e >> 12) & 7u : (uint32_t)OP_EQ + ((e >> 15) & 1u)) << 24;
-                        if (pass && !(e & LE_INLINE)) {
-                            const OpEntry en = T.get(e & 0x1ffu);
-                            lo = (uint32_t)en.tw; hi = (uint32_t)en.qw;
-                        }
-                        if (i == open_i) {
-                            // provisional absolute start, turned into a length by stitch_kernel
-                            const uint64_t abs_start = WIN_BASES * s0 + c;
-                            lo = (uint32_t)abs_start; hi |= (uint32_t)(abs_start >> 32);
-                            P.tile_open_slot[tile] = (int64_t)(slot0 + i);
-                        }
-                        *po = ((uint64_t)hi << 32) | lo;
+                for (uint32_t i = base + lane; i < lim; i += 32, lp += 32, po += 32) {
+                    const uint32_t e = *lp;
+                    uint32_t hi = e & ~LE_LEN, lo = e & LE_LEN;
+                    if (hi == LE_ESCAPE << 24) {
+                        const OpEntry en = T.get(lo);
+                        lo = (uint32_t)en.tw; hi = (uint32_t)en.qw;
+                    }
+                    *po = ((uint64_t)hi << 32) | lo;
+                }
+                if (term == COORD_OPEN && round_end == tile_count) {
+                    // the tile's last run is still open: provisional absolute start, turned into a length by stitch_kernel
+                    __syncwarp();
+                    if (lane == 0 && tile_count - 1 < storable) {
+                        const uint32_t e = S.list[tile_count - 1 - base];
+                        const uint64_t abs_start = WIN_BASES * s0 + (COORD_END - (e & LE_LEN));
+                        P.out[slot0 + tile_count - 1] = ((uint64_t)(e & ~LE_LEN) << 32) | abs_start;
+                        P.tile_open_slot[tile] = (int64_t)(slot0 + tile_count - 1);
                     }
                 }
             }
