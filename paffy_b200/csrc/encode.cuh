@@ -198,7 +198,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
 #pragma unroll
     for (int hb = 0; hb < TILE_ITERS; hb += BATCH) {
         // issue every sequence load of the batch (inactive and pass-through windows read arena word 0: no branches)
-        uint32_t IDX[BATCH];
+        OpEntry EN[BATCH];
         uint64_t T0[BATCH], T1[BATCH], T2[BATCH], Q0[BATCH], Q1[BATCH], Q2[BATCH];
         uint64_t pm_t = 0, pm_q = 0;  // lane 0, first window only: words holding the base before the window
         uint32_t pm_k = 0;
@@ -209,8 +209,8 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const uint32_t w = S.bm[it];
             uint32_t idx = pre + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
             pre += __popc(w);
-            IDX[b] = idx;
             const OpEntry en = T.get(idx);
+            EN[b] = en;
             const bool isM = srel < n_act && !(en.misc & EF_PASS);
             const int32_t tw = isM ? en.tw + 2 * (int32_t)srel : 0;
             const int32_t qw = isM ? en.qw + 2 * (int32_t)srel : 0;
@@ -219,14 +219,15 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             Q0[b] = ldg64(qpn); Q1[b] = ldg64(qpn + 1); Q2[b] = ldg64(qpn + 2);
             if (it == 0 && lane == 0 && isM && !(w & 1u)) {
                 // tile window 0 continues an op: mismatch state of the base just before the tile
-                const uint64_t tp = ((uint64_t)(uint32_t)tw << 5) + (en.misc & 31u);
-                const uint64_t qprev = ((uint64_t)(uint32_t)qw << 5) + ((en.misc >> 5) & 31u) - 1;
+                const unsigned sht = en.misc & 31u, shq = (en.misc >> 5) & 31u;
                 if (EXC && (en.misc & EF_EXC)) {
-                    pm0 = slow_mismatch(P.G, tp - 1, qprev) ? 0x80000000u : 0u;
+                    const uint64_t tp = ((uint64_t)(uint32_t)tw << 5) + sht, qp = ((uint64_t)(uint32_t)qw << 5) + shq;
+                    pm0 = slow_mismatch(P.G, tp - 1, qp - 1) ? 0x80000000u : 0u;
                 } else {
-                    pm_t = ldg64(gw + ((tp - 1) >> 5));
-                    pm_q = ldg64(gw + (qprev >> 5));
-                    pm_k = (uint32_t)((tp - 1) & 31) | ((uint32_t)(qprev & 31) << 5) | (1u << 11);
+                    // the base before the window sits one bit down in the same word, or on top of the word before
+                    pm_t = ldg64(gw + (tw - (sht == 0)));
+                    pm_q = ldg64(gw + (qw - (shq == 0)));
+                    pm_k = ((sht - 1u) & 31u) | (((shq - 1u) & 31u) << 5) | (1u << 11);
                 }
             }
         }
@@ -263,8 +264,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
         for (int b = 0; b < BATCH; b++) {
             const int it = hb + b;
             const uint32_t srel = 32u * it + lane;
-            const uint32_t idx = IDX[b];
-            const OpEntry en = T.get(idx);
+            const OpEntry en = EN[b];
             const bool isM = srel < n_act && !(en.misc & EF_PASS);
             const int32_t rem = entry_rem(en) - WIN_BASES * (int32_t)srel;
             const uint32_t n = !isM ? 0u : rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
