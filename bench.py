@@ -179,6 +179,29 @@ def reference_arm(args, rank):
     print(json.dumps(line))
 
 
+def bind_near_gpu(index):
+    """Pin this process (its host threads and the pinned buffers they first touch) to the CPUs of the GPU's NUMA node,
+    so that staging copies do not cross sockets. No-op when the topology cannot be read."""
+    try:
+        bus = torch.cuda.get_device_properties(index).pci_bus_id
+        dom = getattr(torch.cuda.get_device_properties(index), "pci_domain_id", 0)
+        dev_id = torch.cuda.get_device_properties(index).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev_id:02x}.0"
+        node = int(open(path + "/numa_node").read())
+        if node < 0:
+            return {"numa_node": node}
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return {"numa_node": node, "cpus": len(cpus)}
+    except Exception as e:  # noqa: BLE001 - topology files differ between boxes
+        return {"error": str(e)[:80]}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -208,6 +231,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: paffy_b200 has no CPU path")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    affinity = bind_near_gpu(local) if os.environ.get("PAFGPU_BENCH_AFFINITY", "1") != "0" else None
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -343,6 +367,7 @@ def main():
                "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * el / args.steps,
                "output": "serialised PAF text (device serialiser) copied to pinned host memory",
                "pipeline": f"{len(subs)} sub-batches dealt round-robin to {len(ctxs)} contexts / host threads on the same GPU",
+               "host": {"cpus_visible": len(os.sched_getaffinity(0)), "affinity": affinity},
                "host_wall_ms_per_step_summed_over_threads": {"encode_batch_host": 1e3 * stage_s[0] / args.steps,
                                                               "serialise": 1e3 * stage_s[1] / args.steps,
                                                               "fetch_text": 1e3 * stage_s[2] / args.steps}}
