@@ -92,6 +92,7 @@ struct WarpSmem {
     uint16_t lanex[32];               // events of the tile before lane l
     uint32_t bm[TILE_ITERS];          // bit p: an op starts at tile window p
     uint32_t bmpre[TILE_ITERS];       // op starts before word k of bm
+    uint2 nf[TILE_WIN / 16];          // per 32 half-window words: .x those holding events, .y those an op starts at
 };
 
 // table entry i of the warp's tile: shared memory, or the warp's overflow area in HBM for the rare tile with more
@@ -346,6 +347,15 @@ __device__ __forceinline__ uint32_t window_op(const WarpSmem &S, uint32_t w, uns
     return S.bmpre[w >> 5] + __popc(S.bm[w >> 5] & (0xffffffffu >> (31 - (w & 31)))) - adj;
 }
 
+// bit j of byte -> bit 2j: the lane's op-start windows as a bitmap over its 16 half-window words
+__device__ __forceinline__ uint32_t spread_bits(uint32_t byte) {
+    uint32_t x = byte;
+    x = (x | (x << 4)) & 0x0f0fu;
+    x = (x | (x << 2)) & 0x3333u;
+    x = (x | (x << 1)) & 0x5555u;
+    return x;
+}
+
 // C: events of the lane, the bitmap of its words that hold any, and the lane-relative event prefix of its windows
 __device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t n_win, uint32_t byte, uint32_t pm, uint32_t &cnt,
                                            uint32_t &nz) {
@@ -365,15 +375,9 @@ __device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t 
         }
         prev = m.y;
     }
-}
-
-// bit j of byte -> bit 2j: the lane's op-start windows as a bitmap over its 16 half-window words
-__device__ __forceinline__ uint32_t spread_bits(uint32_t byte) {
-    uint32_t x = byte;
-    x = (x | (x << 4)) & 0x0f0fu;
-    x = (x | (x << 2)) & 0x3333u;
-    x = (x | (x << 1)) & 0x5555u;
-    return x;
+    uint16_t *nf16 = reinterpret_cast<uint16_t *>(S.nf);
+    nf16[4 * (lane >> 1) + (lane & 1)] = (uint16_t)nz;
+    nf16[4 * (lane >> 1) + 2 + (lane & 1)] = (uint16_t)spread_bits(byte);
 }
 
 static_assert(OP_X == OP_EQ + 1, "the X flag of an event is added to OP_EQ");
@@ -385,38 +389,83 @@ __device__ __forceinline__ uint32_t top_bit(uint32_t x) {
     return r;
 }
 
-// coordinate of the lane's first event (cnt > 0)
-__device__ __forceinline__ uint32_t first_event(const WarpSmem &S, unsigned lane, uint32_t fbits, uint32_t nz) {
-    const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 2 + 18 * lane;
-    const uint32_t w = (uint32_t)__ffs((int)nz) - 1u;
-    const uint32_t d = start_bits(M[w], M[(int)w - 1], (fbits >> w) & 1u);
-    return 512u * lane + 32u * w + (uint32_t)__ffs((int)d) - 1u;
+// E1: the events of one round, ranks base .. base + n_walk - 1 of the tile, dealt to the lanes in equal shares BY RANK
+// (not by position: a warp is as slow as its busiest lane, and run starts cluster). A lane finds the window holding
+// the last event of its share (the event prefixes of the count phase, two short binary searches), drops the events of
+// that window ranked above its share, then walks its share last to first, one event per trip whatever word it comes
+// from; words without events are skipped through the tile's bitmap of words holding events (the current group of 32
+// words stays in registers). A run closes where the next event starts: in-lane that is the event handled one trip
+// earlier; the last event of a share gets the first event of the next lane's share afterwards (closing = where the
+// tile's last run closes; only used when the round holds the tile's last event). The entry of rank base + LIST_CAP
+// (first event of the next round, walked only for its coordinate) lands in the sink. Returns the coordinate of the
+// lane's first event.
+__device__ __forceinline__ uint32_t list_round(WarpSmem &S, unsigned lane, uint32_t base, uint32_t n_walk, uint32_t closing) {
+    const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask);
+    const uint32_t q = (n_walk + 31u) >> 5;
+    const uint32_t lo_r = lane * q, hi_r = min(lo_r + q, n_walk);
+    uint32_t next_c = 0;
+    if (lo_r < hi_r) {
+        const uint32_t R = base + hi_r - 1u;  // tile rank of the last event of the share
+        uint32_t t = 0;
+#pragma unroll
+        for (uint32_t step = 16; step; step >>= 1)
+            if ((uint32_t)S.lanex[t + step] <= R) t += step;
+        const uint32_t Rl = R - S.lanex[t];
+        uint32_t W = 8u * t;
+#pragma unroll
+        for (uint32_t step = 4; step; step >>= 1)
+            if ((uint32_t)S.prel[W + step] <= Rl) W += step;
+        // run starts of window W; those ranked above R belong to the next lane
+        uint32_t wi = 2u * W;
+        const uint32_t g0 = wi >> 5;
+        const uint2 nf = S.nf[g0];
+        const uint32_t ix = 2u + wi + 2u * (wi >> 4);
+        const uint32_t m0 = M[ix], m1 = M[ix + 1];
+        uint32_t d0 = start_bits(m0, M[ix - 1], (nf.y >> (wi & 31u)) & 1u), d1 = start_bits(m1, m0, 0u);
+        uint32_t skip = min((uint32_t)S.prel[W] + __popc(d0) + __popc(d1) - 1u - Rl, 64u);
+        if (skip) {
+            unsigned long long dd = ((unsigned long long)d1 << 32) | d0;
+            do dd &= ~(0x8000000000000000ull >> __clzll((long long)dd)); while (--skip);
+            d0 = (uint32_t)dd; d1 = (uint32_t)(dd >> 32);
+        }
+        uint32_t d = d0, m = m0;
+        if (d1) { d = d1; m = m1; wi++; }
+        uint32_t gbase = 32u * g0, fy = nf.y;
+        uint32_t avail = nf.x & ((1u << (wi & 31u)) - 1u);  // words of the group below wi that hold events
+        uint32_t r = hi_r - 1u;
+        for (uint32_t n = hi_r - lo_r; n; n--) {
+            if (d == 0) {
+                if (avail == 0) {  // the share goes on in a group of words further down (bounded: never spins)
+                    do {
+                        gbase -= 32u;
+                        const uint2 nfb = S.nf[(gbase >> 5) & (TILE_WIN / 16 - 1)];
+                        avail = nfb.x; fy = nfb.y;
+                    } while (avail == 0 && gbase);
+                }
+                const uint32_t bit = top_bit(avail) & 31u;
+                avail &= ~(1u << bit);
+                wi = gbase + bit;
+                const uint32_t jx = 2u + wi + 2u * (wi >> 4);
+                m = M[jx];
+                d = start_bits(m, M[jx - 1], (fy >> bit) & 1u);
+            }
+            const uint32_t b = top_bit(d) & 31u;
+            d &= ~(1u << b);
+            const uint32_t c = 32u * wi + b;
+            S.list[r] = (((m >> b) & 1u) << 24) + (next_c - c + ((uint32_t)OP_EQ << 24));
+            next_c = c;
+            r--;
+        }
+    }
+    // the last run of the share closes at the first event of the next share
+    const uint32_t up_c = __shfl_down_sync(FULL, next_c, 1);
+    if (lo_r < hi_r) S.list[hi_r - 1u] += (lane < 31 && lo_r + q < n_walk) ? up_c : closing;
+    return next_c;
 }
 
-// E1: the lane's events, ranks base .. base + LIST_CAP - 1 of the tile, into the list, last event first (next_c = where
-// the lane's last run closes). One event per trip whatever word it comes from, so lanes stay busy as long as they
-// have events left.
-__device__ __forceinline__ void lane_list(WarpSmem &S, unsigned lane, uint32_t fbits, uint32_t nz, uint32_t ex, uint32_t cnt, uint32_t base,
-                                          uint32_t next_c) {
-    const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask) + 2 + 18 * lane;
-    uint32_t r = ex + cnt - 1u - base;  // wraps for events before the round: those go to the sink like the ones behind it
-    uint32_t d = 0, m = 0, c0 = 0;
-    for (;;) {
-        if (d == 0) {
-            if (nz == 0) break;
-            const uint32_t w = top_bit(nz);
-            nz ^= 1u << w;
-            m = M[w];
-            d = start_bits(m, M[(int)w - 1], (fbits >> w) & 1u);
-            c0 = 512u * lane + 32u * w;
-        }
-        const uint32_t b = top_bit(d);
-        d ^= 1u << b;
-        const uint32_t c = c0 + b;
-        S.list[min(r, LIST_SINK)] = (((m >> b) & 1u) << 24) + (next_c - c + ((uint32_t)OP_EQ << 24));
-        next_c = c;
-        r--;
-    }
+// rounds after the first (tiles with more than LIST_CAP events): kept out of line, the hot path stays small
+__device__ __noinline__ void list_round_dense(WarpSmem &S, unsigned lane, uint32_t base, uint32_t n_walk, uint32_t closing) {
+    list_round(S, lane, base, n_walk, closing);
 }
 
 // E1': op pass. Every op that starts inside the tile patches the list: the run before it closes at the previous op's
@@ -511,7 +560,6 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             term = (en.misc & EF_PASS) ? WIN_BASES * n_act : entry_rem(en) <= (int32_t)(WIN_BASES * n_act) ? (uint32_t)entry_rem(en) : COORD_OPEN;
         }
         const uint32_t tile_count = __shfl_sync(FULL, inc, 31);
-        const uint32_t ex = inc - cnt;
         if (lane == 0) s_wcount[wid] = tile_count;
         __syncthreads();
 
@@ -523,21 +571,14 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             for (int w = 0; w < WARPS; w++) agg += s_wcount[w];
             if (lane == 0) st[ct] = (ct == 0 ? ST_INCL : ST_AGG) | agg;
         }
-        const uint32_t fbits = spread_bits(byte);
-        // where the lane's last run closes: at the first event of the next lane that has any, else where the tile's
-        // last op ends (COORD_END when that is beyond the tile: the run stays open)
-        uint32_t next_c;
-        {
-            const unsigned nonempty = __ballot_sync(FULL, cnt != 0);
-            const uint32_t fc = cnt ? first_event(S, lane, fbits, nz) : 0u;
-            const unsigned above = lane < 31 ? nonempty >> (lane + 1) : 0u;
-            const uint32_t nfc = __shfl_sync(FULL, fc, above ? lane + (unsigned)__ffs((int)above) : lane);
-            next_c = above ? nfc : term == COORD_OPEN ? COORD_END : term;
+        // round 0 of the event list, before anybody waits for the look-back
+        const uint32_t closing = term == COORD_OPEN ? COORD_END : term;
+        if (!(ENC_DIAG & 2) && tile_count) {
+            const uint32_t first_c = list_round(S, lane, 0u, min(tile_count, (uint32_t)LIST_CAP + 1u), closing);
             // a run left open by an earlier tile closes at this tile's first event (the op pass corrects it when that
             // event is an op start)
-            if (cnt && !(nonempty & ((1u << lane) - 1u))) P.tile_first_closer[tile] = WIN_BASES * s0 + fc;
+            if (lane == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + first_c;
         }
-        if (!(ENC_DIAG & 2) && cnt && ex < (uint32_t)LIST_CAP) lane_list(S, lane, fbits, nz, ex, cnt, 0u, next_c);
         // ---- D (second half): decoupled look-back over CTA tiles (warp 0)
         if (wid == 0) {
             unsigned long long excl = 0;
@@ -590,7 +631,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             asm volatile("" : "+r"(storable));  // keep the loop's bound check 32 bits wide
             for (uint32_t base = 0; base < tile_count; base += LIST_CAP) {
                 __syncwarp();
-                if (base && cnt && ex < base + LIST_CAP && ex + cnt > base) lane_list(S, lane, fbits, nz, ex, cnt, base, next_c);  // dense tiles
+                if (base) list_round_dense(S, lane, base, min(tile_count - base, (uint32_t)LIST_CAP + 1u), closing);  // dense tiles
                 __syncwarp();
                 op_pass(P, S, T, lane, adj, n_tab, rec_first, base, slot0, tile, s0);
                 __syncwarp();
