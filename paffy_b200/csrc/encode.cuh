@@ -88,7 +88,7 @@ struct WarpSmem {
     uint64_t mask[MASK_PAD + 1];      // mismatch bits of window p at 1 + p + (p >> 3); the pad word before a lane's 8
                                       // windows holds the half-window before them
     uint32_t list[LIST_CAP + 1];      // events of one round (+ sink), see LE_*
-    uint16_t prel[TILE_WIN];          // events of the owning lane before window p
+    alignas(16) uint16_t prel[TILE_WIN];  // events of the owning lane before window p
     uint16_t lanex[32];               // events of the tile before lane l
     uint32_t bm[TILE_ITERS];          // bit p: an op starts at tile window p
     uint32_t bmpre[TILE_ITERS];       // op starts before word k of bm
@@ -195,7 +195,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
     static_assert(TILE_ITERS % BATCH == 0, "BATCH must divide the iterations of a tile");
     const uint64_t *__restrict__ gw = P.G.words;
     uint32_t pre = 0, pm0 = 0;
-    uint32_t acc_rec = INF32, acc_mm = 0;
+    uint32_t cur = 0, acc = 0;  // record (relative to rec_first) being tallied, and the lane's share of its mismatches
 #pragma unroll
     for (int hb = 0; hb < TILE_ITERS; hb += BATCH) {
         // issue every sequence load of the batch (inactive and pass-through windows read arena word 0: no branches)
@@ -302,25 +302,24 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             m0 = (uint32_t)mx;
             m1 = (uint32_t)(mx >> 32);
             S.mask[1 + srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
-            // per-record mismatch tally, flushed when the lane moves to another record
-            if (isM) {
-                const uint32_t rec = entry_rec(en);
-                if (rec != acc_rec) {
-                    if (acc_mm) atomicAdd(P.rec_mism + rec_first + acc_rec, (unsigned long long)acc_mm);
-                    acc_rec = rec;
-                    acc_mm = 0;
+            // per-record mismatch tally. Records do not decrease along the window axis, so the warp tallies one
+            // record at a time and moves on together: one reduction and one atomic per record and tile.
+            {
+                const uint32_t rec = isM ? entry_rec(en) : cur;
+                for (;;) {
+                    acc += rec == cur ? mm_count : 0u;
+                    if (__all_sync(FULL, rec <= cur)) break;
+                    const uint32_t sum = __reduce_add_sync(FULL, acc);
+                    if (lane == 0 && sum) atomicAdd(P.rec_mism + rec_first + cur, (unsigned long long)sum);
+                    acc = 0;
+                    cur = __reduce_min_sync(FULL, rec > cur ? rec : 0xffffffffu);
                 }
-                acc_mm += mm_count;
             }
         }
     }
-    // flush the tallies: one atomic per warp when the whole tile is one record
-    const uint32_t r0 = __shfl_sync(FULL, acc_rec, 0);
-    if (__all_sync(FULL, acc_rec == r0)) {
-        const uint32_t sum = __reduce_add_sync(FULL, acc_mm);
-        if (lane == 0 && sum && r0 != INF32) atomicAdd(P.rec_mism + rec_first + r0, (unsigned long long)sum);
-    } else if (acc_mm && acc_rec != INF32) {
-        atomicAdd(P.rec_mism + rec_first + acc_rec, (unsigned long long)acc_mm);
+    {
+        const uint32_t sum = __reduce_add_sync(FULL, acc);
+        if (lane == 0 && sum) atomicAdd(P.rec_mism + rec_first + cur, (unsigned long long)sum);
     }
     return pm0;
 }
@@ -364,10 +363,11 @@ __device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t 
     cnt = 0;
     nz = 0;
     uint32_t prev = pm;
+    uint32_t pk[TILE_ITERS / 2];
 #pragma unroll
     for (int j = 0; j < TILE_ITERS; j++) {
         const uint2 m = *reinterpret_cast<const uint2 *>(M + 2 * j);
-        S.prel[8 * lane + j] = (uint16_t)cnt;
+        if (j & 1) pk[j >> 1] |= cnt << 16; else pk[j >> 1] = cnt;
         if ((uint32_t)j < n_win) {
             const uint32_t d0 = start_bits(m.x, prev, (byte >> j) & 1u), d1 = start_bits(m.y, m.x, 0u);
             cnt += __popc(d0) + __popc(d1);
@@ -375,6 +375,8 @@ __device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t 
         }
         prev = m.y;
     }
+    static_assert(TILE_ITERS == 8, "the prefixes of a lane's windows go out as one 16-byte store");
+    *reinterpret_cast<uint4 *>(&S.prel[8 * lane]) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
     uint16_t *nf16 = reinterpret_cast<uint16_t *>(S.nf);
     nf16[4 * (lane >> 1) + (lane & 1)] = (uint16_t)nz;
     nf16[4 * (lane >> 1) + 2 + (lane & 1)] = (uint16_t)spread_bits(byte);
