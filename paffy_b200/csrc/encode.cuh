@@ -51,7 +51,9 @@ constexpr int TILE_ITERS = 8;                 // windows per lane per warp tile
 constexpr int TILE_WIN = 32 * TILE_ITERS;     // windows per warp tile
 constexpr int TILE_TAB = TILE_WIN + 2;        // a tile overlaps at most TILE_WIN + 1 ops
 constexpr int TAB_SMEM = 112;                 // table entries kept in shared memory; denser tiles spill the rest to HBM
-constexpr int MASK_PAD = TILE_WIN + TILE_WIN / 8;  // mask of window p sits at p + (p >> 3): conflict-free blocked reads
+constexpr int MASK_PAD = TILE_WIN + TILE_WIN / 16;  // mask of window p sits at p + (p >> 4): striped 8-byte stores (16 lanes = 128
+                                                     // contiguous bytes) and blocked 8-byte loads (lane stride 64 bytes, one more slot
+                                                     // every other lane) are both free of bank conflicts
 constexpr int LIST_CAP = 448;                 // events converted per round
 constexpr uint32_t COORD_OPEN = 0xffffffffu;
 constexpr unsigned long long ST_AGG = 1ull << 62, ST_INCL = 2ull << 62, ST_VAL = (1ull << 62) - 1;
@@ -85,8 +87,8 @@ __device__ __forceinline__ uint32_t entry_rec(const OpEntry &en) { return (uint3
 
 struct WarpSmem {
     OpEntry tab[TAB_SMEM];
-    uint64_t mask[MASK_PAD + 1];      // mismatch bits of window p at 1 + p + (p >> 3); the pad word before a lane's 8
-                                      // windows holds the half-window before them
+    uint64_t mask[MASK_PAD + 1];      // mismatch bits of window p at 1 + p + (p >> 4); the word before a lane's 8
+                                      // windows is the half-window before them (a pad word filled in for even lanes)
     uint32_t list[LIST_CAP + 1];      // events of one round (+ sink), see LE_*
     alignas(16) uint16_t prel[TILE_WIN];  // events of the owning lane before window p
     uint16_t lanex[32];               // events of the tile before lane l
@@ -301,7 +303,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const uint64_t mx = (uint64_t)((int64_t)up >> sh);
             m0 = (uint32_t)mx;
             m1 = (uint32_t)(mx >> 32);
-            S.mask[1 + srel + (srel >> 3)] = ((uint64_t)m1 << 32) | m0;
+            S.mask[1 + srel + (srel >> 4)] = ((uint64_t)m1 << 32) | m0;
             // per-record mismatch tally. Records do not decrease along the window axis, so the warp tallies one
             // record at a time and moves on together: one reduction and one atomic per record and tile.
             {
@@ -358,8 +360,8 @@ __device__ __forceinline__ uint32_t spread_bits(uint32_t byte) {
 // C: events of the lane, the bitmap of its words that hold any, and the lane-relative event prefix of its windows
 __device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t n_win, uint32_t byte, uint32_t pm, uint32_t &cnt,
                                            uint32_t &nz) {
-    uint32_t *M = reinterpret_cast<uint32_t *>(S.mask) + 2 + 18 * lane;
-    M[-1] = pm;  // lane_list reads "the word before" without a special case
+    uint32_t *M = reinterpret_cast<uint32_t *>(S.mask) + 2 + 16 * lane + 2 * (lane >> 1);
+    if (!(lane & 1)) M[-1] = pm;  // pad word: the listing reads "the word before" without a special case
     cnt = 0;
     nz = 0;
     uint32_t prev = pm;
@@ -421,7 +423,7 @@ __device__ __forceinline__ uint32_t list_round(WarpSmem &S, unsigned lane, uint3
         uint32_t wi = 2u * W;
         const uint32_t g0 = wi >> 5;
         const uint2 nf = S.nf[g0];
-        const uint32_t ix = 2u + wi + 2u * (wi >> 4);
+        const uint32_t ix = 2u + wi + 2u * (wi >> 5);
         const uint32_t m0 = M[ix], m1 = M[ix + 1];
         uint32_t d0 = start_bits(m0, M[ix - 1], (nf.y >> (wi & 31u)) & 1u), d1 = start_bits(m1, m0, 0u);
         uint32_t skip = min((uint32_t)S.prel[W] + __popc(d0) + __popc(d1) - 1u - Rl, 64u);
@@ -447,7 +449,7 @@ __device__ __forceinline__ uint32_t list_round(WarpSmem &S, unsigned lane, uint3
                 const uint32_t bit = top_bit(avail) & 31u;
                 avail &= ~(1u << bit);
                 wi = gbase + bit;
-                const uint32_t jx = 2u + wi + 2u * (wi >> 4);
+                const uint32_t jx = 2u + wi + 2u * (wi >> 5);
                 m = M[jx];
                 d = start_bits(m, M[jx - 1], (fy >> bit) & 1u);
             }
@@ -548,7 +550,8 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             // blocked view of the tile
             byte = (S.bm[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
             const uint32_t n_win = 8u * lane >= n_act ? 0u : min(8u, n_act - 8u * lane);
-            pm = lane ? reinterpret_cast<const uint32_t *>(S.mask)[18 * lane - 1] : pm0;
+            // last half-window of the lane before (odd lanes: directly before the lane's words; even lanes: before the pad)
+            pm = lane ? reinterpret_cast<const uint32_t *>(S.mask)[2 + 16 * lane + 2 * (lane >> 1) - ((lane & 1) ? 1 : 3)] : pm0;
             lane_count(S, lane, n_win, byte, pm, cnt, nz);
             inc = cnt;
 #pragma unroll
