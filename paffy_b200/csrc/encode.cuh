@@ -24,6 +24,10 @@
 #pragma once
 #include "kernels.cuh"
 
+#ifndef ENC_ROLL_HB
+#define ENC_ROLL_HB 0  // 1: the batch loop of the compare phase is not unrolled (smaller code)
+#endif
+
 namespace pafgpu {
 
 struct EncodeParams {
@@ -198,7 +202,11 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
     const uint64_t *__restrict__ gw = P.G.words;
     uint32_t pre = 0, pm0 = 0;
     uint32_t cur = 0, acc = 0;  // record (relative to rec_first) being tallied, and the lane's share of its mismatches
+#if ENC_ROLL_HB
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
     for (int hb = 0; hb < TILE_ITERS; hb += BATCH) {
         // issue every sequence load of the batch (inactive and pass-through windows read arena word 0: no branches)
         OpEntry EN[BATCH];
@@ -212,7 +220,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const uint32_t w = S.bm[it];
             uint32_t idx = pre + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
             pre += __popc(w);
-            const OpEntry en = T.get(idx);
+            const OpEntry en = EXC ? T.get(idx) : S.tab[idx];  // (the slow variant also serves tiles whose table spills)
             EN[b] = en;
             const bool isM = srel < n_act && !(en.misc & EF_PASS);
             const int32_t tw = isM ? en.tw + 2 * (int32_t)srel : 0;
@@ -245,7 +253,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
                 const uint32_t idx = pre2 + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
                 pre2 += __popc(w);
                 if (srel < n_act) {
-                    const OpEntry en = T.get(idx);
+                    const OpEntry en = EXC ? T.get(idx) : S.tab[idx];  // (the slow variant also serves tiles whose table spills)
                     if (!(en.misc & EF_PASS)) {
                         const uint64_t *tpn = gw + (en.tw + 2 * (int32_t)srel), *qpn = gw + (en.qw + 2 * (int32_t)srel);
                         // a window spans 3 words, the next lane's window starts 2 words on: the middle word of every
@@ -544,7 +552,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             else { any_exc = false; if (lane < TILE_ITERS) S.bm[lane] = S.bmpre[lane] = 0; }
             uint32_t pm0 = 0;
             if (ENC_DIAG & 24) { for (int q = lane; q < MASK_PAD + 1; q += 32) S.mask[q] = 0x0000100000000100ull * (q & 3); }
-            else pm0 = any_exc ? compare_tile<BATCH, true>(P, S, T, n_act, lane, adj, rec_first)
+            else pm0 = (any_exc || n_tab > (uint32_t)TAB_SMEM) ? compare_tile<BATCH, true>(P, S, T, n_act, lane, adj, rec_first)
                                          : compare_tile<BATCH, false>(P, S, T, n_act, lane, adj, rec_first);
             __syncwarp();
             // blocked view of the tile
