@@ -341,8 +341,8 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
 // length is the distance to the next event, known to the lane that walks its events last to first (the last event of
 // a lane closes at the first event of the next lane that has any, or where the tile's last op ends); the op pass
 // shortens the run before an op start by the bases between the previous op's end and the window boundary, and writes
-// pass-through ops in (code LE_ESCAPE + table index when the length does not fit).
-constexpr uint32_t LE_LEN = 0xffffffu, LE_ESCAPE = 0xffu;
+// pass-through ops in (one whose length does not fit is stored whole after the copy-out, escape_pass).
+constexpr uint32_t LE_LEN = 0xffffffu;
 constexpr uint32_t COORD_END = 64u * 256u;  // stand-in closing coordinate of a run left open at the tile's end
 
 // run-start bits of one 32-base word: m = its mismatch bits, prev = the word before it (top bit used), forced = an op
@@ -482,8 +482,10 @@ __device__ __noinline__ void list_round_dense(WarpSmem &S, unsigned lane, uint32
 
 // E1': op pass. Every op that starts inside the tile patches the list: the run before it closes at the previous op's
 // end, a pass-through op is copied through, the first op of a record leaves the record's first output slot.
-__device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, const TileTab &T, unsigned lane, unsigned adj, uint32_t n_tab, uint32_t rec_first,
+// Returns whether some pass-through op of the round does not fit a list entry (escape_pass stores those).
+__device__ __forceinline__ bool op_pass(const EncodeParams &P, WarpSmem &S, const TileTab &T, unsigned lane, unsigned adj, uint32_t n_tab, uint32_t rec_first,
                                         uint32_t base, unsigned long long slot0, int64_t tile, uint64_t s0) {
+    bool escaped = false;
     for (uint32_t e = lane + (adj ? 0u : 1u); e < n_tab; e += 32) {
         const OpEntry en = T.get(e);
         const uint32_t misc = en.misc;
@@ -501,11 +503,27 @@ __device__ __forceinline__ void op_pass(const EncodeParams &P, WarpSmem &S, cons
         if (k < (uint32_t)LIST_CAP) {
             if (misc & EF_PASS) {
                 const uint32_t len = (uint32_t)en.tw, top = (uint32_t)en.qw;
-                const bool fits = len <= LE_LEN && !(top & LE_LEN) && (top >> 24) != LE_ESCAPE;
-                S.list[k] = fits ? top | len : (LE_ESCAPE << 24) | e;
+                const bool fits = len <= LE_LEN && !(top & LE_LEN);
+                S.list[k] = top | (len & LE_LEN);
+                escaped |= !fits;
             }
             if (misc & EF_HEAD) P.rec_out_begin[rec_first + entry_rec(en)] = (int64_t)(slot0 + r);
         }
+    }
+    return __any_sync(FULL, escaped);
+}
+
+// pass-through ops of the round whose length needs more than the 24 bits of a list entry: stored whole, after the
+// copy-out (out of line: a 16 Mb insertion or deletion is rare)
+__device__ __noinline__ void escape_pass(const EncodeParams &P, const WarpSmem &S, const TileTab &T, unsigned lane, unsigned adj, uint32_t n_tab,
+                                         uint32_t base, unsigned long long slot0) {
+    for (uint32_t e = lane + (adj ? 0u : 1u); e < n_tab; e += 32) {
+        const OpEntry en = T.get(e);
+        const uint32_t w = (en.misc >> ES_WIN) & 0xffu;
+        const uint32_t r = (uint32_t)S.lanex[w >> 3] + S.prel[w];
+        const uint32_t len = (uint32_t)en.tw, top = (uint32_t)en.qw;
+        if ((en.misc & EF_PASS) && r - base < (uint32_t)LIST_CAP && (len > LE_LEN || (top & LE_LEN)) && slot0 + r < (unsigned long long)P.out_cap)
+            P.out[slot0 + r] = ((uint64_t)top << 32) | len;
     }
 }
 
@@ -646,7 +664,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                 __syncwarp();
                 if (base) list_round_dense(S, lane, base, min(tile_count - base, (uint32_t)LIST_CAP + 1u), closing);  // dense tiles
                 __syncwarp();
-                op_pass(P, S, T, lane, adj, n_tab, rec_first, base, slot0, tile, s0);
+                const bool escaped = op_pass(P, S, T, lane, adj, n_tab, rec_first, base, slot0, tile, s0);
                 __syncwarp();
                 const uint32_t round_end = min(base + (uint32_t)LIST_CAP, tile_count);
                 const uint32_t lim = min(round_end, storable);
@@ -654,12 +672,11 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                 uint64_t *po = P.out + slot0 + base + lane;
                 for (uint32_t i = base + lane; i < lim; i += 32, lp += 32, po += 32) {
                     const uint32_t e = *lp;
-                    uint32_t hi = e & ~LE_LEN, lo = e & LE_LEN;
-                    if (hi == LE_ESCAPE << 24) {
-                        const OpEntry en = T.get(lo);
-                        lo = (uint32_t)en.tw; hi = (uint32_t)en.qw;
-                    }
-                    *po = ((uint64_t)hi << 32) | lo;
+                    *po = ((uint64_t)(e & ~LE_LEN) << 32) | (e & LE_LEN);
+                }
+                if (escaped) {
+                    __syncwarp();
+                    escape_pass(P, S, T, lane, adj, n_tab, base, slot0);
                 }
                 if (term == COORD_OPEN && round_end == tile_count) {
                     // the tile's last run is still open: provisional absolute start, turned into a length by stitch_kernel

@@ -56,6 +56,19 @@ def test_long_ops_span_tiles(ctx):
     assert res.n_tiles > 20
 
 
+def test_huge_indels_escape_the_event_list(ctx):
+    """I / D / = ops longer than 2^24 bases do not fit a 32-bit list entry: they are stored whole after the copy-out."""
+    rng = np.random.default_rng(5)
+    big = (1 << 24) + 12345
+    tgt = util.random_seq(rng, 2 * big + 5000, b"A", 0.9)
+    qry = util.random_seq(rng, 2 * big + 5000, b"A", 0.9)
+    ops = [(300, "M"), (big, "D"), (700, "M"), (big + 7, "I"), (64, "M"), (big, "="), (1, "M"), (3, "I"), (900, "M")]
+    q_span = sum(n for n, c in ops if c != "D")
+    recs = [dict(q="q", t="t", qs=0, qe=q_span, ts=0, strand=True, ops=ops),
+            dict(q="q", t="t", qs=17, qe=17 + q_span, ts=33, strand=True, ops=ops)]
+    check_case(ctx, dict(contigs={"t": tgt, "q": qry}, records=recs))
+
+
 def test_dense_flips_overflow_retry(ctx):
     """High-entropy genome: ~37% of bases start a run, exceeding the first capacity guess -> retry path."""
     case = util.random_case(31, n_records=30, contig_len=100000, n_ops=8, max_len=20000, p_main=0.25)
