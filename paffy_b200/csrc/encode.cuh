@@ -543,7 +543,7 @@ __device__ __noinline__ void escape_pass(const EncodeParams &P, const WarpSmem &
 template <int WARPS, int BATCH>
 __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kernel(EncodeParams P) {
     __shared__ WarpSmem SM[WARPS];
-    __shared__ uint32_t s_wcount[2][WARPS];  // by tile parity: a fast warp may count its next tile while a slow one still reads
+    __shared__ uint32_t s_wcount[WARPS];
     __shared__ unsigned long long s_excl;
     __shared__ int64_t s_ticket;
     const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -592,20 +592,15 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             term = (en.misc & EF_PASS) ? WIN_BASES * n_act : entry_rem(en) <= (int32_t)(WIN_BASES * n_act) ? (uint32_t)entry_rem(en) : COORD_OPEN;
         }
         const uint32_t tile_count = __shfl_sync(FULL, inc, 31);
-        if (lane == 0) s_wcount[par][wid] = tile_count;
-        // "counts ready": only warp 0 (which publishes their sum) waits for it, the other warps just arrive and go on
-        // listing their events
-        if (WARPS > 1) {
-            if (wid == 0) asm volatile("barrier.sync 1, %0;" ::"r"(32 * WARPS) : "memory");
-            else asm volatile("barrier.arrive 1, %0;" ::"r"(32 * WARPS) : "memory");
-        }
+        if (lane == 0) s_wcount[wid] = tile_count;
+        __syncthreads();
 
         // ---- D (first half): publish the CTA tile's number of events, then list round 0 before anybody waits
         volatile unsigned long long *st = P.status;
         unsigned long long agg = 0;
         if (wid == 0) {
 #pragma unroll
-            for (int w = 0; w < WARPS; w++) agg += s_wcount[par][w];
+            for (int w = 0; w < WARPS; w++) agg += s_wcount[w];
             if (lane == 0) st[ct] = (ct == 0 ? ST_INCL : ST_AGG) | agg;
         }
         // round 0 of the event list, before anybody waits for the look-back
@@ -661,7 +656,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         if (n_act && !(ENC_DIAG & 1)) {
             unsigned long long slot0 = s_excl;
 #pragma unroll
-            for (int w = 0; w < WARPS; w++) slot0 += (unsigned)w < wid ? s_wcount[par][w] : 0u;
+            for (int w = 0; w < WARPS; w++) slot0 += (unsigned)w < wid ? s_wcount[w] : 0u;
             if (lane == 0 && tile_count == 0) P.tile_first_closer[tile] = term == COORD_OPEN ? INF64 : WIN_BASES * s0 + term;
             // events that may be stored (the host re-runs the pass with a larger buffer when some were dropped)
             uint32_t storable = (unsigned long long)P.out_cap > slot0 ? (uint32_t)min((unsigned long long)tile_count, (unsigned long long)P.out_cap - slot0) : 0u;
