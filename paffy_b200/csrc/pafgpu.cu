@@ -83,6 +83,8 @@ struct pafgpu_ctx {
     cudaEvent_t ev[8] = {};
     std::string err;
     uint64_t host_total = 0;
+    uint64_t *h_words = nullptr;  // pinned + mapped: kernels leave the few words the host has to read here, so that
+                                  // those reads never queue behind bulk copies on a copy engine
     std::mutex mu;  // library callers may encode from several threads (SURVEY 8b threading row)
 
     GenomeStore genome, scratch;
@@ -114,6 +116,23 @@ namespace {
 constexpr int ITERS = 8;
 constexpr uint32_t TILE_WINDOWS = 32u * ITERS;
 enum { SC_BAD = 0, SC_ALIGNED = 1, SC_TOTAL = 2, SC_TICKET = 3, SC_NWIN = 4, SC_TMP = 5, SC_COUNT = 8 };
+
+__global__ void words_out_kernel(volatile uint64_t *host_dst, const uint64_t *src, int n, uint64_t *dev_dst, const uint64_t *dev_src) {
+    if ((int)threadIdx.x < n) host_dst[threadIdx.x] = src[threadIdx.x];
+    if (dev_dst && threadIdx.x == 0) *dev_dst = *dev_src;
+}
+__global__ void scalars_init_kernel(uint64_t *sc) { sc[threadIdx.x] = threadIdx.x == SC_BAD ? ~0ull : 0ull; }
+
+// host_dst[0..n) = device words src[0..n) (n <= 32), through the mapped page; optionally *dev_dst = *dev_src on the way.
+// Synchronises the stream.
+static cudaError_t read_words(pafgpu_ctx *c, uint64_t *host_dst, const uint64_t *src, int n, uint64_t *dev_dst = nullptr,
+                              const uint64_t *dev_src = nullptr) {
+    words_out_kernel<<<1, 32, 0, c->stream>>>(c->h_words, src, n, dev_dst, dev_src);
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) return e;
+    for (int i = 0; i < n; i++) host_dst[i] = ((volatile uint64_t *)c->h_words)[i];
+    return cudaSuccess;
+}
 
 int fail(pafgpu_ctx *c, int code, const std::string &msg) {
     if (c) c->err = msg; else g_create_error = msg;
@@ -273,10 +292,8 @@ int launch_encode_once(pafgpu_ctx *c) {
     }
     CU(cudaEventRecord(c->ev[5], c->stream));
     if (T > 0) stitch_kernel<<<blocks_for(T, 256), 256, 0, c->stream>>>(T, P.tile_open_slot, P.tile_first_closer, P.out, P.out_cap);
-    CU(cudaMemcpyAsync(P.rec_out_begin + c->n_records, sc + SC_TOTAL, 8, cudaMemcpyDeviceToDevice, c->stream));
-    CU(cudaMemcpyAsync(&c->host_total, sc + SC_TOTAL, 8, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaEventRecord(c->ev[7], c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(read_words(c, &c->host_total, sc + SC_TOTAL, 1, (uint64_t *)(P.rec_out_begin + c->n_records), sc + SC_TOTAL));
     CU(cudaGetLastError());
     c->n_out = (int64_t)c->host_total;
     return 0;
@@ -315,8 +332,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     CU(c->rec_out_begin.ensure((size_t)(R + 1) * 8));
     CU(c->rec_mism.ensure((size_t)std::max<int64_t>(R, 1) * 8));
     uint64_t *sc = c->scalars.as<uint64_t>();
-    const uint64_t init[SC_COUNT] = {~0ull, 0, 0, 0, 0, 0, 0, 0};
-    CU(cudaMemcpyAsync(sc, init, sizeof init, cudaMemcpyHostToDevice, c->stream));
+    scalars_init_kernel<<<1, SC_COUNT, 0, c->stream>>>(sc);
 
     CU(cudaEventRecord(c->ev[0], c->stream));
     IngestParams I{};
@@ -350,8 +366,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
                           tfo_cap))
         return rc;
     uint64_t host_sc[SC_COUNT];
-    CU(cudaMemcpyAsync(host_sc, sc, sizeof host_sc, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(read_words(c, host_sc, sc, SC_COUNT));
     if (host_sc[SC_BAD] != ~0ull) {
         char msg[160];
         snprintf(msg, sizeof msg, "record %llu: CIGAR/coordinates walk outside the contig (or unknown contig id)",
@@ -480,6 +495,13 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
         return fail(c, PAFGPU_ENODEVICE, "cudaStreamCreate failed");
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    if (cudaHostAlloc((void **)&ctx->h_words, 64 * sizeof(uint64_t), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        cudaStreamDestroy(ctx->stream);
+        delete ctx;
+        c = nullptr;
+        return fail(c, PAFGPU_ENODEVICE, "cudaHostAlloc failed");
+    }
     {
         int per_sm = 0;
         if (const char *e = getenv("PAFGPU_WARPS")) ctx->enc_warps = atoi(e) == 1 ? 1 : atoi(e) == 2 ? 2 : 4;
@@ -506,6 +528,7 @@ void pafgpu_destroy(pafgpu_ctx *c) {
                       &c->ser_text};
     for (DevBuf *b : bufs) b->release();
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
+    if (c->h_words) cudaFreeHost(c->h_words);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -802,8 +825,7 @@ int pafgpu_serialise(pafgpu_ctx *c, const char *prefix_bytes, const int64_t *pre
     line_begin_kernel<<<blocks_for(R + 1, 256), 256, 0, c->stream>>>(R, c->ser_prefix_begin.as<int64_t>(), c->rec_out_begin.as<int64_t>(),
                                                                      c->ser_optoff.as<uint64_t>(), c->ser_line_begin.as<int64_t>());
     int64_t total = 0;
-    CU(cudaMemcpyAsync(&total, c->ser_line_begin.as<int64_t>() + R, 8, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(read_words(c, (uint64_t *)&total, c->ser_line_begin.as<uint64_t>() + R, 1));
     CU(c->ser_text.ensure((size_t)std::max<int64_t>(total, 8)));
     SerialiseParams S{};
     S.n_records = R; S.n_out = K;
