@@ -83,6 +83,7 @@ struct pafgpu_ctx {
     cudaEvent_t ev[8] = {};
     std::string err;
     uint64_t host_total = 0;
+    cudaEvent_t ev_block = nullptr;  // PAFGPU_BLOCKING_SYNC=1: host threads sleep in stream_sync instead of spinning
     uint64_t *h_words = nullptr;  // pinned + mapped: kernels leave the few words the host has to read here, so that
                                   // those reads never queue behind bulk copies on a copy engine
     std::mutex mu;  // library callers may encode from several threads (SURVEY 8b threading row)
@@ -117,6 +118,13 @@ constexpr int ITERS = 8;
 constexpr uint32_t TILE_WINDOWS = 32u * ITERS;
 enum { SC_BAD = 0, SC_ALIGNED = 1, SC_TOTAL = 2, SC_TICKET = 3, SC_NWIN = 4, SC_TMP = 5, SC_COUNT = 8 };
 
+// wait for the context's stream; with ev_block the thread sleeps (many ranks x contexts on few host cores)
+static cudaError_t stream_sync(pafgpu_ctx *c) {
+    if (!c->ev_block) return cudaStreamSynchronize(c->stream);
+    cudaError_t e = cudaEventRecord(c->ev_block, c->stream);
+    return e != cudaSuccess ? e : cudaEventSynchronize(c->ev_block);
+}
+
 __global__ void words_out_kernel(volatile uint64_t *host_dst, const uint64_t *src, int n, uint64_t *dev_dst, const uint64_t *dev_src) {
     if ((int)threadIdx.x < n) host_dst[threadIdx.x] = src[threadIdx.x];
     if (dev_dst && threadIdx.x == 0) *dev_dst = *dev_src;
@@ -128,7 +136,7 @@ __global__ void scalars_init_kernel(uint64_t *sc) { sc[threadIdx.x] = threadIdx.
 static cudaError_t read_words(pafgpu_ctx *c, uint64_t *host_dst, const uint64_t *src, int n, uint64_t *dev_dst = nullptr,
                               const uint64_t *dev_src = nullptr) {
     words_out_kernel<<<1, 32, 0, c->stream>>>(c->h_words, src, n, dev_dst, dev_src);
-    cudaError_t e = cudaStreamSynchronize(c->stream);
+    cudaError_t e = stream_sync(c);
     if (e != cudaSuccess) return e;
     for (int i = 0; i < n; i++) host_dst[i] = ((volatile uint64_t *)c->h_words)[i];
     return cudaSuccess;
@@ -170,7 +178,7 @@ int genome_grow(pafgpu_ctx *c, GenomeStore &g, int64_t need_bases) {
     if (need_bases <= g.cap_bases) return 0;
     int64_t cap = std::max<int64_t>(need_bases, g.cap_bases + g.cap_bases / 2);
     cap = align_up(cap, ARENA_ALIGN);
-    CU(cudaStreamSynchronize(c->stream));
+    CU(stream_sync(c));
     // +4 words / +2 groups of slack so a window's third word and rank lookups one past the end stay in bounds
     if (cap >= (1ll << 36)) return fail(c, PAFGPU_EINVAL, "genome arena limited to 2^36 bases per GPU (32-bit word indices)");
     CU(g.words.ensure((size_t)(cap / 32 + 4) * 8, (size_t)(g.cap_bases / 32 + 4) * 8, true));
@@ -197,7 +205,7 @@ int genome_pack_copy(pafgpu_ctx *c, GenomeStore &g, const uint8_t *src, int64_t 
                                                                         g.rank.as<uint32_t>() + off / 1024);
     uint64_t n_exc = 0;
     CU(cudaMemcpyAsync(&n_exc, c->woff.as<uint64_t>() + n_groups, 8, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(stream_sync(c));
     if (n_exc) {
         CU(g.exc.ensure((size_t)(g.exc_total + n_exc) * 32, (size_t)g.exc_total * 32));
         exc_fill_kernel<<<blocks_for(n_words, 256), 256, 0, c->stream>>>(src, len, (uint64_t)off / 32, g.flags.as<uint32_t>(),
@@ -212,7 +220,7 @@ int genome_pack_copy(pafgpu_ctx *c, GenomeStore &g, const uint8_t *src, int64_t 
         std::vector<uint32_t> fill((size_t)std::min<int64_t>(g1 - g0, 4), g.exc_total);
         // only the next pad / next contig start is ever consulted before being rewritten; set a few groups
         CU(cudaMemcpyAsync(g.rank.as<uint32_t>() + g0, fill.data(), fill.size() * 4, cudaMemcpyHostToDevice, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
+        CU(stream_sync(c));
     }
     CU(cudaGetLastError());
     return 0;
@@ -253,7 +261,7 @@ int genome_sync_table(pafgpu_ctx *c, GenomeStore &g) {
         CU(cudaMemcpyAsync(g.d_off.p, g.off.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemcpyAsync(g.d_off_rc.p, g.off_rc.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemcpyAsync(g.d_len.p, g.len.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
+        CU(stream_sync(c));
     }
     g.table_dirty = false;
     return 0;
@@ -407,7 +415,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     c->aligned = aligned;
     if (int rc = launch_encode(c, aligned)) return rc;
     CU(cudaEventRecord(c->ev[3], c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(stream_sync(c));
     c->have_batch = true;
     if (res) {
         memset(res, 0, sizeof *res);
@@ -456,7 +464,7 @@ int fetch_ops(pafgpu_ctx *c, uint64_t *out_ops, int64_t *out_op_begin, int64_t *
         CU(cudaMemcpyAsync(out_op_begin, c->rec_out_begin.p, (size_t)(c->n_records + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
     if (rec_mismatch && c->n_records)
         CU(cudaMemcpyAsync(rec_mismatch, c->rec_mism.p, (size_t)c->n_records * 8, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(stream_sync(c));
     return 0;
 }
 
@@ -495,6 +503,8 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
         return fail(c, PAFGPU_ENODEVICE, "cudaStreamCreate failed");
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    if (const char *e = getenv("PAFGPU_BLOCKING_SYNC"))
+        if (atoi(e)) cudaEventCreateWithFlags(&ctx->ev_block, cudaEventBlockingSync | cudaEventDisableTiming);
     if (cudaHostAlloc((void **)&ctx->h_words, 64 * sizeof(uint64_t), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
         cudaGetLastError();
         cudaStreamDestroy(ctx->stream);
@@ -518,7 +528,7 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
 void pafgpu_destroy(pafgpu_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
+    stream_sync(c);
     c->genome.release();
     c->scratch.release();
     DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
@@ -528,6 +538,7 @@ void pafgpu_destroy(pafgpu_ctx *c) {
                       &c->ser_text};
     for (DevBuf *b : bufs) b->release();
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
+    if (c->ev_block) cudaEventDestroy(c->ev_block);
     if (c->h_words) cudaFreeHost(c->h_words);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -655,7 +666,7 @@ int pafgpu_genome_fetch(pafgpu_ctx *c, int64_t id, int64_t start, int64_t len, c
     unpack_kernel<<<blocks_for(len, 256), 256, 0, c->stream>>>(c->genome.view(), (uint64_t)(c->genome.off[(size_t)id] + start), len,
                                                                c->in_seq.as<uint8_t>());
     CU(cudaMemcpyAsync(out, c->in_seq.p, (size_t)len, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(stream_sync(c));
     return 0;
 }
 
@@ -701,7 +712,7 @@ int pafgpu_time_encode(pafgpu_ctx *c, int reps, float *ms_stage, float *ms_kerne
         CU(cudaEventRecord(c->ev[2], c->stream));
         if (int rc = launch_encode(c, c->aligned)) return rc;
         CU(cudaEventRecord(c->ev[3], c->stream));
-        CU(cudaStreamSynchronize(c->stream));
+        CU(stream_sync(c));
         float ms = 0;
         cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]);
         sum += ms;
@@ -793,7 +804,7 @@ int pafgpu_trim(pafgpu_ctx *c, float score_fraction, float max_fraction, const i
         CU(cudaMemcpyAsync(lo.data(), T.lo, (size_t)R * 8, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaMemcpyAsync(hi.data(), T.hi, (size_t)R * 8, cudaMemcpyDeviceToHost, c->stream));
     }
-    CU(cudaStreamSynchronize(c->stream));
+    CU(stream_sync(c));
     CU(cudaGetLastError());
     if (kept_ops) for (int64_t i = 0; i < R; i++) kept_ops[i] = hi[(size_t)i] - lo[(size_t)i];
     c->trimmed = true;
@@ -836,7 +847,7 @@ int pafgpu_serialise(pafgpu_ctx *c, const char *prefix_bytes, const int64_t *pre
     if (R > 0) prefix_copy_kernel<<<blocks_for(R * 32, 256), 256, 0, c->stream>>>(S);
     if (K > 0) op_text_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(S);
     CU(cudaEventRecord(c->ev[1], c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(stream_sync(c));
     CU(cudaGetLastError());
     c->ser_text_bytes = total;
     if (text_bytes_out) *text_bytes_out = total;
@@ -853,7 +864,7 @@ int pafgpu_fetch_text(pafgpu_ctx *c, char *text, int64_t *line_begin) {
         CU(cudaMemcpyAsync(text, c->ser_text.p, (size_t)c->ser_text_bytes, cudaMemcpyDeviceToHost, c->stream));
     if (line_begin)
         CU(cudaMemcpyAsync(line_begin, c->ser_line_begin.p, (size_t)(c->n_records + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(stream_sync(c));
     return 0;
 }
 
