@@ -27,8 +27,11 @@ import torch  # noqa: E402
 
 METRIC = "add_mismatches aligned bp/sec"
 UNIT = "aligned bp/s"
-KERNELS_PER_STEP = 6       # ingest, 3x scan (the last also writes tile_first_op), encode, stitch
-KERNELS_PER_E2E_STEP = 13  # + op_text_len, 3x scan, line_begin, prefix_copy, op_text
+# kernels of ours per batch: scalars_init, ingest, 3x scan (the last also writes tile_first_op), words_out (scalars to the
+# host), encode, stitch, words_out (number of output ops)
+KERNELS_PER_STEP = 9
+# per sub-batch of the e2e pipeline: the above + op_text_len, 3x scan, line_begin, words_out (text size), prefix_copy, op_text
+KERNELS_PER_E2E_SUBBATCH = 17
 
 
 def peaks():
@@ -368,6 +371,7 @@ def main():
                "output": "serialised PAF text (device serialiser) copied to pinned host memory",
                "pipeline": f"{len(subs)} sub-batches per step dealt round-robin to {len(ctxs)} contexts / host threads on the same GPU; the K steps stream back to back, all of them inside the timed region",
                "host": {"cpus_visible": len(os.sched_getaffinity(0)), "affinity": affinity},
+               "gpu_launches_per_step": KERNELS_PER_E2E_SUBBATCH * len(subs),
                "host_wall_ms_per_step_summed_over_threads": {"encode_batch_host": 1e3 * stage_s[0] / args.steps,
                                                               "serialise": 1e3 * stage_s[1] / args.steps,
                                                               "fetch_text": 1e3 * stage_s[2] / args.steps}}

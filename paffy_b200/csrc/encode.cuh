@@ -55,11 +55,17 @@ constexpr int WIN_BASES = 64;
 constexpr int TILE_ITERS = 8;                 // windows per lane per warp tile
 constexpr int TILE_WIN = 32 * TILE_ITERS;     // windows per warp tile
 constexpr int TILE_TAB = TILE_WIN + 2;        // a tile overlaps at most TILE_WIN + 1 ops
-constexpr int TAB_SMEM = 112;                 // table entries kept in shared memory; denser tiles spill the rest to HBM
+#ifndef ENC_TAB_SMEM
+#define ENC_TAB_SMEM 112
+#endif
+#ifndef ENC_LIST_CAP
+#define ENC_LIST_CAP 448
+#endif
+constexpr int TAB_SMEM = ENC_TAB_SMEM;                 // table entries kept in shared memory; denser tiles spill the rest to HBM
 constexpr int MASK_PAD = TILE_WIN + TILE_WIN / 16;  // mask of window p sits at p + (p >> 4): striped 8-byte stores (16 lanes = 128
                                                      // contiguous bytes) and blocked 8-byte loads (lane stride 64 bytes, one more slot
                                                      // every other lane) are both free of bank conflicts
-constexpr int LIST_CAP = 448;                 // events converted per round
+constexpr int LIST_CAP = ENC_LIST_CAP;                 // events converted per round
 constexpr uint32_t COORD_OPEN = 0xffffffffu;
 constexpr unsigned long long ST_AGG = 1ull << 62, ST_INCL = 2ull << 62, ST_VAL = (1ull << 62) - 1;
 

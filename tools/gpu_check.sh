@@ -12,7 +12,7 @@ timeout 600 python bench.py --steps 5 --warmup 3 > $out/bench_c2.json 2> $out/be
 tail -3 $out/bench_c2.err; cat $out/bench_c2.json
 B="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
 timeout 600 $B > $out/plain.log 2>&1 &&
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREG" -c 200 --csv --log-file $out/launches_c2.csv $B > $out/ncu_launch.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREG" -c 400 --csv --log-file $out/launches_c2.csv $B > $out/ncu_launch.log 2>&1
 echo "ncu launches exit $?"
 timeout 600 $B > $out/plain2.log 2>&1 &&
 timeout 1200 ncu --set full --clock-control none --import-source on -k 'regex:^(encode_kernel)' -s 3 -c 1 -o $out/prof_c2 $B > $out/ncu_full.log 2>&1
