@@ -4,7 +4,7 @@
 tag=${1:-run}
 out=gpurun_out/$tag
 mkdir -p $out
-KREG='regex:^(encode_kernel|stitch_kernel|ingest_kernel|scan_|tile_first_op|op_text|prefix_copy|line_begin)'
+KREG='regex:^(encode_kernel|stitch_kernel|ingest_kernel|scan_|scalars_init|words_out|tile_first_op|op_text|prefix_copy|line_begin)'
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $out/smi.csv
 timeout 900 python -m pytest tests -m gpu -x -q > $out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> $out/pytest_gpu.log
 tail -5 $out/pytest_gpu.log
