@@ -203,26 +203,46 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(const uint32_t
                                                                    const uint64_t *__restrict__ block_sums,
                                                                    uint64_t *__restrict__ out, uint32_t *__restrict__ tile_first_op,
                                                                    uint32_t tile_windows, uint64_t tile_cap) {
-    // thread t owns SCAN_ITEMS consecutive items so the block scan runs once
-    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+    // thread t owns SCAN_ITEMS consecutive items so the block scan runs once; a warp's 32 x SCAN_ITEMS items travel
+    // between global memory (coalesced: item = 32 * k + lane) and their owners through shared memory (owner o keeps its
+    // items at o * (SCAN_ITEMS + 1) ..: the odd stride keeps both views off each other's banks)
+    static_assert(SCAN_ITEMS == 16, "index arithmetic below assumes 16 items per thread");
+    __shared__ uint64_t stage[SCAN_THREADS / 32][32 * (SCAN_ITEMS + 1)];
+    const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint64_t *st64 = stage[wid];
+    uint32_t *st32 = reinterpret_cast<uint32_t *>(st64);
+    const int64_t wbase = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)wid * 32 * SCAN_ITEMS;
+    const int64_t base = wbase + (int64_t)lane * SCAN_ITEMS;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const unsigned p = 32u * k + lane;
+        const int64_t i = wbase + p;
+        st32[(p >> 4) * (SCAN_ITEMS + 1) + (p & 15u)] = i < n ? in[i] : 0u;
+    }
+    __syncwarp();
     uint32_t v[SCAN_ITEMS];
     uint64_t s = 0;
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
-        v[k] = (base + k < n) ? in[base + k] : 0u;
+        v[k] = st32[lane * (SCAN_ITEMS + 1) + k];
         s += v[k];
     }
     uint64_t tot;
-    uint64_t run = block_incl_scan(s, &tot) - s + block_sums[blockIdx.x];
+    uint64_t run = block_incl_scan(s, &tot) - s + block_sums[blockIdx.x];  // (its barriers also fence the staging buffer)
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
-        if (base + k < n) {
-            out[base + k] = run;
-            if (tile_first_op && v[k])
-                for (uint64_t t = (run + tile_windows - 1) / tile_windows; t * tile_windows < run + v[k] && t < tile_cap; t++)
-                    tile_first_op[t] = (uint32_t)(base + k);
-        }
+        st64[lane * (SCAN_ITEMS + 1) + k] = run;
+        if (base + k < n && tile_first_op && v[k])
+            for (uint64_t t = (run + tile_windows - 1) / tile_windows; t * tile_windows < run + v[k] && t < tile_cap; t++)
+                tile_first_op[t] = (uint32_t)(base + k);
         run += v[k];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const unsigned p = 32u * k + lane;
+        const int64_t i = wbase + p;
+        if (i < n) out[i] = st64[(p >> 4) * (SCAN_ITEMS + 1) + (p & 15u)];
     }
     if (base <= n - 1 && n - 1 < base + SCAN_ITEMS) out[n] = block_sums[blockIdx.x] + tot;
 }
