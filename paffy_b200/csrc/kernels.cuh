@@ -140,6 +140,9 @@ __global__ void unpack_kernel(Genome G, uint64_t p0, int64_t len, uint8_t *out) 
 // ------------------------------------------------------------------------------------------------
 // Exclusive scan u32 -> u64, three phases (block sums, scan of sums, apply). out has n + 1 entries.
 // ------------------------------------------------------------------------------------------------
+#ifndef SCAN_APPLY_MINB
+#define SCAN_APPLY_MINB 4
+#endif
 constexpr int SCAN_THREADS = 256, SCAN_ITEMS = 16, SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
 __device__ __forceinline__ uint64_t warp_incl_scan(uint64_t v, unsigned lane) {
@@ -199,7 +202,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_spine_kernel(uint64_t *bloc
 }
 // tile_first_op (optional): in[] are windows per op; every warp tile of tile_windows windows learns the op that owns
 // its first window (op j owns windows [out[j], out[j + 1]))
-__global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(const uint32_t *__restrict__ in, int64_t n,
+__global__ void __launch_bounds__(SCAN_THREADS, SCAN_APPLY_MINB) scan_apply_kernel(const uint32_t *__restrict__ in, int64_t n,
                                                                    const uint64_t *__restrict__ block_sums,
                                                                    uint64_t *__restrict__ out, uint32_t *__restrict__ tile_first_op,
                                                                    uint32_t tile_windows, uint64_t tile_cap) {
@@ -300,10 +303,12 @@ __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
     const uint64_t q_base = (uint64_t)(rev ? q_off + (q_len - qe) : q_off + qs);
     uint64_t t_used = 0, q_used = 0, m_sum = 0;
     bool overflow = false;
+    uint64_t w_next = (j0 + gl < j1) ? __ldg(P.ops + j0 + gl) : 0;  // one iteration ahead: two loads in flight per lane
     for (int64_t base = j0; __any_sync(FULL, base < j1); base += G) {
         const int64_t j = base + gl;
         const bool have = j < j1;
-        const uint64_t w = have ? P.ops[j] : 0;
+        const uint64_t w = w_next;
+        w_next = (j + G < j1) ? __ldg(P.ops + j + G) : 0;
         const int code = (int)(w >> 56);
         const uint64_t len = w & LEN_MASK;
         if (have && ((len >> 47) || (code == OP_M && len == 0))) overflow = true;  // negative / absurd length, or a 0M (callers drop those)
