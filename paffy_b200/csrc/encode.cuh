@@ -25,6 +25,9 @@
 #pragma once
 #include "kernels.cuh"
 
+#ifndef ENC_NO_PREFETCH
+#define ENC_NO_PREFETCH 0
+#endif
 #ifndef ENC_ROLL_HB
 #define ENC_ROLL_HB 0  // 1: the batch loop of the compare phase is not unrolled (smaller code)
 #endif
@@ -249,7 +252,7 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
                 }
             }
         }
-        if (hb == 0) {
+        if (hb == 0 && !ENC_NO_PREFETCH) {
             // the first batch's loads are in flight: pull the sequence of every later window of the tile into L2 now, so
             // that only this first batch waits for DRAM
             uint32_t pre2 = pre;
