@@ -452,32 +452,41 @@ __device__ __forceinline__ uint32_t list_round(WarpSmem &S, unsigned lane, uint3
         }
         uint32_t d = d0, m = m0;
         if (d1) { d = d1; m = m1; wi++; }
-        uint32_t gbase = 32u * g0, fy = nf.y;
-        uint32_t avail = nf.x & ((1u << (wi & 31u)) - 1u);  // words of the group below wi that hold events
-        uint32_t r = hi_r - 1u;
-        for (uint32_t n = hi_r - lo_r; n; n--) {
+        // the 32 words below wi as a sliding bitmap (bit i <-> word wb + i; words below 0 do not exist): a share seldom
+        // reaches further down, so the walk hardly ever reloads it
+        int32_t wb = (int32_t)wi - 32;
+        uint32_t avail, fy;
+        auto load_bitmap = [&]() {
+            const int32_t g = wb >> 5;
+            const uint2 lo = g >= 0 ? S.nf[g] : make_uint2(0u, 0u), hi = g >= -1 ? S.nf[(g + 1) & (TILE_WIN / 16 - 1)] : make_uint2(0u, 0u);
+            avail = __funnelshift_r(lo.x, hi.x, (uint32_t)wb & 31u);
+            fy = __funnelshift_r(lo.y, hi.y, (uint32_t)wb & 31u);
+        };
+        load_bitmap();
+        uint32_t nc = (uint32_t)OP_EQ << 24;  // closing coordinate of the run being listed, + the '=' code
+        for (uint32_t r = hi_r - 1u;; r--) {
             if (d == 0) {
-                if (avail == 0) {  // the share goes on in a group of words further down (bounded: never spins)
+                if (avail == 0) {  // bounded: never spins
                     do {
-                        gbase -= 32u;
-                        const uint2 nfb = S.nf[(gbase >> 5) & (TILE_WIN / 16 - 1)];
-                        avail = nfb.x; fy = nfb.y;
-                    } while (avail == 0 && gbase);
+                        wb -= 32;
+                        load_bitmap();
+                    } while (avail == 0 && wb > 0);
                 }
-                const uint32_t bit = top_bit(avail) & 31u;
-                avail &= ~(1u << bit);
-                wi = gbase + bit;
+                const uint32_t bit = top_bit(avail);
+                avail ^= 1u << bit;
+                wi = (uint32_t)(wb + (int32_t)bit) & (2u * TILE_WIN - 1u);  // (the mask only matters if the counts lied)
                 const uint32_t jx = 2u + wi + 2u * (wi >> 5);
                 m = M[jx];
                 d = start_bits(m, M[jx - 1], (fy >> bit) & 1u);
             }
-            const uint32_t b = top_bit(d) & 31u;
-            d &= ~(1u << b);
+            const uint32_t b = top_bit(d);
+            d ^= 1u << b;
             const uint32_t c = 32u * wi + b;
-            S.list[r] = (((m >> b) & 1u) << 24) + (next_c - c + ((uint32_t)OP_EQ << 24));
-            next_c = c;
-            r--;
+            S.list[r] = (((m >> b) & 1u) << 24) + (nc - c);
+            nc = c + ((uint32_t)OP_EQ << 24);
+            if (r == lo_r) break;
         }
+        next_c = nc - ((uint32_t)OP_EQ << 24);
     }
     // the last run of the share closes at the first event of the next share
     const uint32_t up_c = __shfl_down_sync(FULL, next_c, 1);
