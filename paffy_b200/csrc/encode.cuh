@@ -560,7 +560,10 @@ __device__ __noinline__ void escape_pass(const EncodeParams &P, const WarpSmem &
 #endif
 template <int WARPS, int BATCH>
 __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kernel(EncodeParams P) {
-    __shared__ WarpSmem SM[WARPS];
+    // up to 4 warps the tiles' working sets fit static shared memory; the 8-warp variant takes them from dynamic memory
+    extern __shared__ __align__(16) unsigned char enc_dyn_smem[];
+    __shared__ WarpSmem SM_static[WARPS <= 4 ? WARPS : 1];
+    WarpSmem *SM = WARPS <= 4 ? SM_static : reinterpret_cast<WarpSmem *>(enc_dyn_smem);
     __shared__ uint32_t s_wcount[WARPS];
     __shared__ unsigned long long s_excl;
     __shared__ int64_t s_ticket;

@@ -296,6 +296,7 @@ int launch_encode_once(pafgpu_ctx *c) {
         const unsigned grid = (unsigned)std::min<int64_t>(CT, (int64_t)c->sm_count * c->enc_ctas_per_sm);
         if (W == 1) encode_kernel<1, CMP_BATCH><<<grid, 32, 0, c->stream>>>(P);
         else if (W == 2) encode_kernel<2, CMP_BATCH><<<grid, 64, 0, c->stream>>>(P);
+        else if (W == 8) encode_kernel<8, CMP_BATCH><<<grid, 256, 8 * sizeof(WarpSmem), c->stream>>>(P);
         else encode_kernel<4, CMP_BATCH><<<grid, 128, 0, c->stream>>>(P);
     }
     CU(cudaEventRecord(c->ev[5], c->stream));
@@ -514,8 +515,11 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
     }
     {
         int per_sm = 0;
-        if (const char *e = getenv("PAFGPU_WARPS")) ctx->enc_warps = atoi(e) == 1 ? 1 : atoi(e) == 2 ? 2 : 4;
-        cudaError_t oe = ctx->enc_warps == 1   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<1, CMP_BATCH>, 32, 0)
+        if (const char *e = getenv("PAFGPU_WARPS")) ctx->enc_warps = atoi(e) == 1 ? 1 : atoi(e) == 2 ? 2 : atoi(e) == 8 ? 8 : 4;
+        if (ctx->enc_warps == 8)
+            cudaFuncSetAttribute(encode_kernel<8, CMP_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(8 * sizeof(WarpSmem)));
+        cudaError_t oe = ctx->enc_warps == 8   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<8, CMP_BATCH>, 256, 8 * sizeof(WarpSmem))
+                         : ctx->enc_warps == 1   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<1, CMP_BATCH>, 32, 0)
                          : ctx->enc_warps == 2 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<2, CMP_BATCH>, 64, 0)
                                                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<4, CMP_BATCH>, 128, 0);
         if (oe == cudaSuccess && per_sm > 0) ctx->enc_ctas_per_sm = per_sm;
