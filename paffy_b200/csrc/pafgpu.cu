@@ -78,7 +78,7 @@ struct GenomeStore {
 struct pafgpu_ctx {
     int device = 0;
     int sm_count = 148;
-    int enc_ctas_per_sm = 4, enc_warps = 4;
+    int enc_ctas_per_sm = 4, enc_warps = 8;  // 8 warps per CTA: half the tickets and look-backs of 4, still 32 warps/SM
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[8] = {};
     std::string err;
@@ -297,6 +297,7 @@ int launch_encode_once(pafgpu_ctx *c) {
         if (W == 1) encode_kernel<1, CMP_BATCH><<<grid, 32, 0, c->stream>>>(P);
         else if (W == 2) encode_kernel<2, CMP_BATCH><<<grid, 64, 0, c->stream>>>(P);
         else if (W == 8) encode_kernel<8, CMP_BATCH><<<grid, 256, 8 * sizeof(WarpSmem), c->stream>>>(P);
+        else if (W == 16) encode_kernel<16, CMP_BATCH><<<grid, 512, 16 * sizeof(WarpSmem), c->stream>>>(P);
         else encode_kernel<4, CMP_BATCH><<<grid, 128, 0, c->stream>>>(P);
     }
     CU(cudaEventRecord(c->ev[5], c->stream));
@@ -515,10 +516,13 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
     }
     {
         int per_sm = 0;
-        if (const char *e = getenv("PAFGPU_WARPS")) ctx->enc_warps = atoi(e) == 1 ? 1 : atoi(e) == 2 ? 2 : atoi(e) == 8 ? 8 : 4;
+        if (const char *e = getenv("PAFGPU_WARPS")) ctx->enc_warps = atoi(e) == 1 ? 1 : atoi(e) == 2 ? 2 : atoi(e) == 4 ? 4 : atoi(e) == 16 ? 16 : 8;
         if (ctx->enc_warps == 8)
             cudaFuncSetAttribute(encode_kernel<8, CMP_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(8 * sizeof(WarpSmem)));
-        cudaError_t oe = ctx->enc_warps == 8   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<8, CMP_BATCH>, 256, 8 * sizeof(WarpSmem))
+        if (ctx->enc_warps == 16)
+            cudaFuncSetAttribute(encode_kernel<16, CMP_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(16 * sizeof(WarpSmem)));
+        cudaError_t oe = ctx->enc_warps == 16  ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<16, CMP_BATCH>, 512, 16 * sizeof(WarpSmem))
+                         : ctx->enc_warps == 8   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<8, CMP_BATCH>, 256, 8 * sizeof(WarpSmem))
                          : ctx->enc_warps == 1   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<1, CMP_BATCH>, 32, 0)
                          : ctx->enc_warps == 2 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<2, CMP_BATCH>, 64, 0)
                                                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, encode_kernel<4, CMP_BATCH>, 128, 0);
