@@ -155,9 +155,13 @@ void pafgpu_host_free(void *p);
  *      abort on (unknown contig, paf_check failure, bad strand / CIGAR letter) ends the run: every record before it
  *      has been written, the reference's message is printed to stderr and kept in pafgpu_last_error, and 1 is
  *      returned (the reference's exit code). Negative returns are library errors. ------------------------------- */
-enum { PAFGPU_MODE_ADD = 0, PAFGPU_MODE_REMOVE = 1, PAFGPU_MODE_ADD_TRIM = 2 };
+enum { PAFGPU_MODE_ADD = 0, PAFGPU_MODE_REMOVE = 1, PAFGPU_MODE_ADD_TRIM = 2,
+       /* the record loop of paffy_view_main (impl/paf_view.c:152-192): encode every record, then print per-alignment
+        * stats lines (paf_pretty_print without the base-level alignment, impl/paf.c:270-279) and / or the aggregate line.
+        * mode = PAFGPU_MODE_VIEW | PAFGPU_VIEW_PER_ALIGNMENT | PAFGPU_VIEW_AGGREGATE. No paf_check, like the reference. */
+       PAFGPU_MODE_VIEW = 4, PAFGPU_VIEW_PER_ALIGNMENT = 1, PAFGPU_VIEW_AGGREGATE = 2 };
 typedef struct {
-    int mode;                  /* PAFGPU_MODE_*: add_mismatches, add_mismatches -a, add_mismatches | trim */
+    int mode;                  /* PAFGPU_MODE_*: add_mismatches, add_mismatches -a, add_mismatches | trim, view */
     float trim_score_fraction; /* paffy trim -r (reference default 0.05) */
     float trim_max_fraction;   /* paffy trim -t (reference default 1.0) */
     int threads;               /* host threads for parsing / rendering, 0 = all */
@@ -181,6 +185,13 @@ int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char 
  * it by name): same options (-i/--inputFile, -o/--outputFile, -a/--removeMismatches, -l/--logLevel, -h/--help,
  * FASTA files as positionals), same exit codes. Uses CUDA device $PAFFY_B200_DEVICE (default 0). */
 int paffy_add_mismatches_main(int argc, char *argv[]);
+
+/* Drop-in for paffy_view_main (impl/paf_view.c:39-215): options -i/--inputFile, -o/--outputFile, -s/--printAggregateStats,
+ * -t/--noPerAlignmentStats, -u/--errorIfIdentityLowerThanX, -v/--errorIfAlignedBasesLowerThanX, -l/--logLevel, -h/--help,
+ * at least one FASTA positional (else exit 1). Every record is encoded on the GPU exactly as add_mismatches would and
+ * its stats printed from the kernel's tallies. -a/--includeAlignment (base-level rendering of the original-case FASTA
+ * bytes) is refused with exit 1: the device keeps case-folded 2-bit genomes. */
+int paffy_view_main(int argc, char *argv[]);
 
 /* ---- multi-GPU sharding: cut n input-ordered records with the given weights (aligned bases) into
  *      `parts` contiguous ranges of near-equal weight. cuts has parts + 1 entries, cuts[0] = 0, cuts[parts] = n. */

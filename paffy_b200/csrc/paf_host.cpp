@@ -343,6 +343,7 @@ struct Filter {
     int run_batch(int64_t a, int64_t &b);
     int finish_add(int64_t a, int64_t b);
     int finish_trim(int64_t a, int64_t b);
+    int finish_view(int64_t a, int64_t b);
 };
 
 int Filter::run_batch(int64_t a, int64_t &b) {
@@ -404,29 +405,81 @@ int Filter::run_batch(int64_t a, int64_t &b) {
     }
 }
 
-// stats of records [a, b) as paf_stats_calc sees their encoded CIGARs (impl/paf.c:236-260): input ops + the mismatch
-// counts the kernel tallied per record
+// stats of one record as paf_stats_calc sees its encoded CIGAR (impl/paf.c:236-260): input ops + the mismatch count the
+// kernel tallied for the record's M ops. s: matches, mismatches, query_inserts, query_deletes, insert bases, delete bases
+static void rec_stats(const Filter &F, const Rec &r, int64_t mm, int64_t *s) {
+    int64_t m = 0;
+    for (int64_t k = r.op_begin; k < r.op_end; k++) {
+        const int c = op_code(F.in.ops[k]);
+        const int64_t n = op_len(F.in.ops[k]);
+        if (c == OPM) m += n;
+        else if (c == OPEQ) s[0] += n;
+        else if (c == OPX) s[1] += n;
+        else if (c == OPI) { s[2]++; s[4] += n; }
+        else if (c == OPD) { s[3]++; s[5] += n; }
+    }
+    s[0] += m - mm;
+    s[1] += mm;
+}
+
+// totals over records [a, b), as `paffy view -s` accumulates them (impl/paf_view.c:176-178)
 static void add_stats(Filter &F, int64_t a, int64_t b) {
     int64_t *s = F.rep.stats;
     size_t j = 0;
     for (int64_t i = a; i < b; i++) {
-        const Rec &r = F.in.recs[i];
-        int64_t m = 0;
-        for (int64_t k = r.op_begin; k < r.op_end; k++) {
-            const int c = op_code(F.in.ops[k]);
-            const int64_t n = op_len(F.in.ops[k]);
-            if (c == OPM) m += n;
-            else if (c == OPEQ) s[0] += n;
-            else if (c == OPX) s[1] += n;
-            else if (c == OPI) { s[2]++; s[4] += n; }
-            else if (c == OPD) { s[3]++; s[5] += n; }
-        }
         int64_t mm = 0;
         if (j < F.map.size() && F.map[j] == i) mm = F.mism[j++];
-        s[0] += m - mm;
-        s[1] += mm;
+        rec_stats(F, F.in.recs[i], mm, s);
         s[6]++;
     }
+}
+
+// `paffy view` (impl/paf_view.c:152-181): the encoded CIGAR itself is never printed, so nothing but the per-record
+// mismatch tallies of the kernel comes back from the device; the per-alignment line is paf_pretty_print's header
+// (impl/paf.c:270-279: float32 quotients printed with %f).
+int Filter::finish_view(int64_t a, int64_t b) {
+    std::vector<Rec> &R = in.recs;
+    const int64_t nb = (int64_t)map.size();
+    double t0 = now_s();
+    mism.assign((size_t)nb, 0);
+    if (nb) {
+        const int rc = pafgpu_fetch_ops(ctx, nullptr, nullptr, mism.data());
+        if (rc) return rc;
+    }
+    rep.s_gpu += now_s() - t0;
+    t0 = now_s();
+    add_stats(*this, a, b);
+    bool ok = true;
+    if (o.mode & PAFGPU_VIEW_PER_ALIGNMENT) {
+        std::vector<int64_t> mm_of((size_t)(b - a), 0);
+        for (int64_t j = 0; j < nb; j++) mm_of[(size_t)(map[(size_t)j] - a)] = mism[(size_t)j];
+        std::vector<std::string> part((size_t)threads);
+        parallel_for(b - a, threads, [&](int64_t i0, int64_t i1, int t) {
+            std::string &out_s = part[(size_t)t];
+            std::vector<char> line;
+            for (int64_t i = a + i0; i < a + i1; i++) {
+                const Rec &r = R[(size_t)i];
+                int64_t s[6] = {0, 0, 0, 0, 0, 0};
+                rec_stats(*this, r, mm_of[(size_t)(i - a)], s);
+                const float identity = (float)s[0] / (s[0] + s[1]);
+                const float identity_with_gaps = (float)s[0] / (s[0] + s[1] + s[4] + s[5]);
+                line.resize((size_t)r.qname_len + r.tname_len + 512);
+                const int n = snprintf(line.data(), line.size(),
+                                       "Query:%.*s\tQ-start:%lld\tQ-length:%lld\tTarget:%.*s\tT-start:%lld\tT-length:%lld\tSame-strand:%i\t"
+                                       "Score:%lld\tIdentity:%f\tIdentity-with-gaps%f\tAligned-bases:%lld\tQuery-inserts:%lld\t"
+                                       "Query-deletes:%lld\n",
+                                       (int)r.qname_len, r.qname, (long long)r.qs, (long long)(r.qe - r.qs), (int)r.tname_len, r.tname,
+                                       (long long)r.ts, (long long)(r.te - r.ts), (int)r.same_strand, (long long)r.score, identity,
+                                       identity_with_gaps, (long long)(s[0] + s[1]), (long long)s[2], (long long)s[3]);
+                out_s.append(line.data(), (size_t)n);
+            }
+        });
+        rep.s_host += now_s() - t0;
+        t0 = now_s();
+        for (auto &p : part) ok = ok && write_all(out, p.data(), p.size());
+    }
+    rep.s_write += now_s() - t0;
+    return ok ? 0 : pafgpu_internal_fail(ctx, PAFGPU_EIO, "write failed");
 }
 
 int Filter::finish_add(int64_t a, int64_t b) {
@@ -603,7 +656,11 @@ int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char 
     Filter F;
     F.ctx = ctx;
     F.o = opts ? *opts : pafgpu_file_opts{PAFGPU_MODE_ADD, 0.05f, 1.0f, 0, 0};
-    if (F.o.mode < 0 || F.o.mode > 2) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "bad mode");
+    if (F.o.mode < 0 || F.o.mode > 7 || F.o.mode == 3) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "bad mode");
+    const bool view = F.o.mode >= PAFGPU_MODE_VIEW;  // low bits: PAFGPU_VIEW_PER_ALIGNMENT, PAFGPU_VIEW_AGGREGATE
+    auto finish = [&](int64_t x, int64_t y) {
+        return view ? F.finish_view(x, y) : F.o.mode == PAFGPU_MODE_ADD ? F.finish_add(x, y) : F.finish_trim(x, y);
+    };
     F.threads = F.o.threads > 0 ? F.o.threads : hw_threads();
     const int64_t batch_bases = F.o.batch_bases > 0 ? F.o.batch_bases : (int64_t)1 << 34;
     const int64_t batch_ops = (int64_t)1 << 30;
@@ -651,7 +708,8 @@ int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char 
             if (msg.empty()) {
                 if (F.o.mode == PAFGPU_MODE_REMOVE && r.has_cigar) r.op_end = merge_matches(F.in.ops.data(), r.op_begin, r.op_end);
                 std::string why;
-                if (check_record(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, &why)) {
+                // (`view` prints without paf_check: impl/paf_view.c:152-181)
+                if (!view && check_record(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, &why)) {
                     // (the reference prints the record as it stands after encoding; this message shows its input CIGAR)
                     std::string line;
                     render_line(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, line);
@@ -701,14 +759,14 @@ int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char 
             F.rep.s_gpu += now_s() - t0;
             if (brc == 1) {  // a record walks outside its contig: the records before it are still written
                 if (b2 > a) {
-                    const int frc = F.o.mode == PAFGPU_MODE_ADD ? F.finish_add(a, b2) : F.finish_trim(a, b2);
+                    const int frc = finish(a, b2);
                     if (frc < 0) brc = frc;
                     if (frc == 1) { b2 = F.rep.failed_record; }
                 }
                 if (brc == 1 && F.rep.failed_record < 0) F.rep.failed_record = b2;
                 F.rep.records += std::max<int64_t>(0, (F.rep.failed_record >= 0 ? F.rep.failed_record : b2) - a);
             } else if (brc == 0) {
-                brc = F.o.mode == PAFGPU_MODE_ADD ? F.finish_add(a, b) : F.finish_trim(a, b);
+                brc = finish(a, b);
                 if (brc == 1) F.rep.records += F.rep.failed_record - a;
             }
         }
@@ -716,6 +774,13 @@ int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char 
         F.rep.records += b - a;
         F.rep.batches++;
         a = b;
+    }
+    if (view && rc == 0 && (F.o.mode & PAFGPU_VIEW_AGGREGATE)) {  // impl/paf_view.c:183-192
+        const int64_t *t = F.rep.stats;
+        fprintf(F.out, "Total-alignments:%lld\tAvg-Identity:%f\tAvg-Identity-with-gaps:%f\tAligned-bases:%lld\tAligned-bases-with-gaps:%lld\t"
+                       "Query-inserts:%lld\tQuery-deletes:%lld\n",
+                (long long)t[6], (float)t[0] / (t[0] + t[1]), (float)t[0] / (t[0] + t[1] + t[4] + t[5]), (long long)(t[0] + t[1]),
+                (long long)(t[0] + t[1] + t[4] + t[5]), (long long)t[2], (long long)t[3]);
     }
     if (out_path) fclose(F.out); else fflush(F.out);
     if (rc == 1) {
@@ -786,5 +851,103 @@ extern "C" int paffy_add_mismatches_main(int argc, char *argv[]) {
     pafgpu_destroy(ctx);
     if (rc) exit(1);  // st_errAbort / exit(1) in the reference
     if (verbose) fprintf(stderr, "Paffy add_mismatches is done!, %lld seconds have elapsed\n", (long long)(now_s() - t0));
+    return 0;
+}
+
+// ================================================================================================
+// Drop-in subcommand entry point `paffy view` (impl/paf_view.c:39-215).
+namespace {
+void view_usage() {
+    fprintf(stderr, "paffy view [fasta_files]xN [options], version 0.1 (paffy_b200: CUDA sm_100a path)\n");
+    fprintf(stderr, "Pretty print PAF alignments\n");
+    fprintf(stderr, "-i --inputFile : Input paf file to invert. If not specified reads from stdin\n");
+    fprintf(stderr, "-o --outputFile : Output paf file. If not specified outputs to stdout\n");
+    fprintf(stderr, "-a --includeAlignment : Include base level alignment in output (not available on the CUDA path)\n");
+    fprintf(stderr, "-s --printAggregateStats : Print overall stats about the alignments at the end\n");
+    fprintf(stderr, "-t --noPerAlignmentStats : Do not print stats about each paf\n");
+    fprintf(stderr, "-u --errorIfIdentityLowerThanX : Float between 0 and 1. Assert identity is >= X.\n");
+    fprintf(stderr, "-v --errorIfAlignedBasesLowerThanX : Integer >= 0. Assert total aligned based is >= X.\n");
+    fprintf(stderr, "-l --logLevel : Set the log level\n");
+    fprintf(stderr, "-h --help : Print this help message\n");
+}
+}  // namespace
+
+extern "C" int paffy_view_main(int argc, char *argv[]) {
+    const char *input = nullptr, *output = nullptr, *log_level = nullptr;
+    bool include_alignment = false, aggregate = false, per_alignment = true;
+    float min_identity = 0.0f;
+    int64_t min_aligned = 0;
+    static struct option long_options[] = {{"logLevel", required_argument, 0, 'l'},
+                                           {"inputFile", required_argument, 0, 'i'},
+                                           {"outputFile", required_argument, 0, 'o'},
+                                           {"includeAlignment", no_argument, 0, 'a'},
+                                           {"printAggregateStats", no_argument, 0, 's'},
+                                           {"noPerAlignmentStats", no_argument, 0, 't'},
+                                           {"errorIfIdentityLowerThanX", required_argument, 0, 'u'},
+                                           {"errorIfAlignedBasesLowerThanX", required_argument, 0, 'v'},
+                                           {"help", no_argument, 0, 'h'},
+                                           {0, 0, 0, 0}};
+    optind = 1;
+    for (;;) {
+        int idx = 0;
+        const int key = getopt_long(argc, argv, "l:i:o:hastu:v:", long_options, &idx);
+        if (key == -1) break;
+        switch (key) {
+            case 'l': log_level = optarg; break;
+            case 'i': input = optarg; break;
+            case 'o': output = optarg; break;
+            case 'a': include_alignment = true; break;
+            case 's': aggregate = true; break;
+            case 't': per_alignment = false; break;
+            case 'u': min_identity = (float)atof(optarg); break;
+            case 'v': min_aligned = atoi(optarg); break;
+            case 'h': view_usage(); return 0;
+            default: view_usage(); return 1;
+        }
+    }
+    if (optind >= argc) {
+        fprintf(stderr, "Expected at least one sequence file\n");
+        exit(1);
+    }
+    if (include_alignment) {
+        fprintf(stderr, "ERROR: paffy view -a (base-level alignment text) is not available on the CUDA path\n");
+        exit(1);
+    }
+    const bool verbose = log_level && (!strcasecmp(log_level, "INFO") || !strcasecmp(log_level, "DEBUG"));
+    const double t0 = now_s();
+    pafgpu_ctx *ctx = nullptr;
+    const char *dev = getenv("PAFFY_B200_DEVICE");
+    if (pafgpu_create(dev ? atoi(dev) : 0, &ctx)) {
+        fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(nullptr));
+        exit(1);
+    }
+    while (optind < argc) {
+        const char *fa = argv[optind++];
+        if (verbose) fprintf(stderr, "Parsing sequence file : %s\n", fa);
+        if (pafgpu_genome_load_fasta(ctx, fa)) {
+            fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
+            exit(1);
+        }
+    }
+    if (verbose) fprintf(stderr, "Read %i sequences from sequence files\n", (int)pafgpu_genome_num_contigs(ctx));
+    pafgpu_file_opts o{PAFGPU_MODE_VIEW | (per_alignment ? PAFGPU_VIEW_PER_ALIGNMENT : 0) | (aggregate ? PAFGPU_VIEW_AGGREGATE : 0),
+                       0.05f, 1.0f, 0, 0};
+    pafgpu_file_report rep;
+    const int rc = pafgpu_add_mismatches_file(ctx, input, output, &o, &rep);
+    if (rc < 0) fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
+    pafgpu_destroy(ctx);
+    if (rc) exit(1);
+    // the reference's closing asserts (impl/paf_view.c:195-196; asserts are compiled in, include.mk:32). They look at the
+    // totals whether or not -s was given.
+    const int64_t *t = rep.stats;
+    if (!((float)t[0] / (t[0] + t[1]) >= min_identity)) {
+        fprintf(stderr, "paffy view: Assertion `(float)total_matches/(total_matches+total_mismatches) >= error_if_identity_lower_than_this' failed.\n");
+        abort();
+    }
+    if (!(t[0] + t[1] >= min_aligned)) {
+        fprintf(stderr, "paffy view: Assertion `total_matches+total_mismatches >= error_if_aligned_bases_lower_than_this' failed.\n");
+        abort();
+    }
+    if (verbose) fprintf(stderr, "Paffy view is done!, %lld seconds have elapsed\n", (long long)(now_s() - t0));
     return 0;
 }

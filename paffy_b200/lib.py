@@ -23,7 +23,7 @@ ABI_SYMBOLS = [
     "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition", "pafgpu_trim",
 ]
 # reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
-REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
+REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paffy_view_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
 
 
 class PafGpuError(RuntimeError):
@@ -257,8 +257,9 @@ class Context:
         return coords, kept, failed
 
     def add_mismatches_file(self, in_path, out_path, mode=0, trim_r=0.05, trim_t=1.0, threads=0, batch_bases=0):
-        """The whole-file filter (paffy add_mismatches / -a / | trim). -> (rc, FileReport); rc 1 = a record ended the
-        run the way the reference exits 1 (message in self.last_error())."""
+        """The whole-file filter (paffy add_mismatches / -a / | trim; mode 4 | 1 | 2 = paffy view with per-alignment lines
+        and / or the aggregate line). -> (rc, FileReport); rc 1 = a record ended the run the way the reference exits 1
+        (message in self.last_error())."""
         o = FileOpts(mode, trim_r, trim_t, threads, batch_bases)
         rep = FileReport()
         rc = self.L.pafgpu_add_mismatches_file(self.h, in_path.encode(), out_path.encode(), C.byref(o), C.byref(rep))

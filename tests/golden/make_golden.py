@@ -17,6 +17,7 @@ Fixtures
   *.trim.paf               `paffy add_mismatches ... | paffy trim`           (defaults -r 0.05 -t 1.0)
   *.trimf.paf              `paffy add_mismatches ... | paffy trim -f -t 0.3` (fixed end fraction)
   *.view.txt               `paffy add_mismatches ... | paffy view -s -t X.fa` summary line
+  *.viewlines.txt          `paffy view -s X.fa -i X.paf` on the raw input: per-alignment stats lines + summary line
   errors.json              exit code / stdout / stderr head of the failing-record cases
   c1_human_chimp.paf.gz    the reference's own fixture tests/human_chimp.paf (data, gzip'd; config C1)
   c1.json                  size + md5 of the reference outputs for C1 with the seeded synthetic chr10
@@ -75,6 +76,8 @@ def pipeline(stem, fa_path, paf_bytes):
             if os.path.exists(path):
                 os.unlink(path)
     write(stem + ".view.txt", must(["view", "-s", "-t", fa_path], add))
+    # view on the raw (M) input: per-alignment lines + the summary line, i.e. paffy_view_main's own encode
+    write(stem + ".viewlines.txt", must(["view", "-s", fa_path], paf_bytes))
 
 
 def fasta_bytes(contigs, width=60):
@@ -147,6 +150,7 @@ def c1_set(tmp):
     trim = must(["trim"], add)
     view = must(["view", "-s", "-t", fa], add)
     remove = must(["add_mismatches", "-a"], add)
+    viewlines = must(["view", "-s", fa, "-i", REF_FIXTURE])
     info = {
         "input_md5": hashlib.md5(raw).hexdigest(), "input_bytes": len(raw), "records": raw.count(b"\n"),
         "genome": "tests/util.py c1_genome(): numpy default_rng(20261104).integers(0,4,133797422) -> ACGT, one contig chr10",
@@ -154,6 +158,7 @@ def c1_set(tmp):
         "trim_bytes": len(trim), "trim_md5": hashlib.md5(trim).hexdigest(),
         "remove_bytes": len(remove), "remove_md5": hashlib.md5(remove).hexdigest(),
         "view_summary": view.decode(),
+        "viewlines_bytes": len(viewlines), "viewlines_md5": hashlib.md5(viewlines).hexdigest(),
         "add_line_md5": [hashlib.md5(ln).hexdigest()[:12] for ln in add.split(b"\n")[:-1]],
     }
     with open(os.path.join(HERE, "c1.json"), "w") as fh:

@@ -96,6 +96,53 @@ def test_c1_fixture_matches_reference(fresh, tmp_path):
     assert rc == 0 and len(got) == info["trim_bytes"] and hashlib.md5(got).hexdigest() == info["trim_md5"]
 
 
+@pytest.mark.parametrize("stem", SETS)
+@pytest.mark.parametrize("batch_bases", [0, 3000])
+def test_view_file_matches_reference(fresh, stem, batch_bases, tmp_path):
+    """`paffy view -s X.fa -i X.paf` on the raw (M) input: per-alignment stats lines (paf_pretty_print header,
+    impl/paf.c:270-279) + the aggregate line, from the kernel's per-record tallies; -s -t and neither flag too."""
+    fresh.load_fasta(os.path.join(G, stem + ".fa"))
+    want = golden(stem + ".viewlines.txt")
+    out = tmp_path / "view.txt"
+    rc, rep = fresh.add_mismatches_file(os.path.join(G, stem + ".paf"), str(out), mode=4 | 1 | 2, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == want
+    lines = want.splitlines(keepends=True)
+    rc, rep = fresh.add_mismatches_file(os.path.join(G, stem + ".paf"), str(out), mode=4 | 1, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == b"".join(lines[:-1])
+    rc, rep = fresh.add_mismatches_file(os.path.join(G, stem + ".paf"), str(out), mode=4 | 2, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == lines[-1] == golden(stem + ".view.txt")
+
+
+def test_view_c1_fixture_matches_reference(fresh, tmp_path):
+    info = json.load(open(os.path.join(G, "c1.json")))
+    inp, out = tmp_path / "c1.paf", tmp_path / "c1.view"
+    inp.write_bytes(gzip.open(os.path.join(G, "c1_human_chimp.paf.gz")).read())
+    fresh.add_contig("chr10", util.c1_genome())
+    rc, rep = fresh.add_mismatches_file(str(inp), str(out), mode=4 | 1 | 2)
+    got = out.read_bytes()
+    assert rc == 0 and len(got) == info["viewlines_bytes"] and hashlib.md5(got).hexdigest() == info["viewlines_md5"]
+
+
+def test_view_cli_drop_in(tmp_path):
+    """`paffy_b200_cli view` takes the reference's arguments (impl/paf_view.c:39-113) and prints the reference's bytes."""
+    exe = os.path.join(os.path.dirname(paffy_b200.lib.LIB_PATH), "paffy_b200_cli")
+    fa, paf = os.path.join(G, "rand102.fa"), os.path.join(G, "rand102.paf")
+    r = subprocess.run([exe, "view", "-s", fa, "-i", paf], capture_output=True)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout == golden("rand102.viewlines.txt")
+    r = subprocess.run([exe, "view", "--printAggregateStats", "--noPerAlignmentStats", fa], capture_output=True, input=golden("rand102.add.paf"))
+    assert r.returncode == 0 and r.stdout == golden("rand102.view.txt")  # already encoded input: =/X pass through
+    r = subprocess.run([exe, "view", "-i", paf], capture_output=True)
+    assert r.returncode == 1 and b"Expected at least one sequence file" in r.stderr
+    r = subprocess.run([exe, "view", "-t", "-u", "0.999999", fa, "-i", paf], capture_output=True)
+    assert r.returncode == -6 and r.stdout == b""  # the reference's closing assert aborts (impl/paf_view.c:195)
+    r = subprocess.run([exe, "view", "-t", "-u", "0.1", "-v", "10", fa, "-i", paf], capture_output=True)
+    assert r.returncode == 0 and r.stdout == b""
+    r = subprocess.run([exe, "view", os.path.join(G, "edge.fa"), "-i", "/dev/stdin"], capture_output=True,
+                       input=b"q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:25M\nq\t25\t0\t25\t+\tnope\t25\t0\t25\t0\t25\t60\tcg:Z:25M\n")
+    assert r.returncode == 1 and b"No target sequence named: nope found" in r.stderr and r.stdout.count(b"\n") == 1
+
+
 def test_cli_drop_in(tmp_path):
     """`paffy_b200_cli add_mismatches` takes the reference's arguments and prints the reference's bytes."""
     exe = os.path.join(os.path.dirname(paffy_b200.lib.LIB_PATH), "paffy_b200_cli")
