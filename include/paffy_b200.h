@@ -129,6 +129,18 @@ int pafgpu_fetch_text(pafgpu_ctx *ctx, char *text, int64_t *line_begin);
 int pafgpu_trim(pafgpu_ctx *ctx, float score_fraction, float max_fraction, const int64_t *t_end, int64_t *coords,
                 int64_t *kept_ops, uint8_t *failed);
 
+/* Fixed trim, `paffy trim -f -t end_fraction` (paf_trim_end_fraction, inc/paf.h:204, impl/paf.c:589-598 with cigar_trim /
+ * cigar_trim_back :518-576) for the whole batch on the device: (int64)((float)aligned * end_fraction / 2.0) aligned
+ * bases leave each end together with the inserts / deletes met on the way; the op a cut falls in is shortened in place
+ * on the device. Same coords / kept_ops outputs as pafgpu_trim; the following pafgpu_serialise prints the kept ops. */
+int pafgpu_trim_fixed(pafgpu_ctx *ctx, float end_fraction, const int64_t *t_end, int64_t *coords, int64_t *kept_ops);
+
+/* Stage a batch whose records are ALREADY encoded (the input of `paffy trim`, impl/paf_trim.c:113-127, which has no
+ * FASTA): ops, op_begin, q_start, q_end, t_start, same_strand of `batch` (host memory; q_contig / t_contig ignored) go
+ * to the device as if an encode call had produced them, so that pafgpu_trim / pafgpu_trim_fixed, pafgpu_serialise and
+ * pafgpu_fetch_* work on them. No base is compared; per-record mismatch counts read 0. */
+int pafgpu_stage_ops_host(pafgpu_ctx *ctx, const pafgpu_batch *batch);
+
 /* ---- one-record convenience used by the paf.h-compatible paf_encode_mismatches
  *      (impl/paf.c:739-784): sequences are whole-contig host strings, indexed by absolute coordinate.
  *      Packs only the spans the record touches. out_ops is malloc'd (caller frees). ----------------- */
@@ -156,13 +168,17 @@ void pafgpu_host_free(void *p);
  *      has been written, the reference's message is printed to stderr and kept in pafgpu_last_error, and 1 is
  *      returned (the reference's exit code). Negative returns are library errors. ------------------------------- */
 enum { PAFGPU_MODE_ADD = 0, PAFGPU_MODE_REMOVE = 1, PAFGPU_MODE_ADD_TRIM = 2,
+       /* the record loop of paffy_trim_main alone (impl/paf_trim.c:113-127): no FASTA, no encode; the parsed ops are staged
+        * on the device, trimmed there (identity trim, or the fixed trim when trim_score_fraction < 0: `-f -t
+        * trim_max_fraction`), paf_check'ed and serialised */
+       PAFGPU_MODE_TRIM = 3,
        /* the record loop of paffy_view_main (impl/paf_view.c:152-192): encode every record, then print per-alignment
         * stats lines (paf_pretty_print without the base-level alignment, impl/paf.c:270-279) and / or the aggregate line.
         * mode = PAFGPU_MODE_VIEW | PAFGPU_VIEW_PER_ALIGNMENT | PAFGPU_VIEW_AGGREGATE. No paf_check, like the reference. */
        PAFGPU_MODE_VIEW = 4, PAFGPU_VIEW_PER_ALIGNMENT = 1, PAFGPU_VIEW_AGGREGATE = 2 };
 typedef struct {
     int mode;                  /* PAFGPU_MODE_*: add_mismatches, add_mismatches -a, add_mismatches | trim, view */
-    float trim_score_fraction; /* paffy trim -r (reference default 0.05) */
+    float trim_score_fraction; /* paffy trim -r (reference default 0.05); < 0 selects the fixed trim `-f` (modes 2 and 3) */
     float trim_max_fraction;   /* paffy trim -t (reference default 1.0) */
     int threads;               /* host threads for parsing / rendering, 0 = all */
     int64_t batch_bases;       /* aligned bases per GPU batch, 0 = default */

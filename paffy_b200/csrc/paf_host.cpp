@@ -348,6 +348,9 @@ struct Filter {
 
 int Filter::run_batch(int64_t a, int64_t &b) {
     std::vector<Rec> &R = in.recs;
+    // `paffy trim` alone prints every op it was given; the encoder drops zero-length M ops (SURVEY a1-edge ii)
+    const bool trim_only = o.mode == PAFGPU_MODE_TRIM;
+    auto dropped = [&](uint64_t w) { return !trim_only && op_code(w) == OPM && op_len(w) == 0; };
     for (;;) {
         // SoA of the records that carry aligned work; the others are printed by the host as they are
         map.clear();
@@ -355,7 +358,7 @@ int Filter::run_batch(int64_t a, int64_t &b) {
         for (int64_t i = a; i < b; i++) {
             if (!R[i].has_cigar) continue;
             int64_t kept = 0;
-            for (int64_t k = R[i].op_begin; k < R[i].op_end; k++) kept += !(op_code(in.ops[k]) == OPM && op_len(in.ops[k]) == 0);
+            for (int64_t k = R[i].op_begin; k < R[i].op_end; k++) kept += !dropped(in.ops[k]);
             if (!kept) continue;
             map.push_back(i);
             n_ops += kept;
@@ -370,7 +373,7 @@ int Filter::run_batch(int64_t a, int64_t &b) {
         for (int64_t j = 0; j < nb; j++) {
             const Rec &r = R[map[j]];
             int64_t kept = 0;
-            for (int64_t k = r.op_begin; k < r.op_end; k++) kept += !(op_code(in.ops[k]) == OPM && op_len(in.ops[k]) == 0);
+            for (int64_t k = r.op_begin; k < r.op_end; k++) kept += !dropped(in.ops[k]);
             begin[j + 1] = begin[j] + kept;
         }
         uint64_t *ops = p_ops.as<uint64_t>();
@@ -379,7 +382,7 @@ int Filter::run_batch(int64_t a, int64_t &b) {
                 const Rec &r = R[map[j]];
                 uint64_t *w = ops + begin[j];
                 for (int64_t k = r.op_begin; k < r.op_end; k++)
-                    if (!(op_code(in.ops[k]) == OPM && op_len(in.ops[k]) == 0)) *w++ = in.ops[k];
+                    if (!dropped(in.ops[k])) *w++ = in.ops[k];
                 p_qc.as<int32_t>()[j] = qc[map[j]]; p_tc.as<int32_t>()[j] = tc[map[j]];
                 p_qs.as<int64_t>()[j] = r.qs; p_qe.as<int64_t>()[j] = r.qe; p_ts.as<int64_t>()[j] = r.ts;
                 p_st.as<uint8_t>()[j] = r.same_strand ? 1 : 0;
@@ -387,6 +390,7 @@ int Filter::run_batch(int64_t a, int64_t &b) {
         });
         pafgpu_batch B{nb, n_ops, begin, ops, p_qc.as<int32_t>(), p_tc.as<int32_t>(), p_qs.as<int64_t>(), p_qe.as<int64_t>(),
                        p_ts.as<int64_t>(), p_st.as<uint8_t>()};
+        if (trim_only) return pafgpu_stage_ops_host(ctx, &B);
         pafgpu_result res;
         const int rc = pafgpu_encode_batch_host(ctx, &B, &res);
         if (rc == 0) {
@@ -558,7 +562,11 @@ int Filter::finish_trim(int64_t a, int64_t b) {
         std::vector<int64_t> t_end((size_t)nb), coords((size_t)nb * 4);
         std::vector<uint8_t> failed((size_t)nb);
         for (int64_t j = 0; j < nb; j++) t_end[(size_t)j] = R[(size_t)map[(size_t)j]].te;
-        if ((rc = pafgpu_trim(ctx, o.trim_score_fraction, o.trim_max_fraction, t_end.data(), coords.data(), nullptr, failed.data()))) return rc;
+        if (o.trim_score_fraction < 0)  // `paffy trim -f`: fixed end fraction (impl/paf_trim.c:119-121)
+            rc = pafgpu_trim_fixed(ctx, o.trim_max_fraction, t_end.data(), coords.data(), nullptr);
+        else
+            rc = pafgpu_trim(ctx, o.trim_score_fraction, o.trim_max_fraction, t_end.data(), coords.data(), nullptr, failed.data());
+        if (rc) return rc;
         if ((rc = pafgpu_fetch_ops(ctx, nullptr, nullptr, mism.data()))) return rc;
         rep.s_gpu += now_s() - t0;
         t0 = now_s();
@@ -572,7 +580,27 @@ int Filter::finish_trim(int64_t a, int64_t b) {
             std::string why;
             Rec coords_only = r;
             coords_only.has_cigar = false;
-            if (stop == b && (failed[(size_t)j] || check_record(coords_only, nullptr, 0, &why))) {
+            int bad = stop == b ? (failed[(size_t)j] || check_record(coords_only, nullptr, 0, &why)) : 0;
+            if (stop == b && !bad && o.mode == PAFGPU_MODE_TRIM) {
+                // paf_check's op sums after the trim (impl/paf.c:443-459): the trim moves the coordinates by exactly the
+                // spans of the ops it drops, so kept sum - new span = input sum - input span
+                const Rec &r0 = R[(size_t)map[(size_t)j]];
+                int64_t q = 0, t = 0;
+                for (int64_t k = r0.op_begin; k < r0.op_end; k++) {
+                    if (op_code(in.ops[(size_t)k]) != OPD) q += op_len(in.ops[(size_t)k]);
+                    if (op_code(in.ops[(size_t)k]) != OPI) t += op_len(in.ops[(size_t)k]);
+                }
+                const int64_t dq = q - (r0.qe - r0.qs), dt = t - (r0.te - r0.ts);
+                char buf[160];
+                if (dq) {
+                    snprintf(buf, sizeof buf, "Paf cigar alignment does not match query length: %lld vs. %lld", (long long)(r.qe - r.qs + dq), (long long)(r.qe - r.qs));
+                    why = buf; bad = 1;
+                } else if (dt) {
+                    snprintf(buf, sizeof buf, "Paf cigar alignment does not match target length: %lld vs. %lld", (long long)(r.te - r.ts + dt), (long long)(r.te - r.ts));
+                    why = buf; bad = 1;
+                }
+            }
+            if (bad) {
                 stop = map[(size_t)j];
                 if (failed[(size_t)j]) why = "trimmed alignment identity fell below the untrimmed identity (reference assert)";
                 std::string line;
@@ -656,7 +684,8 @@ int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char 
     Filter F;
     F.ctx = ctx;
     F.o = opts ? *opts : pafgpu_file_opts{PAFGPU_MODE_ADD, 0.05f, 1.0f, 0, 0};
-    if (F.o.mode < 0 || F.o.mode > 7 || F.o.mode == 3) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "bad mode");
+    if (F.o.mode < 0 || F.o.mode > 7) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "bad mode");
+    const bool trim_only = F.o.mode == PAFGPU_MODE_TRIM;
     const bool view = F.o.mode >= PAFGPU_MODE_VIEW;  // low bits: PAFGPU_VIEW_PER_ALIGNMENT, PAFGPU_VIEW_AGGREGATE
     auto finish = [&](int64_t x, int64_t y) {
         return view ? F.finish_view(x, y) : F.o.mode == PAFGPU_MODE_ADD ? F.finish_add(x, y) : F.finish_trim(x, y);
@@ -696,7 +725,11 @@ int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char 
         if (r.bad) {
             msg = "ERROR: " + parse_error(r);
         } else {
-            if (F.o.mode != PAFGPU_MODE_REMOVE) {
+            if (trim_only && r.op_end == r.op_begin) {
+                // no cg tag: the identity trim's closing assert sees 0/0 (impl/paf.c:952), the fixed trim reads a NULL
+                // cigar (impl/paf.c:520): the reference dies on this record either way
+                msg = "ERROR: paffy trim needs a cigar on every record (the reference aborts here)";
+            } else if (F.o.mode != PAFGPU_MODE_REMOVE && !trim_only) {
                 const std::string qn(r.qname, r.qname_len), tn(r.tname, r.tname_len);
                 const int64_t q = pafgpu_genome_find(ctx, qn.c_str());
                 const int64_t t = q >= 0 ? pafgpu_genome_find(ctx, tn.c_str()) : -1;
@@ -709,7 +742,8 @@ int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char 
                 if (F.o.mode == PAFGPU_MODE_REMOVE && r.has_cigar) r.op_end = merge_matches(F.in.ops.data(), r.op_begin, r.op_end);
                 std::string why;
                 // (`view` prints without paf_check: impl/paf_view.c:152-181)
-                if (!view && check_record(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, &why)) {
+                // (`paffy trim` checks after the trim only, impl/paf_trim.c:124: finish_trim)
+                if (!view && !trim_only && check_record(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, &why)) {
                     // (the reference prints the record as it stands after encoding; this message shows its input CIGAR)
                     std::string line;
                     render_line(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, line);

@@ -106,6 +106,7 @@ struct pafgpu_ctx {
 
     // last batch
     bool have_batch = false;
+    bool staged_only = false;  // the batch was uploaded already encoded (pafgpu_stage_ops_host): nothing to re-time
     int64_t bad_record = -1;
     int64_t n_records = 0, n_ops = 0, n_out = 0, n_tiles = 0, aligned = 0, retried = 0;
     uint64_t n_win = 0;
@@ -419,6 +420,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     CU(cudaEventRecord(c->ev[3], c->stream));
     CU(stream_sync(c));
     c->have_batch = true;
+    c->staged_only = false;
     if (res) {
         memset(res, 0, sizeof *res);
         res->n_out_ops = c->n_out;
@@ -713,7 +715,7 @@ int pafgpu_result_device_ptrs(pafgpu_ctx *c, const uint64_t **out_ops, const int
 int pafgpu_time_encode(pafgpu_ctx *c, int reps, float *ms_stage, float *ms_kernel) {
     if (!c || reps <= 0) return PAFGPU_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
-    if (!c->have_batch) return fail(c, PAFGPU_ESTATE, "no batch has been encoded");
+    if (!c->have_batch || c->staged_only) return fail(c, PAFGPU_ESTATE, "no batch has been encoded");
     CU(cudaSetDevice(c->device));
     double sum = 0, ksum = 0;
     for (int i = 0; i < reps; i++) {
@@ -779,8 +781,8 @@ int pafgpu_encode_one(pafgpu_ctx *c, const uint64_t *ops, int64_t n_ops, int sam
 }
 
 // ---- device trim (paf_trim_unreliable_tails, impl/paf.c:906-953) -------------------------------------
-int pafgpu_trim(pafgpu_ctx *c, float score_fraction, float max_fraction, const int64_t *t_end, int64_t *coords, int64_t *kept_ops,
-                uint8_t *failed) {
+static int trim_batch(pafgpu_ctx *c, bool fixed, float score_fraction, float max_fraction, const int64_t *t_end, int64_t *coords,
+                      int64_t *kept_ops, uint8_t *failed) {
     if (!c || !t_end || !coords) return PAFGPU_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     if (!c->have_batch) return fail(c, PAFGPU_ESTATE, "no batch has been encoded");
@@ -803,7 +805,8 @@ int pafgpu_trim(pafgpu_ctx *c, float score_fraction, float max_fraction, const i
     T.qs = co; T.qe = co + R; T.ts = co + 2 * R; T.te = co + 3 * R;
     T.lo = c->trim_lo.as<int64_t>(); T.hi = c->trim_hi.as<int64_t>(); T.failed = c->trim_failed.as<uint8_t>();
     T.score_fraction = score_fraction; T.max_fraction = max_fraction;
-    if (R > 0) trim_kernel<<<blocks_for(R, 128), 128, 0, c->stream>>>(T);
+    if (R > 0 && !fixed) trim_kernel<<<blocks_for(R, 128), 128, 0, c->stream>>>(T);
+    if (R > 0 && fixed) trim_fixed_kernel<<<blocks_for(R, 128), 128, 0, c->stream>>>(T, c->out.as<uint64_t>());
     CU(cudaMemcpyAsync(coords, co, 4 * (size_t)R * 8, cudaMemcpyDeviceToHost, c->stream));
     if (failed) CU(cudaMemcpyAsync(failed, T.failed, (size_t)R, cudaMemcpyDeviceToHost, c->stream));
     std::vector<int64_t> lo, hi;
@@ -816,6 +819,49 @@ int pafgpu_trim(pafgpu_ctx *c, float score_fraction, float max_fraction, const i
     CU(cudaGetLastError());
     if (kept_ops) for (int64_t i = 0; i < R; i++) kept_ops[i] = hi[(size_t)i] - lo[(size_t)i];
     c->trimmed = true;
+    return 0;
+}
+
+int pafgpu_trim(pafgpu_ctx *c, float score_fraction, float max_fraction, const int64_t *t_end, int64_t *coords, int64_t *kept_ops,
+                uint8_t *failed) {
+    return trim_batch(c, false, score_fraction, max_fraction, t_end, coords, kept_ops, failed);
+}
+
+int pafgpu_trim_fixed(pafgpu_ctx *c, float end_fraction, const int64_t *t_end, int64_t *coords, int64_t *kept_ops) {
+    if (!(end_fraction >= 0.0f && end_fraction <= 1.0f)) return c ? fail(c, PAFGPU_EINVAL, "end fraction outside [0, 1]") : PAFGPU_EINVAL;
+    return trim_batch(c, true, 0.0f, end_fraction, t_end, coords, kept_ops, nullptr);
+}
+
+// ---- a batch that is already encoded (the input of `paffy trim`): ops go straight to the result buffers ----------
+int pafgpu_stage_ops_host(pafgpu_ctx *c, const pafgpu_batch *b) {
+    if (!c || !b || b->n_records < 0 || b->n_ops < 0) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    const int64_t R = b->n_records, N = b->n_ops;
+    c->have_batch = false;
+    c->trimmed = false;
+    auto up = [&](DevBuf &d, const void *src, size_t bytes) -> int {
+        CU(d.ensure(std::max<size_t>(bytes, 8)));
+        if (bytes) CU(cudaMemcpyAsync(d.p, src, bytes, cudaMemcpyHostToDevice, c->stream));
+        return 0;
+    };
+    int rc;
+    if ((rc = up(c->rec_out_begin, b->op_begin, (size_t)(R + 1) * 8))) return rc;
+    if ((rc = up(c->out, b->ops, (size_t)N * 8))) return rc;
+    if ((rc = up(c->in_qs, b->q_start, (size_t)R * 8))) return rc;
+    if ((rc = up(c->in_qe, b->q_end, (size_t)R * 8))) return rc;
+    if ((rc = up(c->in_ts, b->t_start, (size_t)R * 8))) return rc;
+    if ((rc = up(c->in_strand, b->same_strand, (size_t)R))) return rc;
+    CU(c->rec_mism.ensure((size_t)std::max<int64_t>(R, 1) * 8));
+    CU(cudaMemsetAsync(c->rec_mism.p, 0, (size_t)std::max<int64_t>(R, 1) * 8, c->stream));
+    CU(stream_sync(c));
+    c->last_strand = c->in_strand.as<uint8_t>();
+    c->last_qs = c->in_qs.as<int64_t>(); c->last_qe = c->in_qe.as<int64_t>(); c->last_ts = c->in_ts.as<int64_t>();
+    c->n_records = R; c->n_ops = N; c->n_out = N; c->n_tiles = 0; c->n_win = 0; c->aligned = 0; c->retried = 0;
+    c->bad_record = -1;
+    c->ser_text_bytes = 0;
+    c->have_batch = true;
+    c->staged_only = true;
     return 0;
 }
 

@@ -110,4 +110,64 @@ __global__ void __launch_bounds__(128) trim_kernel(TrimParams P) {
     P.failed[i] = failed ? 1 : 0;
 }
 
+// Fixed trim, `paffy trim -f` (paf_trim_end_fraction, impl/paf.c:589-598 -> paf_trim_ends :578-587 -> cigar_trim /
+// cigar_trim_back :518-576): end = (int64)((float)aligned * fraction / 2.0) aligned bases go from each end, together with
+// every insert / delete met on the way; the op the cut falls in is shortened IN PLACE in `ops` (the only trim that splits
+// an op). One thread per record; plain loads, because the back walk may re-read the op the front walk shortened.
+__device__ __forceinline__ bool trim_is_aligned(int c) { return c == OP_M || c == OP_EQ || c == OP_X; }
+
+__device__ __forceinline__ void trim_fixed_walk(uint64_t *ops, int64_t &lo, int64_t &hi, bool back, int64_t end_bases, int64_t &qc, int64_t &tc,
+                                                int64_t q_sign, int64_t t_sign) {
+    int64_t trimmed = 0;
+    while (hi > lo) {
+        uint64_t *p = ops + (back ? hi - 1 : lo);
+        const uint64_t w = *p;
+        const int c = (int)(w >> 56);
+        const int64_t len = trim_len(w);
+        const bool al = trim_is_aligned(c);
+        if (al && trimmed >= end_bases) break;
+        if (al) {
+            if (trimmed + len > end_bases) {
+                const int64_t i = end_bases - trimmed;
+                *p = ((uint64_t)(len - i) & LEN_MASK) | ((uint64_t)c << 56);
+                qc += q_sign * i;
+                tc += t_sign * i;
+                break;
+            }
+            trimmed += len;
+            qc += q_sign * len;
+            tc += t_sign * len;
+        } else if (c == OP_I) {
+            qc += q_sign * len;
+        } else {
+            tc += t_sign * len;
+        }
+        if (back) hi--; else lo++;
+    }
+}
+
+__global__ void __launch_bounds__(128) trim_fixed_kernel(TrimParams P, uint64_t *ops) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.n_records) return;
+    int64_t qs = P.qs[i], qe = P.qe[i], ts = P.ts[i], te = P.te[i];
+    int64_t lo = P.rec_out_begin[i], hi = P.rec_out_begin[i + 1];
+    int64_t aligned = 0;
+    for (int64_t k = lo; k < hi; k++) {
+        const uint64_t w = ops[k];
+        if (trim_is_aligned((int)(w >> 56))) aligned += trim_len(w);
+    }
+    // int64 * float -> float, / 2.0 -> double, truncated (impl/paf.c:593)
+    const int64_t end_bases = __double2ll_rz(__ddiv_rn((double)__fmul_rn(__ll2float_rn(aligned), P.max_fraction), 2.0));
+    if (P.same_strand[i]) {
+        trim_fixed_walk(ops, lo, hi, false, end_bases, qs, ts, 1, 1);
+        trim_fixed_walk(ops, lo, hi, true, end_bases, qe, te, -1, -1);
+    } else {
+        trim_fixed_walk(ops, lo, hi, false, end_bases, qe, ts, -1, 1);
+        trim_fixed_walk(ops, lo, hi, true, end_bases, qs, te, 1, -1);
+    }
+    P.qs[i] = qs; P.qe[i] = qe; P.ts[i] = ts; P.te[i] = te;
+    P.lo[i] = lo; P.hi[i] = hi;
+    P.failed[i] = 0;
+}
+
 }  // namespace pafgpu
