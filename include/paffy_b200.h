@@ -209,6 +209,12 @@ int paffy_add_mismatches_main(int argc, char *argv[]);
  * bytes) is refused with exit 1: the device keeps case-folded 2-bit genomes. */
 int paffy_view_main(int argc, char *argv[]);
 
+/* Drop-in for paffy_trim_main (impl/paf_trim.c:38-140): options -i/--inputFile, -o/--outputFile, -r/--trimIdentity
+ * (default 0.05), -t/--trimFraction (default 1.0), -f/--fixedTrim, -l/--logLevel, -h/--help; no FASTA. Each batch of
+ * parsed records is staged on the device (pafgpu_stage_ops_host), trimmed there (pafgpu_trim / pafgpu_trim_fixed),
+ * checked like paf_check and printed by the device serialiser. */
+int paffy_trim_main(int argc, char *argv[]);
+
 /* ---- multi-GPU sharding: cut n input-ordered records with the given weights (aligned bases) into
  *      `parts` contiguous ranges of near-equal weight. cuts has parts + 1 entries, cuts[0] = 0, cuts[parts] = n. */
 int pafgpu_partition(const int64_t *weights, int64_t n, int parts, int64_t *cuts);

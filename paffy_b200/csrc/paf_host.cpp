@@ -770,7 +770,7 @@ int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char 
         } else {
             while (b < stop && (b == a || (bases < batch_bases && nops + (R[(size_t)b].op_end - R[(size_t)b].op_begin) < batch_ops))) {
                 for (int64_t k = R[(size_t)b].op_begin; k < R[(size_t)b].op_end; k++)
-                    if (op_code(F.in.ops[(size_t)k]) == OPM) bases += op_len(F.in.ops[(size_t)k]);
+                    if (op_code(F.in.ops[(size_t)k]) == OPM || (trim_only && op_code(F.in.ops[(size_t)k]) >= OPEQ)) bases += op_len(F.in.ops[(size_t)k]);
                 nops += R[(size_t)b].op_end - R[(size_t)b].op_begin;
                 b++;
             }
@@ -983,5 +983,72 @@ extern "C" int paffy_view_main(int argc, char *argv[]) {
         abort();
     }
     if (verbose) fprintf(stderr, "Paffy view is done!, %lld seconds have elapsed\n", (long long)(now_s() - t0));
+    return 0;
+}
+
+// ================================================================================================
+// Drop-in subcommand entry point `paffy trim` (impl/paf_trim.c:38-140): no FASTA; the parsed ops are staged on the
+// device, trimmed there (identity trim by default, -f = fixed end fraction), paf_check'ed and serialised.
+namespace {
+void trim_usage() {
+    fprintf(stderr, "paffy trim [options], version 0.1 (paffy_b200: CUDA sm_100a path)\n");
+    fprintf(stderr, "Trims the ends of the PAF alignments\n");
+    fprintf(stderr, "-i --inputFile : Input paf file. If not specified reads from stdin\n");
+    fprintf(stderr, "-o --outputFile : Output paf file. If not specified outputs to stdout\n");
+    fprintf(stderr, "-r --trimIdentity : Trim tails with alignment identity lower than this fraction of the overall alignment identity (default 0.05)\n");
+    fprintf(stderr, "-t --trimFraction : Fraction (from 0 to 1) of aligned bases to trim from ends of the alignment, or the maximum fraction trimmed by identity (default 1.0)\n");
+    fprintf(stderr, "-f --fixedTrim : Trim a constant fraction (-t) from each end instead of trimming by identity\n");
+    fprintf(stderr, "-l --logLevel : Set the log level\n");
+    fprintf(stderr, "-h --help : Print this help message\n");
+}
+}  // namespace
+
+extern "C" int paffy_trim_main(int argc, char *argv[]) {
+    const char *input = nullptr, *output = nullptr, *log_level = nullptr;
+    float trim_end_fraction = 1.0f, trim_by_identity_fraction = 0.05f;  // impl/paf_trim.c:14-16
+    bool trim_by_identity = true;
+    static struct option long_options[] = {{"logLevel", required_argument, 0, 'l'},     {"inputFile", required_argument, 0, 'i'},
+                                           {"outputFile", required_argument, 0, 'o'},   {"help", no_argument, 0, 'h'},
+                                           {"trimFraction", required_argument, 0, 't'}, {"trimIdentity", required_argument, 0, 'r'},
+                                           {"fixedTrim", no_argument, 0, 'f'},          {0, 0, 0, 0}};
+    optind = 1;
+    for (;;) {
+        int idx = 0;
+        const int key = getopt_long(argc, argv, "l:i:o:ht:r:f", long_options, &idx);
+        if (key == -1) break;
+        switch (key) {
+            case 'l': log_level = optarg; break;
+            case 'i': input = optarg; break;
+            case 'o': output = optarg; break;
+            case 't': trim_end_fraction = (float)atof(optarg); break;
+            case 'r': trim_by_identity_fraction = (float)atof(optarg); break;
+            case 'f': trim_by_identity = false; break;
+            case 'h': trim_usage(); return 0;
+            default: trim_usage(); return 1;
+        }
+    }
+    const bool verbose = log_level && (!strcasecmp(log_level, "INFO") || !strcasecmp(log_level, "DEBUG"));
+    const double t0 = now_s();
+    if (!trim_by_identity && !(trim_end_fraction >= 0.0f && trim_end_fraction <= 1.0f)) {
+        fprintf(stderr, "paffy trim: Assertion `percentage >= 0 && percentage <= 1.0' failed.\n");  // impl/paf.c:591
+        abort();
+    }
+    pafgpu_ctx *ctx = nullptr;
+    const char *dev = getenv("PAFFY_B200_DEVICE");
+    if (pafgpu_create(dev ? atoi(dev) : 0, &ctx)) {
+        fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(nullptr));
+        exit(1);
+    }
+    pafgpu_file_opts o{PAFGPU_MODE_TRIM, trim_by_identity ? trim_by_identity_fraction : -1.0f, trim_end_fraction, 0, 0};
+    if (trim_by_identity && trim_by_identity_fraction < 0) {  // the option's documented range is 0..1; < 0 is the -f switch in the ABI
+        fprintf(stderr, "ERROR: paffy trim -r must be >= 0\n");
+        exit(1);
+    }
+    pafgpu_file_report rep;
+    const int rc = pafgpu_add_mismatches_file(ctx, input, output, &o, &rep);
+    if (rc < 0) fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
+    pafgpu_destroy(ctx);
+    if (rc) exit(1);
+    if (verbose) fprintf(stderr, "Paffy trim is done!, %lld seconds have elapsed\n", (long long)(now_s() - t0));
     return 0;
 }

@@ -21,9 +21,10 @@ ABI_SYMBOLS = [
     "pafgpu_encode_batch_host", "pafgpu_encode_batch_device", "pafgpu_fetch_ops", "pafgpu_result_device_ptrs",
     "pafgpu_serialise", "pafgpu_fetch_text", "pafgpu_encode_one", "pafgpu_time_encode",
     "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition", "pafgpu_trim",
+    "pafgpu_trim_fixed", "pafgpu_stage_ops_host",
 ]
 # reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
-REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paffy_view_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
+REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paffy_view_main", "paffy_trim_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
 
 
 class PafGpuError(RuntimeError):

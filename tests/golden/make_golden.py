@@ -16,6 +16,8 @@ Fixtures
   *.remove.paf             `paffy add_mismatches -a` applied to *.add.paf
   *.trim.paf               `paffy add_mismatches ... | paffy trim`           (defaults -r 0.05 -t 1.0)
   *.trimf.paf              `paffy add_mismatches ... | paffy trim -f -t 0.3` (fixed end fraction)
+  *.trimraw.paf            `paffy trim -r 0.2 -t 0.5` on the raw input (no add_mismatches before it)
+  *.trimfraw.paf           `paffy trim -f -t 0.5` on the raw input
   *.view.txt               `paffy add_mismatches ... | paffy view -s -t X.fa` summary line
   *.viewlines.txt          `paffy view -s X.fa -i X.paf` on the raw input: per-alignment stats lines + summary line
   errors.json              exit code / stdout / stderr head of the failing-record cases
@@ -75,6 +77,13 @@ def pipeline(stem, fa_path, paf_bytes):
             print(f"  {stem}: reference `paffy {' '.join(args)}` exits {rc} ({why}); no fixture")
             if os.path.exists(path):
                 os.unlink(path)
+    # trim straight on the raw (M) input, where M counts as a match (impl/paf.c:823): both trims
+    for suffix, args in ((".trimraw.paf", ["trim", "-r", "0.2", "-t", "0.5"]), (".trimfraw.paf", ["trim", "-f", "-t", "0.5"])):
+        rc, out, err = run(args, paf_bytes)
+        if rc == 0:
+            write(stem + suffix, out)
+        elif os.path.exists(os.path.join(HERE, stem + suffix)):
+            os.unlink(os.path.join(HERE, stem + suffix))
     write(stem + ".view.txt", must(["view", "-s", "-t", fa_path], add))
     # view on the raw (M) input: per-alignment lines + the summary line, i.e. paffy_view_main's own encode
     write(stem + ".viewlines.txt", must(["view", "-s", fa_path], paf_bytes))
@@ -151,6 +160,7 @@ def c1_set(tmp):
     view = must(["view", "-s", "-t", fa], add)
     remove = must(["add_mismatches", "-a"], add)
     viewlines = must(["view", "-s", fa, "-i", REF_FIXTURE])
+    trimf = must(["trim", "-f", "-t", "0.3"], add)
     info = {
         "input_md5": hashlib.md5(raw).hexdigest(), "input_bytes": len(raw), "records": raw.count(b"\n"),
         "genome": "tests/util.py c1_genome(): numpy default_rng(20261104).integers(0,4,133797422) -> ACGT, one contig chr10",
@@ -158,6 +168,7 @@ def c1_set(tmp):
         "trim_bytes": len(trim), "trim_md5": hashlib.md5(trim).hexdigest(),
         "remove_bytes": len(remove), "remove_md5": hashlib.md5(remove).hexdigest(),
         "view_summary": view.decode(),
+        "trimf_bytes": len(trimf), "trimf_md5": hashlib.md5(trimf).hexdigest(),
         "viewlines_bytes": len(viewlines), "viewlines_md5": hashlib.md5(viewlines).hexdigest(),
         "add_line_md5": [hashlib.md5(ln).hexdigest()[:12] for ln in add.split(b"\n")[:-1]],
     }

@@ -143,6 +143,53 @@ def test_view_cli_drop_in(tmp_path):
     assert r.returncode == 1 and b"No target sequence named: nope found" in r.stderr and r.stdout.count(b"\n") == 1
 
 
+@pytest.mark.parametrize("stem", SETS[1:])
+@pytest.mark.parametrize("batch_bases", [0, 3000])
+def test_trim_alone_matches_reference(fresh, stem, batch_bases, tmp_path):
+    """`paffy trim` by itself (impl/paf_trim.c:113-127; no FASTA, no encode): ops staged on the device, identity trim and
+    the fixed trim `-f` (cigar_trim / cigar_trim_back, impl/paf.c:518-576: the one trim that splits ops), on encoded and
+    on raw (M) input, vs the compiled reference's outputs."""
+    out = tmp_path / "out.paf"
+    enc, raw = os.path.join(G, stem + ".add.paf"), os.path.join(G, stem + ".paf")
+    rc, rep = fresh.add_mismatches_file(enc, str(out), mode=3, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == golden(stem + ".trim.paf")
+    rc, rep = fresh.add_mismatches_file(enc, str(out), mode=3, trim_r=-1.0, trim_t=0.3, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == golden(stem + ".trimf.paf")
+    rc, rep = fresh.add_mismatches_file(raw, str(out), mode=3, trim_r=0.2, trim_t=0.5, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == golden(stem + ".trimraw.paf")
+    rc, rep = fresh.add_mismatches_file(raw, str(out), mode=3, trim_r=-1.0, trim_t=0.5, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == golden(stem + ".trimfraw.paf")
+    # add_mismatches | trim -f in one pass (mode 2 with the fixed trim)
+    fresh.load_fasta(os.path.join(G, stem + ".fa"))
+    rc, rep = fresh.add_mismatches_file(raw, str(out), mode=2, trim_r=-1.0, trim_t=0.3, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == golden(stem + ".trimf.paf")
+
+
+def test_trim_c1_and_cli(fresh, tmp_path):
+    """C1 (207 records, 20 k-op CIGARs): add_mismatches on the GPU, then `paffy_b200_cli trim` / `trim -f -t 0.3` on that
+    file, md5 against the reference's `add_mismatches | trim`; error paths of the stand-alone trim."""
+    info = json.load(open(os.path.join(G, "c1.json")))
+    inp, enc, out = tmp_path / "c1.paf", tmp_path / "c1.add.paf", tmp_path / "c1.trim.paf"
+    inp.write_bytes(gzip.open(os.path.join(G, "c1_human_chimp.paf.gz")).read())
+    fresh.add_contig("chr10", util.c1_genome())
+    rc, rep = fresh.add_mismatches_file(str(inp), str(enc))
+    assert rc == 0
+    exe = os.path.join(os.path.dirname(paffy_b200.lib.LIB_PATH), "paffy_b200_cli")
+    r = subprocess.run([exe, "trim", "-i", str(enc), "-o", str(out)], capture_output=True)
+    got = out.read_bytes()
+    assert r.returncode == 0 and len(got) == info["trim_bytes"] and hashlib.md5(got).hexdigest() == info["trim_md5"], r.stderr
+    r = subprocess.run([exe, "trim", "--fixedTrim", "--trimFraction", "0.3"], capture_output=True, input=enc.read_bytes())
+    assert r.returncode == 0 and len(r.stdout) == info["trimf_bytes"] and hashlib.md5(r.stdout).hexdigest() == info["trimf_md5"]
+    # paf_check after the trim: a CIGAR one base short of its coordinates ends the run after the records before it
+    good = "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:20=1X4="
+    bad = "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:20=1X3="
+    r = subprocess.run([exe, "trim"], capture_output=True, input=("\n".join([good, good, bad, good]) + "\n").encode())
+    assert r.returncode == 1 and r.stdout.count(b"\n") == 2
+    assert b"ERROR: Paf cigar alignment does not match query length: 24 vs. 25" in r.stderr
+    r = subprocess.run([exe, "trim", "-x"], capture_output=True)
+    assert r.returncode == 1
+
+
 def test_cli_drop_in(tmp_path):
     """`paffy_b200_cli add_mismatches` takes the reference's arguments and prints the reference's bytes."""
     exe = os.path.join(os.path.dirname(paffy_b200.lib.LIB_PATH), "paffy_b200_cli")
