@@ -152,6 +152,62 @@ def run_reference_cli(fa, paf, workdir):
     return out
 
 
+def file_parity(fa, paf, workdir, device_index):
+    """The same sample file to file through the CUDA path (FASTA load, parse, kernels, device serialiser, write) and
+    byte-compared with what the compiled reference CLI printed: `add_mismatches` (single.out of run_reference_cli),
+    `add_mismatches | trim` and the `add_mismatches | view -s -t` summary line (SURVEY 8d, config C4's pipeline). The
+    reference is the checker here, never the thing measured."""
+    import hashlib
+    import paffy_b200
+    exe = os.path.join(ROOT, "oracle", "_ref", "paffy")
+    ref_add = os.path.join(workdir, "single.out")
+    if not (os.access(exe, os.X_OK) and os.path.exists(ref_add)):
+        return None
+
+    def md5(path):
+        h = hashlib.md5()
+        with open(path, "rb") as fh:
+            for blk in iter(lambda: fh.read(1 << 24), b""):
+                h.update(blk)
+        return h.hexdigest()
+
+    out = {}
+    c = paffy_b200.Context(device_index)
+    try:
+        t0 = time.perf_counter()
+        c.load_fasta(fa)
+        out["fasta_load_s"] = time.perf_counter() - t0
+        ours = os.path.join(workdir, "ours.add.paf")
+        t0 = time.perf_counter()
+        rc, rep = c.add_mismatches_file(paf, ours)
+        out["add_file_to_file_s"] = time.perf_counter() - t0
+        out["records"] = int(rep.records)
+        out["add_bytes"] = os.path.getsize(ours)
+        out["add_bytes_equal"] = rc == 0 and md5(ours) == md5(ref_add)
+        ours_trim, ref_trim = os.path.join(workdir, "ours.trim.paf"), os.path.join(workdir, "ref.trim.paf")
+        t0 = time.perf_counter()
+        rc, rep = c.add_mismatches_file(paf, ours_trim, mode=2)
+        out["add_trim_file_to_file_s"] = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        r = subprocess.run([exe, "trim", "-i", ref_add, "-o", ref_trim], capture_output=True)
+        out["reference_trim_s"] = time.perf_counter() - t0
+        out["trim_bytes_equal"] = (rc == 0 and md5(ours_trim) == md5(ref_trim)) if r.returncode == 0 else None
+        ours_view = os.path.join(workdir, "ours.view.txt")
+        t0 = time.perf_counter()
+        rc, rep = c.add_mismatches_file(paf, ours_view, mode=4 | 2)
+        out["view_file_to_file_s"] = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        r = subprocess.run([exe, "view", "-s", "-t", fa, "-i", ref_add], capture_output=True)
+        out["reference_view_s"] = time.perf_counter() - t0
+        out["view_summary_equal"] = (rc == 0 and open(ours_view, "rb").read() == r.stdout) if r.returncode == 0 else None
+        out["view_summary"] = open(ours_view).read().strip()
+    finally:
+        c.close()
+    out["what"] = ("CUDA path file to file on the cpu_baseline sample vs the compiled reference CLI: add_mismatches, "
+                   "add_mismatches | trim (defaults), add_mismatches | view -s -t; md5 / bytes compared")
+    return out
+
+
 def reference_arm(args, rank):
     """The reference's own CPU implementation (oracle/_ref/ref_bench: unmodified paf_encode_mismatches on all
     host threads) on a bounded sample of the same workload. Rank 0 only."""
@@ -424,6 +480,12 @@ def main():
                 cli["what"] = ("reference CLI `paffy add_mismatches` file to file on the same sample (FASTA load, parse, encode, print): one process, "
                                "then one process per `paffy split_file` shard (per target contig) run concurrently")
                 cpu["reference_cli"] = cli
+                try:
+                    fp = file_parity(fa, paf, d, local)
+                except Exception as e:  # the checker must not take the bench line down
+                    fp = {"error": repr(e)}
+                if fp:
+                    parity["reference_cli"] = fp
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
