@@ -197,6 +197,22 @@ typedef struct {
 int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char *out_path, const pafgpu_file_opts *opts,
                                pafgpu_file_report *report);
 
+/* `paffy add_mismatches ... | paffy filter ...` in one pass (impl/paf_filter.c:26-176): the test of
+ * paffy_filter_main (:123-134) is applied to every record behind the encode, on paf_stats_calc's counts taken from the
+ * input op sums and the kernel's per-record mismatch tallies (float32 identity quotients, double thresholds); lines
+ * that fail are not written (with `invert`, -x, only those are). Fields = the reference's options and defaults:
+ * -s min_chain_score (-1), -t min_alignment_score (-1), -u min_identity (-1.0), -v min_identity_with_gaps (-1.0),
+ * -w max_tile_level (-1 = off), -x invert (0). filter NULL = pafgpu_add_mismatches_file. mode must be PAFGPU_MODE_ADD.
+ * report->stats still covers every encoded record. */
+typedef struct {
+    int64_t min_chain_score, min_alignment_score;
+    double min_identity, min_identity_with_gaps;
+    int64_t max_tile_level;
+    int invert;
+} pafgpu_filter;
+int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, const char *out_path, const pafgpu_file_opts *opts,
+                                        const pafgpu_filter *filter, pafgpu_file_report *report);
+
 /* Drop-in for the reference's subcommand entry point (impl/paf_add_mismatches.c:26; paffy_main.c:52-77 dispatches to
  * it by name): same options (-i/--inputFile, -o/--outputFile, -a/--removeMismatches, -l/--logLevel, -h/--help,
  * FASTA files as positionals), same exit codes. Uses CUDA device $PAFFY_B200_DEVICE (default 0). */

@@ -328,6 +328,7 @@ struct Filter {
     pafgpu_ctx *ctx;
     pafgpu_file_opts o;
     pafgpu_file_report rep{};
+    const pafgpu_filter *flt = nullptr;  // `| paffy filter` fused behind add_mismatches (impl/paf_filter.c:121-156)
     int threads = 1;
     FILE *out = nullptr;
     Parsed in;
@@ -424,6 +425,18 @@ static void rec_stats(const Filter &F, const Rec &r, int64_t mm, int64_t *s) {
     }
     s[0] += m - mm;
     s[1] += mm;
+}
+
+// The test of paffy_filter_main (impl/paf_filter.c:123-134) on the record as add_mismatches prints it: float32 quotients
+// widened to double, compared with the double thresholds (0/0 = NaN fails every >=, so a record without aligned bases
+// never passes); true = the record is written.
+static bool filter_writes(const pafgpu_filter &f, const Rec &r, const int64_t *s) {
+    const double identity = (float)s[0] / (s[0] + s[1]);
+    const double identity_with_gaps = (float)s[0] / (s[0] + s[1] + s[4] + s[5]);
+    const bool pass = r.score >= f.min_alignment_score && r.chain_score >= f.min_chain_score &&
+                      (f.max_tile_level == -1 || r.tile_level <= f.max_tile_level) && identity >= f.min_identity &&
+                      identity_with_gaps >= f.min_identity_with_gaps;
+    return f.invert ? !pass : pass;
 }
 
 // totals over records [a, b), as `paffy view -s` accumulates them (impl/paf_view.c:176-178)
@@ -526,7 +539,34 @@ int Filter::finish_add(int64_t a, int64_t b) {
     // write in input order: device text for the batch records, host text for the records without aligned work
     const char *text = p_text.as<char>();
     bool ok = true;
-    if (nb == b - a) {
+    if (flt) {
+        // fused `| paffy filter`: the counts are the input op sums + the kernel's tallies; lines that fail are skipped
+        std::string plain;
+        int64_t j = 0, run_from = -1;  // run_from: first device line of the pending run of written lines
+        auto flush = [&](int64_t upto) {
+            if (run_from >= 0) ok = ok && write_all(out, text + line_begin[(size_t)run_from], (size_t)(line_begin[(size_t)upto] - line_begin[(size_t)run_from]));
+            run_from = -1;
+        };
+        for (int64_t i = a; i < b && ok; i++) {
+            const bool dev = j < nb && map[(size_t)j] == i;
+            int64_t st[6] = {0, 0, 0, 0, 0, 0};
+            rec_stats(*this, R[(size_t)i], dev ? mism[(size_t)j] : 0, st);
+            const bool keep = filter_writes(*flt, R[(size_t)i], st);
+            if (dev) {
+                if (keep && run_from < 0) run_from = j;
+                if (!keep) flush(j);
+                j++;
+            } else {
+                flush(j);
+                if (keep) {
+                    plain.clear();
+                    render_line(R[(size_t)i], nullptr, 0, plain);
+                    ok = ok && write_all(out, plain.data(), plain.size());
+                }
+            }
+        }
+        flush(nb);
+    } else if (nb == b - a) {
         ok = write_all(out, text, (size_t)text_bytes);
     } else {
         std::string plain;
@@ -680,9 +720,16 @@ int pafgpu_partition(const int64_t *weights, int64_t n, int parts, int64_t *cuts
 
 int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char *out_path, const pafgpu_file_opts *opts,
                                pafgpu_file_report *report) {
+    return pafgpu_add_mismatches_file_filtered(ctx, in_path, out_path, opts, nullptr, report);
+}
+
+int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, const char *out_path, const pafgpu_file_opts *opts,
+                                        const pafgpu_filter *filter, pafgpu_file_report *report) {
     if (!ctx && !(opts && opts->mode == PAFGPU_MODE_REMOVE)) return PAFGPU_EINVAL;  // -a is host-only text work
+    if (filter && opts && opts->mode != PAFGPU_MODE_ADD) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "the fused filter follows add_mismatches (mode 0) only");
     Filter F;
     F.ctx = ctx;
+    F.flt = filter;
     F.o = opts ? *opts : pafgpu_file_opts{PAFGPU_MODE_ADD, 0.05f, 1.0f, 0, 0};
     if (F.o.mode < 0 || F.o.mode > 7) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "bad mode");
     const bool trim_only = F.o.mode == PAFGPU_MODE_TRIM;

@@ -21,7 +21,7 @@ ABI_SYMBOLS = [
     "pafgpu_encode_batch_host", "pafgpu_encode_batch_device", "pafgpu_fetch_ops", "pafgpu_result_device_ptrs",
     "pafgpu_serialise", "pafgpu_fetch_text", "pafgpu_encode_one", "pafgpu_time_encode",
     "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition", "pafgpu_trim",
-    "pafgpu_trim_fixed", "pafgpu_stage_ops_host",
+    "pafgpu_trim_fixed", "pafgpu_stage_ops_host", "pafgpu_add_mismatches_file_filtered",
 ]
 # reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
 REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paffy_view_main", "paffy_trim_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
@@ -42,6 +42,12 @@ class Batch(C.Structure):
 class FileOpts(C.Structure):
     _fields_ = [("mode", C.c_int), ("trim_score_fraction", C.c_float), ("trim_max_fraction", C.c_float), ("threads", C.c_int),
                 ("batch_bases", C.c_int64)]
+
+
+class FileFilter(C.Structure):
+    """pafgpu_filter: the options of `paffy filter` (impl/paf_filter.c:26-33) with the reference's defaults."""
+    _fields_ = [("min_chain_score", C.c_int64), ("min_alignment_score", C.c_int64), ("min_identity", C.c_double),
+                ("min_identity_with_gaps", C.c_double), ("max_tile_level", C.c_int64), ("invert", C.c_int)]
 
 
 class FileReport(C.Structure):
@@ -103,6 +109,7 @@ def load():
     L.pafgpu_host_free.argtypes = [vp]
     L.pafgpu_host_free.restype = None
     L.pafgpu_add_mismatches_file.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(FileOpts), C.POINTER(FileReport)]
+    L.pafgpu_add_mismatches_file_filtered.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(FileOpts), C.POINTER(FileFilter), C.POINTER(FileReport)]
     L.pafgpu_partition.argtypes = [vp, i64, C.c_int, vp]
     L.pafgpu_trim.argtypes = [vp, C.c_float, C.c_float, vp, vp, vp, vp]
     _lib = L
@@ -264,6 +271,17 @@ class Context:
         o = FileOpts(mode, trim_r, trim_t, threads, batch_bases)
         rep = FileReport()
         rc = self.L.pafgpu_add_mismatches_file(self.h, in_path.encode(), out_path.encode(), C.byref(o), C.byref(rep))
+        if rc < 0:
+            self._check(rc)
+        return rc, rep
+
+    def add_mismatches_filter_file(self, in_path, out_path, min_chain_score=-1, min_alignment_score=-1, min_identity=-1.0,
+                                   min_identity_with_gaps=-1.0, max_tile_level=-1, invert=False, batch_bases=0):
+        """`paffy add_mismatches | paffy filter -s -t -u -v -w [-x]` in one pass -> (rc, FileReport)."""
+        o = FileOpts(0, 0.05, 1.0, 0, batch_bases)
+        f = FileFilter(min_chain_score, min_alignment_score, min_identity, min_identity_with_gaps, max_tile_level, int(invert))
+        rep = FileReport()
+        rc = self.L.pafgpu_add_mismatches_file_filtered(self.h, in_path.encode(), out_path.encode(), C.byref(o), C.byref(f), C.byref(rep))
         if rc < 0:
             self._check(rc)
         return rc, rep

@@ -18,6 +18,7 @@ Fixtures
   *.trimf.paf              `paffy add_mismatches ... | paffy trim -f -t 0.3` (fixed end fraction)
   *.trimraw.paf            `paffy trim -r 0.2 -t 0.5` on the raw input (no add_mismatches before it)
   *.trimfraw.paf           `paffy trim -f -t 0.5` on the raw input
+  *.filter_{u,vx,t}.paf    `paffy add_mismatches ... | paffy filter -u 0.5`, `... -v 0.4 -x`, `... -t 1 -s -1 -w 3`
   *.view.txt               `paffy add_mismatches ... | paffy view -s -t X.fa` summary line
   *.viewlines.txt          `paffy view -s X.fa -i X.paf` on the raw input: per-alignment stats lines + summary line
   errors.json              exit code / stdout / stderr head of the failing-record cases
@@ -85,6 +86,10 @@ def pipeline(stem, fa_path, paf_bytes):
         elif os.path.exists(os.path.join(HERE, stem + suffix)):
             os.unlink(os.path.join(HERE, stem + suffix))
     write(stem + ".view.txt", must(["view", "-s", "-t", fa_path], add))
+    # add_mismatches | filter (impl/paf_filter.c): identity, identity with gaps inverted, alignment score
+    write(stem + ".filter_u.paf", must(["filter", "-u", "0.5"], add))
+    write(stem + ".filter_vx.paf", must(["filter", "-v", "0.4", "-x"], add))
+    write(stem + ".filter_t.paf", must(["filter", "-t", "1", "-s", "-1", "-w", "3"], add))
     # view on the raw (M) input: per-alignment lines + the summary line, i.e. paffy_view_main's own encode
     write(stem + ".viewlines.txt", must(["view", "-s", fa_path], paf_bytes))
 

@@ -190,6 +190,25 @@ def test_trim_c1_and_cli(fresh, tmp_path):
     assert r.returncode == 1
 
 
+@pytest.mark.parametrize("stem", SETS)
+@pytest.mark.parametrize("batch_bases", [0, 3000])
+def test_add_then_filter_matches_reference(fresh, stem, batch_bases, tmp_path):
+    """`paffy add_mismatches | paffy filter` fused (impl/paf_filter.c:123-134 on the kernel's tallies): identity, identity
+    with gaps inverted, alignment score / tile level; defaults drop only the records without aligned bases (0/0)."""
+    fresh.load_fasta(os.path.join(G, stem + ".fa"))
+    inp, out = os.path.join(G, stem + ".paf"), tmp_path / "out.paf"
+    rc, rep = fresh.add_mismatches_filter_file(inp, str(out), min_identity=0.5, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == golden(stem + ".filter_u.paf")
+    rc, rep = fresh.add_mismatches_filter_file(inp, str(out), min_identity_with_gaps=0.4, invert=True, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == golden(stem + ".filter_vx.paf")
+    rc, rep = fresh.add_mismatches_filter_file(inp, str(out), min_alignment_score=1, max_tile_level=3, batch_bases=batch_bases)
+    assert rc == 0 and out.read_bytes() == golden(stem + ".filter_t.paf")
+    assert util.view_summary(list(rep.stats)).encode() == golden(stem + ".view.txt")  # the totals cover every record
+    want = golden(stem + ".add.paf")
+    gu, gvx = golden(stem + ".filter_u.paf"), golden(stem + ".filter_vx.paf")
+    assert 0 < gu.count(b"\n") < want.count(b"\n") and 0 < gvx.count(b"\n") < want.count(b"\n")
+
+
 def test_cli_drop_in(tmp_path):
     """`paffy_b200_cli add_mismatches` takes the reference's arguments and prints the reference's bytes."""
     exe = os.path.join(os.path.dirname(paffy_b200.lib.LIB_PATH), "paffy_b200_cli")
