@@ -28,6 +28,10 @@
 #ifndef ENC_NO_PREFETCH
 #define ENC_NO_PREFETCH 0
 #endif
+#ifndef ENC_SHFL_T2
+#define ENC_SHFL_T2 0  // 1: the third word of a window comes from the next lane's first word by shuffle when both windows
+                       // belong to the same op (4 instead of 6 sequence loads per window on the common path)
+#endif
 #ifndef ENC_ROLL_HB
 #define ENC_ROLL_HB 0  // 1: the batch loop of the compare phase is not unrolled (smaller code)
 #endif
@@ -221,6 +225,9 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
         // issue every sequence load of the batch (inactive and pass-through windows read arena word 0: no branches)
         OpEntry EN[BATCH];
         uint64_t T0[BATCH], T1[BATCH], T2[BATCH], Q0[BATCH], Q1[BATCH], Q2[BATCH];
+#if ENC_SHFL_T2
+        bool NB[BATCH];
+#endif
         uint64_t pm_t = 0, pm_q = 0;  // lane 0, first window only: words holding the base before the window
         uint32_t pm_k = 0;
 #pragma unroll
@@ -236,8 +243,18 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const int32_t tw = isM ? en.tw + 2 * (int32_t)srel : 0;
             const int32_t qw = isM ? en.qw + 2 * (int32_t)srel : 0;
             const uint64_t *tpn = gw + tw, *qpn = gw + qw;
+#if ENC_SHFL_T2
+            // the next lane's window continues the same op: its first word is my third one
+            const uint32_t idx_n = __shfl_down_sync(FULL, idx, 1);
+            NB[b] = lane < 31 && idx_n == idx && isM && srel + 1 < n_act;
+            T0[b] = ldg64(tpn); T1[b] = ldg64(tpn + 1);
+            Q0[b] = ldg64(qpn); Q1[b] = ldg64(qpn + 1);
+            T2[b] = Q2[b] = 0;
+            if (!NB[b]) { T2[b] = ldg64(tpn + 2); Q2[b] = ldg64(qpn + 2); }
+#else
             T0[b] = ldg64(tpn); T1[b] = ldg64(tpn + 1); T2[b] = ldg64(tpn + 2);
             Q0[b] = ldg64(qpn); Q1[b] = ldg64(qpn + 1); Q2[b] = ldg64(qpn + 2);
+#endif
             if (it == 0 && lane == 0 && isM && !(w & 1u)) {
                 // tile window 0 continues an op: mismatch state of the base just before the tile
                 const unsigned sht = en.misc & 31u, shq = (en.misc >> 5) & 31u;
@@ -291,6 +308,12 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const uint32_t n = !isM ? 0u : rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
             const uint32_t misc = en.misc;
             const unsigned sht = misc & 31u, shq = (misc >> 5) & 31u;
+#if ENC_SHFL_T2
+            {
+                const uint64_t t0n = __shfl_down_sync(FULL, T0[b], 1), q0n = __shfl_down_sync(FULL, Q0[b], 1);
+                if (NB[b]) { T2[b] = t0n; Q2[b] = q0n; }
+            }
+#endif
             const uint32_t tl0 = __funnelshift_r((uint32_t)T0[b], (uint32_t)T1[b], sht);
             const uint32_t tl1 = __funnelshift_r((uint32_t)T1[b], (uint32_t)T2[b], sht);
             const uint32_t th0 = __funnelshift_r((uint32_t)(T0[b] >> 32), (uint32_t)(T1[b] >> 32), sht);

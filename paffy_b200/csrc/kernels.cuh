@@ -359,6 +359,75 @@ __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
     if (threadIdx.x == 0 && block_aligned) atomicAdd(P.aligned, block_aligned);  // one global atomic per block, not per record
 }
 
+// ---- FASTA sequence text -> contiguous sequence bytes (the admission rules of fastaReadToFunction,
+// bioioC.c:186-203): newline, space and tab are dropped, every other byte must be a letter or '-'. raw holds the bytes
+// between a header line and the next '>'. Two passes over tiles of FA_TILE bytes: kept bytes per tile (+ the position of
+// the first inadmissible byte), an exclusive scan of the tile counts, then each tile re-derives its in-tile offsets
+// (thread-owned runs of FA_PER_THREAD bytes, block scan through shared memory) and copies its kept bytes out.
+constexpr int FA_THREADS = 256, FA_PER_THREAD = 16, FA_TILE = FA_THREADS * FA_PER_THREAD;
+
+__device__ __forceinline__ bool fa_dropped(unsigned char ch) { return ch == '\n' || ch == ' ' || ch == '\t'; }
+__device__ __forceinline__ bool fa_admissible(unsigned char ch) {
+    return (ch >= 'A' && ch <= 'Z') || (ch >= 'a' && ch <= 'z') || ch == '-';  // isalpha in the C locale, or '-'
+}
+
+__global__ void __launch_bounds__(FA_THREADS) fasta_count_kernel(const unsigned char *__restrict__ raw, int64_t n, uint32_t *tile_kept,
+                                                                  unsigned long long *first_bad) {
+    __shared__ uint32_t warp_sum[FA_THREADS / 32];
+    const int64_t b0 = (int64_t)blockIdx.x * FA_TILE + (int64_t)threadIdx.x * FA_PER_THREAD;
+    uint32_t kept = 0;
+#pragma unroll
+    for (int k = 0; k < FA_PER_THREAD; k++) {
+        const int64_t i = b0 + k;
+        if (i < n) {
+            const unsigned char ch = raw[i];
+            if (!fa_dropped(ch)) {
+                kept++;
+                if (!fa_admissible(ch)) atomicMin(first_bad, (unsigned long long)i);
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) kept += __shfl_xor_sync(FULL, kept, o);
+    if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = kept;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int w = 0; w < FA_THREADS / 32; w++) t += warp_sum[w];
+        tile_kept[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(FA_THREADS) fasta_compact_kernel(const unsigned char *__restrict__ raw, int64_t n,
+                                                                    const uint64_t *__restrict__ tile_off, unsigned char *out) {
+    __shared__ uint32_t warp_sum[FA_THREADS / 32];
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t b0 = (int64_t)blockIdx.x * FA_TILE + (int64_t)threadIdx.x * FA_PER_THREAD;
+    unsigned char keep[FA_PER_THREAD];
+    uint32_t kept = 0;
+#pragma unroll
+    for (int k = 0; k < FA_PER_THREAD; k++) {
+        const int64_t i = b0 + k;
+        const unsigned char ch = i < n ? raw[i] : (unsigned char)'\n';
+        keep[k] = ch;
+        kept += !fa_dropped(ch);
+    }
+    uint32_t incl = kept;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(FULL, incl, o);
+        if (lane >= (unsigned)o) incl += v;
+    }
+    if (lane == 31) warp_sum[warp] = incl;
+    __syncthreads();
+    uint32_t before = incl - kept;
+    for (unsigned w = 0; w < warp; w++) before += warp_sum[w];
+    unsigned char *dst = out + tile_off[blockIdx.x] + before;
+#pragma unroll
+    for (int k = 0; k < FA_PER_THREAD; k++)
+        if (!fa_dropped(keep[k])) *dst++ = keep[k];
+}
+
 // first op of each warp tile: op j owns windows [woff[j], woff[j+1])
 __global__ void tile_first_op_kernel(const uint64_t *__restrict__ woff, int64_t n_ops, uint32_t tile_windows,
                                      uint32_t *tile_first_op) {

@@ -17,6 +17,11 @@
 #include <unordered_map>
 #include <vector>
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 using namespace pafgpu;
 
 namespace {
@@ -99,6 +104,8 @@ struct pafgpu_ctx {
     DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
     // trim
     DevBuf trim_coords, trim_lo, trim_hi, trim_failed;
+    // FASTA reader: raw sequence text of one record, kept bytes per tile and their scan, {first bad byte, kept total}
+    DevBuf fa_raw, fa_tile_kept, fa_tile_off, fa_scal;
     bool trimmed = false;
     const uint8_t *last_strand = nullptr;
     const int64_t *last_qs = nullptr, *last_qe = nullptr, *last_ts = nullptr;
@@ -588,67 +595,81 @@ int64_t pafgpu_genome_add_contig_device(pafgpu_ctx *c, const char *name, const v
     return genome_add_device(c, c->genome, name, static_cast<const uint8_t *>(seq_dev), len);
 }
 
+// One FASTA record whose sequence text (everything between the header line and the next '>') is raw[0..n): the text goes
+// to the device as it is, fasta_count_kernel / fasta_compact_kernel drop newline, space and tab and test every other
+// byte, and the contiguous sequence is packed straight from device memory.
+static int fasta_add_record(pafgpu_ctx *c, const std::string &name, const char *raw, int64_t n) {
+    CU(c->in_seq.ensure((size_t)std::max<int64_t>(n, 16)));
+    if (n == 0) {
+        const int64_t id = genome_add_device(c, c->genome, name.c_str(), c->in_seq.as<uint8_t>(), 0);
+        return id < 0 ? (int)id : 0;
+    }
+    const int64_t nt = (n + FA_TILE - 1) / FA_TILE;
+    CU(c->fa_raw.ensure((size_t)n));
+    CU(c->fa_tile_kept.ensure((size_t)nt * 4));
+    CU(c->fa_tile_off.ensure((size_t)(nt + 1) * 8));
+    CU(c->fa_scal.ensure(16));
+    CU(cudaMemcpyAsync(c->fa_raw.p, raw, (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemsetAsync(c->fa_scal.p, 0xff, 8, c->stream));
+    uint64_t *scal = c->fa_scal.as<uint64_t>();
+    fasta_count_kernel<<<(unsigned)nt, FA_THREADS, 0, c->stream>>>(c->fa_raw.as<unsigned char>(), n, c->fa_tile_kept.as<uint32_t>(),
+                                                                  (unsigned long long *)scal);
+    if (int rc = scan_u32(c, c->fa_tile_kept.as<uint32_t>(), nt, c->fa_tile_off.as<uint64_t>(), scal + 1)) return rc;
+    uint64_t host[2] = {0, 0};
+    CU(read_words(c, host, scal, 2));
+    if (host[0] != ~0ull) {  // bioioC.c:196-199
+        char msg[96];
+        snprintf(msg, sizeof msg, "!!Got an unexpected character in input fasta sequence: '%c' ", raw[host[0]]);
+        return fail(c, PAFGPU_EFASTA, msg);
+    }
+    fasta_compact_kernel<<<(unsigned)nt, FA_THREADS, 0, c->stream>>>(c->fa_raw.as<unsigned char>(), n, c->fa_tile_off.as<uint64_t>(),
+                                                                    c->in_seq.as<unsigned char>());
+    CU(cudaGetLastError());
+    const int64_t id = genome_add_device(c, c->genome, name.c_str(), c->in_seq.as<uint8_t>(), (int64_t)host[1]);
+    return id < 0 ? (int)id : 0;
+}
+
 int pafgpu_genome_load_fasta(pafgpu_ctx *c, const char *path) {
     if (!c || !path) return PAFGPU_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
-    FILE *fh = fopen(path, "rb");
-    if (!fh) return fail(c, PAFGPU_EIO, std::string("cannot open ") + path);
-    // Reader state machine with the admission rules of bioioC.c:155-209: everything before the first
-    // '>' is skipped; the header is the whole line; a '>' anywhere in the sequence starts a new record.
-    std::vector<char> buf(1 << 22);
-    std::string name, seq;
-    enum { PRE, HEADER, SEQ } st = PRE;
-    int rc = 0;
-    size_t got;
-    auto flush = [&]() -> int {
-        const int64_t id = genome_add_host(c, c->genome, name.c_str(), seq.data(), (int64_t)seq.size());
-        return id < 0 ? (int)id : 0;
-    };
-    while (rc == 0 && (got = fread(buf.data(), 1, buf.size(), fh)) > 0) {
-        size_t i = 0;
-        while (i < got && rc == 0) {
-            if (st == PRE) {
-                const char *p = (const char *)memchr(buf.data() + i, '>', got - i);
-                if (!p) { i = got; break; }
-                i = (size_t)(p - buf.data()) + 1;
-                st = HEADER; name.clear(); seq.clear();
-            } else if (st == HEADER) {
-                const char *p = (const char *)memchr(buf.data() + i, '\n', got - i);
-                const size_t e = p ? (size_t)(p - buf.data()) : got;
-                name.append(buf.data() + i, e - i);
-                i = e;
-                if (p) { i++; st = SEQ; }
-            } else {
-                const char ch = buf[i];
-                if (ch == '>') {
-                    rc = flush();
-                    st = HEADER; name.clear(); seq.clear();
-                    i++;
-                } else if (ch == '\n' || ch == ' ' || ch == '\t') {
-                    i++;
-                } else {
-                    // consume a run of admissible bytes up to the next separator
-                    size_t e = i;
-                    while (e < got) {
-                        const unsigned char u = (unsigned char)buf[e];
-                        if (u == '\n' || u == ' ' || u == '\t' || u == '>') break;
-                        if (!isalpha(u) && u != '-') {
-                            char msg[96];
-                            snprintf(msg, sizeof msg, "!!Got an unexpected character in input fasta sequence: '%c' ", (char)u);
-                            rc = fail(c, PAFGPU_EFASTA, msg);
-                            break;
-                        }
-                        e++;
-                    }
-                    seq.append(buf.data() + i, e - i);
-                    i = e;
-                }
-            }
-        }
+    // the file as one byte range: mapped when it is a regular file, read whole otherwise (pipes)
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return fail(c, PAFGPU_EIO, std::string("cannot open ") + path);
+    struct stat sb;
+    const char *d = nullptr;
+    size_t n = 0;
+    void *map = MAP_FAILED;
+    std::vector<char> whole;
+    if (fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size > 0) {
+        map = mmap(nullptr, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+        if (map != MAP_FAILED) { d = (const char *)map; n = (size_t)sb.st_size; }
     }
-    fclose(fh);
-    if (rc == 0 && st != PRE) rc = flush();  // EOF right after a header still yields an (empty) contig
+    if (map == MAP_FAILED) {
+        char tmp[1 << 16];
+        ssize_t got;
+        while ((got = read(fd, tmp, sizeof tmp)) > 0) whole.insert(whole.end(), tmp, tmp + got);
+        d = whole.data(); n = whole.size();
+    }
+    close(fd);
+    // Record boundaries with the rules of bioioC.c:155-209: everything before the first '>' is skipped; the header is the
+    // whole line (a '>' inside it belongs to the name); a '>' anywhere after it starts the next record; EOF right after
+    // a header still yields an (empty) contig.
+    int rc = 0;
+    const char *p = n ? (const char *)memchr(d, '>', n) : nullptr;
+    const char *end = d + n;
+    while (p && rc == 0) {
+        const char *hs = p + 1;
+        const char *nl = hs < end ? (const char *)memchr(hs, '\n', (size_t)(end - hs)) : nullptr;
+        const std::string name(hs, nl ? nl : end);
+        const char *sb0 = nl ? nl + 1 : end;
+        const char *nx = sb0 < end ? (const char *)memchr(sb0, '>', (size_t)(end - sb0)) : nullptr;
+        rc = fasta_add_record(c, name, sb0, (int64_t)((nx ? nx : end) - sb0));
+        p = nx;
+    }
+    const cudaError_t se = stream_sync(c);  // the mapping goes away below; every copy out of it must have happened
+    if (map != MAP_FAILED) munmap(map, (size_t)sb.st_size);
+    if (rc == 0 && se != cudaSuccess) return fail(c, PAFGPU_ENODEVICE, std::string("FASTA load: ") + cudaGetErrorString(se));
     return rc;
 }
 

@@ -209,6 +209,49 @@ def test_add_then_filter_matches_reference(fresh, stem, batch_bases, tmp_path):
     assert 0 < gu.count(b"\n") < want.count(b"\n") and 0 < gvx.count(b"\n") < want.count(b"\n")
 
 
+def test_device_fasta_reader_matches_oracle(fresh, tmp_path):
+    """pafgpu_genome_load_fasta: record boundaries on the host (memchr), separator removal + admission test + compaction on
+    the device (fasta_count_kernel / fasta_compact_kernel), against the oracle's restatement of fastaReadToFunction
+    (bioioC.c:155-209): text before the first '>', whole-line names, '>' in the middle of a line, spaces and tabs, ragged
+    lines, tiles that end inside a line, an empty record, a repeated name, EOF right after a header, soft-masked / IUPAC /
+    '-' bytes; then the inadmissible-byte error."""
+    import numpy as np
+    from oracle import pyoracle as O
+    rng = np.random.default_rng(5)
+    alpha = np.frombuffer(b"ACGTacgtNnRYKMSWBDHV-", dtype=np.uint8)
+    def seq(n):
+        return alpha[rng.integers(0, len(alpha) if n < 3000 else 8, n)].tobytes()
+    def wrap(b, widths):
+        out, i, k = [], 0, 0
+        while i < len(b):
+            w = widths[k % len(widths)]; k += 1
+            out.append(b[i:i + w]); i += w
+        return b"\n".join(out) + b"\n"
+    big = seq(300000)
+    fa = (b"junk before the first header\n\n>c1 with a description > and a bracket\n" + wrap(seq(777), [60]) +
+          b">empty\n>c2\n" + wrap(seq(5000), [1, 7, 4096, 13]).replace(b"\n", b" \n\t", 3) + b"ACGT>c3 starts mid-line\n" +
+          wrap(big, [100]) + b">c2\n" + wrap(seq(4096 * 3), [4095, 4097]) + b">last header at EOF")
+    path = tmp_path / "quirks.fa"
+    path.write_bytes(fa)
+    want = O.Fasta([str(path)])
+    fresh.load_fasta(str(path))
+    assert len(want) == 5
+    for name in ["c1 with a description > and a bracket", "empty", "c2", "c3 starts mid-line", "last header at EOF"]:
+        w = want.get(name)
+        cid = fresh.find(name)
+        assert w is not None and cid >= 0, name
+        assert fresh.contig_length(cid) == len(w), name
+        if len(w):
+            assert fresh.fetch_bases(cid, 0, len(w)) == w.upper(), name
+    assert fresh.find("c1") < 0
+    bad = tmp_path / "bad.fa"
+    bad.write_bytes(b">ok\nACGT\n>broken\n" + wrap(seq(9000), [80]) + b"AC\rGT\nAC1GT\n")
+    with pytest.raises(paffy_b200.lib.PafGpuError) as e:
+        fresh.load_fasta(str(bad))
+    assert e.value.code == -5 and "unexpected character in input fasta sequence: '\r'" in str(e.value)
+    assert fresh.find("ok") >= 0 and fresh.find("broken") < 0
+
+
 def test_cli_drop_in(tmp_path):
     """`paffy_b200_cli add_mismatches` takes the reference's arguments and prints the reference's bytes."""
     exe = os.path.join(os.path.dirname(paffy_b200.lib.LIB_PATH), "paffy_b200_cli")
