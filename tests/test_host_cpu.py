@@ -68,3 +68,26 @@ def test_sharding_world_size_2_gloo():
     ok, mine, total = q.get(timeout=120)
     [p.join(60) for p in ps]
     assert ok and abs(mine - total / 2) < 100000
+
+
+def test_cli_option_handling_without_a_gpu():
+    """What the subcommand entry points decide before any device is touched, against the reference's mains: `view` without
+    a FASTA exits 1 (impl/paf_view.c:110-113), -h prints the usage and returns 0, an unknown flag returns 1
+    (impl/paf_trim.c:89-91), and nothing falls back to a CPU path: with no device the commands that compare bases fail."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(paffy_b200.lib.LIB_PATH), "paffy_b200_cli")
+    r = subprocess.run([exe, "view", "-i", os.path.join(G, "edge.paf")], capture_output=True)
+    assert r.returncode == 1 and b"Expected at least one sequence file" in r.stderr and r.stdout == b""
+    for cmd in ("add_mismatches", "view", "trim"):
+        r = subprocess.run([exe, cmd, "-h"], capture_output=True)
+        assert r.returncode == 0 and b"paffy " + cmd.encode() in r.stderr, cmd
+        r = subprocess.run([exe, cmd, "--noSuchOption"], capture_output=True)
+        assert r.returncode == 1, cmd
+    r = subprocess.run([exe, "view", "-a", os.path.join(G, "edge.fa"), "-i", os.path.join(G, "edge.paf")], capture_output=True)
+    assert r.returncode == 1 and b"not available on the CUDA path" in r.stderr
+    if paffy_b200.load().pafgpu_device_count() == 0:
+        for args in (["add_mismatches", os.path.join(G, "edge.fa"), "-i", os.path.join(G, "edge.paf")],
+                     ["view", os.path.join(G, "edge.fa"), "-i", os.path.join(G, "edge.paf")],
+                     ["trim", "-i", os.path.join(G, "rand101.add.paf")]):
+            r = subprocess.run([exe] + args, capture_output=True)
+            assert r.returncode == 1 and r.stdout == b"" and b"ERROR" in r.stderr, args
