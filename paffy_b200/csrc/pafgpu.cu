@@ -278,7 +278,7 @@ int genome_sync_table(pafgpu_ctx *c, GenomeStore &g) {
 #ifndef ENC_BATCH
 #define ENC_BATCH 2
 #endif
-constexpr int ENC_WARPS = 4, CMP_BATCH = ENC_BATCH;
+constexpr int CMP_BATCH = ENC_BATCH;
 
 // one pass of encode_kernel + stitch_kernel for c->last; leaves the output op count in c->n_out
 int launch_encode_once(pafgpu_ctx *c) {
