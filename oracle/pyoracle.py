@@ -12,6 +12,8 @@ ORACLE_SO = os.path.join(HERE, "libpaf_oracle.so")
 REF_DIR = os.path.join(HERE, "_ref")
 REF_PAFFY = os.path.join(REF_DIR, "paffy")
 REF_BENCH = os.path.join(REF_DIR, "ref_bench")
+UNIT_TESTS = os.path.join(REF_DIR, "b200_unit_tests")   # the reference's unit tests linked against the product
+LINKED_PAFFY = os.path.join(REF_DIR, "paffy_linked")   # the reference's paffy_main.c linked against the product
 
 
 def build(ref=True):
@@ -19,6 +21,10 @@ def build(ref=True):
     subprocess.run(["make", "-s", "-C", HERE, "oracle"], check=True)
     if ref and os.path.isdir("/root/reference/impl"):
         subprocess.run(["make", "-s", "-j8", "-C", HERE, "ref"], check=True)
+        # the link proof of the drop-in boundary: the reference's unchanged unit tests and paffy_main.c against the
+        # product library (which must have been built first)
+        if os.path.exists(os.path.join(HERE, "..", "paffy_b200", "libpaffy_b200_stpaf.a")):
+            subprocess.run(["make", "-s", "-j8", "-C", HERE, "linkproof"], check=True)
 
 
 class OPaf(C.Structure):

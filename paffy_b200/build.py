@@ -6,9 +6,10 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpaffy_b200.so")
-SOURCES = ["pafgpu.cu", "paf_host.cpp", "paf_compat.cpp"]
+SOURCES = ["pafgpu.cu", "paf_host.cpp", "paf_compat.cpp", "paf_api.cpp"]
 CLI = os.path.join(HERE, "paffy_b200_cli")
-HEADERS = ["kernels.cuh", "encode.cuh", "serialise.cuh", "internal.h", "paffy_main.c", os.path.join("..", "..", "include", "paf_b200_compat.h"), os.path.join("..", "..", "include", "paffy_b200.h")]
+STPAF = os.path.join(HERE, "libpaffy_b200_stpaf.a")
+HEADERS = ["kernels.cuh", "encode.cuh", "serialise.cuh", "trim.cuh", "internal.h", "paf_text.h", "paf_sonlib.c", "paffy_main.c", os.path.join("..", "..", "include", "paf_b200_compat.h"), os.path.join("..", "..", "include", "paffy_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--use_fast_math=false",
               "-Xcompiler", "-fPIC,-O3,-Wall,-fvisibility=default", "-Xptxas", "-v", "-shared", "-cudart", "shared",
               "-Xlinker", "-Bsymbolic"]
@@ -49,6 +50,18 @@ def build(force=False, verbose=False):
     if r.returncode:
         sys.stderr.write(r.stdout + r.stderr)
         raise RuntimeError("building the CLI failed")
+    # the sonLib-container functions of paf.h (read_pafs, write_pafs, paf_shatter ...) as a static archive for host
+    # programs that bring their own sonLib (include/paf_b200_compat.h)
+    obj = os.path.join(HERE, "paf_sonlib.o")
+    r = subprocess.run(["gcc", "-std=gnu99", "-O2", "-fPIC", "-Wall", "-c", os.path.join(CSRC, "paf_sonlib.c"), "-o", obj],
+                       capture_output=True, text=True)
+    if r.returncode == 0:
+        if os.path.exists(STPAF):
+            os.unlink(STPAF)
+        r = subprocess.run(["ar", "rcs", STPAF, obj], capture_output=True, text=True)
+    if r.returncode:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("building libpaffy_b200_stpaf.a failed")
     return LIB
 
 
