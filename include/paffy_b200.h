@@ -43,6 +43,11 @@ int pafgpu_device_count(void);
 /* Create a context bound to one CUDA device (one context per GPU; multi-GPU = one per rank). */
 int pafgpu_create(int device, pafgpu_ctx **out);
 void pafgpu_destroy(pafgpu_ctx *ctx);
+/* A second context on the same GPU that SHARES the parent's packed genome (no copy): its own stream and work buffers, so
+ * that the H2D copy of one batch, the kernels of another and the D2H copy of a third overlap on one device. The genome
+ * must not be modified while siblings encode. (The reference has no counterpart: it is single-threaded.) */
+int pafgpu_create_sibling(pafgpu_ctx *parent, pafgpu_ctx **out);
+int pafgpu_device_of(const pafgpu_ctx *ctx);
 const char *pafgpu_last_error(const pafgpu_ctx *ctx); /* ctx may be NULL: last creation error */
 
 /* ---- genome store: replaces the name -> char* hash the reference fills with
@@ -65,6 +70,17 @@ int64_t pafgpu_genome_num_contigs(const pafgpu_ctx *ctx);
 /* Read bases [start, start+len) of a contig back as the upper-cased bytes the kernel compares. */
 int pafgpu_genome_fetch(pafgpu_ctx *ctx, int64_t contig, int64_t start, int64_t len, char *out);
 
+/* Replicate the packed genome of `src` into `dst` (another GPU of the box) with a device-to-device copy over NVLink /
+ * NVSwitch (cudaMemcpyPeerAsync) instead of loading the FASTA once per GPU: the reference's multi-process recipe
+ * (tests/paf_pipeline_test.sh:42-67) re-reads both FASTA files in every shard process. Same device: shares the store. */
+int pafgpu_genome_clone(pafgpu_ctx *dst, pafgpu_ctx *src);
+/* Persisted packed genome: write / read the packed arena + contig table, so that the next process of a
+ * pipeline skips fastaReadToFunction (bioioC.c:155-232) altogether. `key` (may be NULL) is stored in the file and must
+ * be equal at load time (callers put the FASTA paths, sizes and mtimes there); a differing key or a damaged file makes
+ * the load fail (PAFGPU_ESTATE / PAFGPU_EIO) and the caller reads the FASTA instead. */
+int pafgpu_genome_save(pafgpu_ctx *ctx, const char *path, const char *key);
+int pafgpu_genome_load_packed(pafgpu_ctx *ctx, const char *path, const char *key);
+
 /* ---- batch description: replaces the per-record fields paf_encode_mismatches reads from Paf
  *      (impl/paf.c:746,751-752: target_start, query_start, query_end, same_strand) and the
  *      Cigar array (inc/paf.h:67-73), flattened for a whole batch of records. ---------------------- */
@@ -86,11 +102,11 @@ typedef struct {
     int64_t aligned_bases;  /* sum of input M lengths (the unit of the throughput metric) */
     int64_t n_windows;      /* 64-base work windows scheduled */
     int64_t n_tiles;        /* warp tiles scheduled */
-    int64_t retried;        /* always 0 (kept for ABI stability) */
+    int64_t retried;        /* 1 when the output buffer guess was too small and the encode pass ran twice */
     float ms_ingest;        /* CUDA-event time of the CIGAR ingest kernels */
     float ms_encode;        /* CUDA-event time of the whole encode stage: resets + compare + scan + emit + stitch */
-    float ms_kernel;        /* CUDA-event time of compare_kernel alone (reads the sequences; the roofline kernel) */
-    float ms_emit;          /* CUDA-event time of emit_kernel + stitch (writes the output ops) */
+    float ms_kernel;        /* CUDA-event time of encode_kernel alone (reads the sequences, writes the output ops: the roofline kernel) */
+    float ms_emit;          /* CUDA-event time of stitch_kernel (closes runs left open across warp tiles) */
 } pafgpu_result;
 
 /* Run CIGAR ingest + the base-comparison kernel on one batch (a1 + a7 of SURVEY.md section 8).

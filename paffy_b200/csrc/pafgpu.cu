@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -31,8 +32,9 @@ thread_local std::string g_create_error;
 struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
-    // grow to at least `bytes`; keep the first `keep` bytes
-    cudaError_t ensure(size_t bytes, size_t keep = 0, bool zero_new = false) {
+    // grow to at least `bytes`; keep the first `keep` bytes. The zero fill and the copy of the kept bytes are ordered on
+    // `stream` (the context's stream: kernels that follow on it see them) and have finished when this returns.
+    cudaError_t ensure(size_t bytes, size_t keep = 0, bool zero_new = false, cudaStream_t stream = nullptr) {
         if (bytes <= cap) return cudaSuccess;
         size_t want = std::max(bytes, cap + cap / 2);
         void *q = nullptr;
@@ -42,8 +44,10 @@ struct DevBuf {
             e = cudaMalloc(&q, want);
             if (e != cudaSuccess) return e;
         }
-        if (zero_new) cudaMemset(q, 0, want);
-        if (keep && p) cudaMemcpy(q, p, std::min(keep, cap), cudaMemcpyDeviceToDevice);
+        if (zero_new) e = cudaMemsetAsync(q, 0, want, stream);
+        if (e == cudaSuccess && keep && p) e = cudaMemcpyAsync(q, p, std::min(keep, cap), cudaMemcpyDeviceToDevice, stream);
+        if (e == cudaSuccess && (zero_new || (keep && p))) e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) { cudaFree(q); return e; }
         if (p) cudaFree(p);
         p = q;
         cap = want;
@@ -67,6 +71,8 @@ struct GenomeStore {
     std::unordered_map<std::string, int64_t> index;
     DevBuf d_off, d_off_rc, d_len;
     bool table_dirty = true;
+    int device = 0;
+    std::mutex mu;  // sibling contexts share one store (pafgpu_create_sibling): the lazy table upload is serialised
 
     Genome view() const { return Genome{words.as<uint64_t>(), flags.as<uint32_t>(), rank.as<uint32_t>(), exc.as<uint8_t>()}; }
     void reset() {
@@ -76,6 +82,13 @@ struct GenomeStore {
         table_dirty = true;
     }
     void release() { words.release(); flags.release(); rank.release(); exc.release(); d_off.release(); d_off_rc.release(); d_len.release(); }
+    ~GenomeStore() {
+        int cur = 0;
+        cudaGetDevice(&cur);
+        cudaSetDevice(device);
+        release();
+        cudaSetDevice(cur);
+    }
 };
 
 }  // namespace
@@ -93,7 +106,9 @@ struct pafgpu_ctx {
                                   // those reads never queue behind bulk copies on a copy engine
     std::mutex mu;  // library callers may encode from several threads (SURVEY 8b threading row)
 
-    GenomeStore genome, scratch;
+    std::shared_ptr<GenomeStore> genome_ref = std::make_shared<GenomeStore>();  // shared by sibling contexts on the same device
+    GenomeStore &G() const { return *genome_ref; }
+    GenomeStore scratch;
 
     // staging for host batches
     DevBuf in_op_begin, in_ops, in_qc, in_tc, in_qs, in_qe, in_ts, in_strand, in_seq;
@@ -189,9 +204,9 @@ int genome_grow(pafgpu_ctx *c, GenomeStore &g, int64_t need_bases) {
     CU(stream_sync(c));
     // +4 words / +2 groups of slack so a window's third word and rank lookups one past the end stay in bounds
     if (cap >= (1ll << 36)) return fail(c, PAFGPU_EINVAL, "genome arena limited to 2^36 bases per GPU (32-bit word indices)");
-    CU(g.words.ensure((size_t)(cap / 32 + 4) * 8, (size_t)(g.cap_bases / 32 + 4) * 8, true));
-    CU(g.flags.ensure((size_t)(cap / 1024 + 2) * 4, (size_t)(g.cap_bases / 1024 + 2) * 4, true));
-    CU(g.rank.ensure((size_t)(cap / 1024 + 2) * 4, (size_t)(g.cap_bases / 1024 + 2) * 4, true));
+    CU(g.words.ensure((size_t)(cap / 32 + 4) * 8, (size_t)(g.cap_bases / 32 + 4) * 8, true, c->stream));
+    CU(g.flags.ensure((size_t)(cap / 1024 + 2) * 4, (size_t)(g.cap_bases / 1024 + 2) * 4, true, c->stream));
+    CU(g.rank.ensure((size_t)(cap / 1024 + 2) * 4, (size_t)(g.cap_bases / 1024 + 2) * 4, true, c->stream));
     g.cap_bases = cap;
     return 0;
 }
@@ -215,7 +230,7 @@ int genome_pack_copy(pafgpu_ctx *c, GenomeStore &g, const uint8_t *src, int64_t 
     CU(cudaMemcpyAsync(&n_exc, c->woff.as<uint64_t>() + n_groups, 8, cudaMemcpyDeviceToHost, c->stream));
     CU(stream_sync(c));
     if (n_exc) {
-        CU(g.exc.ensure((size_t)(g.exc_total + n_exc) * 32, (size_t)g.exc_total * 32));
+        CU(g.exc.ensure((size_t)(g.exc_total + n_exc) * 32, (size_t)g.exc_total * 32, false, c->stream));
         exc_fill_kernel<<<blocks_for(n_words, 256), 256, 0, c->stream>>>(src, len, (uint64_t)off / 32, g.flags.as<uint32_t>(),
                                                                           g.rank.as<uint32_t>(), g.exc.as<uint8_t>(), n_words, rc);
         g.exc_total += (uint32_t)n_exc;
@@ -260,6 +275,7 @@ int64_t genome_add_host(pafgpu_ctx *c, GenomeStore &g, const char *name, const c
 }
 
 int genome_sync_table(pafgpu_ctx *c, GenomeStore &g) {
+    std::lock_guard<std::mutex> lk(g.mu);
     if (!g.table_dirty) return 0;
     const size_t n = g.off.size();
     CU(g.d_off.ensure(std::max<size_t>(n, 1) * 8));
@@ -538,16 +554,27 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
         if (oe == cudaSuccess && per_sm > 0) ctx->enc_ctas_per_sm = per_sm;
     }
     ctx->scalars.ensure(SC_COUNT * 8);
+    ctx->G().device = device;
     *out = ctx;
     return 0;
 }
+
+int pafgpu_create_sibling(pafgpu_ctx *parent, pafgpu_ctx **out) {
+    if (!parent || !out) return PAFGPU_EINVAL;
+    const int rc = pafgpu_create(parent->device, out);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(parent->mu);
+    (*out)->genome_ref = parent->genome_ref;  // the store the new context was created with is dropped (it owns nothing yet)
+    return 0;
+}
+
+int pafgpu_device_of(const pafgpu_ctx *c) { return c ? c->device : PAFGPU_EINVAL; }
 
 void pafgpu_destroy(pafgpu_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     stream_sync(c);
-    c->genome.release();
-    c->scratch.release();
+    c->scratch.release();  // (the shared genome store goes with its last context)
     DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
                       &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
                       &c->status, &c->tile_first_closer, &c->tile_open_slot, &c->tab_overflow, &c->out, &c->rec_out_begin, &c->rec_mism,
@@ -577,14 +604,14 @@ int pafgpu_genome_reserve(pafgpu_ctx *c, int64_t total_bases) {
     if (!c) return PAFGPU_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
-    return genome_grow(c, c->genome, c->genome.next_off + 2 * total_bases + 4 * ARENA_ALIGN);  // forward + reverse-complement copies
+    return genome_grow(c, c->G(), c->G().next_off + 2 * total_bases + 4 * ARENA_ALIGN);  // forward + reverse-complement copies
 }
 
 int64_t pafgpu_genome_add_contig(pafgpu_ctx *c, const char *name, const char *seq, int64_t len) {
     if (!c || !name || (!seq && len)) return PAFGPU_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
-    return genome_add_host(c, c->genome, name, seq, len);
+    return genome_add_host(c, c->G(), name, seq, len);
 }
 
 int64_t pafgpu_genome_add_contig_device(pafgpu_ctx *c, const char *name, const void *seq_dev, int64_t len) {
@@ -592,7 +619,7 @@ int64_t pafgpu_genome_add_contig_device(pafgpu_ctx *c, const char *name, const v
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
     CU(cudaDeviceSynchronize());  // the producer of seq_dev may be on another stream
-    return genome_add_device(c, c->genome, name, static_cast<const uint8_t *>(seq_dev), len);
+    return genome_add_device(c, c->G(), name, static_cast<const uint8_t *>(seq_dev), len);
 }
 
 // One FASTA record whose sequence text (everything between the header line and the next '>') is raw[0..n): the text goes
@@ -601,7 +628,7 @@ int64_t pafgpu_genome_add_contig_device(pafgpu_ctx *c, const char *name, const v
 static int fasta_add_record(pafgpu_ctx *c, const std::string &name, const char *raw, int64_t n) {
     CU(c->in_seq.ensure((size_t)std::max<int64_t>(n, 16)));
     if (n == 0) {
-        const int64_t id = genome_add_device(c, c->genome, name.c_str(), c->in_seq.as<uint8_t>(), 0);
+        const int64_t id = genome_add_device(c, c->G(), name.c_str(), c->in_seq.as<uint8_t>(), 0);
         return id < 0 ? (int)id : 0;
     }
     const int64_t nt = (n + FA_TILE - 1) / FA_TILE;
@@ -625,7 +652,7 @@ static int fasta_add_record(pafgpu_ctx *c, const std::string &name, const char *
     fasta_compact_kernel<<<(unsigned)nt, FA_THREADS, 0, c->stream>>>(c->fa_raw.as<unsigned char>(), n, c->fa_tile_off.as<uint64_t>(),
                                                                     c->in_seq.as<unsigned char>());
     CU(cudaGetLastError());
-    const int64_t id = genome_add_device(c, c->genome, name.c_str(), c->in_seq.as<uint8_t>(), (int64_t)host[1]);
+    const int64_t id = genome_add_device(c, c->G(), name.c_str(), c->in_seq.as<uint8_t>(), (int64_t)host[1]);
     return id < 0 ? (int)id : 0;
 }
 
@@ -675,29 +702,183 @@ int pafgpu_genome_load_fasta(pafgpu_ctx *c, const char *path) {
 
 int64_t pafgpu_genome_find(const pafgpu_ctx *c, const char *name) {
     if (!c || !name) return PAFGPU_EINVAL;
-    auto it = c->genome.index.find(name);
-    return it == c->genome.index.end() ? (int64_t)PAFGPU_ENOCONTIG : it->second;
+    auto it = c->G().index.find(name);
+    return it == c->G().index.end() ? (int64_t)PAFGPU_ENOCONTIG : it->second;
 }
 
 int64_t pafgpu_genome_contig_length(const pafgpu_ctx *c, int64_t id) {
-    if (!c || id < 0 || id >= (int64_t)c->genome.len.size()) return PAFGPU_ENOCONTIG;
-    return c->genome.len[(size_t)id];
+    if (!c || id < 0 || id >= (int64_t)c->G().len.size()) return PAFGPU_ENOCONTIG;
+    return c->G().len[(size_t)id];
 }
 
-int64_t pafgpu_genome_num_contigs(const pafgpu_ctx *c) { return c ? (int64_t)c->genome.index.size() : PAFGPU_EINVAL; }
+int64_t pafgpu_genome_num_contigs(const pafgpu_ctx *c) { return c ? (int64_t)c->G().index.size() : PAFGPU_EINVAL; }
 
 int pafgpu_genome_fetch(pafgpu_ctx *c, int64_t id, int64_t start, int64_t len, char *out) {
     if (!c || !out) return PAFGPU_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
-    if (id < 0 || id >= (int64_t)c->genome.len.size()) return fail(c, PAFGPU_ENOCONTIG, "bad contig id");
-    if (start < 0 || len < 0 || start + len > c->genome.len[(size_t)id]) return fail(c, PAFGPU_EBOUNDS, "range outside contig");
+    if (id < 0 || id >= (int64_t)c->G().len.size()) return fail(c, PAFGPU_ENOCONTIG, "bad contig id");
+    if (start < 0 || len < 0 || start + len > c->G().len[(size_t)id]) return fail(c, PAFGPU_EBOUNDS, "range outside contig");
     if (len == 0) return 0;
     CU(cudaSetDevice(c->device));
     CU(c->in_seq.ensure((size_t)len));
-    unpack_kernel<<<blocks_for(len, 256), 256, 0, c->stream>>>(c->genome.view(), (uint64_t)(c->genome.off[(size_t)id] + start), len,
+    unpack_kernel<<<blocks_for(len, 256), 256, 0, c->stream>>>(c->G().view(), (uint64_t)(c->G().off[(size_t)id] + start), len,
                                                                c->in_seq.as<uint8_t>());
     CU(cudaMemcpyAsync(out, c->in_seq.p, (size_t)len, cudaMemcpyDeviceToHost, c->stream));
     CU(stream_sync(c));
+    return 0;
+}
+
+
+// ---- genome replication and persistence ----------------------------------------------------------------------------
+// Bytes of each arena array in use (everything behind next_off is zero / not consulted).
+namespace {
+struct ArenaBytes { size_t words, flags, rank, exc; };
+ArenaBytes arena_bytes(const GenomeStore &g) {
+    return ArenaBytes{(size_t)(g.next_off / 32 + 4) * 8, (size_t)(g.next_off / 1024 + 2) * 4, (size_t)(g.next_off / 1024 + 2) * 4,
+                      std::max<size_t>((size_t)g.exc_total * 32, 32)};
+}
+// a fresh store on c's device holding the host-side tables of src and zeroed arrays of the same capacity
+int genome_shell(pafgpu_ctx *c, const GenomeStore &src, std::shared_ptr<GenomeStore> &out) {
+    auto g = std::make_shared<GenomeStore>();
+    g->device = c->device;
+    g->cap_bases = 0;
+    g->next_off = src.next_off; g->exc_total = src.exc_total;
+    g->names = src.names; g->off = src.off; g->off_rc = src.off_rc; g->len = src.len; g->index = src.index;
+    g->table_dirty = true;
+    if (int rc = genome_grow(c, *g, std::max<int64_t>(src.next_off + ARENA_ALIGN, ARENA_ALIGN))) return rc;
+    CU(g->exc.ensure(arena_bytes(src).exc));
+    out = g;
+    return 0;
+}
+}  // namespace
+
+// The packed genome of `src` copied GPU to GPU into `dst` (cudaMemcpyPeerAsync: NVLink / NVSwitch when peer access is
+// available, staged through the host otherwise): multi-GPU runs pack the FASTA once, not once per GPU.
+int pafgpu_genome_clone(pafgpu_ctx *dst, pafgpu_ctx *src) {
+    if (!dst || !src) return PAFGPU_EINVAL;
+    if (dst == src || dst->genome_ref == src->genome_ref) return 0;
+    pafgpu_ctx *c = dst;
+    std::lock_guard<std::mutex> lk(dst->mu);
+    std::shared_ptr<GenomeStore> from = src->genome_ref;
+    CU(cudaSetDevice(dst->device));
+    if (dst->device == from->device) { dst->genome_ref = from; return 0; }  // same GPU: share, do not copy
+    if (cudaDeviceEnablePeerAccess(from->device, 0) != cudaSuccess) cudaGetLastError();  // already enabled / not possible: the copy still works
+    std::shared_ptr<GenomeStore> g;
+    if (int rc = genome_shell(dst, *from, g)) return rc;
+    const ArenaBytes nb = arena_bytes(*from);
+    CU(cudaMemcpyPeerAsync(g->words.p, dst->device, from->words.p, from->device, nb.words, dst->stream));
+    CU(cudaMemcpyPeerAsync(g->flags.p, dst->device, from->flags.p, from->device, nb.flags, dst->stream));
+    CU(cudaMemcpyPeerAsync(g->rank.p, dst->device, from->rank.p, from->device, nb.rank, dst->stream));
+    if (from->exc.p) CU(cudaMemcpyPeerAsync(g->exc.p, dst->device, from->exc.p, from->device, std::min(nb.exc, from->exc.cap), dst->stream));
+    CU(stream_sync(dst));
+    dst->genome_ref = g;
+    return 0;
+}
+
+// Packed-genome file (the FASTA load is repeated by every process of a pipeline; the packed arena is
+// half the size of the FASTA text and loads at copy speed). Layout: magic, key, counters, contig table, the four arrays.
+namespace {
+const char GENOME_MAGIC[8] = {'P', 'A', 'F', 'B', '2', 'G', '0', '1'};
+bool put(FILE *f, const void *p, size_t n) { return n == 0 || fwrite(p, 1, n, f) == n; }
+bool get(FILE *f, void *p, size_t n) { return n == 0 || fread(p, 1, n, f) == n; }
+}  // namespace
+
+int pafgpu_genome_save(pafgpu_ctx *c, const char *path, const char *key) {
+    if (!c || !path) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    GenomeStore &g = c->G();
+    const std::string tmp = std::string(path) + ".tmp";
+    FILE *f = fopen(tmp.c_str(), "wb");
+    if (!f) return fail(c, PAFGPU_EIO, std::string("cannot write ") + tmp);
+    const std::string k = key ? key : "";
+    const ArenaBytes nb = arena_bytes(g);
+    const uint64_t head[8] = {(uint64_t)k.size(), (uint64_t)g.next_off, g.exc_total, (uint64_t)g.names.size(), nb.words, nb.flags, nb.rank, nb.exc};
+    bool ok = put(f, GENOME_MAGIC, 8) && put(f, head, sizeof head) && put(f, k.data(), k.size());
+    for (size_t i = 0; ok && i < g.names.size(); i++) {
+        const uint64_t row[4] = {(uint64_t)g.names[i].size(), (uint64_t)g.off[i], (uint64_t)g.off_rc[i], (uint64_t)g.len[i]};
+        ok = put(f, row, sizeof row) && put(f, g.names[i].data(), g.names[i].size());
+    }
+    // arrays: device -> pinned staging -> file, a slice at a time
+    const size_t slice = (size_t)64 << 20;
+    void *stage = pafgpu_host_alloc((int64_t)slice);
+    if (!stage) { fclose(f); return fail(c, PAFGPU_ENODEVICE, "pinned host allocation failed"); }
+    const DevBuf *arr[4] = {&g.words, &g.flags, &g.rank, &g.exc};
+    const size_t bytes[4] = {nb.words, nb.flags, nb.rank, nb.exc};
+    cudaError_t ce = cudaSuccess;
+    for (int a = 0; ok && a < 4 && ce == cudaSuccess; a++)
+        for (size_t at = 0; ok && at < bytes[a] && ce == cudaSuccess; at += slice) {
+            const size_t n = std::min(slice, bytes[a] - at);
+            if (arr[a]->p && at + n <= arr[a]->cap) {
+                ce = cudaMemcpyAsync(stage, (const char *)arr[a]->p + at, n, cudaMemcpyDeviceToHost, c->stream);
+                if (ce == cudaSuccess) ce = stream_sync(c);
+            } else {
+                memset(stage, 0, n);
+            }
+            ok = put(f, stage, n);
+        }
+    pafgpu_host_free(stage);
+    ok = (fclose(f) == 0) && ok;
+    if (ce != cudaSuccess) { remove(tmp.c_str()); return fail(c, PAFGPU_ENODEVICE, std::string("genome save: ") + cudaGetErrorString(ce)); }
+    if (!ok || rename(tmp.c_str(), path) != 0) { remove(tmp.c_str()); return fail(c, PAFGPU_EIO, std::string("cannot write ") + path); }
+    return 0;
+}
+
+int pafgpu_genome_load_packed(pafgpu_ctx *c, const char *path, const char *key) {
+    if (!c || !path) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    FILE *f = fopen(path, "rb");
+    if (!f) return fail(c, PAFGPU_EIO, std::string("cannot open ") + path);
+    char magic[8];
+    uint64_t head[8];
+    const std::string want = key ? key : "";
+    std::string k;
+    bool ok = get(f, magic, 8) && memcmp(magic, GENOME_MAGIC, 8) == 0 && get(f, head, sizeof head) && head[0] < (1u << 20);
+    if (ok) { k.resize((size_t)head[0]); ok = get(f, &k[0], k.size()); }
+    if (!ok || k != want) { fclose(f); return fail(c, PAFGPU_ESTATE, ok ? "packed genome was made from other inputs (key differs)" : "not a packed genome file"); }
+    GenomeStore src;  // host tables only
+    src.device = c->device;
+    src.next_off = (int64_t)head[1]; src.exc_total = (uint32_t)head[2];
+    for (uint64_t i = 0; ok && i < head[3]; i++) {
+        uint64_t row[4];
+        ok = get(f, row, sizeof row) && row[0] < (1u << 20);
+        if (!ok) break;
+        std::string name((size_t)row[0], '\0');
+        ok = get(f, &name[0], name.size());
+        src.names.push_back(name); src.off.push_back((int64_t)row[1]); src.off_rc.push_back((int64_t)row[2]); src.len.push_back((int64_t)row[3]);
+        src.index[name] = (int64_t)i;  // a repeated name points at the newest contig
+    }
+    std::shared_ptr<GenomeStore> g;
+    if (ok) {
+        const ArenaBytes nb = arena_bytes(src);
+        ok = nb.words == head[4] && nb.flags == head[5] && nb.rank == head[6] && nb.exc == head[7];
+    }
+    if (!ok) { fclose(f); return fail(c, PAFGPU_EIO, "packed genome file is damaged"); }
+    if (int rc = genome_shell(c, src, g)) { fclose(f); return rc; }
+    const size_t slice = (size_t)64 << 20;
+    char *stage[2] = {(char *)pafgpu_host_alloc((int64_t)slice), (char *)pafgpu_host_alloc((int64_t)slice)};
+    cudaEvent_t done[2] = {nullptr, nullptr};
+    cudaError_t ce = (stage[0] && stage[1]) ? cudaSuccess : cudaErrorMemoryAllocation;
+    for (int i = 0; i < 2 && ce == cudaSuccess; i++) ce = cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming);
+    DevBuf *arr[4] = {&g->words, &g->flags, &g->rank, &g->exc};
+    int turn = 0;
+    for (int a = 0; ok && a < 4 && ce == cudaSuccess; a++)
+        for (size_t at = 0; ok && at < head[4 + a] && ce == cudaSuccess; at += slice, turn ^= 1) {
+            const size_t n = std::min<size_t>(slice, head[4 + a] - at);
+            ce = cudaEventSynchronize(done[turn]);  // the copy that last used this staging buffer
+            if (ce != cudaSuccess) break;
+            ok = get(f, stage[turn], n);
+            if (!ok) break;
+            ce = cudaMemcpyAsync((char *)arr[a]->p + at, stage[turn], n, cudaMemcpyHostToDevice, c->stream);
+            if (ce == cudaSuccess) ce = cudaEventRecord(done[turn], c->stream);
+        }
+    if (ce == cudaSuccess) ce = stream_sync(c);
+    for (int i = 0; i < 2; i++) { if (done[i]) cudaEventDestroy(done[i]); pafgpu_host_free(stage[i]); }
+    fclose(f);
+    if (ce != cudaSuccess) return fail(c, PAFGPU_ENODEVICE, std::string("packed genome load: ") + cudaGetErrorString(ce));
+    if (!ok) return fail(c, PAFGPU_EIO, "packed genome file is truncated");
+    c->genome_ref = g;
     return 0;
 }
 
@@ -706,7 +887,7 @@ int pafgpu_encode_batch_host(pafgpu_ctx *c, const pafgpu_batch *b, pafgpu_result
     if (!c) return PAFGPU_EINVAL;
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
-    return encode_host(c, c->genome, b, res);
+    return encode_host(c, c->G(), b, res);
 }
 
 int pafgpu_encode_batch_device(pafgpu_ctx *c, const pafgpu_batch *b, pafgpu_result *res) {
@@ -714,7 +895,7 @@ int pafgpu_encode_batch_device(pafgpu_ctx *c, const pafgpu_batch *b, pafgpu_resu
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
     CU(cudaDeviceSynchronize());  // inputs may have been produced on another stream
-    return encode_device(c, c->genome, b, res);
+    return encode_device(c, c->G(), b, res);
 }
 
 int pafgpu_fetch_ops(pafgpu_ctx *c, uint64_t *out_ops, int64_t *out_op_begin, int64_t *rec_mismatch) {

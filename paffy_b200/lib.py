@@ -22,6 +22,7 @@ ABI_SYMBOLS = [
     "pafgpu_serialise", "pafgpu_fetch_text", "pafgpu_encode_one", "pafgpu_time_encode",
     "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition", "pafgpu_trim",
     "pafgpu_trim_fixed", "pafgpu_stage_ops_host", "pafgpu_add_mismatches_file_filtered",
+    "pafgpu_create_sibling", "pafgpu_device_of", "pafgpu_genome_clone", "pafgpu_genome_save", "pafgpu_genome_load_packed",
 ]
 # reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
 REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paffy_view_main", "paffy_trim_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
