@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define PAFGPU_ABI_VERSION 1
+#define PAFGPU_ABI_VERSION 2
 
 enum {
     PAFGPU_OK = 0,
@@ -48,6 +48,10 @@ void pafgpu_destroy(pafgpu_ctx *ctx);
  * must not be modified while siblings encode. (The reference has no counterpart: it is single-threaded.) */
 int pafgpu_create_sibling(pafgpu_ctx *parent, pafgpu_ctx **out);
 int pafgpu_device_of(const pafgpu_ctx *ctx);
+/* The k-th helper context of `parent` on `device`: created on first use, owned by the parent (destroyed with it), its
+ * genome kept equal to the parent's (shared on the same GPU, cloned GPU to GPU elsewhere). The file pipeline uses these
+ * so that repeated calls do not pay context, stream and buffer creation again. */
+int pafgpu_helper(pafgpu_ctx *parent, int device, int k, pafgpu_ctx **out);
 const char *pafgpu_last_error(const pafgpu_ctx *ctx); /* ctx may be NULL: last creation error */
 
 /* ---- genome store: replaces the name -> char* hash the reference fills with
@@ -100,7 +104,7 @@ typedef struct {
 typedef struct {
     int64_t n_out_ops;      /* total output CigarRecord words */
     int64_t aligned_bases;  /* sum of input M lengths (the unit of the throughput metric) */
-    int64_t n_windows;      /* 64-base work windows scheduled */
+    int64_t n_windows;      /* work windows (128 bases) scheduled */
     int64_t n_tiles;        /* warp tiles scheduled */
     int64_t retried;        /* 1 when the output buffer guess was too small and the encode pass ran twice */
     float ms_ingest;        /* CUDA-event time of the CIGAR ingest kernels */
@@ -135,6 +139,25 @@ int pafgpu_serialise(pafgpu_ctx *ctx, const char *prefix_bytes, const int64_t *p
                      int64_t *text_bytes_out, float *ms_out);
 /* Copy the serialised text (text_bytes_out bytes) and optionally per-record line offsets (n_records+1). */
 int pafgpu_fetch_text(pafgpu_ctx *ctx, char *text, int64_t *line_begin);
+
+/* ---- PAF text in, PAF text out: replaces, for a chunk of whole lines, paf_read_with_buffer /
+ *      paf_parse / cigar_parse (impl/paf.c:70-111, 137-218), the contig lookups (impl/paf_add_mismatches.c:116-127),
+ *      paf_encode_mismatches, paf_check (impl/paf.c:427-461) and paf_write_to_buffer (impl/paf.c:317-389) of
+ *      `paffy add_mismatches`: the raw bytes go to the device, are split into lines and fields, parsed, looked up, encoded
+ *      and rendered there; the finished text is fetched with pafgpu_fetch_text. `text` is free of '\r'. A record the
+ *      reference would abort on is only located (first_bad): the records before it are processed, the caller prints
+ *      the reference's message for that line (bytes [bad_line_begin, bad_line_end) of `text`). ------------------------ */
+typedef struct {
+    int64_t records;        /* records processed (= lines before first_bad, or all) */
+    int64_t records_in;     /* lines of the chunk */
+    int64_t n_ops, n_out_ops, aligned_bases;
+    int64_t text_bytes;     /* bytes of output text waiting on the device */
+    int64_t first_bad;      /* -1, or the index of the first record the reference would abort on */
+    int64_t bad_line_begin, bad_line_end;
+    int64_t stats[7];       /* as pafgpu_file_report.stats, for the processed records */
+    float ms_parse, ms_ingest, ms_kernel, ms_encode, ms_render; /* CUDA-event ms: text -> SoA, ingest, encode_kernel, encode stage, SoA -> text */
+} pafgpu_text_result;
+int pafgpu_add_mismatches_text(pafgpu_ctx *ctx, const char *text, int64_t n_bytes, pafgpu_text_result *res);
 
 /* ---- device trim: replaces paf_trim_unreliable_tails (inc/paf.h:269, impl/paf.c:906-953) for the whole batch, on the
  *      encoded ops still resident on the device. score_fraction / max_fraction are `paffy trim -r / -t`. t_end: host
@@ -198,6 +221,10 @@ typedef struct {
     float trim_max_fraction;   /* paffy trim -t (reference default 1.0) */
     int threads;               /* host threads for parsing / rendering, 0 = all */
     int64_t batch_bases;       /* aligned bases per GPU batch, 0 = default */
+    int gpus;                  /* GPUs of the box the job is sharded over (the context's own first), 0 = $PAFFY_GPUS (a count,
+                                  "all", or a comma-separated device list) or 1. The packed genome is cloned GPU to GPU. */
+    int streams;               /* contexts (stream + work buffers) per GPU so that copies and kernels overlap, 0 = $PAFFY_STREAMS or 2 */
+    int64_t chunk_bytes;       /* bytes of PAF text per chunk (the unit that is read, dealt to a GPU and written in order), 0 = 48 MiB */
 } pafgpu_file_opts;
 typedef struct {
     int64_t records;           /* records written */
@@ -207,9 +234,13 @@ typedef struct {
     int64_t stats[7];          /* paf_stats_calc totals over the encoded records + record count, as `paffy view -s`
                                   accumulates them (impl/paf_view.c:176-178): matches, mismatches, query_inserts,
                                   query_deletes, query_insert_bases, query_delete_bases, records */
-    double s_read, s_parse, s_gpu, s_host, s_write; /* wall seconds per stage */
+    double s_read, s_parse, s_gpu, s_host, s_write; /* seconds per stage, summed over the worker threads (they overlap) */
+    double s_total;            /* wall seconds of the whole call */
+    int64_t chunks, gpus, workers; /* chunks processed; GPUs and worker contexts used */
 } pafgpu_file_report;
-/* in_path / out_path NULL = stdin / stdout. */
+/* in_path / out_path NULL = stdin / stdout. The call streams: the input is read in chunks of whole lines, chunks are
+ * processed concurrently (opts->streams contexts on each of opts->gpus GPUs) and written in input order, so memory is
+ * bounded by the chunks in flight and output starts before the input ends, like the reference's record loop. */
 int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char *out_path, const pafgpu_file_opts *opts,
                                pafgpu_file_report *report);
 

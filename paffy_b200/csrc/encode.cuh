@@ -1,18 +1,19 @@
 // encode.cuh - the base-comparison scan (a1 + a7 of SURVEY.md section 8): M ops -> =/X runs.
 // Restates paf_encode_mismatches (impl/paf.c:739-784); nothing is copied from it.
 //
-// Work axis = 64-base windows of all ops of the batch (an M op of length n owns ceil(n/64) windows,
-// every other op owns one), cut into warp tiles of 256 windows; a CTA takes the next CTA tile (one warp
+// Work axis = windows of WIN_BASES bases (128 by default: 4 bit-sliced words) of all ops of the batch (an M op of length
+// n owns ceil(n / WIN_BASES) windows, every other op owns one), cut into warp tiles of 16 384 window-axis bases (512
+// words: 16 per lane); a CTA takes the next CTA tile (one warp
 // tile per warp) from a ticket counter, so megabase CIGARs spread over the whole grid. ONE kernel, one
 // pass over the sequences, no scratch round trip through HBM:
 //   A  op table     op lanes load the tile's ops once and leave, per op, everything a window needs in
 //                   shared memory (word index + bit phase of target and query, bases left, flags) plus a
 //                   bitmap of the windows at which an op starts, so a window finds its op with a popcount.
-//   B  compare      striped (window = 32 * iteration + lane, coalesced): every lane issues the 6 x 64-bit
-//                   loads of several windows at once, funnel-shifts the bit planes into phase ('-' strand
+//   B  compare      striped (window = 32 * iteration + lane, coalesced): every lane issues the WIN_WORDS + 1 64-bit
+//                   loads per stream of a window (or of several windows) at once, funnel-shifts the bit planes into phase ('-' strand
 //                   queries are read from the reverse-complement copy of the contig), one LOP3 per plane -> one mismatch bit per base. The 64-bit
 //                   mask of every window goes to shared memory; mismatches are tallied per record.
-//   C  count        blocked (lane owns 8 consecutive windows): run starts per lane, warp scan.
+//   C  count        blocked (lane owns 16 consecutive words): run starts per lane, warp scan.
 //   D  look-back    the CTA publishes its number of output ops and obtains the number before it with a
 //                   decoupled look-back over the tiles ticketed earlier (those are already running, so the
 //                   wait is short and cannot deadlock).
@@ -31,6 +32,10 @@
 #ifndef ENC_SHFL_T2
 #define ENC_SHFL_T2 0  // 1: the third word of a window comes from the next lane's first word by shuffle when both windows
                        // belong to the same op (4 instead of 6 sequence loads per window on the common path)
+#endif
+#ifndef ENC_LDG128
+#define ENC_LDG128 1   // 1: the WIN_WORDS + 1 words of a window come from aligned 128-bit loads (the pair holding the first word
+                       // and the pairs behind it), the word parity of the first one picked with selects: fewer, wider L1 requests
 #endif
 #ifndef ENC_ROLL_HB
 #define ENC_ROLL_HB 0  // 1: the batch loop of the compare phase is not unrolled (smaller code)
@@ -58,9 +63,16 @@ struct EncodeParams {
     struct OpEntry *tab_overflow;   // TILE_TAB entries per resident warp: table entries TAB_SMEM.. of tiles with many short ops
 };
 
-constexpr int WIN_BASES = 64;
-constexpr int TILE_ITERS = 8;                 // windows per lane per warp tile
+#ifndef ENC_WIN_WORDS
+#define ENC_WIN_WORDS 4
+#endif
+constexpr int WIN_WORDS = ENC_WIN_WORDS;      // 32-base words per window (2 or 4)
+constexpr int WIN_BASES = 32 * WIN_WORDS;
+constexpr int LANE_WORDS = 16;                // words a lane owns in the blocked view (512 bases)
+constexpr int TILE_ITERS = LANE_WORDS / WIN_WORDS;  // windows per lane per warp tile
 constexpr int TILE_WIN = 32 * TILE_ITERS;     // windows per warp tile
+constexpr int TILE_WORDS = 32 * LANE_WORDS;   // 32-base words per warp tile
+static_assert(WIN_WORDS == 2 || WIN_WORDS == 4, "windows of 64 or 128 bases");
 constexpr int TILE_TAB = TILE_WIN + 2;        // a tile overlaps at most TILE_WIN + 1 ops
 #ifndef ENC_TAB_SMEM
 #define ENC_TAB_SMEM 112
@@ -69,9 +81,9 @@ constexpr int TILE_TAB = TILE_WIN + 2;        // a tile overlaps at most TILE_WI
 #define ENC_LIST_CAP 448
 #endif
 constexpr int TAB_SMEM = ENC_TAB_SMEM;                 // table entries kept in shared memory; denser tiles spill the rest to HBM
-constexpr int MASK_PAD = TILE_WIN + TILE_WIN / 16;  // mask of window p sits at p + (p >> 4): striped 8-byte stores (16 lanes = 128
-                                                     // contiguous bytes) and blocked 8-byte loads (lane stride 64 bytes, one more slot
-                                                     // every other lane) are both free of bank conflicts
+constexpr int MASK_WORDS = 2 + TILE_WORDS + 2 * (TILE_WORDS / 32);  // mismatch bits of word k sit at 32-bit index 2 + k + 2 * (k >> 5):
+                                                     // striped 8-byte stores and blocked 8-byte loads (lane stride 64 bytes, one more
+                                                     // 8-byte slot every other lane) are both free of bank conflicts
 constexpr int LIST_CAP = ENC_LIST_CAP;                 // events converted per round
 constexpr uint32_t COORD_OPEN = 0xffffffffu;
 constexpr unsigned long long ST_AGG = 1ull << 62, ST_INCL = 2ull << 62, ST_VAL = (1ull << 62) - 1;
@@ -92,10 +104,10 @@ struct __align__(16) OpEntry {
     uint32_t misc;   // bits 0-4 target phase, 5-9 query phase, then EF_* flags and ES_* fields
 };
 constexpr uint32_t EF_PASS = 1u << 11, EF_EXC = 1u << 13;
-// ops that start inside the tile: bits 14-21 the tile window they start at, 22-27 bases between the previous M op's
-// end and that window boundary (64 - bases in its last window), 28 first op of its record
+// ops that start inside the tile: bits 14-21 the tile window they start at, 22-28 bases between the previous M op's
+// end and that window boundary (WIN_BASES - bases in its last window), 29 first op of its record
 constexpr int ES_WIN = 14, ES_GAP = 22;
-constexpr uint32_t EF_HEAD = 1u << 28;
+constexpr uint32_t EF_HEAD = 1u << 29;
 constexpr int32_t REM_CLAMP = 0xffff;
 __device__ __forceinline__ int32_t entry_rem(const struct OpEntry &en);
 __device__ __forceinline__ uint32_t entry_rec(const struct OpEntry &en);
@@ -105,14 +117,14 @@ __device__ __forceinline__ uint32_t entry_rec(const OpEntry &en) { return (uint3
 
 struct WarpSmem {
     OpEntry tab[TAB_SMEM];
-    uint64_t mask[MASK_PAD + 1];      // mismatch bits of window p at 1 + p + (p >> 4); the word before a lane's 8
-                                      // windows is the half-window before them (a pad word filled in for even lanes)
+    alignas(8) uint32_t mask[MASK_WORDS];  // mismatch bits of word k at 2 + k + 2 * (k >> 5); the word before a lane's 16
+                                      // words is the word before them (a pad word filled in for even lanes)
     uint32_t list[LIST_CAP + 1];      // events of one round (+ sink), see LE_*
     alignas(16) uint16_t prel[TILE_WIN];  // events of the owning lane before window p
     uint16_t lanex[32];               // events of the tile before lane l
     uint32_t bm[TILE_ITERS];          // bit p: an op starts at tile window p
     uint32_t bmpre[TILE_ITERS];       // op starts before word k of bm
-    uint2 nf[TILE_WIN / 16];          // per 32 half-window words: .x those holding events, .y those an op starts at
+    uint2 nf[TILE_WORDS / 32];        // per 32 words: .x those holding events, .y those an op starts at
 };
 
 // table entry i of the warp's tile: shared memory, or the warp's overflow area in HBM for the rare tile with more
@@ -188,7 +200,7 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
             if (wo >= s0) {
                 const uint32_t w = (uint32_t)(wo - s0);
                 const uint32_t gap = prev_end ? WIN_BASES * w - prev_end : 0u;
-                en.misc |= (w << ES_WIN) | ((gap & 63u) << ES_GAP) | ((rec >> 31) ? EF_HEAD : 0u);
+                en.misc |= (w << ES_WIN) | ((gap & (uint32_t)(WIN_BASES - 1)) << ES_GAP) | ((rec >> 31) ? EF_HEAD : 0u);
                 atomicOr(&S.bm[w >> 5], 1u << (w & 31));
             }
             en.rem |= (int32_t)(((rec & 0x7fffffffu) - rec_first) << 16);
@@ -200,10 +212,16 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
     }
     any_exc = __any_sync(FULL, exc);
     __syncwarp();
-    if (lane < TILE_ITERS) {
-        uint32_t pre = 0;
-        for (unsigned q = 0; q < lane; q++) pre += __popc(S.bm[q]);
-        S.bmpre[lane] = pre;
+    {
+        // op starts before word k of the bitmap (all lanes take part in the shuffles; TILE_ITERS <= 8 words)
+        const uint32_t mine = lane < TILE_ITERS ? (uint32_t)__popc(S.bm[lane]) : 0u;
+        uint32_t inc = mine;
+#pragma unroll
+        for (int o = 1; o < TILE_ITERS; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(FULL, inc, o);
+            if (lane >= (unsigned)o) inc += t;
+        }
+        if (lane < TILE_ITERS) S.bmpre[lane] = inc - mine;
     }
     __syncwarp();
 }
@@ -213,6 +231,7 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
 template <int BATCH, bool EXC>
 __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem &S, const TileTab &T, uint32_t n_act, unsigned lane, unsigned adj, uint32_t rec_first) {
     static_assert(TILE_ITERS % BATCH == 0, "BATCH must divide the iterations of a tile");
+    constexpr int WW = WIN_WORDS;
     const uint64_t *__restrict__ gw = P.G.words;
     uint32_t pre = 0, pm0 = 0;
     uint32_t cur = 0, acc = 0;  // record (relative to rec_first) being tallied, and the lane's share of its mismatches
@@ -224,9 +243,11 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
     for (int hb = 0; hb < TILE_ITERS; hb += BATCH) {
         // issue every sequence load of the batch (inactive and pass-through windows read arena word 0: no branches)
         OpEntry EN[BATCH];
-        uint64_t T0[BATCH], T1[BATCH], T2[BATCH], Q0[BATCH], Q1[BATCH], Q2[BATCH];
-#if ENC_SHFL_T2
-        bool NB[BATCH];
+        uint64_t TW[BATCH][WW + 1], QW[BATCH][WW + 1];
+#if ENC_LDG128
+        constexpr int NP = (WW + 2) / 2;  // aligned pairs that cover WW + 1 words starting at either parity
+        uint4 TP[BATCH][NP], QP[BATCH][NP];
+        bool t_odd[BATCH], q_odd[BATCH];
 #endif
         uint64_t pm_t = 0, pm_q = 0;  // lane 0, first window only: words holding the base before the window
         uint32_t pm_k = 0;
@@ -240,20 +261,23 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const OpEntry en = EXC ? T.get(idx) : S.tab[idx];  // (the slow variant also serves tiles whose table spills)
             EN[b] = en;
             const bool isM = srel < n_act && !(en.misc & EF_PASS);
-            const int32_t tw = isM ? en.tw + 2 * (int32_t)srel : 0;
-            const int32_t qw = isM ? en.qw + 2 * (int32_t)srel : 0;
-            const uint64_t *tpn = gw + tw, *qpn = gw + qw;
-#if ENC_SHFL_T2
-            // the next lane's window continues the same op: its first word is my third one
-            const uint32_t idx_n = __shfl_down_sync(FULL, idx, 1);
-            NB[b] = lane < 31 && idx_n == idx && isM && srel + 1 < n_act;
-            T0[b] = ldg64(tpn); T1[b] = ldg64(tpn + 1);
-            Q0[b] = ldg64(qpn); Q1[b] = ldg64(qpn + 1);
-            T2[b] = Q2[b] = 0;
-            if (!NB[b]) { T2[b] = ldg64(tpn + 2); Q2[b] = ldg64(qpn + 2); }
+            const int32_t tw = isM ? en.tw + WW * (int32_t)srel : 0;
+            const int32_t qw = isM ? en.qw + WW * (int32_t)srel : 0;
+#if ENC_LDG128
+            {
+                const uint4 *tp4 = reinterpret_cast<const uint4 *>(gw + (tw & ~1)), *qp4 = reinterpret_cast<const uint4 *>(gw + (qw & ~1));
+                t_odd[b] = tw & 1; q_odd[b] = qw & 1;
+#pragma unroll
+                for (int k = 0; k < NP; k++) TP[b][k] = __ldg(tp4 + k);
+#pragma unroll
+                for (int k = 0; k < NP; k++) QP[b][k] = __ldg(qp4 + k);
+            }
 #else
-            T0[b] = ldg64(tpn); T1[b] = ldg64(tpn + 1); T2[b] = ldg64(tpn + 2);
-            Q0[b] = ldg64(qpn); Q1[b] = ldg64(qpn + 1); Q2[b] = ldg64(qpn + 2);
+            const uint64_t *tpn = gw + tw, *qpn = gw + qw;
+#pragma unroll
+            for (int k = 0; k <= WW; k++) TW[b][k] = ldg64(tpn + k);
+#pragma unroll
+            for (int k = 0; k <= WW; k++) QW[b][k] = ldg64(qpn + k);
 #endif
             if (it == 0 && lane == 0 && isM && !(w & 1u)) {
                 // tile window 0 continues an op: mismatch state of the base just before the tile
@@ -282,11 +306,11 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
                 if (srel < n_act) {
                     const OpEntry en = EXC ? T.get(idx) : S.tab[idx];  // (the slow variant also serves tiles whose table spills)
                     if (!(en.misc & EF_PASS)) {
-                        const uint64_t *tpn = gw + (en.tw + 2 * (int32_t)srel), *qpn = gw + (en.qw + 2 * (int32_t)srel);
-                        // a window spans 3 words, the next lane's window starts 2 words on: the middle word of every
+                        const uint64_t *tpn = gw + (en.tw + WW * (int32_t)srel), *qpn = gw + (en.qw + WW * (int32_t)srel);
+                        // a window spans WW + 1 words, the next lane's window starts WW words on: the middle word of every
                         // window touches every 32-byte sector of the op's span
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(tpn + 1));
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(qpn + 1));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(tpn + WW / 2));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(qpn + WW / 2));
                     }
                 }
             }
@@ -308,43 +332,61 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
             const uint32_t n = !isM ? 0u : rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
             const uint32_t misc = en.misc;
             const unsigned sht = misc & 31u, shq = (misc >> 5) & 31u;
-#if ENC_SHFL_T2
+            uint32_t m[WW];
+#if ENC_LDG128
             {
-                const uint64_t t0n = __shfl_down_sync(FULL, T0[b], 1), q0n = __shfl_down_sync(FULL, Q0[b], 1);
-                if (NB[b]) { T2[b] = t0n; Q2[b] = q0n; }
+                // word j of the loaded pairs: .x/.y of pair j / 2 when j is even, .z/.w when it is odd
+                auto word = [](const uint4 *pp, int j) -> uint64_t {
+                    const uint4 v = pp[j >> 1];
+                    return (j & 1) ? ((uint64_t)v.w << 32) | v.z : ((uint64_t)v.y << 32) | v.x;
+                };
+#pragma unroll
+                for (int k = 0; k <= WW; k++) {
+                    TW[b][k] = t_odd[b] ? word(TP[b], k + 1) : word(TP[b], k);
+                    QW[b][k] = q_odd[b] ? word(QP[b], k + 1) : word(QP[b], k);
+                }
             }
 #endif
-            const uint32_t tl0 = __funnelshift_r((uint32_t)T0[b], (uint32_t)T1[b], sht);
-            const uint32_t tl1 = __funnelshift_r((uint32_t)T1[b], (uint32_t)T2[b], sht);
-            const uint32_t th0 = __funnelshift_r((uint32_t)(T0[b] >> 32), (uint32_t)(T1[b] >> 32), sht);
-            const uint32_t th1 = __funnelshift_r((uint32_t)(T1[b] >> 32), (uint32_t)(T2[b] >> 32), sht);
-            const uint32_t ql0 = __funnelshift_r((uint32_t)Q0[b], (uint32_t)Q1[b], shq);
-            const uint32_t ql1 = __funnelshift_r((uint32_t)Q1[b], (uint32_t)Q2[b], shq);
-            const uint32_t qh0 = __funnelshift_r((uint32_t)(Q0[b] >> 32), (uint32_t)(Q1[b] >> 32), shq);
-            const uint32_t qh1 = __funnelshift_r((uint32_t)(Q1[b] >> 32), (uint32_t)(Q2[b] >> 32), shq);
-            uint32_t m0 = (tl0 ^ ql0) | (th0 ^ qh0);
-            uint32_t m1 = (tl1 ^ ql1) | (th1 ^ qh1);
+#pragma unroll
+            for (int k = 0; k < WW; k++) {
+                const uint32_t tl = __funnelshift_r((uint32_t)TW[b][k], (uint32_t)TW[b][k + 1], sht);
+                const uint32_t th = __funnelshift_r((uint32_t)(TW[b][k] >> 32), (uint32_t)(TW[b][k + 1] >> 32), sht);
+                const uint32_t ql = __funnelshift_r((uint32_t)QW[b][k], (uint32_t)QW[b][k + 1], shq);
+                const uint32_t qh = __funnelshift_r((uint32_t)(QW[b][k] >> 32), (uint32_t)(QW[b][k + 1] >> 32), shq);
+                m[k] = (tl ^ ql) | (th ^ qh);
+            }
             if (EXC && isM && (misc & EF_EXC)) {
-                const uint64_t tp = ((uint64_t)(uint32_t)(en.tw + 2 * (int32_t)srel) << 5) + sht;
-                const uint64_t qlo = ((uint64_t)(uint32_t)(en.qw + 2 * (int32_t)srel) << 5) + shq;
+                const uint64_t tp = ((uint64_t)(uint32_t)(en.tw + WW * (int32_t)srel) << 5) + sht;
+                const uint64_t qlo = ((uint64_t)(uint32_t)(en.qw + WW * (int32_t)srel) << 5) + shq;
                 if (span_has_exception(P.G, tp, tp + n - 1) || span_has_exception(P.G, qlo, qlo + n - 1)) {
-                    m0 = m1 = 0;
-                    for (uint32_t k = 0; k < n; k++) {
-                        const unsigned mm = slow_mismatch(P.G, tp + k, qlo + k);
-                        if (k < 32) m0 |= mm << k; else m1 |= mm << (k - 32);
+#pragma unroll
+                    for (int k = 0; k < WW; k++) {
+                        uint32_t mk = 0;
+                        for (uint32_t j = 32u * k; j < n && j < 32u * k + 32u; j++) mk |= slow_mismatch(P.G, tp + j, qlo + j) << (j & 31u);
+                        m[k] = mk;
                     }
                 }
             }
             // bases beyond the op's end do not exist: shifting them out leaves the op's last base on top, the tally
             // counts what is left, and the arithmetic shift back copies that last base over the tail, so that no run
-            // appears to start behind the end (the next window starts another op)
-            const unsigned sh = isM ? WIN_BASES - n : 0u;
-            const uint64_t up = (isM ? ((uint64_t)m1 << 32) | m0 : 0ull) << sh;
-            const uint32_t mm_count = __popcll(up);
-            const uint64_t mx = (uint64_t)((int64_t)up >> sh);
-            m0 = (uint32_t)mx;
-            m1 = (uint32_t)(mx >> 32);
-            S.mask[1 + srel + (srel >> 4)] = ((uint64_t)m1 << 32) | m0;
+            // appears to start behind the end (the next window starts another op). 64 bases at a time; a half that lies
+            // wholly behind the end repeats the top bit of the half before it.
+            uint32_t mm_count = 0;
+            uint64_t below = 0;
+            const uint32_t wdx = 2u + WW * srel + 2u * ((WW * srel) >> 5);
+#pragma unroll
+            for (int h = 0; h < WW / 2; h++) {
+                const uint64_t raw = isM ? ((uint64_t)m[2 * h + 1] << 32) | m[2 * h] : 0ull;
+                const bool some = n > 64u * h;  // this half holds bases of the op (always true for the first half of an M window)
+                const uint32_t nh = n - 64u * h;
+                const unsigned sh = (isM && some && nh < 64u) ? 64u - nh : 0u;
+                const uint64_t src = (h == 0 || some) ? raw : (uint64_t)((int64_t)below >> 63);
+                const uint64_t up = src << sh;
+                mm_count += (h == 0 || some) ? (uint32_t)__popcll(up) : 0u;
+                const uint64_t mx = (uint64_t)((int64_t)up >> sh);
+                below = mx;
+                *reinterpret_cast<uint64_t *>(&S.mask[wdx + 2 * h]) = mx;
+            }
             // per-record mismatch tally. Records do not decrease along the window axis, so the warp tallies one
             // record at a time and moves on together: one reduction and one atomic per record and tile.
             {
@@ -367,16 +409,16 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
     return pm0;
 }
 
-// ---- C / E: blocked view. Lane owns tile windows 8 * lane .. 8 * lane + 7 = 16 half-window words of 32 bases.
+// ---- C / E: blocked view. Lane owns tile words 16 * lane .. 16 * lane + 15 (32 bases each) = TILE_ITERS windows.
 // An "event" is an output op: the start of an =/X run, or a pass-through op (its window holds no mismatch bits and
-// starts an op, so it shows up as one forced start bit). Coordinates are tile-relative (64 * window + base).
+// starts an op, so it shows up as one forced start bit). Coordinates are tile-relative (32 * word + base).
 // List entry of an event (32 bits) = its output word squeezed: bits 24-31 the op code, bits 0-23 the length. A run's
 // length is the distance to the next event, known to the lane that walks its events last to first (the last event of
 // a lane closes at the first event of the next lane that has any, or where the tile's last op ends); the op pass
 // shortens the run before an op start by the bases between the previous op's end and the window boundary, and writes
 // pass-through ops in (one whose length does not fit is stored whole after the copy-out, escape_pass).
 constexpr uint32_t LE_LEN = 0xffffffu;
-constexpr uint32_t COORD_END = 64u * 256u;  // stand-in closing coordinate of a run left open at the tile's end
+constexpr uint32_t COORD_END = 32u * TILE_WORDS;  // stand-in closing coordinate of a run left open at the tile's end
 
 // run-start bits of one 32-base word: m = its mismatch bits, prev = the word before it (top bit used), forced = an op
 // starts at bit 0
@@ -389,19 +431,24 @@ __device__ __forceinline__ uint32_t window_op(const WarpSmem &S, uint32_t w, uns
     return S.bmpre[w >> 5] + __popc(S.bm[w >> 5] & (0xffffffffu >> (31 - (w & 31)))) - adj;
 }
 
-// bit j of byte -> bit 2j: the lane's op-start windows as a bitmap over its 16 half-window words
-__device__ __forceinline__ uint32_t spread_bits(uint32_t byte) {
-    uint32_t x = byte;
-    x = (x | (x << 4)) & 0x0f0fu;
-    x = (x | (x << 2)) & 0x3333u;
-    x = (x | (x << 1)) & 0x5555u;
+// the lane's op-start windows (bit j = its window j) as a bitmap over its 16 words: bit j -> bit WIN_WORDS * j
+__device__ __forceinline__ uint32_t spread_bits(uint32_t starts) {
+    uint32_t x = starts;
+    if (WIN_WORDS == 2) {
+        x = (x | (x << 4)) & 0x0f0fu;
+        x = (x | (x << 2)) & 0x3333u;
+        x = (x | (x << 1)) & 0x5555u;
+    } else {
+        x = (x | (x << 6)) & 0x0303u;
+        x = (x | (x << 3)) & 0x1111u;
+    }
     return x;
 }
 
 // C: events of the lane, the bitmap of its words that hold any, and the lane-relative event prefix of its windows
-__device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t n_win, uint32_t byte, uint32_t pm, uint32_t &cnt,
+__device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t n_win, uint32_t starts, uint32_t pm, uint32_t &cnt,
                                            uint32_t &nz) {
-    uint32_t *M = reinterpret_cast<uint32_t *>(S.mask) + 2 + 16 * lane + 2 * (lane >> 1);
+    uint32_t *M = S.mask + 2 + 16 * lane + 2 * (lane >> 1);
     if (!(lane & 1)) M[-1] = pm;  // pad word: the listing reads "the word before" without a special case
     cnt = 0;
     nz = 0;
@@ -409,20 +456,25 @@ __device__ __forceinline__ void lane_count(WarpSmem &S, unsigned lane, uint32_t 
     uint32_t pk[TILE_ITERS / 2];
 #pragma unroll
     for (int j = 0; j < TILE_ITERS; j++) {
-        const uint2 m = *reinterpret_cast<const uint2 *>(M + 2 * j);
         if (j & 1) pk[j >> 1] |= cnt << 16; else pk[j >> 1] = cnt;
-        if ((uint32_t)j < n_win) {
-            const uint32_t d0 = start_bits(m.x, prev, (byte >> j) & 1u), d1 = start_bits(m.y, m.x, 0u);
-            cnt += __popc(d0) + __popc(d1);
-            nz |= (d0 ? 1u : 0u) << (2 * j) | (d1 ? 2u : 0u) << (2 * j);
+        const bool live = (uint32_t)j < n_win;
+#pragma unroll
+        for (int h = 0; h < WIN_WORDS / 2; h++) {
+            const uint2 m = *reinterpret_cast<const uint2 *>(M + WIN_WORDS * j + 2 * h);
+            if (live) {
+                const uint32_t d0 = start_bits(m.x, prev, h == 0 ? (starts >> j) & 1u : 0u), d1 = start_bits(m.y, m.x, 0u);
+                cnt += __popc(d0) + __popc(d1);
+                nz |= ((d0 ? 1u : 0u) | (d1 ? 2u : 0u)) << (WIN_WORDS * j + 2 * h);
+            }
+            prev = m.y;
         }
-        prev = m.y;
     }
-    static_assert(TILE_ITERS == 8, "the prefixes of a lane's windows go out as one 16-byte store");
-    *reinterpret_cast<uint4 *>(&S.prel[8 * lane]) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    static_assert(TILE_ITERS == 8 || TILE_ITERS == 4, "the prefixes of a lane's windows go out as one store");
+    if (TILE_ITERS == 8) *reinterpret_cast<uint4 *>(&S.prel[TILE_ITERS * lane]) = make_uint4(pk[0], pk[1], pk[TILE_ITERS / 2 - 2], pk[TILE_ITERS / 2 - 1]);
+    else *reinterpret_cast<uint2 *>(&S.prel[TILE_ITERS * lane]) = make_uint2(pk[0], pk[1]);
     uint16_t *nf16 = reinterpret_cast<uint16_t *>(S.nf);
     nf16[4 * (lane >> 1) + (lane & 1)] = (uint16_t)nz;
-    nf16[4 * (lane >> 1) + 2 + (lane & 1)] = (uint16_t)spread_bits(byte);
+    nf16[4 * (lane >> 1) + 2 + (lane & 1)] = (uint16_t)spread_bits(starts);
 }
 
 static_assert(OP_X == OP_EQ + 1, "the X flag of an event is added to OP_EQ");
@@ -445,7 +497,7 @@ __device__ __forceinline__ uint32_t top_bit(uint32_t x) {
 // (first event of the next round, walked only for its coordinate) lands in the sink. Returns the coordinate of the
 // lane's first event.
 __device__ __forceinline__ uint32_t list_round(WarpSmem &S, unsigned lane, uint32_t base, uint32_t n_walk, uint32_t closing) {
-    const uint32_t *M = reinterpret_cast<const uint32_t *>(S.mask);
+    const uint32_t *M = S.mask;
     const uint32_t q = (n_walk + 31u) >> 5;
     const uint32_t lo_r = lane * q, hi_r = min(lo_r + q, n_walk);
     uint32_t next_c = 0;
@@ -456,32 +508,37 @@ __device__ __forceinline__ uint32_t list_round(WarpSmem &S, unsigned lane, uint3
         for (uint32_t step = 16; step; step >>= 1)
             if ((uint32_t)S.lanex[t + step] <= R) t += step;
         const uint32_t Rl = R - S.lanex[t];
-        uint32_t W = 8u * t;
+        uint32_t W = (uint32_t)TILE_ITERS * t;
 #pragma unroll
-        for (uint32_t step = 4; step; step >>= 1)
+        for (uint32_t step = TILE_ITERS / 2; step; step >>= 1)
             if ((uint32_t)S.prel[W + step] <= Rl) W += step;
-        // run starts of window W; those ranked above R belong to the next lane
-        uint32_t wi = 2u * W;
-        const uint32_t g0 = wi >> 5;
-        const uint2 nf = S.nf[g0];
-        const uint32_t ix = 2u + wi + 2u * (wi >> 5);
-        const uint32_t m0 = M[ix], m1 = M[ix + 1];
-        uint32_t d0 = start_bits(m0, M[ix - 1], (nf.y >> (wi & 31u)) & 1u), d1 = start_bits(m1, m0, 0u);
-        uint32_t skip = min((uint32_t)S.prel[W] + __popc(d0) + __popc(d1) - 1u - Rl, 64u);
-        if (skip) {
-            unsigned long long dd = ((unsigned long long)d1 << 32) | d0;
-            do dd &= ~(0x8000000000000000ull >> __clzll((long long)dd)); while (--skip);
-            d0 = (uint32_t)dd; d1 = (uint32_t)(dd >> 32);
+        // run starts of window W, word by word: the word that holds the event of lane rank Rl; its events ranked above
+        // belong to the next lane
+        uint32_t wi = (uint32_t)WIN_WORDS * W;
+        const uint32_t ix0 = 2u + wi + 2u * (wi >> 5);
+        uint32_t d = 0, m = 0, skip = 0;
+        {
+            const uint32_t forced0 = (S.nf[wi >> 5].y >> (wi & 31u)) & 1u;
+            uint32_t cum = S.prel[W], prevw = M[ix0 - 1], sel = 0;
+#pragma unroll
+            for (int k = 0; k < WIN_WORDS; k++) {
+                const uint32_t mk = M[ix0 + k];
+                const uint32_t dk = start_bits(mk, prevw, k == 0 ? forced0 : 0u);
+                const uint32_t ck = __popc(dk);
+                if (cum <= Rl && Rl < cum + ck) { d = dk; m = mk; sel = (uint32_t)k; skip = cum + ck - 1u - Rl; }
+                cum += ck;
+                prevw = mk;
+            }
+            wi += sel;
         }
-        uint32_t d = d0, m = m0;
-        if (d1) { d = d1; m = m1; wi++; }
+        for (skip = min(skip, 31u); skip; skip--) d &= ~(0x80000000u >> __clz((int)d));
         // the 32 words below wi as a sliding bitmap (bit i <-> word wb + i; words below 0 do not exist): a share seldom
         // reaches further down, so the walk hardly ever reloads it
         int32_t wb = (int32_t)wi - 32;
         uint32_t avail, fy;
         auto load_bitmap = [&]() {
             const int32_t g = wb >> 5;
-            const uint2 lo = g >= 0 ? S.nf[g] : make_uint2(0u, 0u), hi = g >= -1 ? S.nf[(g + 1) & (TILE_WIN / 16 - 1)] : make_uint2(0u, 0u);
+            const uint2 lo = g >= 0 ? S.nf[g] : make_uint2(0u, 0u), hi = g >= -1 ? S.nf[(g + 1) & (TILE_WORDS / 32 - 1)] : make_uint2(0u, 0u);
             avail = __funnelshift_r(lo.x, hi.x, (uint32_t)wb & 31u);
             fy = __funnelshift_r(lo.y, hi.y, (uint32_t)wb & 31u);
         };
@@ -497,7 +554,7 @@ __device__ __forceinline__ uint32_t list_round(WarpSmem &S, unsigned lane, uint3
                 }
                 const uint32_t bit = top_bit(avail);
                 avail ^= 1u << bit;
-                wi = (uint32_t)(wb + (int32_t)bit) & (2u * TILE_WIN - 1u);  // (the mask only matters if the counts lied)
+                wi = (uint32_t)(wb + (int32_t)bit) & (uint32_t)(TILE_WORDS - 1);  // (the mask only matters if the counts lied)
                 const uint32_t jx = 2u + wi + 2u * (wi >> 5);
                 m = M[jx];
                 d = start_bits(m, M[jx - 1], (fy >> bit) & 1u);
@@ -532,9 +589,9 @@ __device__ __forceinline__ bool op_pass(const EncodeParams &P, WarpSmem &S, cons
         const OpEntry en = T.get(e);
         const uint32_t misc = en.misc;
         const uint32_t w = (misc >> ES_WIN) & 0xffu;
-        const uint32_t r = (uint32_t)S.lanex[w >> 3] + S.prel[w];
+        const uint32_t r = (uint32_t)S.lanex[w / (uint32_t)TILE_ITERS] + S.prel[w];
         const uint32_t k = r - base;
-        const uint32_t gap = (misc >> ES_GAP) & 63u;
+        const uint32_t gap = (misc >> ES_GAP) & (uint32_t)(WIN_BASES - 1);
         if (k == 0) {
             // the run before this op lives in an earlier round (already stored) or an earlier tile (stitch_kernel)
             if (base == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + WIN_BASES * w - gap;
@@ -562,7 +619,7 @@ __device__ __noinline__ void escape_pass(const EncodeParams &P, const WarpSmem &
     for (uint32_t e = lane + (adj ? 0u : 1u); e < n_tab; e += 32) {
         const OpEntry en = T.get(e);
         const uint32_t w = (en.misc >> ES_WIN) & 0xffu;
-        const uint32_t r = (uint32_t)S.lanex[w >> 3] + S.prel[w];
+        const uint32_t r = (uint32_t)S.lanex[w / (uint32_t)TILE_ITERS] + S.prel[w];
         const uint32_t len = (uint32_t)en.tw, top = (uint32_t)en.qw;
         if ((en.misc & EF_PASS) && r - base < (uint32_t)LIST_CAP && (len > LE_LEN || (top & LE_LEN)) && slot0 + r < (unsigned long long)P.out_cap)
             P.out[slot0 + r] = ((uint64_t)top << 32) | len;
@@ -587,43 +644,46 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
     extern __shared__ __align__(16) unsigned char enc_dyn_smem[];
     __shared__ WarpSmem SM_static[WARPS <= 4 ? WARPS : 1];
     WarpSmem *SM = WARPS <= 4 ? SM_static : reinterpret_cast<WarpSmem *>(enc_dyn_smem);
-    __shared__ uint32_t s_wcount[WARPS];
+    __shared__ uint32_t s_wcounts[2][WARPS];  // by iteration parity: a fast warp's next count must not overwrite what a slow one still reads
     __shared__ unsigned long long s_excl;
     __shared__ int64_t s_ticket;
+    __shared__ uint32_t s_claim;  // finished listings, all iterations: the first warp of an iteration to finish does the look-back
     const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     WarpSmem &S = SM[wid];
     const TileTab T{S, P.tab_overflow + ((size_t)blockIdx.x * WARPS + wid) * TILE_TAB};
 
     // the ticket of the next CTA tile is taken while the current one is finished (its latency hides behind the
     // conversion pass and the barrier that publishes the look-back result also publishes it)
-    if (threadIdx.x == 0) s_ticket = (int64_t)atomicAdd(P.ticket, 1u);
+    if (threadIdx.x == 0) { s_ticket = (int64_t)atomicAdd(P.ticket, 1u); s_claim = 0; }
     __syncthreads();
     int64_t ct = s_ticket;
+    uint32_t iter = 0;
     // first op of this warp's tile; for every later tile it is fetched (and the tile's op arrays pulled into L2) while
     // the previous tile is converted, so a tile does not start with a chain of DRAM round trips
     uint32_t first_op = ct * WARPS + wid < P.n_tiles ? __ldg(P.tile_first_op + ct * WARPS + wid) : 0u;
     while (ct < P.n_cta_tiles) {
+        uint32_t *s_wcount = s_wcounts[iter & 1u];
         const int64_t tile = ct * WARPS + wid;
         const uint64_t s0 = (uint64_t)tile * TILE_WIN;
         const uint32_t n_act = s0 < P.n_win ? (uint32_t)min((uint64_t)TILE_WIN, P.n_win - s0) : 0u;
 
         unsigned adj = 0;
-        uint32_t cnt = 0, nz = 0, inc = 0, byte = 0, pm = 0, term = COORD_OPEN, n_tab = 0, rec_first = 0;
+        uint32_t cnt = 0, nz = 0, inc = 0, starts = 0, pm = 0, term = COORD_OPEN, n_tab = 0, rec_first = 0;
         if (n_act) {
             bool any_exc;
             if (!(ENC_DIAG & 16)) build_table(P, S, T, (int64_t)first_op, s0, s0 + n_act, lane, adj, n_tab, rec_first, any_exc);
             else { any_exc = false; if (lane < TILE_ITERS) S.bm[lane] = S.bmpre[lane] = 0; }
             uint32_t pm0 = 0;
-            if (ENC_DIAG & 24) { for (int q = lane; q < MASK_PAD + 1; q += 32) S.mask[q] = 0x0000100000000100ull * (q & 3); }
+            if (ENC_DIAG & 24) { for (int q = lane; q < MASK_WORDS; q += 32) S.mask[q] = 0x100u * (q & 3); }
             else pm0 = (any_exc || n_tab > (uint32_t)TAB_SMEM) ? compare_tile<BATCH, true>(P, S, T, n_act, lane, adj, rec_first)
                                          : compare_tile<BATCH, false>(P, S, T, n_act, lane, adj, rec_first);
             __syncwarp();
             // blocked view of the tile
-            byte = (S.bm[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
-            const uint32_t n_win = 8u * lane >= n_act ? 0u : min(8u, n_act - 8u * lane);
-            // last half-window of the lane before (odd lanes: directly before the lane's words; even lanes: before the pad)
-            pm = lane ? reinterpret_cast<const uint32_t *>(S.mask)[2 + 16 * lane + 2 * (lane >> 1) - ((lane & 1) ? 1 : 3)] : pm0;
-            lane_count(S, lane, n_win, byte, pm, cnt, nz);
+            starts = (S.bm[((uint32_t)TILE_ITERS * lane) >> 5] >> (((uint32_t)TILE_ITERS * lane) & 31u)) & ((1u << TILE_ITERS) - 1u);
+            const uint32_t n_win = (uint32_t)TILE_ITERS * lane >= n_act ? 0u : min((uint32_t)TILE_ITERS, n_act - (uint32_t)TILE_ITERS * lane);
+            // last word of the lane before (odd lanes: directly before the lane's words; even lanes: before the pad)
+            pm = lane ? S.mask[2 + 16 * lane + 2 * (lane >> 1) - ((lane & 1) ? 1 : 3)] : pm0;
+            lane_count(S, lane, n_win, starts, pm, cnt, nz);
             inc = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -639,14 +699,14 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         if (lane == 0) s_wcount[wid] = tile_count;
         __syncthreads();
 
-        // ---- D (first half): publish the CTA tile's number of events, then list round 0 before anybody waits
+        // ---- D (first half): publish the CTA tile's number of events, then list round 0 before anybody waits.
+        // (atomicMax: the inclusive word written later by another warp must win whatever order the two stores land in;
+        // its flag bits make it the larger value)
         volatile unsigned long long *st = P.status;
         unsigned long long agg = 0;
-        if (wid == 0) {
 #pragma unroll
-            for (int w = 0; w < WARPS; w++) agg += s_wcount[w];
-            if (lane == 0) st[ct] = (ct == 0 ? ST_INCL : ST_AGG) | agg;
-        }
+        for (int w = 0; w < WARPS; w++) agg += s_wcount[w];
+        if (wid == 0 && lane == 0) atomicMax(P.status + ct, (ct == 0 ? ST_INCL : ST_AGG) | agg);
         // round 0 of the event list, before anybody waits for the look-back
         const uint32_t closing = term == COORD_OPEN ? COORD_END : term;
         if (!(ENC_DIAG & 2) && tile_count) {
@@ -655,8 +715,12 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
             // event is an op start)
             if (lane == 0) P.tile_first_closer[tile] = WIN_BASES * s0 + first_c;
         }
-        // ---- D (second half): decoupled look-back over CTA tiles (warp 0)
-        if (wid == 0) {
+        // ---- D (second half): decoupled look-back over CTA tiles, by the first warp of the CTA that has finished its
+        // listing (it would only wait for the others at the barrier below)
+        uint32_t claim = 0;
+        if (lane == 0) claim = atomicAdd(&s_claim, 1u);
+        claim = __shfl_sync(FULL, claim, 0);
+        if (claim == iter * (uint32_t)WARPS) {
             unsigned long long excl = 0;
             if (ct > 0 && !(ENC_DIAG & 32)) {
                 int64_t j = ct - 1 - (int64_t)lane;
@@ -683,7 +747,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                     if (incl) break;
                     j -= 32;
                 }
-                if (lane == 0) st[ct] = ST_INCL | (excl + agg);
+                if (lane == 0) atomicMax(P.status + ct, ST_INCL | (excl + agg));
             }
             if (lane == 0) {
                 s_excl = excl;
@@ -747,6 +811,7 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         }
         first_op = next_first_op;
         ct = next_ct;
+        iter++;
     }
 }
 

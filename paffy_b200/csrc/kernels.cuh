@@ -19,6 +19,10 @@ constexpr unsigned FULL = 0xffffffffu;
 constexpr uint32_t INF32 = 0xffffffffu;
 constexpr uint64_t INF64 = ~0ull;
 constexpr int ARENA_ALIGN = 1024;  // bases; contig offsets and pads are multiples of this
+#ifndef ENC_WIN_WORDS
+#define ENC_WIN_WORDS 4
+#endif
+constexpr int WINDOW_BASES = 32 * ENC_WIN_WORDS;  // bases per work window of the encode kernel (encode.cuh)
 
 // ------------------------------------------------------------------------------------------------
 // Genome arena: 2 bits/base (A0 C1 G2 T3), bit-sliced per 32 bases: one 64-bit word holds the low
@@ -254,7 +258,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_APPLY_MINB) scan_apply_kern
 // CIGAR ingest (a4 -> SoA): one warp per record walks its ops in strides of 32, turning the
 // reference's running cursors (qi, tj of impl/paf.c:746-775) into warp prefix sums. Per op it
 // writes the absolute arena position of its first target and query base, the owning record and the
-// number of 64-base work windows (1 for a pass-through op).
+// number of work windows of WINDOW_BASES bases (1 for a pass-through op).
 // ------------------------------------------------------------------------------------------------
 struct IngestParams {
     int64_t n_records, n_ops;
@@ -271,6 +275,10 @@ struct IngestParams {
     unsigned long long *bad_record;  // min index of a record that fails validation (init ~0)
     unsigned long long *aligned;     // sum of M lengths
     int has_exceptions;              // 0: the genome holds only ACGT, no op can touch the exception plane
+    // text mode (batches parsed on the device, paftext.cuh): a record without ops is legal and is left alone; a record with
+    // a cigar must also pass paf_check's op sums (impl/paf.c:440-459): sum of non-D lengths = query span, non-I = target span
+    const int64_t *t_end;            // null outside text mode
+    const uint8_t *has_cg;
 };
 
 // G lanes per record (8, 16 or 32, chosen by the host from the mean ops per record) so that short CIGARs do not leave
@@ -291,7 +299,9 @@ __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
         rev = P.same_strand[r] == 0;
         qs = P.q_start[r]; qe = P.q_end[r]; ts = P.t_start[r];
     }
-    bool ok = live && qc >= 0 && qc < P.n_contigs && tc >= 0 && tc < P.n_contigs && j1 > j0 && qs >= 0 && ts >= 0 && qs <= qe;
+    const bool text_mode = P.t_end != nullptr;
+    const bool exempt = text_mode && live && j1 == j0 && !P.has_cg[r];  // no cigar: nothing is dereferenced or checked
+    bool ok = live && qc >= 0 && qc < P.n_contigs && tc >= 0 && tc < P.n_contigs && (j1 > j0 || text_mode) && qs >= 0 && ts >= 0 && qs <= qe;
     int64_t q_len = 0, t_len = 0, q_off = 0, t_off = 0;
     if (ok) {
         q_len = P.contig_len[qc]; t_len = P.contig_len[tc];
@@ -327,7 +337,7 @@ __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
                 const uint64_t qd = q_used + (q_inc - ql);
                 qp = q_base + qd;
                 if (code == OP_M) {
-                    nw = (uint32_t)((len + 63) >> 6);
+                    nw = (uint32_t)((len + (WINDOW_BASES - 1)) / WINDOW_BASES);
                     m_sum += len;
                     // bounds of this op decide whether its spans may be dereferenced at all
                     const bool inside = (ts + (int64_t)(t_used + t_inc) <= t_len) &&
@@ -349,8 +359,9 @@ __global__ void __launch_bounds__(256) ingest_kernel(IngestParams P) {
     // memory safety: the walk must stay inside both contigs (the reference has UB here, a1-edge vii)
     const unsigned group_mask = G == 32 ? FULL : ((1u << G) - 1u) << (lane & ~(unsigned)(G - 1));
     overflow = (__ballot_sync(FULL, overflow) & group_mask) != 0;
-    const bool inside = ok && !overflow && ts + (int64_t)t_used <= t_len && (rev ? qe - (int64_t)q_used >= 0 : qs + (int64_t)q_used <= q_len);
-    if (live && !inside && gl == 0) atomicMin(P.bad_record, (unsigned long long)r);
+    bool inside = ok && !overflow && ts + (int64_t)t_used <= t_len && (rev ? qe - (int64_t)q_used >= 0 : qs + (int64_t)q_used <= q_len);
+    if (text_mode && inside && ((int64_t)q_used != qe - qs || (int64_t)t_used != P.t_end[r] - ts)) inside = false;  // paf_check's sums
+    if (live && !inside && !exempt && gl == 0) atomicMin(P.bad_record, (unsigned long long)r);
     if (!inside) m_sum = 0;
 #pragma unroll
     for (int o = 16; o; o >>= 1) m_sum += __shfl_xor_sync(FULL, m_sum, o);

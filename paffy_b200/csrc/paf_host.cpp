@@ -11,6 +11,10 @@
 
 #include <algorithm>
 #include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <map>
+#include <mutex>
 #include <climits>
 #include <cstdio>
 #include <cstdlib>
@@ -27,36 +31,26 @@ namespace {
 using namespace paftext;
 
 
-// ---- reading: the whole input, split into lines the way the reference's line reader does (sonLibFile.c:42-71:
-// '\r' dropped everywhere, a last line without '\n' still counts, a trailing empty line ends the input) ----------
-bool slurp(FILE *fh, std::string &buf) {
-    char tmp[1 << 16];
-    size_t got;
-    while ((got = fread(tmp, 1, sizeof tmp, fh)) > 0) buf.append(tmp, got);
-    return !ferror(fh);
-}
-
 struct Parsed {
     std::vector<Rec> recs;
     std::vector<uint64_t> ops;
 };
 
-// parse lines [begin, end) of `text` (already free of '\r') on `threads` workers, keeping input order
-void parse_all(const std::string &text, int threads, Parsed &out) {
-    const size_t n = text.size();
+// parse the lines of text[0, n) (already free of '\r') on `threads` workers, keeping input order
+void parse_all(const char *text, size_t n, int threads, Parsed &out) {
     threads = std::max(1, std::min<int>(threads, (int)(n / (1 << 16)) + 1));
     std::vector<size_t> cut(threads + 1, n);
     cut[0] = 0;
     for (int t = 1; t < threads; t++) {
         size_t p = n / threads * t;
-        const void *nl = p < n ? memchr(text.data() + p, '\n', n - p) : nullptr;
-        cut[t] = nl ? (size_t)((const char *)nl - text.data()) + 1 : n;
+        const void *nl = p < n ? memchr(text + p, '\n', n - p) : nullptr;
+        cut[t] = nl ? (size_t)((const char *)nl - text) + 1 : n;
     }
     for (int t = 1; t <= threads; t++) cut[t] = std::max(cut[t], cut[t - 1]);
     std::vector<Parsed> part(threads);
     auto work = [&](int t) {
         Parsed &P = part[t];
-        const char *p = text.data() + cut[t], *e = text.data() + cut[t + 1];
+        const char *p = text + cut[t], *e = text + cut[t + 1];
         while (p < e) {
             const char *nl = (const char *)memchr(p, '\n', (size_t)(e - p));
             const char *le = nl ? nl : e;
@@ -102,7 +96,11 @@ void parallel_for(int64_t n, int threads, F f) {  // f(begin, end, thread)
 #include "internal.h"
 
 #include <chrono>
+#include <cerrno>
 #include <getopt.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 namespace {
 
@@ -141,7 +139,11 @@ struct Pinned {  // pinned host buffer that only grows
     template <class T> T *as() { return static_cast<T *>(p); }
 };
 
-bool write_all(FILE *fh, const char *p, size_t n) { return n == 0 || fwrite(p, 1, n, fh) == n; }
+bool write_all(std::string *sink, const char *p, size_t n) {
+    sink->append(p, n);
+    return true;
+}
+
 
 }  // namespace
 
@@ -155,7 +157,8 @@ struct Filter {
     pafgpu_file_report rep{};
     const pafgpu_filter *flt = nullptr;  // `| paffy filter` fused behind add_mismatches (impl/paf_filter.c:121-156)
     int threads = 1;
-    FILE *out = nullptr;
+    bool device_text = false;  // plain add_mismatches: the PAF text is parsed and rendered on the device
+    std::string *out = nullptr;  // output bytes of the chunk being processed, in input order (written by the ordered writer)
     Parsed in;
     std::string err;           // message of the record that ended the run
     // per-record
@@ -548,42 +551,141 @@ int pafgpu_add_mismatches_file(pafgpu_ctx *ctx, const char *in_path, const char 
     return pafgpu_add_mismatches_file_filtered(ctx, in_path, out_path, opts, nullptr, report);
 }
 
-int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, const char *out_path, const pafgpu_file_opts *opts,
-                                        const pafgpu_filter *filter, pafgpu_file_report *report) {
-    if (!ctx && !(opts && opts->mode == PAFGPU_MODE_REMOVE)) return PAFGPU_EINVAL;  // -a is host-only text work
-    if (filter && opts && opts->mode != PAFGPU_MODE_ADD) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "the fused filter follows add_mismatches (mode 0) only");
-    Filter F;
-    F.ctx = ctx;
-    F.flt = filter;
-    F.o = opts ? *opts : pafgpu_file_opts{PAFGPU_MODE_ADD, 0.05f, 1.0f, 0, 0};
-    if (F.o.mode < 0 || F.o.mode > 7) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "bad mode");
+}  // extern "C"
+
+// ================================================================================================
+// The streaming pipeline: the reference reads, encodes and writes one record at a time
+// (impl/paf_add_mismatches.c:106-140); here a reader thread cuts the input into chunks of whole lines, worker threads
+// (one per context: `streams` sibling contexts on each of `gpus` devices, the packed genome shared on a device and
+// cloned GPU to GPU between devices) run a chunk each through parse -> validate -> GPU batches -> text, and the calling
+// thread writes the finished chunks in input order. Memory is bounded by the chunks in flight, the first output
+// leaves before the input ends, and a record the reference would abort on ends the run with everything before it
+// written. One job is thereby sharded over the GPUs of the box by contiguous record ranges with no
+// collective: a range is a chunk, ranges are dealt to whichever GPU is free, outputs are concatenated in input order.
+namespace {
+
+struct ChunkIn {
+    int64_t seq = 0;
+    std::vector<char> text;  // whole lines, free of '\r'
+};
+
+// Pinned host buffers for finished output text, shared by all pipelines of the process and kept between calls (pinning
+// memory costs more than filling it): a worker leases one for the text of a chunk, the writer hands it back.
+struct PinnedPool {
+    std::mutex mu;
+    std::vector<Pinned *> idle;
+    Pinned *get(int64_t bytes) {
+        Pinned *p = nullptr;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            // the smallest idle buffer that is large enough, else the largest one (it grows)
+            size_t best = idle.size();
+            for (size_t i = 0; i < idle.size(); i++) {
+                if (best == idle.size()) { best = i; continue; }
+                const bool fits_i = idle[i]->cap >= bytes, fits_b = idle[best]->cap >= bytes;
+                if (fits_i != fits_b ? fits_i : (fits_i ? idle[i]->cap < idle[best]->cap : idle[i]->cap > idle[best]->cap)) best = i;
+            }
+            if (best < idle.size()) { p = idle[best]; idle.erase(idle.begin() + (ptrdiff_t)best); }
+        }
+        if (!p) p = new Pinned();
+        if (!p->ensure(bytes)) { delete p; return nullptr; }
+        return p;
+    }
+    void put(Pinned *p) {
+        if (!p) return;
+        std::lock_guard<std::mutex> lk(mu);
+        idle.push_back(p);
+    }
+};
+PinnedPool g_pinned;
+
+struct ChunkOut {
+    int rc = 0;                // 0, 1 (a record ended the run; everything before it is in `bytes`), < 0 library error
+    std::string err;
+    std::string bytes;         // host-assembled output ...
+    Pinned *lease = nullptr;   // ... or text that came off the device in one piece (written after `bytes`)
+    int64_t lease_bytes = 0;
+    int64_t n_records = 0;     // records of the chunk (parsed)
+    pafgpu_file_report rep{};  // the chunk's share: records written, aligned bases, batches, stats, stage seconds;
+                               // failed_record is chunk-relative
+    int code = 0;              // library error code behind rc < 0
+    bool ready = false;
+};
+
+// The message the reference would die with on the line [b, e) (parse error, unknown contig, paf_check), or the bounds
+// message when the record passes all of those (it then walks outside its contig, which is undefined behaviour there).
+std::string failing_line_message(pafgpu_ctx *ctx, const char *b, const char *e, int64_t index) {
+    Rec r;
+    std::vector<uint64_t> ops;
+    parse_line(b, e, r, ops);
+    if (r.bad) return "ERROR: " + parse_error(r);
+    const std::string qn(r.qname, r.qname_len), tn(r.tname, r.tname_len);
+    if (pafgpu_genome_find(ctx, qn.c_str()) < 0) return "No query sequence named: " + qn + " found";
+    if (pafgpu_genome_find(ctx, tn.c_str()) < 0) return "No target sequence named: " + tn + " found";
+    std::string why;
+    if (check_record(r, ops.data() + r.op_begin, r.op_end - r.op_begin, &why)) {
+        std::string line;
+        render_line(r, ops.data() + r.op_begin, r.op_end - r.op_begin, line);
+        return "ERROR: " + why + " " + line;
+    }
+    char buf[160];
+    snprintf(buf, sizeof buf, "ERROR: record %lld: CIGAR/coordinates walk outside the contig", (long long)index);
+    return buf;
+}
+
+// `paffy add_mismatches` for one chunk with the text handled on the device end to end (pafgpu_add_mismatches_text): the
+// host only moves bytes
+void process_chunk_device(Filter &F, const char *text, size_t n_text, ChunkOut &R) {
+    pafgpu_text_result tr;
+    double t0 = now_s();
+    const int rc = pafgpu_add_mismatches_text(F.ctx, text, (int64_t)n_text, &tr);
+    if (rc < 0) { R.rc = R.code = rc; R.err = pafgpu_last_error(F.ctx); return; }
+    R.n_records = tr.records_in;
+    R.rep = pafgpu_file_report{};
+    R.rep.failed_record = -1;
+    R.rep.records = tr.records;
+    R.rep.aligned_bases = tr.aligned_bases;
+    R.rep.batches = 1;
+    for (int k = 0; k < 7; k++) R.rep.stats[k] = tr.stats[k];
+    if (tr.text_bytes > 0) {
+        R.lease = g_pinned.get(tr.text_bytes);
+        if (!R.lease) { R.rc = R.code = PAFGPU_ENODEVICE; R.err = "pinned host allocation failed"; return; }
+        const int frc = pafgpu_fetch_text(F.ctx, R.lease->as<char>(), nullptr);
+        if (frc < 0) { R.rc = R.code = frc; R.err = pafgpu_last_error(F.ctx); return; }
+        R.lease_bytes = tr.text_bytes;
+    }
+    R.rep.s_gpu = now_s() - t0;
+    if (tr.first_bad >= 0) {
+        R.rc = 1;
+        R.rep.failed_record = tr.first_bad;
+        R.err = failing_line_message(F.ctx, text + tr.bad_line_begin, text + tr.bad_line_end, tr.first_bad);
+    }
+}
+
+// everything the per-record loop of the reference does, for the records of one chunk
+void process_chunk(Filter &F, const char *text, size_t n_text, ChunkOut &R) {
+    pafgpu_ctx *ctx = F.ctx;
+    if (F.device_text) { process_chunk_device(F, text, n_text, R); return; }
     const bool trim_only = F.o.mode == PAFGPU_MODE_TRIM;
     const bool view = F.o.mode >= PAFGPU_MODE_VIEW;  // low bits: PAFGPU_VIEW_PER_ALIGNMENT, PAFGPU_VIEW_AGGREGATE
     auto finish = [&](int64_t x, int64_t y) {
         return view ? F.finish_view(x, y) : F.o.mode == PAFGPU_MODE_ADD ? F.finish_add(x, y) : F.finish_trim(x, y);
     };
-    F.threads = F.o.threads > 0 ? F.o.threads : hw_threads();
     const int64_t batch_bases = F.o.batch_bases > 0 ? F.o.batch_bases : (int64_t)1 << 34;
     const int64_t batch_ops = (int64_t)1 << 30;
+    F.rep = pafgpu_file_report{};
     F.rep.failed_record = -1;
+    F.err.clear();
+    F.out = &R.bytes;
+    F.in.recs.clear();
+    F.in.ops.clear();
 
     double t0 = now_s();
-    FILE *fin = in_path ? fopen(in_path, "rb") : stdin;
-    if (!fin) return pafgpu_internal_fail(ctx, PAFGPU_EIO, (std::string("cannot open ") + in_path).c_str());
-    std::string text;
-    const bool read_ok = slurp(fin, text);
-    if (in_path) fclose(fin);
-    if (!read_ok) return pafgpu_internal_fail(ctx, PAFGPU_EIO, "read failed");
-    text.erase(std::remove(text.begin(), text.end(), '\r'), text.end());  // the line reader drops '\r' (sonLibFile.c:49-51)
-    F.rep.s_read = now_s() - t0;
-    t0 = now_s();
-    parse_all(text, F.threads, F.in);
+    parse_all(text, n_text, F.threads, F.in);
     F.rep.s_parse = now_s() - t0;
-    F.out = out_path ? fopen(out_path, "wb") : stdout;
-    if (!F.out) return pafgpu_internal_fail(ctx, PAFGPU_EIO, (std::string("cannot open ") + out_path).c_str());
-
-    std::vector<Rec> &R = F.in.recs;
-    const int64_t n = (int64_t)R.size();
+    std::vector<Rec> &Rv = F.in.recs;
+    const int64_t n = (int64_t)Rv.size();
+    R.n_records = n;
     int rc = 0;
     // ---- the record that ends the run, found in input order before anything is computed: parse failures, unknown
     // contigs (impl/paf_add_mismatches.c:116-127) and paf_check (impl/paf.c:427-461; encoding keeps every sum it tests)
@@ -591,44 +693,67 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
     int64_t stop = n;
     F.qc.assign((size_t)n, -1);
     F.tc.assign((size_t)n, -1);
-    for (int64_t i = 0; i < n; i++) {
-        Rec &r = R[(size_t)i];
-        std::string msg;
-        if (r.bad) {
-            msg = "ERROR: " + parse_error(r);
-        } else {
-            if (trim_only && r.op_end == r.op_begin) {
+    {
+        // the lookups and checks of all records in parallel; the first failing record (input order) decides
+        std::atomic<int64_t> first_bad{n};
+        std::vector<uint8_t> bad((size_t)n, 0);
+        parallel_for(n, F.threads, [&](int64_t i0, int64_t i1, int) {
+            std::string name;
+            for (int64_t i = i0; i < i1; i++) {
+                Rec &r = Rv[(size_t)i];
+                bool fails = r.bad != 0;
+                if (!fails) {
+                    if (trim_only && r.op_end == r.op_begin) {
+                        fails = true;
+                    } else if (F.o.mode != PAFGPU_MODE_REMOVE && !trim_only) {
+                        name.assign(r.qname, r.qname_len);
+                        const int64_t q = pafgpu_genome_find(ctx, name.c_str());
+                        name.assign(r.tname, r.tname_len);
+                        const int64_t t = q >= 0 ? pafgpu_genome_find(ctx, name.c_str()) : -1;
+                        F.qc[(size_t)i] = (int32_t)q;
+                        F.tc[(size_t)i] = (int32_t)t;
+                        fails = q < 0 || t < 0;
+                    }
+                    if (!fails) {
+                        if (F.o.mode == PAFGPU_MODE_REMOVE && r.has_cigar) r.op_end = merge_matches(F.in.ops.data(), r.op_begin, r.op_end);
+                        // (`view` prints without paf_check: impl/paf_view.c:152-181; `paffy trim` checks after the trim only,
+                        // impl/paf_trim.c:124: finish_trim)
+                        if (!view && !trim_only && check_record(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, nullptr)) fails = true;
+                    }
+                }
+                if (fails) {
+                    bad[(size_t)i] = 1;
+                    int64_t cur = first_bad.load();
+                    while (i < cur && !first_bad.compare_exchange_weak(cur, i)) {}
+                    break;  // later records of this share cannot be the first
+                }
+            }
+        });
+        if (first_bad.load() < n) {
+            const int64_t i = first_bad.load();
+            Rec &r = Rv[(size_t)i];
+            std::string msg;
+            if (r.bad) {
+                msg = "ERROR: " + parse_error(r);
+            } else if (trim_only && r.op_end == r.op_begin) {
                 // no cg tag: the identity trim's closing assert sees 0/0 (impl/paf.c:952), the fixed trim reads a NULL
                 // cigar (impl/paf.c:520): the reference dies on this record either way
                 msg = "ERROR: paffy trim needs a cigar on every record (the reference aborts here)";
-            } else if (F.o.mode != PAFGPU_MODE_REMOVE && !trim_only) {
-                const std::string qn(r.qname, r.qname_len), tn(r.tname, r.tname_len);
-                const int64_t q = pafgpu_genome_find(ctx, qn.c_str());
-                const int64_t t = q >= 0 ? pafgpu_genome_find(ctx, tn.c_str()) : -1;
-                if (q < 0) msg = "No query sequence named: " + qn + " found";
-                else if (t < 0) msg = "No target sequence named: " + tn + " found";
-                F.qc[(size_t)i] = (int32_t)q;
-                F.tc[(size_t)i] = (int32_t)t;
-            }
-            if (msg.empty()) {
-                if (F.o.mode == PAFGPU_MODE_REMOVE && r.has_cigar) r.op_end = merge_matches(F.in.ops.data(), r.op_begin, r.op_end);
+            } else if (F.o.mode != PAFGPU_MODE_REMOVE && !trim_only && (F.qc[(size_t)i] < 0 || F.tc[(size_t)i] < 0)) {
+                if (F.qc[(size_t)i] < 0) msg = "No query sequence named: " + std::string(r.qname, r.qname_len) + " found";
+                else msg = "No target sequence named: " + std::string(r.tname, r.tname_len) + " found";
+            } else {
                 std::string why;
-                // (`view` prints without paf_check: impl/paf_view.c:152-181)
-                // (`paffy trim` checks after the trim only, impl/paf_trim.c:124: finish_trim)
-                if (!view && !trim_only && check_record(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, &why)) {
-                    // (the reference prints the record as it stands after encoding; this message shows its input CIGAR)
-                    std::string line;
-                    render_line(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, line);
-                    msg = "ERROR: " + why + " " + line;
-                }
+                check_record(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, &why);
+                // (the reference prints the record as it stands after encoding; this message shows its input CIGAR)
+                std::string line;
+                render_line(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, line);
+                msg = "ERROR: " + why + " " + line;
             }
-        }
-        if (!msg.empty()) {
             stop = i;
             F.err = msg;
             F.rep.failed_record = i;
             rc = 1;
-            break;
         }
     }
     F.rep.s_host += now_s() - t0;
@@ -640,10 +765,10 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
         if (F.o.mode == PAFGPU_MODE_REMOVE) {
             b = std::min<int64_t>(stop, a + (1 << 20));
         } else {
-            while (b < stop && (b == a || (bases < batch_bases && nops + (R[(size_t)b].op_end - R[(size_t)b].op_begin) < batch_ops))) {
-                for (int64_t k = R[(size_t)b].op_begin; k < R[(size_t)b].op_end; k++)
+            while (b < stop && (b == a || (bases < batch_bases && nops + (Rv[(size_t)b].op_end - Rv[(size_t)b].op_begin) < batch_ops))) {
+                for (int64_t k = Rv[(size_t)b].op_begin; k < Rv[(size_t)b].op_end; k++)
                     if (op_code(F.in.ops[(size_t)k]) == OPM || (trim_only && op_code(F.in.ops[(size_t)k]) >= OPEQ)) bases += op_len(F.in.ops[(size_t)k]);
-                nops += R[(size_t)b].op_end - R[(size_t)b].op_begin;
+                nops += Rv[(size_t)b].op_end - Rv[(size_t)b].op_begin;
                 b++;
             }
         }
@@ -653,24 +778,22 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
             std::vector<std::string> part((size_t)F.threads);
             parallel_for(b - a, F.threads, [&](int64_t i0, int64_t i1, int t) {
                 for (int64_t i = a + i0; i < a + i1; i++)
-                    render_line(R[(size_t)i], F.in.ops.data() + R[(size_t)i].op_begin, R[(size_t)i].op_end - R[(size_t)i].op_begin, part[(size_t)t]);
+                    render_line(Rv[(size_t)i], F.in.ops.data() + Rv[(size_t)i].op_begin, Rv[(size_t)i].op_end - Rv[(size_t)i].op_begin, part[(size_t)t]);
             });
             F.rep.s_host += now_s() - t0;
-            for (auto &s : part)
-                if (!write_all(F.out, s.data(), s.size())) brc = pafgpu_internal_fail(ctx, PAFGPU_EIO, "write failed");
+            for (auto &sp : part) write_all(F.out, sp.data(), sp.size());
         } else {
             t0 = now_s();
             int64_t b2 = b;
             brc = F.run_batch(a, b2);
             F.rep.s_gpu += now_s() - t0;
             if (brc == 1) {  // a record walks outside its contig: the records before it are still written
+                F.rep.failed_record = b2;  // (earlier than any record the checks above found: those lie at or behind `stop`)
                 if (b2 > a) {
                     const int frc = finish(a, b2);
                     if (frc < 0) brc = frc;
-                    if (frc == 1) { b2 = F.rep.failed_record; }
                 }
-                if (brc == 1 && F.rep.failed_record < 0) F.rep.failed_record = b2;
-                F.rep.records += std::max<int64_t>(0, (F.rep.failed_record >= 0 ? F.rep.failed_record : b2) - a);
+                F.rep.records += std::max<int64_t>(0, F.rep.failed_record - a);
             } else if (brc == 0) {
                 brc = finish(a, b);
                 if (brc == 1) F.rep.records += F.rep.failed_record - a;
@@ -681,19 +804,287 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
         F.rep.batches++;
         a = b;
     }
-    if (view && rc == 0 && (F.o.mode & PAFGPU_VIEW_AGGREGATE)) {  // impl/paf_view.c:183-192
-        const int64_t *t = F.rep.stats;
-        fprintf(F.out, "Total-alignments:%lld\tAvg-Identity:%f\tAvg-Identity-with-gaps:%f\tAligned-bases:%lld\tAligned-bases-with-gaps:%lld\t"
-                       "Query-inserts:%lld\tQuery-deletes:%lld\n",
-                (long long)t[6], (float)t[0] / (t[0] + t[1]), (float)t[0] / (t[0] + t[1] + t[4] + t[5]), (long long)(t[0] + t[1]),
-                (long long)(t[0] + t[1] + t[4] + t[5]), (long long)t[2], (long long)t[3]);
+    R.rc = rc;
+    R.err = F.err;
+    R.rep = F.rep;
+    if (rc < 0) { R.code = rc; R.err = ctx ? pafgpu_last_error(ctx) : "library error"; }
+}
+
+// reads whole lines into chunks of about `chunk_bytes` (sonLibFile.c:42-71: '\r' dropped, a last line without '\n' counts).
+// read(2) returns what a pipe holds right now: a chunk ends at the last newline once it is full OR the pipe has run
+// dry, so a slow producer sees its first lines come out before it closes the stream.
+struct ChunkReader {
+    int fd;
+    size_t chunk_bytes;
+    std::vector<char> carry;  // the incomplete last line of the previous read (holds no newline)
+    bool eof = false;
+    int64_t seq = 0;
+    // false at end of input (or read error: *failed)
+    bool next(ChunkIn &c, bool *failed) {
+        c.text.clear();
+        if (eof && carry.empty()) return false;
+        c.text.swap(carry);
+        size_t last_nl = 0;  // one past the last newline seen
+        while (!eof) {
+            const size_t have = c.text.size();
+            const size_t want = chunk_bytes > have ? chunk_bytes - have : std::max<size_t>(chunk_bytes, 256);
+            c.text.resize(have + want);
+            ssize_t got;
+            do got = ::read(fd, c.text.data() + have, want); while (got < 0 && errno == EINTR);
+            if (got < 0) { *failed = true; return false; }
+            c.text.resize(have + (size_t)got);
+            if (got == 0) { eof = true; break; }
+            for (size_t k = c.text.size(); k > have; k--)
+                if (c.text[k - 1] == '\n') { last_nl = k; break; }
+            // full, or the source has nothing more for now: hand over the whole lines read so far
+            if (last_nl && (c.text.size() >= chunk_bytes || (size_t)got < want)) break;
+        }
+        if (!eof) {
+            carry.assign(c.text.begin() + (ptrdiff_t)last_nl, c.text.end());
+            c.text.resize(last_nl);
+        }
+        if (c.text.empty()) return false;
+        if (memchr(c.text.data(), '\r', c.text.size()))
+            c.text.erase(std::remove(c.text.begin(), c.text.end(), '\r'), c.text.end());  // the line reader drops '\r' (sonLibFile.c:49-51)
+        c.seq = seq++;
+        return true;
     }
-    if (out_path) fclose(F.out); else fflush(F.out);
-    if (rc == 1) {
-        fprintf(stderr, "%s\n", F.err.c_str());
-        pafgpu_internal_fail(ctx, 1, F.err.c_str());
+};
+
+std::vector<int> device_list(pafgpu_ctx *ctx, int gpus_opt) {
+    std::vector<int> devs;
+    if (!ctx) return devs;
+    const int first = pafgpu_device_of(ctx), avail = pafgpu_device_count();
+    devs.push_back(first);
+    const char *e = getenv("PAFFY_GPUS");
+    if (gpus_opt <= 0 && e && strchr(e, ',')) {  // an explicit list: the context's own device stays first
+        for (const char *p = e; *p;) {
+            const int d = atoi(p);
+            if (d >= 0 && d < avail && std::find(devs.begin(), devs.end(), d) == devs.end()) devs.push_back(d);
+            p = strchr(p, ',');
+            if (!p) break;
+            p++;
+        }
+        return devs;
     }
-    if (report) *report = F.rep;
+    int want = gpus_opt > 0 ? gpus_opt : (e ? (strcmp(e, "all") == 0 ? avail : atoi(e)) : 1);
+    want = std::max(1, std::min(want, avail));
+    for (int d = 0; (int)devs.size() < want && d < avail; d++)
+        if (d != first) devs.push_back(d);
+    return devs;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, const char *out_path, const pafgpu_file_opts *opts,
+                                        const pafgpu_filter *filter, pafgpu_file_report *report) {
+    if (!ctx && !(opts && opts->mode == PAFGPU_MODE_REMOVE)) return PAFGPU_EINVAL;  // -a is host-only text work
+    if (filter && opts && opts->mode != PAFGPU_MODE_ADD) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "the fused filter follows add_mismatches (mode 0) only");
+    const pafgpu_file_opts o = opts ? *opts : pafgpu_file_opts{PAFGPU_MODE_ADD, 0.05f, 1.0f, 0, 0, 0, 0, 0};
+    if (o.mode < 0 || o.mode > 7) return pafgpu_internal_fail(ctx, PAFGPU_EINVAL, "bad mode");
+    const bool view = o.mode >= PAFGPU_MODE_VIEW;
+    pafgpu_file_report rep{};
+    rep.failed_record = -1;
+    const double t_start = now_s();
+
+    // ---- contexts: `streams` per device; device 0 of the list is the caller's, the others hold a clone of its genome.
+    // The helpers belong to the caller's context and outlive this call (created once, reused by the next call).
+    std::vector<pafgpu_ctx *> ctxs;
+    const std::vector<int> devs = device_list(ctx, o.gpus);
+    int streams = o.streams > 0 ? o.streams : 2;
+    if (const char *e = getenv("PAFFY_STREAMS")) if (o.streams <= 0 && atoi(e) > 0) streams = atoi(e);
+    streams = std::min(streams, 8);
+    if (ctx) {
+        for (size_t d = 0; d < devs.size(); d++)
+            for (int k = 0; k < streams; k++) {
+                pafgpu_ctx *h = ctx;
+                if (d > 0 || k > 0)
+                    if (int rc = pafgpu_helper(ctx, devs[d], k, &h)) return rc;
+                ctxs.push_back(h);
+            }
+    } else {
+        ctxs.assign(2, nullptr);  // `add_mismatches -a`: two host workers
+    }
+    const int W = (int)ctxs.size();
+    rep.gpus = (int64_t)devs.size();
+    rep.workers = W;
+
+    FILE *fin = in_path ? fopen(in_path, "rb") : stdin;
+    if (!fin) { return pafgpu_internal_fail(ctx, PAFGPU_EIO, (std::string("cannot open ") + in_path).c_str()); }
+    if (!out_path) fflush(stdout);
+    const int out_fd = out_path ? open(out_path, O_WRONLY | O_CREAT | O_TRUNC, 0666) : fileno(stdout);
+    if (out_fd < 0) {
+        if (in_path) fclose(fin);
+        return pafgpu_internal_fail(ctx, PAFGPU_EIO, (std::string("cannot open ") + out_path).c_str());
+    }
+    struct stat out_st;
+    const bool out_regular = out_path && fstat(out_fd, &out_st) == 0 && S_ISREG(out_st.st_mode);
+    int64_t out_off = 0;  // regular files: bytes written so far (large pieces go out as parallel pwrites)
+    auto write_out = [&](const char *p, size_t n) -> bool {
+        if (n == 0) return true;
+        bool ok = true;
+        const size_t piece = (size_t)8 << 20;
+        if (out_regular && n >= 2 * piece) {
+            const int nt = (int)std::min<size_t>(6, n / piece);
+            std::vector<std::thread> th;
+            std::atomic<bool> good{true};
+            for (int t = 0; t < nt; t++)
+                th.emplace_back([&, t]() {
+                    size_t a0 = n * (size_t)t / (size_t)nt, a1 = n * (size_t)(t + 1) / (size_t)nt;
+                    while (a0 < a1) {
+                        const ssize_t w = pwrite(out_fd, p + a0, a1 - a0, (off_t)(out_off + (int64_t)a0));
+                        if (w < 0) { if (errno == EINTR) continue; good = false; return; }
+                        a0 += (size_t)w;
+                    }
+                });
+            for (auto &x : th) x.join();
+            ok = good.load();
+        } else {
+            size_t a0 = 0;
+            while (a0 < n) {
+                const ssize_t w = out_regular ? pwrite(out_fd, p + a0, n - a0, (off_t)(out_off + (int64_t)a0)) : ::write(out_fd, p + a0, n - a0);
+                if (w < 0) { if (errno == EINTR) continue; ok = false; break; }
+                a0 += (size_t)w;
+            }
+        }
+        out_off += (int64_t)n;
+        return ok;
+    };
+
+    // ---- queues
+    const bool device_text = ctx && o.mode == PAFGPU_MODE_ADD && !filter && !getenv("PAFFY_HOST_PARSE");
+    const size_t chunk_bytes = (size_t)std::min<int64_t>(o.chunk_bytes > 0 ? o.chunk_bytes : (int64_t)32 << 20, (int64_t)1 << 30);
+    std::mutex mu;
+    std::condition_variable cv_job, cv_done, cv_room;
+    std::deque<ChunkIn> jobs;
+    std::map<int64_t, ChunkOut> done;
+    bool reader_done = false, read_failed = false;
+    std::atomic<bool> stop{false};
+    int64_t in_flight = 0;  // chunks read and not yet written: bounds the memory
+    const int64_t max_in_flight = W + 2;
+    double s_read = 0;
+
+    std::thread reader([&]() {
+        ChunkReader rd{fileno(fin), chunk_bytes};
+        for (;;) {
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv_room.wait(lk, [&] { return in_flight < max_in_flight || stop.load(); });
+                if (stop.load()) break;
+            }
+            ChunkIn c;
+            const double t0 = now_s();
+            bool failed = false;
+            const bool more = rd.next(c, &failed);
+            s_read += now_s() - t0;
+            std::lock_guard<std::mutex> lk(mu);
+            if (failed) read_failed = true;
+            if (!more) break;
+            in_flight++;
+            jobs.push_back(std::move(c));
+            cv_job.notify_one();
+        }
+        std::lock_guard<std::mutex> lk(mu);
+        reader_done = true;
+        cv_job.notify_all();
+        cv_done.notify_all();
+    });
+
+    const int threads_total = o.threads > 0 ? o.threads : hw_threads();
+    std::vector<std::thread> workers;
+    for (int w = 0; w < W; w++)
+        workers.emplace_back([&, w]() {
+            Filter F;
+            F.ctx = ctxs[(size_t)w];
+            F.flt = filter;
+            F.o = o;
+            F.device_text = device_text;
+            F.threads = std::max(1, threads_total / W);
+            for (;;) {
+                ChunkIn c;
+                {
+                    std::unique_lock<std::mutex> lk(mu);
+                    cv_job.wait(lk, [&] { return !jobs.empty() || reader_done || stop.load(); });
+                    if (stop.load() || jobs.empty()) break;
+                    c = std::move(jobs.front());
+                    jobs.pop_front();
+                }
+                ChunkOut R;
+                process_chunk(F, c.text.data(), c.text.size(), R);
+                R.ready = true;
+                std::lock_guard<std::mutex> lk(mu);
+                done.emplace(c.seq, std::move(R));
+                cv_done.notify_all();
+            }
+        });
+
+    // ---- ordered writer (this thread)
+    int rc = 0;
+    std::string err;
+    int64_t next_seq = 0, records_before = 0;
+    bool wrote_ok = true;
+    for (;;) {
+        ChunkOut R;
+        {
+            std::unique_lock<std::mutex> lk(mu);
+            cv_done.wait(lk, [&] { return done.count(next_seq) || (reader_done && in_flight == 0); });
+            auto it = done.find(next_seq);
+            if (it == done.end()) break;  // input exhausted, everything written
+            R = std::move(it->second);
+            done.erase(it);
+        }
+        const double t0 = now_s();
+        wrote_ok = write_out(R.bytes.data(), R.bytes.size()) && write_out(R.lease ? R.lease->as<char>() : nullptr, (size_t)R.lease_bytes);
+        g_pinned.put(R.lease);
+        R.lease = nullptr;
+        rep.s_write += now_s() - t0;
+        rep.records += R.rep.records;
+        rep.aligned_bases += R.rep.aligned_bases;
+        rep.batches += R.rep.batches;
+        for (int k = 0; k < 7; k++) rep.stats[k] += R.rep.stats[k];
+        rep.s_parse += R.rep.s_parse; rep.s_gpu += R.rep.s_gpu; rep.s_host += R.rep.s_host; rep.s_write += R.rep.s_write;
+        rep.chunks++;
+        if (R.rc != 0 || !wrote_ok) {
+            rc = !wrote_ok ? PAFGPU_EIO : R.rc;
+            err = !wrote_ok ? "write failed" : R.err;
+            if (R.rc == 1) rep.failed_record = records_before + R.rep.failed_record;
+            break;
+        }
+        records_before += R.n_records;
+        next_seq++;
+        std::lock_guard<std::mutex> lk(mu);
+        in_flight--;
+        cv_room.notify_one();
+    }
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        stop.store(true);
+        cv_room.notify_all();
+        cv_job.notify_all();
+    }
+    reader.join();
+    for (auto &t : workers) t.join();
+    for (auto &kv : done) g_pinned.put(kv.second.lease);  // chunks finished behind the one that ended the run
+    if (rc == 0 && read_failed) { rc = PAFGPU_EIO; err = "read failed"; }
+    rep.s_read = s_read;
+
+    if (view && rc == 0 && (o.mode & PAFGPU_VIEW_AGGREGATE)) {  // impl/paf_view.c:183-192
+        const int64_t *t = rep.stats;
+        char line[512];
+        const int len = snprintf(line, sizeof line, "Total-alignments:%lld\tAvg-Identity:%f\tAvg-Identity-with-gaps:%f\tAligned-bases:%lld\tAligned-bases-with-gaps:%lld\t"
+                                 "Query-inserts:%lld\tQuery-deletes:%lld\n",
+                                 (long long)t[6], (float)t[0] / (t[0] + t[1]), (float)t[0] / (t[0] + t[1] + t[4] + t[5]), (long long)(t[0] + t[1]),
+                                 (long long)(t[0] + t[1] + t[4] + t[5]), (long long)t[2], (long long)t[3]);
+        if (!write_out(line, (size_t)len) && rc == 0) { rc = PAFGPU_EIO; err = "write failed"; }
+    }
+    if (in_path) fclose(fin);
+    if (out_path && close(out_fd) != 0 && rc == 0) { rc = PAFGPU_EIO; err = "write failed"; }
+    rep.s_total = now_s() - t_start;
+    if (rc == 1) fprintf(stderr, "%s\n", err.c_str());
+    if (rc != 0) pafgpu_internal_fail(ctx, rc, err.c_str());
+    if (report) *report = rep;
     return rc;
 }
 

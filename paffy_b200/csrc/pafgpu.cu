@@ -5,6 +5,7 @@
 #include "encode.cuh"
 #include "serialise.cuh"
 #include "trim.cuh"
+#include "paftext.cuh"
 #include "internal.h"
 
 #include <algorithm>
@@ -71,6 +72,10 @@ struct GenomeStore {
     std::unordered_map<std::string, int64_t> index;
     DevBuf d_off, d_off_rc, d_len;
     bool table_dirty = true;
+    DevBuf d_names, d_name_blob;  // name -> contig id hash table for the device PAF parser (paftext.cuh)
+    uint32_t name_mask = 0;
+    bool names_dirty = true;
+    uint64_t generation = 0;  // bumped by every change of the contig set
     int device = 0;
     std::mutex mu;  // sibling contexts share one store (pafgpu_create_sibling): the lazy table upload is serialised
 
@@ -79,9 +84,12 @@ struct GenomeStore {
         next_off = ARENA_ALIGN;
         exc_total = 0;
         names.clear(); off.clear(); off_rc.clear(); len.clear(); index.clear();
-        table_dirty = true;
+        table_dirty = names_dirty = true;
     }
-    void release() { words.release(); flags.release(); rank.release(); exc.release(); d_off.release(); d_off_rc.release(); d_len.release(); }
+    void release() {
+        words.release(); flags.release(); rank.release(); exc.release(); d_off.release(); d_off_rc.release(); d_len.release();
+        d_names.release(); d_name_blob.release();
+    }
     ~GenomeStore() {
         int cur = 0;
         cudaGetDevice(&cur);
@@ -99,12 +107,16 @@ struct pafgpu_ctx {
     int enc_ctas_per_sm = 4, enc_warps = 8;  // 8 warps per CTA: half the tickets and look-backs of 4, still 32 warps/SM
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[8] = {};
+    cudaEvent_t ev_tx[4] = {};  // text path: parse begin / end, render begin / end
     std::string err;
     uint64_t host_total = 0;
     cudaEvent_t ev_block = nullptr;  // PAFGPU_BLOCKING_SYNC=1: host threads sleep in stream_sync instead of spinning
     uint64_t *h_words = nullptr;  // pinned + mapped: kernels leave the few words the host has to read here, so that
                                   // those reads never queue behind bulk copies on a copy engine
     std::mutex mu;  // library callers may encode from several threads (SURVEY 8b threading row)
+    // helper contexts of the file pipeline (extra streams on this GPU, primaries on the other GPUs), kept for later calls
+    struct Helper { int device, k; pafgpu_ctx *ctx; const void *genome_of; uint64_t generation; };
+    std::vector<Helper> helpers;
 
     std::shared_ptr<GenomeStore> genome_ref = std::make_shared<GenomeStore>();  // shared by sibling contexts on the same device
     GenomeStore &G() const { return *genome_ref; }
@@ -119,6 +131,11 @@ struct pafgpu_ctx {
     DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
     // trim
     DevBuf trim_coords, trim_lo, trim_hi, trim_failed;
+    // device PAF text ingest (paftext.cuh): chunk text, delimiter positions, parsed columns, parsed ops
+    DevBuf tx_text, tx_tile_nl, tx_tile_tab, tx_nl_off, tx_tab_off, tx_nl_pos, tx_tab_pos, tx_line_tab0, tx_cols, tx_tile_ops, tx_op_off, tx_ops,
+        tx_scal;
+    const int64_t *ingest_t_end = nullptr;   // text mode: paf_check's op sums are tested by the ingest kernel, records without
+    const uint8_t *ingest_has_cg = nullptr;  // ops are legal
     // FASTA reader: raw sequence text of one record, kept bytes per tile and their scan, {first bad byte, kept total}
     DevBuf fa_raw, fa_tile_kept, fa_tile_off, fa_scal;
     bool trimmed = false;
@@ -137,8 +154,7 @@ struct pafgpu_ctx {
 
 namespace {
 
-constexpr int ITERS = 8;
-constexpr uint32_t TILE_WINDOWS = 32u * ITERS;
+constexpr uint32_t TILE_WINDOWS = (uint32_t)TILE_WIN;
 enum { SC_BAD = 0, SC_ALIGNED = 1, SC_TOTAL = 2, SC_TICKET = 3, SC_NWIN = 4, SC_TMP = 5, SC_COUNT = 8 };
 
 // wait for the context's stream; with ev_block the thread sleeps (many ranks x contexts on few host cores)
@@ -264,7 +280,8 @@ int64_t genome_add_device(pafgpu_ctx *c, GenomeStore &g, const char *name, const
     g.len.push_back(len);
     g.index[g.names.back()] = id;  // a repeated name points at the newest contig (sonLibHash.c:68-73)
     g.next_off = off + 2 * span;
-    g.table_dirty = true;
+    g.table_dirty = g.names_dirty = true;
+    g.generation++;
     return id;
 }
 
@@ -292,7 +309,7 @@ int genome_sync_table(pafgpu_ctx *c, GenomeStore &g) {
 }
 
 #ifndef ENC_BATCH
-#define ENC_BATCH 2
+#define ENC_BATCH (ENC_WIN_WORDS == 4 ? 1 : 2)  // windows whose loads a lane issues together: 10 / 12 64-bit loads in flight
 #endif
 constexpr int CMP_BATCH = ENC_BATCH;
 
@@ -377,6 +394,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
     I.contig_off = g.d_off.as<int64_t>(); I.contig_off_rc = g.d_off_rc.as<int64_t>(); I.contig_len = g.d_len.as<int64_t>(); I.n_contigs = (int64_t)g.off.size();
     I.G = g.view();
     I.has_exceptions = g.exc_total > 0;
+    I.t_end = c->ingest_t_end; I.has_cg = c->ingest_has_cg;
     I.tpos = c->tpos.as<uint64_t>(); I.qpos = c->qpos.as<uint64_t>();
     I.op_rec = c->op_rec.as<uint32_t>(); I.nwin = c->nwin.as<uint32_t>();
     I.bad_record = (unsigned long long *)(sc + SC_BAD);
@@ -530,6 +548,7 @@ int pafgpu_create(int device, pafgpu_ctx **out) {
         return fail(c, PAFGPU_ENODEVICE, "cudaStreamCreate failed");
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    for (auto &ev : ctx->ev_tx) cudaEventCreate(&ev);
     if (const char *e = getenv("PAFGPU_BLOCKING_SYNC"))
         if (atoi(e)) cudaEventCreateWithFlags(&ctx->ev_block, cudaEventBlockingSync | cudaEventDisableTiming);
     if (cudaHostAlloc((void **)&ctx->h_words, 64 * sizeof(uint64_t), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
@@ -572,6 +591,8 @@ int pafgpu_device_of(const pafgpu_ctx *c) { return c ? c->device : PAFGPU_EINVAL
 
 void pafgpu_destroy(pafgpu_ctx *c) {
     if (!c) return;
+    for (auto &h : c->helpers) pafgpu_destroy(h.ctx);
+    c->helpers.clear();
     cudaSetDevice(c->device);
     stream_sync(c);
     c->scratch.release();  // (the shared genome store goes with its last context)
@@ -579,9 +600,12 @@ void pafgpu_destroy(pafgpu_ctx *c) {
                       &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
                       &c->status, &c->tile_first_closer, &c->tile_open_slot, &c->tab_overflow, &c->out, &c->rec_out_begin, &c->rec_mism,
                       &c->scalars, &c->trim_coords, &c->trim_lo, &c->trim_hi, &c->trim_failed, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
-                      &c->ser_text};
+                      &c->ser_text, &c->tx_text, &c->tx_tile_nl, &c->tx_tile_tab, &c->tx_nl_off, &c->tx_tab_off, &c->tx_nl_pos, &c->tx_tab_pos,
+                      &c->tx_line_tab0, &c->tx_cols, &c->tx_tile_ops, &c->tx_op_off, &c->tx_ops, &c->tx_scal, &c->fa_raw, &c->fa_tile_kept,
+                      &c->fa_tile_off, &c->fa_scal};
     for (DevBuf *b : bufs) b->release();
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
+    for (auto &ev : c->ev_tx) if (ev) cudaEventDestroy(ev);
     if (c->ev_block) cudaEventDestroy(c->ev_block);
     if (c->h_words) cudaFreeHost(c->h_words);
     cudaStreamDestroy(c->stream);
@@ -594,7 +618,7 @@ int64_t pafgpu_last_bad_record(const pafgpu_ctx *c) { return c ? c->bad_record :
 
 void *pafgpu_host_alloc(int64_t bytes) {
     void *p = nullptr;
-    if (bytes <= 0 || cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (bytes <= 0 || cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     return p;
 }
 void pafgpu_host_free(void *p) { if (p) cudaFreeHost(p); }
@@ -772,6 +796,41 @@ int pafgpu_genome_clone(pafgpu_ctx *dst, pafgpu_ctx *src) {
     if (from->exc.p) CU(cudaMemcpyPeerAsync(g->exc.p, dst->device, from->exc.p, from->device, std::min(nb.exc, from->exc.cap), dst->stream));
     CU(stream_sync(dst));
     dst->genome_ref = g;
+    return 0;
+}
+
+// k-th helper context of `parent` on `device` (k >= 1 on the parent's own device, k >= 0 elsewhere), created on first use
+// and kept until the parent is destroyed; its genome is the parent's (shared on the same GPU, cloned GPU to GPU - again
+// only when the parent's contig set changed - on another).
+int pafgpu_helper(pafgpu_ctx *parent, int device, int k, pafgpu_ctx **out) {
+    if (!parent || !out) return PAFGPU_EINVAL;
+    *out = nullptr;
+    pafgpu_ctx::Helper *h = nullptr;
+    for (auto &x : parent->helpers)
+        if (x.device == device && x.k == k) h = &x;
+    if (!h) {
+        pafgpu_ctx *c = nullptr;
+        if (int rc = pafgpu_create(device, &c)) return rc;
+        parent->helpers.push_back(pafgpu_ctx::Helper{device, k, c, nullptr, 0});
+        h = &parent->helpers.back();
+    }
+    const GenomeStore *want = parent->genome_ref.get();
+    if (device == parent->device) {
+        h->ctx->genome_ref = parent->genome_ref;
+    } else if (h->genome_of != want || h->generation != want->generation) {
+        // another helper on that device may hold the clone already
+        pafgpu_ctx *holder = nullptr;
+        for (auto &x : parent->helpers)
+            if (x.device == device && x.ctx != h->ctx && x.genome_of == want && x.generation == want->generation) holder = x.ctx;
+        if (holder) h->ctx->genome_ref = holder->genome_ref;
+        else if (int rc = pafgpu_genome_clone(h->ctx, parent)) {
+            pafgpu_internal_fail(parent, rc, pafgpu_last_error(h->ctx));
+            return rc;
+        }
+    }
+    h->genome_of = want;
+    h->generation = want->generation;
+    *out = h->ctx;
     return 0;
 }
 
@@ -981,6 +1040,239 @@ int pafgpu_encode_one(pafgpu_ctx *c, const uint64_t *ops, int64_t n_ops, int sam
     if (mismatches) *mismatches = mm;
     return 0;
 }
+
+}  // extern "C"
+
+// ---- PAF text in, PAF text out, all of it on the device -------------------------------------------
+namespace {
+
+uint64_t host_name_hash(const std::string &s) {  // = name_hash (paftext.cuh)
+    uint64_t h = 1469598103934665603ull;
+    for (unsigned char ch : s) { h ^= ch; h *= 1099511628211ull; }
+    return h ? h : 1;
+}
+
+// name -> contig id table of the genome on the device (a repeated name points at the newest contig, as the host map does)
+int genome_sync_names(pafgpu_ctx *c, GenomeStore &g) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.names_dirty) return 0;
+    uint32_t cap = 16;
+    while (cap < 2 * g.index.size() + 2) cap *= 2;
+    std::vector<NameEntry> tab(cap, NameEntry{0, 0, 0, -1, 0});
+    std::string blob;
+    for (const auto &kv : g.index) {
+        const uint64_t h = host_name_hash(kv.first);
+        uint32_t slot = (uint32_t)h & (cap - 1);
+        while (tab[slot].hash) slot = (slot + 1) & (cap - 1);
+        tab[slot] = NameEntry{h, (uint32_t)blob.size(), (uint32_t)kv.first.size(), (int32_t)kv.second, 0};
+        blob += kv.first;
+    }
+    CU(g.d_names.ensure((size_t)cap * sizeof(NameEntry)));
+    CU(g.d_name_blob.ensure(std::max<size_t>(blob.size(), 16)));
+    CU(cudaMemcpyAsync(g.d_names.p, tab.data(), (size_t)cap * sizeof(NameEntry), cudaMemcpyHostToDevice, c->stream));
+    if (!blob.empty()) CU(cudaMemcpyAsync(g.d_name_blob.p, blob.data(), blob.size(), cudaMemcpyHostToDevice, c->stream));
+    CU(stream_sync(c));
+    g.name_mask = cap - 1;
+    g.names_dirty = false;
+    return 0;
+}
+
+// carve typed arrays out of one device buffer
+struct Carver {
+    char *base;
+    size_t at = 0;
+    template <class T> T *take(size_t n) {
+        at = (at + 15) & ~(size_t)15;
+        T *p = reinterpret_cast<T *>(base + at);
+        at += n * sizeof(T);
+        return p;
+    }
+};
+
+}  // namespace
+
+extern "C" int pafgpu_add_mismatches_text(pafgpu_ctx *c, const char *text, int64_t n_bytes, pafgpu_text_result *res) {
+    if (!c || !res || n_bytes < 0 || (n_bytes && !text)) return PAFGPU_EINVAL;
+    if (n_bytes >= ((int64_t)1 << 31)) return fail(c, PAFGPU_EINVAL, "text chunk too large: cut it (32-bit byte offsets)");
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    memset(res, 0, sizeof *res);
+    res->first_bad = -1;
+    c->have_batch = false;
+    c->ser_text_bytes = 0;
+    if (n_bytes == 0) return 0;
+    GenomeStore &g = c->G();
+    if (int rc = genome_sync_names(c, g)) return rc;
+    if (int rc = genome_sync_table(c, g)) return rc;
+    // the text ends with a newline on the device (a last line without one still counts, sonLibFile.c:42-71)
+    const bool add_nl = text[n_bytes - 1] != '\n';
+    const int64_t n = n_bytes + (add_nl ? 1 : 0);
+    const int64_t n_tiles_tx = (n + TX_TILE - 1) / TX_TILE;
+    CU(c->tx_text.ensure((size_t)n + 64));
+    CU(c->tx_tile_nl.ensure((size_t)n_tiles_tx * 4));
+    CU(c->tx_tile_tab.ensure((size_t)n_tiles_tx * 4));
+    CU(c->tx_nl_off.ensure((size_t)(n_tiles_tx + 1) * 8));
+    CU(c->tx_tab_off.ensure((size_t)(n_tiles_tx + 1) * 8));
+    CU(c->tx_tile_ops.ensure((size_t)n_tiles_tx * 4));
+    CU(c->tx_op_off.ensure((size_t)(n_tiles_tx + 1) * 8));
+    CU(c->tx_scal.ensure(32 * 8));
+    CU(c->scalars.ensure(SC_COUNT * 8));
+    char *d_text = c->tx_text.as<char>();
+    uint64_t *scal = c->tx_scal.as<uint64_t>();  // [0] first bad record, [1] newlines, [2] tabs, [3] ops, [4..11] totals, [12] mismatches
+    CU(cudaEventRecord(c->ev_tx[0], c->stream));
+    CU(cudaMemcpyAsync(d_text, text, (size_t)n_bytes, cudaMemcpyHostToDevice, c->stream));
+    if (add_nl) CU(cudaMemsetAsync(d_text + n_bytes, '\n', 1, c->stream));
+    CU(cudaMemsetAsync(d_text + n, 0, 32, c->stream));
+    CU(cudaMemsetAsync(scal, 0, 32 * 8, c->stream));
+    CU(cudaMemsetAsync(scal, 0xff, 8, c->stream));
+    tx_count_delims_kernel<<<(unsigned)n_tiles_tx, TX_THREADS, 0, c->stream>>>(d_text, n, c->tx_tile_nl.as<uint32_t>(), c->tx_tile_tab.as<uint32_t>());
+    if (int rc = scan_u32(c, c->tx_tile_nl.as<uint32_t>(), n_tiles_tx, c->tx_nl_off.as<uint64_t>(), scal + 1)) return rc;
+    if (int rc = scan_u32(c, c->tx_tile_tab.as<uint32_t>(), n_tiles_tx, c->tx_tab_off.as<uint64_t>(), scal + 2)) return rc;
+    uint64_t counts[2];
+    CU(read_words(c, counts, scal + 1, 2));
+    int64_t R = (int64_t)counts[0];
+    const int64_t n_tabs = (int64_t)counts[1];
+    const int64_t R_all = R;
+    if (R >= ((int64_t)1 << 31)) return fail(c, PAFGPU_EINVAL, "text chunk holds too many records: cut it");
+    CU(c->tx_nl_pos.ensure((size_t)std::max<int64_t>(R, 1) * 4));
+    CU(c->tx_tab_pos.ensure((size_t)(n_tabs + 1) * 4));
+    CU(c->tx_line_tab0.ensure((size_t)(R + 1) * 4));
+    // parsed columns
+    const size_t Rz = (size_t)R + 1;
+    CU(c->tx_cols.ensure(Rz * (7 * 4 + 13 * 8 + 3 + 2 * 4 + 8 + 4 + 8) + 64 * 16));
+    Carver cv{c->tx_cols.as<char>()};
+    TextRecords T{};
+    T.line_begin = cv.take<uint32_t>(Rz); T.qn_off = cv.take<uint32_t>(Rz); T.qn_len = cv.take<uint32_t>(Rz);
+    T.tn_off = cv.take<uint32_t>(Rz); T.tn_len = cv.take<uint32_t>(Rz); T.cg_begin = cv.take<uint32_t>(Rz); T.cg_end = cv.take<uint32_t>(Rz);
+    T.qlen = cv.take<int64_t>(Rz); T.qs = cv.take<int64_t>(Rz); T.qe = cv.take<int64_t>(Rz); T.tlen = cv.take<int64_t>(Rz);
+    T.ts = cv.take<int64_t>(Rz); T.te = cv.take<int64_t>(Rz); T.nmatch = cv.take<int64_t>(Rz); T.nbases = cv.take<int64_t>(Rz);
+    T.mapq = cv.take<int64_t>(Rz); T.score = cv.take<int64_t>(Rz); T.tl = cv.take<int64_t>(Rz); T.cn = cv.take<int64_t>(Rz);
+    T.s1 = cv.take<int64_t>(Rz);
+    T.type = cv.take<uint8_t>(Rz); T.strand = cv.take<uint8_t>(Rz); T.has_cg = cv.take<uint8_t>(Rz);
+    T.q_contig = cv.take<int32_t>(Rz); T.t_contig = cv.take<int32_t>(Rz);
+    int64_t *op_begin = cv.take<int64_t>(Rz);
+    uint32_t *prefix_len = cv.take<uint32_t>(Rz);
+    uint32_t *nl_pos = c->tx_nl_pos.as<uint32_t>(), *tab_pos = c->tx_tab_pos.as<uint32_t>(), *line_tab0 = c->tx_line_tab0.as<uint32_t>();
+    CU(cudaMemsetAsync(tab_pos + n_tabs, 0xff, 4, c->stream));  // sentinel behind the last tab
+    CU(cudaMemsetAsync(line_tab0, 0, 4, c->stream));
+    CU(cudaMemsetAsync(op_begin, 0, 8, c->stream));
+    tx_scatter_delims_kernel<<<(unsigned)n_tiles_tx, TX_THREADS, 0, c->stream>>>(d_text, n, c->tx_nl_off.as<uint64_t>(), c->tx_tab_off.as<uint64_t>(),
+                                                                                nl_pos, tab_pos, line_tab0);
+    ParseParams PP{};
+    PP.text = d_text; PP.n_records = R; PP.nl_pos = nl_pos; PP.tab_pos = tab_pos; PP.line_tab0 = line_tab0; PP.R = T;
+    PP.names = g.d_names.as<NameEntry>(); PP.name_mask = g.name_mask; PP.name_blob = g.d_name_blob.as<char>();
+    PP.first_bad = (unsigned long long *)scal;
+    if (R > 0) tx_parse_records_kernel<<<blocks_for(R, 128), 128, 0, c->stream>>>(PP);
+    OpsParams OP{};
+    OP.text = d_text; OP.n = n; OP.n_records = R; OP.nl_off = c->tx_nl_off.as<uint64_t>(); OP.cg_begin = T.cg_begin; OP.cg_end = T.cg_end;
+    OP.tile_ops = c->tx_tile_ops.as<uint32_t>(); OP.op_off = c->tx_op_off.as<uint64_t>(); OP.op_begin = op_begin;
+    OP.first_bad = (unsigned long long *)scal;
+    tx_ops_kernel<false><<<(unsigned)n_tiles_tx, TX_THREADS, 0, c->stream>>>(OP);
+    if (int rc = scan_u32(c, c->tx_tile_ops.as<uint32_t>(), n_tiles_tx, c->tx_op_off.as<uint64_t>(), scal + 3)) return rc;
+    uint64_t after_ops[4];
+    CU(read_words(c, after_ops, scal, 4));
+    int64_t N = (int64_t)after_ops[3];
+    CU(c->tx_ops.ensure((size_t)std::max<int64_t>(N, 1) * 8));
+    OP.ops = c->tx_ops.as<uint64_t>();
+    tx_ops_kernel<true><<<(unsigned)n_tiles_tx, TX_THREADS, 0, c->stream>>>(OP);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(c->ev_tx[1], c->stream));
+    int64_t first_bad = after_ops[0] == ~0ull ? -1 : (int64_t)after_ops[0];
+
+    // ---- ingest + encode on the records before the first bad one; the ingest kernel may find an earlier one (a record
+    // that walks outside its contig, or fails paf_check's op sums)
+    pafgpu_result er{};
+    for (int attempt = 0;; attempt++) {
+        if (first_bad >= 0 && first_bad < R) {
+            R = first_bad;
+            CU(cudaMemcpyAsync(&N, op_begin + R, 8, cudaMemcpyDeviceToHost, c->stream));
+            CU(stream_sync(c));
+        }
+        if (R == 0) break;
+        pafgpu_batch b{R, N, op_begin, c->tx_ops.as<uint64_t>(), T.q_contig, T.t_contig, T.qs, T.qe, T.ts, T.strand};
+        c->ingest_t_end = T.te;
+        c->ingest_has_cg = T.has_cg;
+        const int rc = encode_device(c, g, &b, &er);
+        c->ingest_t_end = nullptr;
+        c->ingest_has_cg = nullptr;
+        if (rc == PAFGPU_EBOUNDS && c->bad_record >= 0 && c->bad_record < R && attempt < 4) {
+            first_bad = c->bad_record;
+            continue;
+        }
+        if (rc) return rc;
+        break;
+    }
+    res->records = R;
+    res->records_in = R_all;
+    res->first_bad = first_bad >= 0 && first_bad < R_all ? first_bad : -1;
+    if (res->first_bad >= 0) {
+        uint32_t ends[2] = {0, 0};
+        if (res->first_bad > 0) CU(cudaMemcpyAsync(&ends[0], nl_pos + res->first_bad - 1, 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(&ends[1], nl_pos + res->first_bad, 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(stream_sync(c));
+        res->bad_line_begin = res->first_bad > 0 ? (int64_t)ends[0] + 1 : 0;
+        res->bad_line_end = std::min<int64_t>(ends[1], n_bytes);
+    }
+    if (R == 0) { c->have_batch = false; return 0; }
+    res->n_ops = N; res->n_out_ops = c->n_out; res->aligned_bases = er.aligned_bases;
+    res->ms_ingest = er.ms_ingest; res->ms_kernel = er.ms_kernel; res->ms_encode = er.ms_encode;
+    cudaEventElapsedTime(&res->ms_parse, c->ev_tx[0], c->ev_tx[1]);
+
+    // ---- output text: prefix of every record measured, the lines laid out, prefixes and ops rendered in place
+    const int64_t K = c->n_out;
+    CU(cudaEventRecord(c->ev_tx[2], c->stream));
+    tx_empty_out_begin_kernel<<<blocks_for(R, 256), 256, 0, c->stream>>>(R, op_begin, c->op_rec.as<uint32_t>(), N,
+                                                                         (const unsigned long long *)(c->scalars.as<uint64_t>() + SC_TOTAL),
+                                                                         c->rec_out_begin.as<int64_t>());
+    PrefixParams PR{};
+    PR.text = d_text; PR.n_records = R; PR.R = T; PR.prefix_len = prefix_len;
+    tx_prefix_kernel<false><<<blocks_for(R, 128), 128, 0, c->stream>>>(PR);
+    CU(c->ser_prefix_begin.ensure((size_t)(R + 1) * 8));
+    if (int rc = scan_u32(c, prefix_len, R, c->ser_prefix_begin.as<uint64_t>(), nullptr)) return rc;
+    CU(c->ser_oplen.ensure((size_t)std::max<int64_t>(K, 1) * 4));
+    CU(c->ser_optoff.ensure((size_t)(K + 1) * 8));
+    CU(c->ser_line_begin.ensure((size_t)(R + 1) * 8));
+    if (K > 0)
+        op_text_len_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(c->out.as<uint64_t>(), K, c->ser_oplen.as<uint32_t>(),
+                                                                                          c->rec_out_begin.as<int64_t>(), R, nullptr, nullptr);
+    if (int rc = scan_u32(c, c->ser_oplen.as<uint32_t>(), K, c->ser_optoff.as<uint64_t>(), nullptr)) return rc;
+    line_begin_kernel<<<blocks_for(R + 1, 256), 256, 0, c->stream>>>(R, c->ser_prefix_begin.as<int64_t>(), c->rec_out_begin.as<int64_t>(),
+                                                                     c->ser_optoff.as<uint64_t>(), c->ser_line_begin.as<int64_t>());
+    // totals for the report while the layout is read back
+    tx_op_totals_kernel<<<(unsigned)std::min<int64_t>(blocks_for(N, 256 * 8), 1184), 256, 0, c->stream>>>(c->tx_ops.as<uint64_t>(), N,
+                                                                                                     (unsigned long long *)(scal + 4));
+    tx_sum_kernel<<<(unsigned)std::min<int64_t>(blocks_for(R, 256 * 8), 1184), 256, 0, c->stream>>>((const unsigned long long *)c->rec_mism.p, R,
+                                                                                               (unsigned long long *)(scal + 12));
+    int64_t total = 0;
+    CU(read_words(c, (uint64_t *)&total, c->ser_line_begin.as<uint64_t>() + R, 1));
+    CU(c->ser_text.ensure((size_t)std::max<int64_t>(total, 8)));
+    SerialiseParams S{};
+    S.n_records = R; S.n_out = K;
+    S.out = c->out.as<uint64_t>(); S.rec_out_begin = c->rec_out_begin.as<int64_t>();
+    S.op_toff = c->ser_optoff.as<uint64_t>();
+    S.prefix = nullptr; S.prefix_begin = c->ser_prefix_begin.as<int64_t>();
+    S.line_begin = c->ser_line_begin.as<int64_t>(); S.text = c->ser_text.as<char>();
+    PR.line_begin = c->ser_line_begin.as<int64_t>(); PR.out = c->ser_text.as<char>();
+    tx_prefix_kernel<true><<<blocks_for(R, 128), 128, 0, c->stream>>>(PR);
+    if (K > 0) op_text_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(S);
+    CU(cudaEventRecord(c->ev_tx[3], c->stream));
+    uint64_t tot[9];
+    CU(read_words(c, tot, scal + 4, 9));
+    CU(cudaGetLastError());
+    cudaEventElapsedTime(&res->ms_render, c->ev_tx[2], c->ev_tx[3]);
+    const int64_t mm = (int64_t)tot[8];
+    res->stats[0] = (int64_t)tot[0] + (int64_t)tot[1] - mm;  // matches: M and = bases that are no mismatches
+    res->stats[1] = (int64_t)tot[2] + mm;
+    res->stats[2] = (int64_t)tot[3]; res->stats[3] = (int64_t)tot[5];
+    res->stats[4] = (int64_t)tot[4]; res->stats[5] = (int64_t)tot[6];
+    res->stats[6] = R;
+    res->text_bytes = total;
+    c->ser_text_bytes = total;
+    c->trimmed = false;
+    return 0;
+}
+
+extern "C" {
 
 // ---- device trim (paf_trim_unreliable_tails, impl/paf.c:906-953) -------------------------------------
 static int trim_batch(pafgpu_ctx *c, bool fixed, float score_fraction, float max_fraction, const int64_t *t_end, int64_t *coords,

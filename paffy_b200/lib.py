@@ -22,7 +22,7 @@ ABI_SYMBOLS = [
     "pafgpu_serialise", "pafgpu_fetch_text", "pafgpu_encode_one", "pafgpu_time_encode",
     "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition", "pafgpu_trim",
     "pafgpu_trim_fixed", "pafgpu_stage_ops_host", "pafgpu_add_mismatches_file_filtered",
-    "pafgpu_create_sibling", "pafgpu_device_of", "pafgpu_genome_clone", "pafgpu_genome_save", "pafgpu_genome_load_packed",
+    "pafgpu_add_mismatches_text", "pafgpu_create_sibling", "pafgpu_helper", "pafgpu_device_of", "pafgpu_genome_clone", "pafgpu_genome_save", "pafgpu_genome_load_packed",
 ]
 # reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
 REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paffy_view_main", "paffy_trim_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
@@ -42,7 +42,7 @@ class Batch(C.Structure):
 
 class FileOpts(C.Structure):
     _fields_ = [("mode", C.c_int), ("trim_score_fraction", C.c_float), ("trim_max_fraction", C.c_float), ("threads", C.c_int),
-                ("batch_bases", C.c_int64)]
+                ("batch_bases", C.c_int64), ("gpus", C.c_int), ("streams", C.c_int), ("chunk_bytes", C.c_int64)]
 
 
 class FileFilter(C.Structure):
@@ -54,7 +54,15 @@ class FileFilter(C.Structure):
 class FileReport(C.Structure):
     _fields_ = [("records", C.c_int64), ("aligned_bases", C.c_int64), ("batches", C.c_int64), ("failed_record", C.c_int64),
                 ("stats", C.c_int64 * 7), ("s_read", C.c_double), ("s_parse", C.c_double), ("s_gpu", C.c_double),
-                ("s_host", C.c_double), ("s_write", C.c_double)]
+                ("s_host", C.c_double), ("s_write", C.c_double), ("s_total", C.c_double), ("chunks", C.c_int64), ("gpus", C.c_int64),
+                ("workers", C.c_int64)]
+
+
+class TextResult(C.Structure):
+    _fields_ = [("records", C.c_int64), ("records_in", C.c_int64), ("n_ops", C.c_int64), ("n_out_ops", C.c_int64),
+                ("aligned_bases", C.c_int64), ("text_bytes", C.c_int64), ("first_bad", C.c_int64), ("bad_line_begin", C.c_int64),
+                ("bad_line_end", C.c_int64), ("stats", C.c_int64 * 7), ("ms_parse", C.c_float), ("ms_ingest", C.c_float),
+                ("ms_kernel", C.c_float), ("ms_encode", C.c_float), ("ms_render", C.c_float)]
 
 
 class Result(C.Structure):
@@ -112,6 +120,12 @@ def load():
     L.pafgpu_add_mismatches_file.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(FileOpts), C.POINTER(FileReport)]
     L.pafgpu_add_mismatches_file_filtered.argtypes = [vp, C.c_char_p, C.c_char_p, C.POINTER(FileOpts), C.POINTER(FileFilter), C.POINTER(FileReport)]
     L.pafgpu_partition.argtypes = [vp, i64, C.c_int, vp]
+    L.pafgpu_create_sibling.argtypes = [vp, C.POINTER(vp)]
+    L.pafgpu_add_mismatches_text.argtypes = [vp, vp, i64, C.POINTER(TextResult)]
+    L.pafgpu_genome_clone.argtypes = [vp, vp]
+    L.pafgpu_genome_save.argtypes = [vp, C.c_char_p, C.c_char_p]
+    L.pafgpu_genome_load_packed.argtypes = [vp, C.c_char_p, C.c_char_p]
+    L.pafgpu_stage_ops_host.argtypes = [vp, C.POINTER(Batch)]
     L.pafgpu_trim.argtypes = [vp, C.c_float, C.c_float, vp, vp, vp, vp]
     _lib = L
     return L
@@ -127,11 +141,11 @@ def partition(weights, parts):
     return cuts
 
 
-def remove_mismatches_file(in_path, out_path, threads=0):
+def remove_mismatches_file(in_path, out_path, threads=0, chunk_bytes=0):
     """`paffy add_mismatches -a` (host-only text work: no CUDA device needed). -> (rc, FileReport)"""
-    o = FileOpts(1, 0.05, 1.0, threads, 0)
+    o = FileOpts(1, 0.05, 1.0, threads, 0, 0, 0, chunk_bytes)
     rep = FileReport()
-    rc = load().pafgpu_add_mismatches_file(None, in_path.encode(), out_path.encode(), C.byref(o), C.byref(rep))
+    rc = load().pafgpu_add_mismatches_file(None, in_path.encode() if in_path else None, out_path.encode() if out_path else None, C.byref(o), C.byref(rep))
     return rc, rep
 
 
@@ -165,6 +179,28 @@ class Context:
         if getattr(self, "h", None):
             self.L.pafgpu_destroy(self.h)
             self.h = None
+
+    def sibling(self):
+        """A second context on the same GPU sharing this one's packed genome (own stream and buffers): copies and kernels
+        of different batches overlap without a second genome copy."""
+        s = Context.__new__(Context)
+        s.L = self.L
+        h = C.c_void_p()
+        rc = self.L.pafgpu_create_sibling(self.h, C.byref(h))
+        if rc:
+            raise PafGpuError(rc, self.L.pafgpu_last_error(None).decode())
+        s.h, s.n_records, s.result = h, 0, None
+        return s
+
+    def add_mismatches_text(self, text):
+        """PAF text (bytes, free of \r) in, PAF text out, parsed / encoded / rendered on the device. -> (TextResult, bytes)"""
+        res = TextResult()
+        buf = np.frombuffer(text, dtype=np.uint8)
+        self._check(self.L.pafgpu_add_mismatches_text(self.h, buf.ctypes.data, buf.size, C.byref(res)))
+        out = np.empty(res.text_bytes, dtype=np.uint8)
+        if res.text_bytes:
+            self._check(self.L.pafgpu_fetch_text(self.h, out.ctypes.data, None))
+        return res, out.tobytes()
 
     __del__ = close
 
@@ -224,6 +260,15 @@ class Context:
         self.result = res
         return res
 
+    def stage_ops(self, op_begin, ops, q_start, q_end, t_start, same_strand):
+        """Upload ops as if an encode had produced them (pafgpu_stage_ops_host): serialise / trim then work on them."""
+        want = [np.int64, np.uint64, np.int64, np.int64, np.int64, np.uint8]
+        a = [np.ascontiguousarray(x, dtype=t) for x, t in zip([op_begin, ops, q_start, q_end, t_start, same_strand], want)]
+        n_records = int(a[0].shape[0]) - 1
+        b = Batch(n_records, int(a[1].shape[0]), _ptr(a[0]), _ptr(a[1]), None, None, _ptr(a[2]), _ptr(a[3]), _ptr(a[4]), _ptr(a[5]))
+        self._check(self.L.pafgpu_stage_ops_host(self.h, C.byref(b)))
+        self.n_records = n_records
+
     def fetch_ops(self, want_ops=True, pinned=None):
         """-> (out_ops uint64[n_out], out_op_begin int64[R+1], rec_mismatch int64[R])"""
         n_out, R = self.result.n_out_ops, self.n_records
@@ -265,11 +310,11 @@ class Context:
                                        failed.ctypes.data))
         return coords, kept, failed
 
-    def add_mismatches_file(self, in_path, out_path, mode=0, trim_r=0.05, trim_t=1.0, threads=0, batch_bases=0):
+    def add_mismatches_file(self, in_path, out_path, mode=0, trim_r=0.05, trim_t=1.0, threads=0, batch_bases=0, gpus=0, streams=0, chunk_bytes=0):
         """The whole-file filter (paffy add_mismatches / -a / | trim; mode 4 | 1 | 2 = paffy view with per-alignment lines
         and / or the aggregate line). -> (rc, FileReport); rc 1 = a record ended the run the way the reference exits 1
         (message in self.last_error())."""
-        o = FileOpts(mode, trim_r, trim_t, threads, batch_bases)
+        o = FileOpts(mode, trim_r, trim_t, threads, batch_bases, gpus, streams, chunk_bytes)
         rep = FileReport()
         rc = self.L.pafgpu_add_mismatches_file(self.h, in_path.encode(), out_path.encode(), C.byref(o), C.byref(rep))
         if rc < 0:
@@ -277,9 +322,9 @@ class Context:
         return rc, rep
 
     def add_mismatches_filter_file(self, in_path, out_path, min_chain_score=-1, min_alignment_score=-1, min_identity=-1.0,
-                                   min_identity_with_gaps=-1.0, max_tile_level=-1, invert=False, batch_bases=0):
+                                   min_identity_with_gaps=-1.0, max_tile_level=-1, invert=False, batch_bases=0, gpus=0, streams=0, chunk_bytes=0):
         """`paffy add_mismatches | paffy filter -s -t -u -v -w [-x]` in one pass -> (rc, FileReport)."""
-        o = FileOpts(0, 0.05, 1.0, 0, batch_bases)
+        o = FileOpts(0, 0.05, 1.0, 0, batch_bases, gpus, streams, chunk_bytes)
         f = FileFilter(min_chain_score, min_alignment_score, min_identity, min_identity_with_gaps, max_tile_level, int(invert))
         rep = FileReport()
         rc = self.L.pafgpu_add_mismatches_file_filtered(self.h, in_path.encode(), out_path.encode(), C.byref(o), C.byref(f), C.byref(rep))

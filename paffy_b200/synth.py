@@ -193,15 +193,36 @@ CONFIGS = {
     "C2": (24, 125_000_000, 1_000_000, ("normal", 10_000, 2_000, 2_000, 20_000), 0.01, 0.001),
     "C3": (24, 125_000_000, 50_000, ("loguniform", 1e5, 5e6), 0.005, 0.0005),
     "C4": (24, 125_000_000, 10_000_000, ("uniform", 1_000, 5_000), 0.01, 0.001),
+    # config 5 of BASELINE.json: 20 M records of C2's shape, ONE record list sharded over the GPUs of the box
+    "C5": (24, 125_000_000, 20_000_000, ("normal", 10_000, 2_000, 2_000, 20_000), 0.01, 0.001),
     "tiny": (4, 200_000, 2_000, ("normal", 3_000, 1_000, 500, 8_000), 0.01, 0.001),
     "small": (4, 5_000_000, 40_000, ("normal", 10_000, 2_000, 2_000, 20_000), 0.01, 0.001),
 }
 
 
+def shard(rec, lo, hi):
+    """Records [lo, hi) of a record set (the ops re-based), e.g. one rank's contiguous range of a job."""
+    out = {}
+    ob = rec["op_begin"]
+    o0, o1 = int(ob[lo].item()), int(ob[hi].item())
+    for k, v in rec.items():
+        if k == "op_begin":
+            out[k] = (ob[lo:hi + 1] - o0).contiguous()
+        elif k == "ops":
+            out[k] = v[o0:o1].contiguous()
+        elif torch.is_tensor(v) and v.dim() == 1 and v.numel() == rec["n"]:
+            out[k] = v[lo:hi].contiguous()
+        else:
+            out[k] = v
+    out["n"] = hi - lo
+    return out
+
+
 def build_workload(ctx, name, device, seed=MASTER_SEED, scale=1.0, shuffle=True, keep_ascii=(), rank=0):
     """Generate config `name`, load the genome into ctx (device-resident ASCII -> packed on the GPU) and
     return the record set (torch tensors on `device`). keep_ascii: contig indices whose ASCII is kept
-    (host bytes) for CPU-baseline FASTA files. `rank` offsets the record seed so ranks get disjoint shards."""
+    (host bytes) for CPU-baseline FASTA files. `rank` offsets the record seed so ranks get disjoint shards
+    (weak scaling); strong scaling generates the same list (rank 0's) everywhere and cuts it with shard()."""
     n_contigs, clen, n_rec, law, s, g = CONFIGS[name]
     n_rec = max(n_contigs, int(n_rec * scale))
     parts, kept = [], {}

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     lib = paffy_b200.load()
     for name in declared_symbols():
         assert hasattr(lib, name), f"libpaffy_b200.so does not export {name}"
-    assert lib.pafgpu_abi_version() == 1
+    assert lib.pafgpu_abi_version() == 2
 
 
 def test_reference_named_entry_points_are_exported():
@@ -41,7 +41,7 @@ def test_reference_named_entry_points_are_exported():
 def test_result_struct_layout_matches_header():
     # 5 x int64 + 4 x float, padded to 8
     assert C.sizeof(L.Result) == 56 and C.sizeof(L.Batch) == 80
-    assert C.sizeof(L.FileOpts) == 24 and C.sizeof(L.FileReport) == 128
+    assert C.sizeof(L.FileOpts) == 40 and C.sizeof(L.FileReport) == 160
 
 
 def test_no_cpu_fallback():

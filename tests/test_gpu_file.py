@@ -34,7 +34,8 @@ def golden(name):
 def test_add_mismatches_file_matches_reference(fresh, stem, batch_bases, tmp_path):
     fresh.load_fasta(os.path.join(G, stem + ".fa"))
     out = tmp_path / "out.paf"
-    rc, rep = fresh.add_mismatches_file(os.path.join(G, stem + ".paf"), str(out), batch_bases=batch_bases)
+    # (plain add_mismatches parses the text on the device: one GPU batch per chunk of text)
+    rc, rep = fresh.add_mismatches_file(os.path.join(G, stem + ".paf"), str(out), batch_bases=batch_bases, chunk_bytes=1500 if batch_bases else 0)
     assert rc == 0
     assert out.read_bytes() == golden(stem + ".add.paf")
     assert util.view_summary(list(rep.stats)).encode() == golden(stem + ".view.txt")
@@ -330,3 +331,195 @@ def test_device_trim_matches_oracle(ctx, seed):
             want = [p.query_start, p.query_end, p.target_start, p.target_end]
             assert [int(coords[k][i]) for k in range(4)] == want, (i, sf, mf)
             assert int(kept[i]) == p.n_ops and not failed[i]
+
+
+# ---- round 2: the streaming pipeline, one job over the GPUs of the box, the persisted packed genome --------------------
+@pytest.mark.parametrize("stem", SETS[1:])
+@pytest.mark.parametrize("mode,suffix", [(0, ".add.paf"), (2, ".trim.paf"), (4 | 1 | 2, ".viewlines.txt")])
+def test_small_chunks_and_several_streams_give_the_same_bytes(fresh, stem, mode, suffix, tmp_path):
+    """Chunks of a few lines dealt to 3 sibling contexts (shared genome, own streams) and written in input order."""
+    fresh.load_fasta(os.path.join(G, stem + ".fa"))
+    out = tmp_path / "out.paf"
+    src = stem + ".paf"
+    rc, rep = fresh.add_mismatches_file(os.path.join(G, src), str(out), mode=mode, streams=3, chunk_bytes=600)
+    assert rc == 0
+    assert out.read_bytes() == golden(stem + suffix)
+    assert rep.chunks >= 3 and rep.workers == 3 and rep.gpus == 1
+
+
+def test_one_job_sharded_over_the_gpus_of_the_box(fresh, tmp_path):
+    """contiguous record ranges dealt to the GPUs (genome cloned GPU to GPU), outputs concatenated in input order,
+    byte-equal to the reference's single-process output. With one visible GPU the same code runs with one device."""
+    n_dev = paffy_b200.load().pafgpu_device_count()
+    want_gpus = min(2, n_dev)
+    for stem in SETS[1:]:
+        c = paffy_b200.Context(0)
+        try:
+            c.load_fasta(os.path.join(G, stem + ".fa"))
+            out = tmp_path / (stem + ".out")
+            rc, rep = c.add_mismatches_file(os.path.join(G, stem + ".paf"), str(out), gpus=want_gpus, streams=2, chunk_bytes=900)
+            assert rc == 0 and rep.gpus == want_gpus and rep.workers == 2 * want_gpus and rep.chunks >= 3
+            assert out.read_bytes() == golden(stem + ".add.paf")
+            assert util.view_summary(list(rep.stats)).encode() == golden(stem + ".view.txt")
+        finally:
+            c.close()
+
+
+def test_genome_clone_between_contexts(tmp_path):
+    """pafgpu_genome_clone: a context on (another) device encodes against the cloned genome exactly like the source."""
+    L = paffy_b200.load()
+    n_dev = L.pafgpu_device_count()
+    a, b = paffy_b200.Context(0), paffy_b200.Context(n_dev - 1)
+    try:
+        a.load_fasta(os.path.join(G, "rand103.fa"))
+        assert L.pafgpu_genome_clone(b.h, a.h) == 0
+        assert b.num_contigs() == a.num_contigs()
+        out = tmp_path / "o.paf"
+        rc, rep = b.add_mismatches_file(os.path.join(G, "rand103.paf"), str(out))
+        assert rc == 0 and out.read_bytes() == golden("rand103.add.paf")
+    finally:
+        a.close()
+        b.close()
+
+
+def test_packed_genome_save_and_load(tmp_path):
+    """the packed arena written once and read back by a later process gives byte-identical output; a
+    differing key or a damaged file is refused."""
+    L = paffy_b200.load()
+    L.pafgpu_genome_save.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+    L.pafgpu_genome_load_packed.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+    path = str(tmp_path / "g.pafb200").encode()
+    for stem in ("edge", "rand102"):
+        a = paffy_b200.Context(0)
+        a.load_fasta(os.path.join(G, stem + ".fa"))
+        assert L.pafgpu_genome_save(a.h, path, b"key-1") == 0
+        n = a.num_contigs()
+        a.close()
+        b = paffy_b200.Context(0)
+        try:
+            assert L.pafgpu_genome_load_packed(b.h, path, b"another key") == -7  # PAFGPU_ESTATE
+            assert L.pafgpu_genome_load_packed(b.h, path, b"key-1") == 0
+            assert b.num_contigs() == n
+            out = tmp_path / "o.paf"
+            rc, rep = b.add_mismatches_file(os.path.join(G, stem + ".paf"), str(out))
+            assert rc == 0 and out.read_bytes() == golden(stem + ".add.paf")
+            blob = open(path, "rb").read()
+            open(path, "wb").write(blob[: len(blob) // 2])
+            assert L.pafgpu_genome_load_packed(b.h, path, b"key-1") == -6  # PAFGPU_EIO
+        finally:
+            b.close()
+
+
+def test_failure_ordering_across_chunks(fresh, tmp_path):
+    """A bad record in a late chunk: every record before it is written, nothing after it, whatever chunk finished first."""
+    fresh.load_fasta(os.path.join(G, "edge.fa"))
+    good = "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:25M"
+    bad = "nosuch\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:25M"
+    inp, out = tmp_path / "in.paf", tmp_path / "out.paf"
+    inp.write_text("\n".join([good] * 211 + [bad] + [good] * 300) + "\n")
+    rc, rep = fresh.add_mismatches_file(str(inp), str(out), streams=3, chunk_bytes=700)
+    assert rc == 1 and rep.failed_record == 211 and rep.records == 211
+    assert out.read_text().count("\n") == 211
+    assert "No query sequence named: nosuch found" in fresh.last_error()
+
+
+# ---- round 2: PAF text parsed and rendered on the device (SURVEY 8f rank 1) ------------------------------------------
+def _decorated_lines(case):
+    """Lines of a random case dressed up with everything paf_parse tolerates (impl/paf.c:137-209): extra and malformed tags,
+    tags in any order, runs of tabs, no cg tag, an empty cg value, a repeated cg tag, 0M ops, negative numbers."""
+    out = []
+    for i, line in enumerate(util.case_lines(case)):
+        f = line.split("\t")
+        head, cg = f[:12], f[-1]
+        k = i % 11
+        if k == 1:
+            f = head + ["NM:i:5", "zz:Z:abc", "tp:A:P", cg]
+        elif k == 2:
+            f = head + [cg, "tp:A:S", "tl:i:3"]
+        elif k == 3:
+            f = head[:3] + ["", ""] + head[3:] + ["", "tp:A:I", cg, ""]
+        elif k == 4:
+            f = head + ["tp:A:P"]
+        elif k == 5:
+            f = head + ["cg:Z:", "AS:i:77"]
+        elif k == 6:
+            f = head + ["cg:Z:5M", "tp:A:P", cg]
+        elif k == 7:
+            f = head + ["AS:i:-12", "cn:i:7", "s1:i:99", cg]
+        elif k == 8:
+            f = head + ["tp:A:P", cg.replace("M", "M0M", 1) + "0M"]
+        elif k == 9:
+            f = head + ["x", "ab:c", "tl:i:1", cg]
+        elif k == 10:
+            f = head + ["tl:i:2", cg]
+        out.append("\t".join(f))
+    return out
+
+
+@pytest.mark.parametrize("seed", [5, 6])
+def test_device_text_path_matches_the_reference_on_decorated_lines(fresh, seed, tmp_path):
+    """The device parser / renderer against the compiled reference CLI (the oracle's file filter where the reference binary
+    is absent), and against this library's own host-parse path: same bytes, same totals."""
+    from oracle import pyoracle as O
+    case = util.random_case(seed, n_records=150, contig_len=30000, n_ops=14, max_len=900, p_weird=0.002)
+    fa, paf = tmp_path / "g.fa", tmp_path / "in.paf"
+    with open(fa, "wb") as fh:
+        for name, seq in case["contigs"].items():
+            fh.write(b">" + name.encode() + b"\n" + seq + b"\n")
+    lines = _decorated_lines(case)
+    paf.write_text("\n".join(lines))  # no newline behind the last line
+    want = tmp_path / "want.paf"
+    if O.ref_available():
+        r = subprocess.run([O.REF_PAFFY, "add_mismatches", str(fa), "-i", str(paf), "-o", str(want)], capture_output=True)
+        assert r.returncode == 0, r.stderr[-500:]
+    else:
+        rc, _, _ = O.Fasta([str(fa)]).add_mismatches_file(str(paf), str(want))
+        assert rc == 0
+    fresh.load_fasta(str(fa))
+    out = tmp_path / "out.paf"
+    rc, rep = fresh.add_mismatches_file(str(paf), str(out), chunk_bytes=5000)
+    assert rc == 0 and rep.records == len(lines) and rep.chunks > 3
+    assert out.read_bytes() == want.read_bytes()
+    os.environ["PAFFY_HOST_PARSE"] = "1"
+    try:
+        out2 = tmp_path / "out2.paf"
+        rc, rep2 = fresh.add_mismatches_file(str(paf), str(out2), chunk_bytes=5000)
+    finally:
+        del os.environ["PAFFY_HOST_PARSE"]
+    assert rc == 0 and out2.read_bytes() == want.read_bytes()
+    assert list(rep2.stats) == list(rep.stats) and rep2.aligned_bases == rep.aligned_bases
+
+
+def test_device_text_path_locates_the_record_the_reference_aborts_on(fresh, tmp_path):
+    """Every kind of failing record, each behind good ones and in a late chunk: same stdout, record index and message as the
+    host-parse path (which tests/golden/errors.json pins to the reference)."""
+    fresh.load_fasta(os.path.join(G, "edge.fa"))
+    good = "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:25M"
+    bads = ["q\t25\t0\t25\t*\tt\t25\t0\t25\t0\t25\t60\tcg:Z:25M",          # strand
+            "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:20M5Q",        # cigar letter
+            "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:20M5",         # digits without a letter
+            "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\ttp:A:Z\tcg:Z:25M",  # tp value
+            "q\t25\t0\t25\t+\tt\t25\t0\t25",                               # too few fields
+            "nosuch\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:25M",     # unknown query
+            "q\t25\t0\t25\t+\tnosuch\t25\t0\t25\t0\t25\t60\tcg:Z:25M",     # unknown target
+            "q\t25\t0\t10\t+\tt\t25\t0\t9\t0\t0\t60\tcg:Z:9M",             # paf_check: query sum
+            "q\t25\t0\t9\t+\tt\t25\t0\t10\t0\t0\t60\tcg:Z:9M",             # paf_check: target sum
+            "q\t25\t30\t35\t+\tt\t25\t0\t5\t0\t0\t60\tcg:Z:5M",            # paf_check: coordinates
+            "q\t100\t50\t75\t+\tt\t100\t50\t75\t0\t25\t60\tcg:Z:25M"]      # walks outside the contig
+    for bad in bads:
+        inp = tmp_path / "in.paf"
+        inp.write_text("\n".join([good] * 57 + [bad] + [good] * 40) + "\n")
+        got = {}
+        for host_parse in (False, True):
+            if host_parse:
+                os.environ["PAFFY_HOST_PARSE"] = "1"
+            try:
+                out = tmp_path / f"out{int(host_parse)}.paf"
+                rc, rep = fresh.add_mismatches_file(str(inp), str(out), chunk_bytes=900)
+                got[host_parse] = (rc, rep.failed_record, rep.records, out.read_bytes(), fresh.last_error().replace("record 57", "record N").split("record")[0])
+            finally:
+                os.environ.pop("PAFFY_HOST_PARSE", None)
+        assert got[False][0] == 1 and got[False][1] == 57 and got[False][2] == 57, bad
+        assert got[False][3].count(b"\n") == 57
+        assert got[False][:4] == got[True][:4], bad
+        assert got[False][4] == got[True][4], (bad, got[False][4], got[True][4])

@@ -91,3 +91,47 @@ def test_cli_option_handling_without_a_gpu():
                      ["trim", "-i", os.path.join(G, "rand101.add.paf")]):
             r = subprocess.run([exe] + args, capture_output=True)
             assert r.returncode == 1 and r.stdout == b"" and b"ERROR" in r.stderr, args
+
+
+# ---- the streaming pipeline (reader thread -> chunk workers -> ordered writer), on the mode that needs no GPU ----------
+@pytest.mark.parametrize("chunk", [64, 1000, 1 << 20])
+def test_chunked_pipeline_gives_the_same_bytes(chunk, tmp_path):
+    """Chunks of whole lines processed by concurrent workers and written in input order: same bytes whatever the chunk size
+    (64 bytes = every line its own chunk, lines longer than a chunk included)."""
+    out = tmp_path / "o.paf"
+    rc, rep = paffy_b200.remove_mismatches_file(os.path.join(G, "rand102.add.paf"), str(out), chunk_bytes=chunk)
+    assert rc == 0
+    want = open(os.path.join(G, "rand102.remove.paf"), "rb").read()
+    assert out.read_bytes() == want
+    assert rep.records == want.count(b"\n") and rep.workers == 2
+    if chunk == 64:
+        assert rep.chunks > rep.records // 4
+
+
+def test_failure_in_a_later_chunk_keeps_input_order(tmp_path):
+    good = "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:10=2X13="
+    bad = "q\t25\t0\t10\t+\tt\t25\t0\t9\t0\t0\t60\tcg:Z:9="
+    inp, out = tmp_path / "i.paf", tmp_path / "o.paf"
+    inp.write_text("\n".join([good] * 137 + [bad] + [good] * 200) + "\n")
+    rc, rep = paffy_b200.remove_mismatches_file(str(inp), str(out), chunk_bytes=300)
+    assert rc == 1 and rep.failed_record == 137 and rep.records == 137
+    assert out.read_text() == "q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tAS:i:0\tcg:Z:25M\n" * 137
+
+
+def test_output_starts_before_the_input_ends():
+    """The reference streams record by record (impl/paf_add_mismatches.c:106-140): in a pipe the first lines must come out
+    while the producer still holds its end open."""
+    import select
+    import subprocess
+    exe = os.path.join(os.path.dirname(paffy_b200.lib.LIB_PATH), "paffy_b200_cli")
+    p = subprocess.Popen([exe, "add_mismatches", "-a"], stdin=subprocess.PIPE, stdout=subprocess.PIPE, bufsize=0)
+    line = b"q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:10=2X13=\n"
+    p.stdin.write(line * 3)
+    ready, _, _ = select.select([p.stdout], [], [], 20)
+    assert ready, "no output while stdin is still open"
+    first = os.read(p.stdout.fileno(), 1 << 16)
+    assert first.startswith(b"q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tAS:i:0\tcg:Z:25M\n")
+    p.stdin.write(line * 2)
+    p.stdin.close()
+    rest = p.stdout.read()
+    assert p.wait() == 0 and (first + rest).count(b"\n") == 5
