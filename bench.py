@@ -89,18 +89,22 @@ def render_prefixes(rec):
     return np.frombuffer("".join(parts).encode(), dtype=np.uint8), begin
 
 
-def cpu_sample(workload, scale, n_sample, device):
-    """A bounded sample of the same workload (same generator, law and rates) restricted to contig pairs
-    1 and 2 (one '+', one '-'), written as FASTA + PAF for the compiled reference."""
+def cpu_sample(workload, scale, n_sample, device, n_pairs=4):
+    """A bounded sample of the same workload (same generator, law and rates) on `n_pairs` contig pairs spread over the
+    genome, both strands (even pairs are '+', odd ones '-'), written as FASTA + PAF for the compiled reference."""
     from paffy_b200 import synth
     n_contigs, clen, n_rec, law, s, g = synth.CONFIGS[workload]
     d = tempfile.mkdtemp(prefix="paffy_b200_cpu_")
     fa, paf = os.path.join(d, "sample.fa"), os.path.join(d, "sample.paf")
     total_m = 0
     with open(fa, "wb") as ffa, open(paf, "w") as fpaf:
-        for i in range(min(2, n_contigs)):
+        n_pairs = max(1, min(n_pairs, n_contigs))
+        picks = sorted({(k * (n_contigs - 1)) // max(n_pairs - 1, 1) for k in range(n_pairs)}) if n_pairs > 1 else [0]
+        if len(picks) > 1 and all(i % 2 == picks[0] % 2 for i in picks):
+            picks[1] += 1  # both strands
+        for i in picks:
             c = synth.make_contig(i, clen, s, g, synth.MASTER_SEED, device, keep_truth=False)
-            p = synth.contig_records(c, n_sample // 2, law, synth.MASTER_SEED + 4242, device)
+            p = synth.contig_records(c, max(1, n_sample // len(picks)), law, synth.MASTER_SEED + 4242, device)
             p["q_len"] = torch.full((p["n"],), c.Lq, dtype=torch.int64)
             p["clen"] = clen
             for name, asc in ((c.name_t, c.t_ascii), (c.name_q, c.q_ascii)):
@@ -149,10 +153,17 @@ def run_reference_cli(fa, paf, workdir):
     ok = all(p.wait() == 0 for p in procs)
     out["parallel_processes"] = len(shards)
     out["parallel_wall_s"] = time.perf_counter() - t0 if ok else None
+    out["nproc"] = os.cpu_count()
+    out["concurrency"] = len(shards)  # one process per split_file shard, all at once (each loads the whole FASTA of the sample)
+    try:
+        out["ram_gb"] = round(int(open("/proc/meminfo").readline().split()[1]) / 2 ** 20, 1)
+    except Exception:
+        out["ram_gb"] = None
+    out["fasta_bytes"] = os.path.getsize(fa)
     return out
 
 
-def file_parity(fa, paf, workdir, device_index):
+def file_parity(fa, paf, workdir, c):
     """The same sample file to file through the CUDA path (FASTA load, parse, kernels, device serialiser, write) and
     byte-compared with what the compiled reference CLI printed: `add_mismatches` (single.out of run_reference_cli),
     `add_mismatches | trim` and the `add_mismatches | view -s -t` summary line (SURVEY 8d, config C4's pipeline). The
@@ -172,11 +183,12 @@ def file_parity(fa, paf, workdir, device_index):
         return h.hexdigest()
 
     out = {}
-    c = paffy_b200.Context(device_index)
     try:
+        c2 = paffy_b200.Context(0)
         t0 = time.perf_counter()
-        c.load_fasta(fa)
+        c2.load_fasta(fa)  # timed only: the comparison below runs on the caller's context (the whole genome)
         out["fasta_load_s"] = time.perf_counter() - t0
+        c2.close()
         ours = os.path.join(workdir, "ours.add.paf")
         t0 = time.perf_counter()
         rc, rep = c.add_mismatches_file(paf, ours)
@@ -202,7 +214,7 @@ def file_parity(fa, paf, workdir, device_index):
         out["view_summary_equal"] = (rc == 0 and open(ours_view, "rb").read() == r.stdout) if r.returncode == 0 else None
         out["view_summary"] = open(ours_view).read().strip()
     finally:
-        c.close()
+        pass
     out["what"] = ("CUDA path file to file on the cpu_baseline sample vs the compiled reference CLI: add_mismatches, "
                    "add_mismatches | trim (defaults), add_mismatches | view -s -t; md5 / bytes compared")
     return out
@@ -226,7 +238,7 @@ def reference_arm(args, rank):
     secs = sum(r["encode_s"] for r in reps)
     bp = sum(r["aligned_bp"] for r in reps)
     value = bp / secs
-    sample = (f"{reps[0]['records']} records of workload {args.workload} on contig pairs t1/q1 (+) and t2/q2 (-), {reps[0]['aligned_bp']} aligned bp per step; "
+    sample = (f"{reps[0]['records']} records of workload {args.workload} on 4 contig pairs (both strands), {reps[0]['aligned_bp']} aligned bp per step; "
               f"paf_encode_mismatches only (FASTA load {out['load_s']:.1f}s and PAF parse {reps[0]['parse_s']:.2f}s excluded)")
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * secs / len(reps), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
@@ -261,25 +273,61 @@ def bind_near_gpu(index):
         return {"error": str(e)[:80]}
 
 
+class DevArray:
+    """A device buffer of the library as something torch.as_tensor can wrap without a copy."""
+    def __init__(self, ptr, n, typestr="<i8"):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def make_input_text(ctx, rec, pre_b, pre_o):
+    """The workload as PAF text (what `paffy add_mismatches` reads): the INPUT ops are staged on the device as they are and
+    printed behind the host-rendered fields by the device serialiser. Not timed."""
+    host = {k: rec[k].cpu().numpy() for k in ("op_begin", "qs", "qe", "ts", "strand")}
+    ctx.stage_ops(host["op_begin"], rec["ops"].cpu().numpy().view(np.uint64), host["qs"], host["qe"], host["ts"], host["strand"])
+    n, _ = ctx.serialise(pre_b, pre_o)
+    text, _ = ctx.fetch_text(want_lines=False)
+    return text[:n]
+
+
+def md5_file(path):
+    import hashlib
+    h = hashlib.md5()
+    with open(path, "rb") as fh:
+        for blk in iter(lambda: fh.read(1 << 24), b""):
+            h.update(blk)
+    return h.hexdigest()
+
+
+CPU_SAMPLE = {"C2": 100000, "C3": 500, "C4": 100000, "C5": 100000, "small": 20000, "tiny": 2000}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="paffy_b200")
-    ap.add_argument("--workload", default="C2")
+    ap.add_argument("--workload", default=None, help="C2 (default at 1 GPU), C5 (default at N > 1: one job, strong scaling), C3, C4, small, tiny")
     ap.add_argument("--scale", type=float, default=1.0, help="fraction of the workload's record count")
-    ap.add_argument("--cpu-sample", type=int, default=100000, help="records in the CPU-baseline sample")
+    ap.add_argument("--scaling", default=None, choices=["strong", "weak"], help="N > 1: shard ONE record list (default) or one list per rank")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="records in the CPU-baseline sample (0 = per workload)")
+    ap.add_argument("--cpu-contigs", type=int, default=4, help="contig pairs the CPU sample is drawn from (24 = all: 6 GB of FASTA per reference process)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-e2e-file", action="store_true")
     ap.add_argument("--e2e-subbatches", type=int, default=8)
     ap.add_argument("--e2e-contexts", type=int, default=4)
+    ap.add_argument("--file-streams", type=int, default=3)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.workload is None:
+        args.workload = "C2" if world == 1 else "C5"
+    if not args.cpu_sample:
+        args.cpu_sample = CPU_SAMPLE.get(args.workload, 100000)
     if args.impl == "reference":
         reference_arm(args, rank)
         return
@@ -297,11 +345,21 @@ def main():
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "NONE"  # keep stdout to the one JSON line (NCCL prints its version there)
         dist.init_process_group("nccl", device_id=dev)
+    strong = world > 1 and args.scaling != "weak"
 
     ctx = paffy_b200.Context(local)
     t_gen = time.time()
-    rec = synth.build_workload(ctx, args.workload, dev, scale=args.scale, rank=rank)
+    # strong scaling: every rank generates the SAME input-ordered record list (the job), pafgpu_partition cuts it into
+    # `world` contiguous ranges of near-equal aligned bases, a rank keeps its own range; the packed genome is replicated
+    rec = synth.build_workload(ctx, args.workload, dev, scale=args.scale, rank=0 if strong else rank)
+    job_records = rec["n"]
+    my_range = (0, rec["n"])
+    if strong:
+        cuts = paffy_b200.partition(rec["sum_m"].cpu().numpy(), world)
+        my_range = (int(cuts[rank]), int(cuts[rank + 1]))
+        rec = synth.shard(rec, *my_range)
     torch.cuda.synchronize()
+    torch.cuda.empty_cache()
     t_gen = time.time() - t_gen
     R, N = rec["n"], rec["ops"].numel()
     dev_arrays = [rec["op_begin"], rec["ops"], rec["q_contig"], rec["t_contig"], rec["qs"], rec["qe"], rec["ts"], rec["strand"]]
@@ -311,6 +369,13 @@ def main():
         if dist is not None:
             dist.barrier()
             torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
 
     # ---- device-resident steps ------------------------------------------------------------------
     res = None
@@ -330,39 +395,42 @@ def main():
     t0 = time.perf_counter()
     ms_kernel = ms_stage = ms_ingest = ms_emit = 0.0
     for _ in range(args.steps):
-        res = ctx.encode_batch(*dev_arrays)
+        res = ctx.encode_batch(*dev_arrays)  # synchronous: returns when the step's kernels have finished
         ms_kernel += res.ms_kernel
         ms_stage += res.ms_encode
         ms_ingest += res.ms_ingest
         ms_emit += res.ms_emit
+    torch.cuda.synchronize()
+    own = time.perf_counter() - t0   # this rank's K steps; the closing barrier is not part of anybody's time
     barrier()
-    elapsed = time.perf_counter() - t0
+    elapsed = max_over_ranks(own)
     clk = clocks.stop() if clocks else None
     A, n_out = int(res.aligned_bases), int(res.n_out_ops)
-    t = torch.tensor([elapsed, float(A)], dtype=torch.float64, device=dev)
+    # outputs "gathered in input order": per rank (records, output ops, a checksum of the output words), rank = range order
+    ops_ptr, _, _ = ctx.result_device_ptrs()
+    out_sum = int(torch.as_tensor(DevArray(ops_ptr, n_out), device=dev).sum().item()) if n_out else 0
+    mine = torch.tensor([float(A), float(R), float(n_out), float(out_sum % (1 << 52)), float(my_range[0]), float(my_range[1])], dtype=torch.float64, device=dev)
     if dist is not None:
-        tmax = t.clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        elapsed, A_total = tmax[0].item(), t[1].item()
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
     else:
-        A_total = float(A)
+        allr = [mine]
+    shards = [{"rank": i, "records": [int(t[4].item()), int(t[5].item())], "aligned_bp": int(t[0].item()), "output_ops": int(t[2].item()),
+               "output_checksum": int(t[3].item())} for i, t in enumerate(allr)]
+    A_total = float(sum(sh["aligned_bp"] for sh in shards))
     value = A_total * args.steps / elapsed
 
     # ---- end to end through the host C ABI ----------------------------------------------------------
     # The batch lives in pinned host memory; every step copies it to the device, runs ingest + encode + device
     # serialiser and copies the finished PAF text back to pinned host memory. The records are cut into sub-batches
-    # that are dealt to a few contexts (one host thread and one stream each, same GPU) so that the H2D copy of one
-    # sub-batch, the kernels of another and the D2H copy of a third overlap; nothing else differs from one big call.
+    # that are dealt to a few SIBLING contexts (own stream and buffers, the packed genome shared) so that the H2D copy
+    # of one sub-batch, the kernels of another and the D2H copy of a third overlap.
     e2e = None
+    pre_b = pre_o = None
+    soa_md5 = None
     if not args.no_e2e:
         from concurrent.futures import ThreadPoolExecutor
-        ctxs = [ctx]
-        for _ in range(max(1, args.e2e_contexts) - 1):
-            c2 = paffy_b200.Context(local)
-            synth.build_workload(c2, args.workload, dev, scale=args.scale, rank=rank)  # same genome in every context
-            ctxs.append(c2)
-        torch.cuda.synchronize()
+        ctxs = [ctx] + [ctx.sibling() for _ in range(max(1, args.e2e_contexts) - 1)]
         host = [a.cpu() for a in dev_arrays]
         pre_b, pre_o = render_prefixes(rec)
         ob = host[0].numpy()
@@ -381,7 +449,7 @@ def main():
             po = torch.from_numpy((pre_o[r0:r1 + 1] - pre_o[r0]).copy()).pin_memory()
             nps = [a.numpy() for a in arrs]
             nps[1] = nps[1].view(np.uint64)
-            subs.append({"arrs": arrs, "np": nps, "pb": pb, "po": po, "out": None})
+            subs.append({"arrs": arrs, "np": nps, "pb": pb, "po": po, "out": None, "n": 0})
             h2d += sum(a.numel() * a.element_size() for a in arrs) + pb.numel() + po.numel() * 8
 
         stage_s = [0.0, 0.0, 0.0]
@@ -397,11 +465,12 @@ def main():
             if sb["out"] is None or sb["out"].numel() < nbytes:
                 sb["out"] = torch.empty(int(nbytes * 1.05) + 64, dtype=torch.uint8).pin_memory()
             c.fetch_text(pinned=sb["out"].numpy(), want_lines=False)
+            sb["n"] = nbytes
             stage_s[2] += time.perf_counter() - t_c
             return nbytes
 
-        def worker(c, mine, n_steps):
-            return sum(run_sub(c, sb) for _ in range(n_steps) for sb in mine)
+        def worker(c, mine_, n_steps):
+            return sum(run_sub(c, sb) for _ in range(n_steps) for sb in mine_)
 
         pool = ThreadPoolExecutor(len(ctxs))
 
@@ -416,16 +485,19 @@ def main():
         stage_s[:] = [0.0, 0.0, 0.0]
         t0 = time.perf_counter()
         d2h = e2e_steps(args.steps)
+        own = time.perf_counter() - t0
         barrier()
-        el = time.perf_counter() - t0
-        if dist is not None:
-            tt = torch.tensor([el], dtype=torch.float64, device=dev)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            el = tt.item()
+        el = max_over_ranks(own)
+        if world == 1:
+            import hashlib
+            h = hashlib.md5()
+            for sb in subs:
+                h.update(sb["out"].numpy()[:sb["n"]].tobytes())
+            soa_md5 = h.hexdigest()
         e2e = {"value": A_total * args.steps / el, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * el / args.steps,
-               "output": "serialised PAF text (device serialiser) copied to pinned host memory",
-               "pipeline": f"{len(subs)} sub-batches per step dealt round-robin to {len(ctxs)} contexts / host threads on the same GPU; the K steps stream back to back, all of them inside the timed region",
+               "what": "pafgpu_encode_batch_host + pafgpu_serialise + pafgpu_fetch_text on parsed SoA arrays and host-rendered line heads in pinned memory",
+               "pipeline": f"{len(subs)} sub-batches per step dealt round-robin to {len(ctxs)} sibling contexts (one stream each, ONE packed genome) on the GPU; the K steps stream back to back, all of them inside the timed region",
                "host": {"cpus_visible": len(os.sched_getaffinity(0)), "affinity": affinity},
                "gpu_launches_per_step": KERNELS_PER_E2E_SUBBATCH * len(subs),
                "host_wall_ms_per_step_summed_over_threads": {"encode_batch_host": 1e3 * stage_s[0] / args.steps,
@@ -434,8 +506,58 @@ def main():
         pool.shutdown()
         for c2 in ctxs[1:]:
             c2.close()
-        # restore the whole batch as the library's last batch (the roofline section below re-reads its result)
-        res = ctx.encode_batch(*dev_arrays)
+        del subs
+
+    # ---- end to end through the reference's own interface: PAF file in, PAF file out ---------------------------------
+    # `paffy add_mismatches -i in.paf -o out.paf` with the FASTA already packed (its load is reported beside it): the text
+    # is read in chunks, parsed, encoded and rendered on the device, written in input order (pafgpu_add_mismatches_file,
+    # what paffy_add_mismatches_main runs). Files live in tmpfs. At N > 1 rank 0 drives all N GPUs of the box from one
+    # process (the product's multi-GPU path) on the first million records of the job; the other ranks wait.
+    e2e_file = None
+    if not args.no_e2e_file:
+        barrier()
+        if rank == 0:
+            try:
+                base = "/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir()
+                d = tempfile.mkdtemp(prefix="paffy_b200_bench_", dir=base)
+                sub = synth.shard(rec, 0, min(R, 1_000_000)) if R > 1_000_000 else rec
+                if pre_b is None or sub is not rec:
+                    pre_b2, pre_o2 = render_prefixes(sub)
+                else:
+                    pre_b2, pre_o2 = pre_b, pre_o
+                text = make_input_text(ctx, sub, pre_b2, pre_o2)
+                fin, fout = os.path.join(d, "in.paf"), os.path.join(d, "out.paf")
+                text.tofile(fin)
+                A_file = int(sub["sum_m"].sum().item())
+                del text
+                rep = None
+                for _ in range(2):
+                    rc, rep = ctx.add_mismatches_file(fin, fout, gpus=world, streams=args.file_streams)
+                    assert rc == 0, ctx.last_error()
+                k_file = max(2, min(args.steps, 5))
+                t0 = time.perf_counter()
+                for _ in range(k_file):
+                    rc, rep = ctx.add_mismatches_file(fin, fout, gpus=world, streams=args.file_streams)
+                el = (time.perf_counter() - t0) / k_file
+                out_md5 = md5_file(fout)
+                e2e_file = {"value": A_file / el, "unit": UNIT, "s_per_pass": el, "passes": k_file, "records": int(sub["n"]),
+                            "aligned_bp": A_file, "input_bytes": os.path.getsize(fin), "output_bytes": os.path.getsize(fout),
+                            "h2d_bytes_per_step": os.path.getsize(fin), "d2h_bytes_per_step": os.path.getsize(fout),
+                            "gpus": int(rep.gpus), "workers": int(rep.workers), "chunks": int(rep.chunks),
+                            "stage_s_summed_over_workers": {"read": rep.s_read, "gpu": rep.s_gpu, "write": rep.s_write},
+                            "what": "pafgpu_add_mismatches_file (the record loop of paffy_add_mismatches_main): PAF text file in tmpfs -> PAF text file in tmpfs, "
+                                    "text parsed and rendered on the device; genome already packed in HBM",
+                            "output_md5": out_md5,
+                            "equals_soa_path_output": (out_md5 == soa_md5) if (soa_md5 and sub is rec) else None}
+                for f in (fin, fout):
+                    os.unlink(f)
+                os.rmdir(d)
+            except Exception as e:  # noqa: BLE001 - the extra figure must not take the bench line down
+                e2e_file = {"error": repr(e)[:300]}
+        barrier()
+
+    # restore the whole batch as the library's last batch (the roofline section below re-reads its result)
+    res = ctx.encode_batch(*dev_arrays)
 
     # ---- roofline of the dominant kernel ---------------------------------------------------------------
     peak, peak_src = peaks()
@@ -454,7 +576,10 @@ def main():
     tr = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr):
         try:
-            roofline["traffic"] = json.load(open(tr)).get(args.workload)
+            t = json.load(open(tr)).get(args.workload)
+            if t:
+                roofline["traffic"] = t["bytes"] if isinstance(t, dict) else t
+                roofline["traffic_source"] = t.get("source") if isinstance(t, dict) else "ncu --set full capture under profiles/ (see profiles/traffic.json)"
         except Exception:
             pass
 
@@ -462,13 +587,13 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
-        d, fa, paf, _ = cpu_sample(args.workload, args.scale, args.cpu_sample, dev)
+        d, fa, paf, _ = cpu_sample(args.workload, args.scale, args.cpu_sample, dev, args.cpu_contigs)
         out = run_reference(fa, paf, cores, 2)
         if out is not None:
             r = out["reps"][-1]
             one = run_reference(fa, paf, 1, 1)["reps"][0] if cores > 1 else r
             cpu = {"value": r["aligned_bp"] / r["encode_s"], "unit": UNIT, "cores": cores, "kind": "reference",
-                   "sample": f"{r['records']} records of {args.workload}'s generator on contig pairs t1/q1 (+) and t2/q2 (-), {r['aligned_bp']} aligned bp; "
+                   "sample": f"{r['records']} records of {args.workload}'s generator on {args.cpu_contigs} contig pairs (both strands), {r['aligned_bp']} aligned bp; "
                              f"unmodified paf_encode_mismatches on {cores} pthreads, FASTA load ({out['load_s']:.1f} s) and PAF parse ({r['parse_s']:.2f} s) excluded",
                    "single_thread_value": one["aligned_bp"] / one["encode_s"], "fasta_load_s": out["load_s"], "parse_s": r["parse_s"]}
             cli = run_reference_cli(fa, paf, d)
@@ -478,28 +603,39 @@ def main():
                 if cli.get("parallel_wall_s"):
                     cli["parallel_bp_per_s_end_to_end"] = r["aligned_bp"] / cli["parallel_wall_s"]
                 cli["what"] = ("reference CLI `paffy add_mismatches` file to file on the same sample (FASTA load, parse, encode, print): one process, "
-                               "then one process per `paffy split_file` shard (per target contig) run concurrently")
+                               "then one process per `paffy split_file` shard (per target contig) run concurrently, every process loading the whole FASTA")
                 cpu["reference_cli"] = cli
                 try:
-                    fp = file_parity(fa, paf, d, local)
+                    # the sample's records live on contigs of the full genome already packed in `ctx`: the byte comparison
+                    # runs against the 24-contig arena, not a genome of the sample's contigs alone
+                    fp = file_parity(fa, paf, d, ctx)
                 except Exception as e:  # the checker must not take the bench line down
                     fp = {"error": repr(e)}
                 if fp:
                     parity["reference_cli"] = fp
+                    for k in ("add_bytes_equal", "trim_bytes_equal", "view_summary_equal"):
+                        cpu["parity_" + k] = fp.get(k)
 
     if rank == 0:
+        wl = synth.CONFIGS[args.workload]
+        config = {"workload": f"{args.workload}: {wl[0]}x{wl[1]} bp target+query genomes, {job_records} records in the job"
+                              + (f", sharded over {world} GPUs by aligned bases (contiguous ranges, pafgpu_partition)" if strong else f", {R} records/GPU")
+                              + f", scale {args.scale}",
+                  "records_this_rank": int(R), "input_ops": int(N), "output_ops": n_out,
+                  "aligned_bp_per_step_this_rank": A, "aligned_bp_per_step_all_ranks": int(A_total),
+                  "sharding": ("ONE record list cut into contiguous ranges of near-equal aligned bases, one range per rank" if strong
+                               else "one record list per rank") + "; packed genome replicated; no data-path collective (outputs concatenate in rank order)",
+                  "shards": shards,
+                  "l2": "inputs larger than L2 (packed genome 1.5 GB + op arrays); no flush needed",
+                  "timing": "K synchronous steps; every rank times its own K steps between the opening barrier and its own last synchronize, the maximum over ranks is taken",
+                  "parity_generator_truth": parity["mismatch_counts_equal"] and parity["output_op_counts_equal"]}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "u8", "data": "synthetic",
-                "config": {"workload": f"{args.workload}: {synth.CONFIGS[args.workload][0]}x{synth.CONFIGS[args.workload][1]} bp target+query genomes, "
-                                       f"{R} records/GPU, scale {args.scale}", "records_per_gpu": int(R), "input_ops": int(N), "output_ops": n_out,
-                           "aligned_bp_per_step_per_gpu": A, "sharding": "records sharded by rank, packed genome replicated, no collective",
-                           "l2": "inputs larger than L2 (packed genome 1.5 GB + op arrays); no flush needed",
-                           "timing": "K synchronous steps between barrier+synchronize; per-stage CUDA events inside the library"},
+                "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
+                "dtype": "u8", "data": "synthetic", "config": config,
                 "device_ms": {"ingest": ms_ingest / args.steps, "encode_stage": ms_stage / args.steps, "encode_kernel": k_ms,
                               "stitch_kernel": ms_emit / args.steps, "retried": int(res.retried)},
-                "gpu_launches": KERNELS_PER_STEP * args.steps, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clk,
-                "parity": parity, "gen_s": t_gen}
+                "gpu_launches": KERNELS_PER_STEP * args.steps, "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_file": e2e_file,
+                "clocks": clk, "parity": parity, "gen_s": t_gen}
         print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()

@@ -187,6 +187,16 @@ int pafgpu_encode_one(pafgpu_ctx *ctx, const uint64_t *ops, int64_t n_ops, int s
                       int64_t query_end, int64_t target_start, const char *query_seq, const char *target_seq,
                       uint64_t **out_ops, int64_t *n_out, int64_t *mismatches);
 
+/* The same for a record whose contigs are already packed in the context's genome (ids from pafgpu_genome_add_contig /
+ * pafgpu_genome_find): nothing but the record travels. This is what paf_encode_mismatches does after the first call with
+ * a given sequence pointer. */
+int pafgpu_encode_one_resident(pafgpu_ctx *ctx, const uint64_t *ops, int64_t n_ops, int same_strand, int64_t query_start,
+                               int64_t query_end, int64_t target_start, int64_t q_contig, int64_t t_contig, uint64_t **out_ops,
+                               int64_t *n_out, int64_t *mismatches);
+/* Forget every contig of the genome store (the arena keeps its capacity); arena bases in use (both copies and pads). */
+int pafgpu_genome_clear(pafgpu_ctx *ctx);
+int64_t pafgpu_genome_total_bases(const pafgpu_ctx *ctx);
+
 /* Kernel self-timing for bench.py: re-run the encode stage of the last submitted batch `reps` times
  * (inputs and genome resident in HBM). ms_stage: mean CUDA-event ms of resets + kernel + stitch;
  * ms_kernel: mean CUDA-event ms of the base-comparison kernel alone. */

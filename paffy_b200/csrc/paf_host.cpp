@@ -8,6 +8,7 @@
 // paf_write_to_buffer (impl/paf.c:317-389); the trim pass (impl/paf.c:811-953) runs on the device (trim.cuh). Nothing is copied.
 // There is no CPU implementation of the base comparison here: every M op goes through the CUDA kernels.
 #include "../../include/paffy_b200.h"
+#include "../../include/paf_b200_compat.h"
 
 #include <algorithm>
 #include <atomic>
@@ -124,18 +125,26 @@ std::string parse_error(const Rec &r) {
     return buf;
 }
 
-struct Pinned {  // pinned host buffer that only grows
+struct Pinned {  // pinned host buffer that only grows (plain memory where no CUDA device exists: `add_mismatches -a`)
     void *p = nullptr;
     int64_t cap = 0;
+    bool pageable = false;
+    void release() {
+        if (p) { if (pageable) free(p); else pafgpu_host_free(p); }
+        p = nullptr;
+        cap = 0;
+    }
     bool ensure(int64_t bytes) {
         if (bytes <= cap) return true;
-        if (p) pafgpu_host_free(p);
+        release();
         cap = bytes + bytes / 4 + 4096;
         p = pafgpu_host_alloc(cap);
+        pageable = false;
+        if (!p && pafgpu_device_count() == 0) { p = malloc((size_t)cap); pageable = true; }
         if (!p) cap = 0;
         return p != nullptr;
     }
-    ~Pinned() { if (p) pafgpu_host_free(p); }
+    ~Pinned() { release(); }
     template <class T> T *as() { return static_cast<T *>(p); }
 };
 
@@ -566,7 +575,9 @@ namespace {
 
 struct ChunkIn {
     int64_t seq = 0;
-    std::vector<char> text;  // whole lines, free of '\r'
+    Pinned *buf = nullptr;   // leased from g_pinned (the device path copies straight out of it); whole lines, free of '\r'
+    size_t n = 0;
+    const char *data() const { return buf ? static_cast<const char *>(buf->p) : nullptr; }
 };
 
 // Pinned host buffers for finished output text, shared by all pipelines of the process and kept between calls (pinning
@@ -812,40 +823,53 @@ void process_chunk(Filter &F, const char *text, size_t n_text, ChunkOut &R) {
 
 // reads whole lines into chunks of about `chunk_bytes` (sonLibFile.c:42-71: '\r' dropped, a last line without '\n' counts).
 // read(2) returns what a pipe holds right now: a chunk ends at the last newline once it is full OR the pipe has run
-// dry, so a slow producer sees its first lines come out before it closes the stream.
+// dry, so a slow producer sees its first lines come out before it closes the stream. The bytes land in pinned memory.
 struct ChunkReader {
     int fd;
     size_t chunk_bytes;
     std::vector<char> carry;  // the incomplete last line of the previous read (holds no newline)
     bool eof = false;
     int64_t seq = 0;
-    // false at end of input (or read error: *failed)
+    // false at end of input (or read error / allocation failure: *failed)
     bool next(ChunkIn &c, bool *failed) {
-        c.text.clear();
+        c.n = 0;
         if (eof && carry.empty()) return false;
-        c.text.swap(carry);
+        size_t cap = std::max(chunk_bytes, carry.size()) + (1 << 16);
+        c.buf = g_pinned.get((int64_t)cap);
+        if (!c.buf) { *failed = true; return false; }
+        char *d = c.buf->as<char>();
+        size_t have = carry.size();
+        if (have) memcpy(d, carry.data(), have);
+        carry.clear();
         size_t last_nl = 0;  // one past the last newline seen
         while (!eof) {
-            const size_t have = c.text.size();
-            const size_t want = chunk_bytes > have ? chunk_bytes - have : std::max<size_t>(chunk_bytes, 256);
-            c.text.resize(have + want);
+            if (have + 4096 > cap) {  // a line longer than the chunk: grow (keeping the bytes)
+                Pinned *bigger = g_pinned.get((int64_t)(2 * cap));
+                if (!bigger) { *failed = true; g_pinned.put(c.buf); c.buf = nullptr; return false; }
+                memcpy(bigger->p, d, have);
+                g_pinned.put(c.buf);
+                c.buf = bigger;
+                d = c.buf->as<char>();
+                cap *= 2;
+            }
+            const size_t want = chunk_bytes > have ? std::min(chunk_bytes - have, cap - have) : std::min<size_t>(std::max<size_t>(chunk_bytes, 256), cap - have);
             ssize_t got;
-            do got = ::read(fd, c.text.data() + have, want); while (got < 0 && errno == EINTR);
-            if (got < 0) { *failed = true; return false; }
-            c.text.resize(have + (size_t)got);
+            do got = ::read(fd, d + have, want); while (got < 0 && errno == EINTR);
+            if (got < 0) { *failed = true; g_pinned.put(c.buf); c.buf = nullptr; return false; }
             if (got == 0) { eof = true; break; }
-            for (size_t k = c.text.size(); k > have; k--)
-                if (c.text[k - 1] == '\n') { last_nl = k; break; }
+            for (size_t k = have + (size_t)got; k > have; k--)
+                if (d[k - 1] == '\n') { last_nl = k; break; }
+            have += (size_t)got;
             // full, or the source has nothing more for now: hand over the whole lines read so far
-            if (last_nl && (c.text.size() >= chunk_bytes || (size_t)got < want)) break;
+            if (last_nl && (have >= chunk_bytes || (size_t)got < want)) break;
         }
         if (!eof) {
-            carry.assign(c.text.begin() + (ptrdiff_t)last_nl, c.text.end());
-            c.text.resize(last_nl);
+            carry.assign(d + last_nl, d + have);
+            have = last_nl;
         }
-        if (c.text.empty()) return false;
-        if (memchr(c.text.data(), '\r', c.text.size()))
-            c.text.erase(std::remove(c.text.begin(), c.text.end(), '\r'), c.text.end());  // the line reader drops '\r' (sonLibFile.c:49-51)
+        if (have == 0) { g_pinned.put(c.buf); c.buf = nullptr; return false; }
+        if (memchr(d, '\r', have)) have = (size_t)(std::remove(d, d + have, '\r') - d);  // the line reader drops '\r' (sonLibFile.c:49-51)
+        c.n = have;
         c.seq = seq++;
         return true;
     }
@@ -925,9 +949,9 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
     auto write_out = [&](const char *p, size_t n) -> bool {
         if (n == 0) return true;
         bool ok = true;
-        const size_t piece = (size_t)8 << 20;
+        const size_t piece = (size_t)4 << 20;
         if (out_regular && n >= 2 * piece) {
-            const int nt = (int)std::min<size_t>(6, n / piece);
+            const int nt = (int)std::min<size_t>((size_t)std::max(2, std::min(hw_threads() - 2, 16)), n / piece);
             std::vector<std::thread> th;
             std::atomic<bool> good{true};
             for (int t = 0; t < nt; t++)
@@ -1012,7 +1036,9 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
                     jobs.pop_front();
                 }
                 ChunkOut R;
-                process_chunk(F, c.text.data(), c.text.size(), R);
+                process_chunk(F, c.data(), c.n, R);
+                g_pinned.put(c.buf);
+                c.buf = nullptr;
                 R.ready = true;
                 std::lock_guard<std::mutex> lk(mu);
                 done.emplace(c.seq, std::move(R));
@@ -1067,6 +1093,7 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
     reader.join();
     for (auto &t : workers) t.join();
     for (auto &kv : done) g_pinned.put(kv.second.lease);  // chunks finished behind the one that ended the run
+    for (auto &c : jobs) g_pinned.put(c.buf);
     if (rc == 0 && read_failed) { rc = PAFGPU_EIO; err = "read failed"; }
     rep.s_read = s_read;
 
@@ -1089,6 +1116,47 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
 }
 
 }  // extern "C"
+
+
+// ================================================================================================
+// FASTA positionals of a subcommand -> packed genome in the context. With $PAFFY_B200_CACHE=<dir> the packed arena is
+// persisted there, keyed by the paths, sizes and modification times of the FASTA files: the next process of a pipeline
+// (tests/paf_pipeline_test.sh runs add_mismatches once per split_file shard, each re-reading both FASTA files) reads the
+// packed file at copy speed instead of parsing the FASTA again.
+namespace {
+int load_genome(pafgpu_ctx *ctx, int argc, char *argv[], int first, bool verbose) {
+    std::string key;
+    for (int i = first; i < argc; i++) {
+        struct stat st;
+        char buf[96];
+        if (stat(argv[i], &st) != 0) { key.clear(); break; }
+        snprintf(buf, sizeof buf, "|%lld|%lld.%09ld;", (long long)st.st_size, (long long)st.st_mtim.tv_sec, (long)st.st_mtim.tv_nsec);
+        key += argv[i];
+        key += buf;
+    }
+    const char *dir = getenv("PAFFY_B200_CACHE");
+    std::string cache;
+    if (dir && *dir && !key.empty()) {
+        uint64_t h = 1469598103934665603ull;
+        for (unsigned char ch : key) { h ^= ch; h *= 1099511628211ull; }
+        char name[40];
+        snprintf(name, sizeof name, "/%016llx.pafb200", (unsigned long long)h);
+        cache = std::string(dir) + name;
+        if (pafgpu_genome_load_packed(ctx, cache.c_str(), key.c_str()) == 0) {
+            if (verbose) fprintf(stderr, "Read %i packed sequences from %s\n", (int)pafgpu_genome_num_contigs(ctx), cache.c_str());
+            return 0;
+        }
+    }
+    for (int i = first; i < argc; i++) {
+        if (verbose) fprintf(stderr, "Parsing sequence file : %s\n", argv[i]);
+        if (pafgpu_genome_load_fasta(ctx, argv[i])) return 1;
+    }
+    if (verbose) fprintf(stderr, "Read %i sequences from sequence files\n", (int)pafgpu_genome_num_contigs(ctx));
+    if (!cache.empty() && pafgpu_genome_save(ctx, cache.c_str(), key.c_str()) && verbose)
+        fprintf(stderr, "could not write %s: %s\n", cache.c_str(), pafgpu_last_error(ctx));
+    return 0;
+}
+}  // namespace
 
 // ================================================================================================
 // Drop-in subcommand entry point (impl/paf_add_mismatches.c:26-160).
@@ -1132,16 +1200,11 @@ extern "C" int paffy_add_mismatches_main(int argc, char *argv[]) {
         fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(nullptr));
         exit(1);
     }
-    while (optind < argc) {
-        const char *fa = argv[optind++];
-        if (verbose) fprintf(stderr, "Parsing sequence file : %s\n", fa);
-        if (ctx && pafgpu_genome_load_fasta(ctx, fa)) {
-            fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
-            exit(1);
-        }
+    if (ctx && load_genome(ctx, argc, argv, optind, verbose)) {
+        fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
+        exit(1);
     }
-    if (verbose && ctx) fprintf(stderr, "Read %i sequences from sequence files\n", (int)pafgpu_genome_num_contigs(ctx));
-    pafgpu_file_opts o{remove ? PAFGPU_MODE_REMOVE : PAFGPU_MODE_ADD, 0.05f, 1.0f, 0, 0};
+    pafgpu_file_opts o{remove ? PAFGPU_MODE_REMOVE : PAFGPU_MODE_ADD, 0.05f, 1.0f, 0, 0, 0, 0, 0};
     pafgpu_file_report rep;
     const int rc = pafgpu_add_mismatches_file(ctx, input, output, &o, &rep);
     if (rc < 0) fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
@@ -1154,12 +1217,82 @@ extern "C" int paffy_add_mismatches_main(int argc, char *argv[]) {
 // ================================================================================================
 // Drop-in subcommand entry point `paffy view` (impl/paf_view.c:39-215).
 namespace {
+// FASTA file -> name -> sequence bytes as they stand in the file (fastaReadToFunction's rules, bioioC.c:155-209: the header
+// is the whole line, '>' anywhere ends a record, newline / space / tab are dropped, any other byte must be a letter or
+// '-', a repeated name replaces the earlier sequence). Only `view -a` needs the bytes on the host.
+bool read_fasta_host(const char *path, std::map<std::string, std::string> &seqs) {
+    FILE *fh = fopen(path, "rb");
+    if (!fh) { fprintf(stderr, "ERROR: cannot open %s\n", path); return false; }
+    std::string all;
+    char tmp[1 << 16];
+    size_t got;
+    while ((got = fread(tmp, 1, sizeof tmp, fh)) > 0) all.append(tmp, got);
+    fclose(fh);
+    size_t p = all.find('>');
+    while (p != std::string::npos) {
+        const size_t nl = all.find('\n', p + 1);
+        const std::string name = all.substr(p + 1, nl == std::string::npos ? std::string::npos : nl - p - 1);
+        const size_t b = nl == std::string::npos ? all.size() : nl + 1;
+        const size_t nx = all.find('>', b);
+        const size_t e = nx == std::string::npos ? all.size() : nx;
+        std::string seq;
+        seq.reserve(e - b);
+        for (size_t i = b; i < e; i++) {
+            const unsigned char ch = (unsigned char)all[i];
+            if (ch == '\n' || ch == ' ' || ch == '\t') continue;
+            if (!((ch >= 'A' && ch <= 'Z') || (ch >= 'a' && ch <= 'z') || ch == '-')) {
+                fprintf(stderr, "ERROR: !!Got an unexpected character in input fasta sequence: '%c' \n", ch);
+                return false;
+            }
+            seq.push_back((char)ch);
+        }
+        seqs[name] = std::move(seq);
+        p = nx;
+    }
+    return true;
+}
+
+// the record loop of paffy_view_main with -a (impl/paf_view.c:151-183) on the paf.h surface; totals as -s accumulates them
+int view_with_alignment(int argc, char *argv[], int first_fasta, const char *input, const char *output, bool aggregate, bool verbose,
+                        int64_t *totals) {
+    std::map<std::string, std::string> seqs;
+    for (int i = first_fasta; i < argc; i++) {
+        if (verbose) fprintf(stderr, "Parsing sequence file : %s\n", argv[i]);
+        if (!read_fasta_host(argv[i], seqs)) return 1;
+    }
+    FILE *fin = input ? fopen(input, "r") : stdin, *fout = output ? fopen(output, "w") : stdout;
+    if (!fin || !fout) { fprintf(stderr, "ERROR: cannot open %s\n", !fin ? input : output); return 1; }
+    int64_t cap = 100;
+    char *line = (char *)malloc((size_t)cap);
+    for (Paf *paf; (paf = paf_read_with_buffer(fin, true, &line, &cap)) != nullptr;) {
+        auto q = seqs.find(paf->query_name), t = seqs.find(paf->target_name);
+        if (q == seqs.end()) { fprintf(stderr, "No query sequence named: %s found\n", paf->query_name); exit(1); }
+        if (t == seqs.end()) { fprintf(stderr, "No target sequence named: %s found\n", paf->target_name); exit(1); }
+        paf_encode_mismatches(paf, &q->second[0], &t->second[0]);
+        paf_pretty_print(paf, &q->second[0], &t->second[0], fout, true);
+        if (aggregate) {
+            paf_stats_calc(paf, &totals[0], &totals[1], &totals[2], &totals[3], &totals[4], &totals[5], false);
+            totals[6]++;
+        }
+        paf_destruct(paf);
+    }
+    free(line);
+    if (aggregate)
+        fprintf(fout, "Total-alignments:%lld\tAvg-Identity:%f\tAvg-Identity-with-gaps:%f\tAligned-bases:%lld\tAligned-bases-with-gaps:%lld\t"
+                      "Query-inserts:%lld\tQuery-deletes:%lld\n",
+                (long long)totals[6], (float)totals[0] / (totals[0] + totals[1]), (float)totals[0] / (totals[0] + totals[1] + totals[4] + totals[5]),
+                (long long)(totals[0] + totals[1]), (long long)(totals[0] + totals[1] + totals[4] + totals[5]), (long long)totals[2], (long long)totals[3]);
+    if (input) fclose(fin);
+    if (output) fclose(fout); else fflush(fout);
+    return 0;
+}
+
 void view_usage() {
     fprintf(stderr, "paffy view [fasta_files]xN [options], version 0.1 (paffy_b200: CUDA sm_100a path)\n");
     fprintf(stderr, "Pretty print PAF alignments\n");
     fprintf(stderr, "-i --inputFile : Input paf file to invert. If not specified reads from stdin\n");
     fprintf(stderr, "-o --outputFile : Output paf file. If not specified outputs to stdout\n");
-    fprintf(stderr, "-a --includeAlignment : Include base level alignment in output (not available on the CUDA path)\n");
+    fprintf(stderr, "-a --includeAlignment : Include base level alignment in output\n");
     fprintf(stderr, "-s --printAggregateStats : Print overall stats about the alignments at the end\n");
     fprintf(stderr, "-t --noPerAlignmentStats : Do not print stats about each paf\n");
     fprintf(stderr, "-u --errorIfIdentityLowerThanX : Float between 0 and 1. Assert identity is >= X.\n");
@@ -1206,37 +1339,37 @@ extern "C" int paffy_view_main(int argc, char *argv[]) {
         fprintf(stderr, "Expected at least one sequence file\n");
         exit(1);
     }
-    if (include_alignment) {
-        fprintf(stderr, "ERROR: paffy view -a (base-level alignment text) is not available on the CUDA path\n");
-        exit(1);
-    }
     const bool verbose = log_level && (!strcasecmp(log_level, "INFO") || !strcasecmp(log_level, "DEBUG"));
     const double t0 = now_s();
-    pafgpu_ctx *ctx = nullptr;
-    const char *dev = getenv("PAFFY_B200_DEVICE");
-    if (pafgpu_create(dev ? atoi(dev) : 0, &ctx)) {
-        fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(nullptr));
-        exit(1);
-    }
-    while (optind < argc) {
-        const char *fa = argv[optind++];
-        if (verbose) fprintf(stderr, "Parsing sequence file : %s\n", fa);
-        if (pafgpu_genome_load_fasta(ctx, fa)) {
+    pafgpu_file_report rep{};
+    if (include_alignment && per_alignment) {
+        // -a prints the ORIGINAL bytes of both sequences (case kept) beside every record: the record loop of the reference
+        // (impl/paf_view.c:151-183) over the paf.h surface - paf_encode_mismatches still compares the bases on the GPU,
+        // against whole contigs that stay packed in HBM between records (paf_compat.cpp)
+        if (view_with_alignment(argc, argv, optind, input, output, aggregate, verbose, rep.stats)) exit(1);
+    } else {
+        pafgpu_ctx *ctx = nullptr;
+        const char *dev = getenv("PAFFY_B200_DEVICE");
+        if (pafgpu_create(dev ? atoi(dev) : 0, &ctx)) {
+            fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(nullptr));
+            exit(1);
+        }
+        if (load_genome(ctx, argc, argv, optind, verbose)) {
             fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
             exit(1);
         }
+        pafgpu_file_opts o{PAFGPU_MODE_VIEW | (per_alignment ? PAFGPU_VIEW_PER_ALIGNMENT : 0) | (aggregate ? PAFGPU_VIEW_AGGREGATE : 0),
+                           0.05f, 1.0f, 0, 0, 0, 0, 0};
+        const int rc = pafgpu_add_mismatches_file(ctx, input, output, &o, &rep);
+        if (rc < 0) fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
+        pafgpu_destroy(ctx);
+        if (rc) exit(1);
     }
-    if (verbose) fprintf(stderr, "Read %i sequences from sequence files\n", (int)pafgpu_genome_num_contigs(ctx));
-    pafgpu_file_opts o{PAFGPU_MODE_VIEW | (per_alignment ? PAFGPU_VIEW_PER_ALIGNMENT : 0) | (aggregate ? PAFGPU_VIEW_AGGREGATE : 0),
-                       0.05f, 1.0f, 0, 0};
-    pafgpu_file_report rep;
-    const int rc = pafgpu_add_mismatches_file(ctx, input, output, &o, &rep);
-    if (rc < 0) fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(ctx));
-    pafgpu_destroy(ctx);
-    if (rc) exit(1);
-    // the reference's closing asserts (impl/paf_view.c:195-196; asserts are compiled in, include.mk:32). They look at the
-    // totals whether or not -s was given.
-    const int64_t *t = rep.stats;
+    // the reference's closing asserts (impl/paf_view.c:195-196; asserts are compiled in, include.mk:32). The totals they
+    // test are only accumulated under -s (:176-178): without it they see 0 / 0 = NaN, the first assert fires and the
+    // reference aborts (exit 134) - here as well, after the output has been written.
+    int64_t zero[7] = {0, 0, 0, 0, 0, 0, 0};
+    const int64_t *t = aggregate ? rep.stats : zero;
     if (!((float)t[0] / (t[0] + t[1]) >= min_identity)) {
         fprintf(stderr, "paffy view: Assertion `(float)total_matches/(total_matches+total_mismatches) >= error_if_identity_lower_than_this' failed.\n");
         abort();
@@ -1302,7 +1435,7 @@ extern "C" int paffy_trim_main(int argc, char *argv[]) {
         fprintf(stderr, "ERROR: %s\n", pafgpu_last_error(nullptr));
         exit(1);
     }
-    pafgpu_file_opts o{PAFGPU_MODE_TRIM, trim_by_identity ? trim_by_identity_fraction : -1.0f, trim_end_fraction, 0, 0};
+    pafgpu_file_opts o{PAFGPU_MODE_TRIM, trim_by_identity ? trim_by_identity_fraction : -1.0f, trim_end_fraction, 0, 0, 0, 0, 0};
     if (trim_by_identity && trim_by_identity_fraction < 0) {  // the option's documented range is 0..1; < 0 is the -f switch in the ABI
         fprintf(stderr, "ERROR: paffy trim -r must be >= 0\n");
         exit(1);

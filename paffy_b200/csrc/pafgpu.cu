@@ -441,6 +441,7 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
 
     EncodeParams &P = c->last;
     P.G = g.view();
+    P.arena_words = (uint64_t)(g.cap_bases / 32 + 4);
     P.ops = b->ops; P.woff = c->woff.as<uint64_t>(); P.tpos = c->tpos.as<uint64_t>(); P.qpos = c->qpos.as<uint64_t>();
     P.op_rec = c->op_rec.as<uint32_t>(); P.tile_first_op = c->tile_first_op.as<uint32_t>();
     P.n_ops = N; P.n_win = n_win; P.n_tiles = n_tiles;
@@ -1273,6 +1274,54 @@ extern "C" int pafgpu_add_mismatches_text(pafgpu_ctx *c, const char *text, int64
 }
 
 extern "C" {
+
+// One record against contigs that are already packed in the context's genome (the cache behind paf_encode_mismatches):
+// a batch of one through the normal path. out_ops is malloc'd (caller frees).
+int pafgpu_encode_one_resident(pafgpu_ctx *c, const uint64_t *ops, int64_t n_ops, int same_strand, int64_t query_start, int64_t query_end,
+                               int64_t target_start, int64_t q_contig, int64_t t_contig, uint64_t **out_ops, int64_t *n_out, int64_t *mismatches) {
+    if (!c || !ops || n_ops < 0 || !out_ops || !n_out) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    std::vector<uint64_t> kept;
+    kept.reserve((size_t)n_ops);
+    for (int64_t k = 0; k < n_ops; k++)
+        if (!((int)(ops[k] >> 56) == OP_M && (ops[k] & LEN_MASK) == 0)) kept.push_back(ops[k]);  // zero-length M ops vanish (a1-edge ii)
+    *out_ops = nullptr;
+    *n_out = 0;
+    if (mismatches) *mismatches = 0;
+    if (kept.empty()) { *out_ops = (uint64_t *)malloc(8); return 0; }
+    const int64_t op_begin[2] = {0, (int64_t)kept.size()};
+    const int32_t qc = (int32_t)q_contig, tc = (int32_t)t_contig;
+    const uint8_t strand = same_strand ? 1 : 0;
+    pafgpu_batch b{1, (int64_t)kept.size(), op_begin, kept.data(), &qc, &tc, &query_start, &query_end, &target_start, &strand};
+    pafgpu_result res;
+    if (int rc = encode_host(c, c->G(), &b, &res)) return rc;
+    uint64_t *o = (uint64_t *)malloc((size_t)std::max<int64_t>(res.n_out_ops, 1) * 8);
+    int64_t mm = 0;
+    if (int rc = fetch_ops(c, o, nullptr, &mm)) { free(o); return rc; }
+    *out_ops = o;
+    *n_out = res.n_out_ops;
+    if (mismatches) *mismatches = mm;
+    return 0;
+}
+
+// forget every contig (the arena keeps its capacity)
+int pafgpu_genome_clear(pafgpu_ctx *c) {
+    if (!c) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    CU(cudaSetDevice(c->device));
+    CU(stream_sync(c));
+    GenomeStore &g = c->G();
+    g.reset();
+    g.generation++;
+    if (g.words.p) CU(cudaMemsetAsync(g.words.p, 0, g.words.cap, c->stream));
+    if (g.flags.p) CU(cudaMemsetAsync(g.flags.p, 0, g.flags.cap, c->stream));
+    if (g.rank.p) CU(cudaMemsetAsync(g.rank.p, 0, g.rank.cap, c->stream));
+    CU(stream_sync(c));
+    return 0;
+}
+
+int64_t pafgpu_genome_total_bases(const pafgpu_ctx *c) { return c ? c->G().next_off : PAFGPU_EINVAL; }
 
 // ---- device trim (paf_trim_unreliable_tails, impl/paf.c:906-953) -------------------------------------
 static int trim_batch(pafgpu_ctx *c, bool fixed, float score_fraction, float max_fraction, const int64_t *t_end, int64_t *coords,

@@ -22,7 +22,7 @@ ABI_SYMBOLS = [
     "pafgpu_serialise", "pafgpu_fetch_text", "pafgpu_encode_one", "pafgpu_time_encode",
     "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition", "pafgpu_trim",
     "pafgpu_trim_fixed", "pafgpu_stage_ops_host", "pafgpu_add_mismatches_file_filtered",
-    "pafgpu_add_mismatches_text", "pafgpu_create_sibling", "pafgpu_helper", "pafgpu_device_of", "pafgpu_genome_clone", "pafgpu_genome_save", "pafgpu_genome_load_packed",
+    "pafgpu_add_mismatches_text", "pafgpu_create_sibling", "pafgpu_helper", "pafgpu_encode_one_resident", "pafgpu_genome_clear", "pafgpu_genome_total_bases", "pafgpu_device_of", "pafgpu_genome_clone", "pafgpu_genome_save", "pafgpu_genome_load_packed",
 ]
 # reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
 REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paffy_view_main", "paffy_trim_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
@@ -277,6 +277,12 @@ class Context:
         mism = np.empty(R, dtype=np.int64)
         self._check(self.L.pafgpu_fetch_ops(self.h, _ptr(ops) if want_ops else None, begin.ctypes.data, mism.ctypes.data))
         return ops, begin, mism
+
+    def result_device_ptrs(self):
+        """-> raw device pointers (output ops uint64[n_out], out_op_begin int64[R+1], rec_mismatch int64[R]) of the last batch."""
+        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self._check(self.L.pafgpu_result_device_ptrs(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
 
     def time_encode(self, reps):
         stage, kernel = C.c_float(), C.c_float()

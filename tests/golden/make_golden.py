@@ -21,6 +21,7 @@ Fixtures
   *.filter_{u,vx,t}.paf    `paffy add_mismatches ... | paffy filter -u 0.5`, `... -v 0.4 -x`, `... -t 1 -s -1 -w 3`
   *.view.txt               `paffy add_mismatches ... | paffy view -s -t X.fa` summary line
   *.viewlines.txt          `paffy view -s X.fa -i X.paf` on the raw input: per-alignment stats lines + summary line
+  *.viewa.txt              `paffy view -a -s X.fa -i X.paf`: the base-level alignment blocks (original-case bytes) as well
   errors.json              exit code / stdout / stderr head of the failing-record cases
   c1_human_chimp.paf.gz    the reference's own fixture tests/human_chimp.paf (data, gzip'd; config C1)
   c1.json                  size + md5 of the reference outputs for C1 with the seeded synthetic chr10
@@ -92,6 +93,7 @@ def pipeline(stem, fa_path, paf_bytes):
     write(stem + ".filter_t.paf", must(["filter", "-t", "1", "-s", "-1", "-w", "3"], add))
     # view on the raw (M) input: per-alignment lines + the summary line, i.e. paffy_view_main's own encode
     write(stem + ".viewlines.txt", must(["view", "-s", fa_path], paf_bytes))
+    write(stem + ".viewa.txt", must(["view", "-a", "-s", fa_path], paf_bytes))
 
 
 def fasta_bytes(contigs, width=60):

@@ -137,8 +137,10 @@ def test_view_cli_drop_in(tmp_path):
     assert r.returncode == 1 and b"Expected at least one sequence file" in r.stderr
     r = subprocess.run([exe, "view", "-t", "-u", "0.999999", fa, "-i", paf], capture_output=True)
     assert r.returncode == -6 and r.stdout == b""  # the reference's closing assert aborts (impl/paf_view.c:195)
+    r = subprocess.run([exe, "view", "-s", "-t", "-u", "0.1", "-v", "10", fa, "-i", paf], capture_output=True)
+    assert r.returncode == 0 and r.stdout == golden("rand102.view.txt")
     r = subprocess.run([exe, "view", "-t", "-u", "0.1", "-v", "10", fa, "-i", paf], capture_output=True)
-    assert r.returncode == 0 and r.stdout == b""
+    assert r.returncode == -6  # without -s the totals stay 0: NaN fails the assert, as in the reference
     r = subprocess.run([exe, "view", os.path.join(G, "edge.fa"), "-i", "/dev/stdin"], capture_output=True,
                        input=b"q\t25\t0\t25\t+\tt\t25\t0\t25\t0\t25\t60\tcg:Z:25M\nq\t25\t0\t25\t+\tnope\t25\t0\t25\t0\t25\t60\tcg:Z:25M\n")
     assert r.returncode == 1 and b"No target sequence named: nope found" in r.stderr and r.stdout.count(b"\n") == 1
@@ -523,3 +525,51 @@ def test_device_text_path_locates_the_record_the_reference_aborts_on(fresh, tmp_
         assert got[False][3].count(b"\n") == 57
         assert got[False][:4] == got[True][:4], bad
         assert got[False][4] == got[True][4], (bad, got[False][4], got[True][4])
+
+
+# ---- round 2: view -a, the closing asserts of view, the persisted genome behind the CLI ---------------------------------
+CLI = os.path.join(os.path.dirname(paffy_b200.lib.LIB_PATH), "paffy_b200_cli")
+
+
+@pytest.mark.parametrize("stem", SETS)
+def test_view_with_alignment_matches_reference(stem, tmp_path):
+    """`paffy view -a -s`: per-alignment lines, the three-row alignment blocks in the FASTA's original case, the aggregate
+    line - byte-equal to the compiled reference's output."""
+    fa, paf = os.path.join(G, stem + ".fa"), os.path.join(G, stem + ".paf")
+    r = subprocess.run([CLI, "view", "-a", "-s", fa, "-i", paf], capture_output=True)
+    assert r.returncode == 0, r.stderr[-500:]
+    assert r.stdout == golden(stem + ".viewa.txt")
+    out = tmp_path / "o.txt"
+    r = subprocess.run([CLI, "view", "-a", "-s", fa, "-i", paf, "-o", str(out)], capture_output=True)
+    assert r.returncode == 0 and out.read_bytes() == golden(stem + ".viewa.txt")
+
+
+def test_view_without_aggregate_stats_aborts_like_the_reference():
+    """impl/paf_view.c:195: the totals are only accumulated under -s; without it the identity assert sees NaN and the
+    reference aborts. Same exit (SIGABRT) here."""
+    fa, paf = os.path.join(G, "edge.fa"), os.path.join(G, "edge.add.paf")
+    r = subprocess.run([CLI, "view", fa, "-i", paf], capture_output=True)
+    assert r.returncode == -6 and b"Assertion" in r.stderr
+    r = subprocess.run([CLI, "view", "-s", fa, "-i", paf], capture_output=True)
+    assert r.returncode == 0
+
+
+def test_cli_uses_the_packed_genome_cache(tmp_path):
+    """$PAFFY_B200_CACHE: the first run parses the FASTA and leaves the packed arena, the second one loads it; a FASTA whose
+    size / mtime changed is parsed again. Same bytes out every time."""
+    import shutil
+    cache = tmp_path / "cache"
+    cache.mkdir()
+    fa = tmp_path / "g.fa"
+    shutil.copy(os.path.join(G, "rand101.fa"), fa)
+    env = dict(os.environ, PAFFY_B200_CACHE=str(cache))
+    args = [CLI, "add_mismatches", str(fa), "-i", os.path.join(G, "rand101.paf"), "-l", "INFO"]
+    r1 = subprocess.run(args, capture_output=True, env=env)
+    assert r1.returncode == 0 and r1.stdout == golden("rand101.add.paf") and b"Parsing sequence file" in r1.stderr
+    assert len(list(cache.iterdir())) == 1
+    r2 = subprocess.run(args, capture_output=True, env=env)
+    assert r2.returncode == 0 and r2.stdout == golden("rand101.add.paf")
+    assert b"packed sequences" in r2.stderr and b"Parsing sequence file" not in r2.stderr
+    os.utime(fa, (1, 1))
+    r3 = subprocess.run(args, capture_output=True, env=env)
+    assert r3.returncode == 0 and r3.stdout == golden("rand101.add.paf") and b"Parsing sequence file" in r3.stderr
