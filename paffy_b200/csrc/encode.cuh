@@ -37,11 +37,6 @@
 #define ENC_LDG128 1   // 1: the WIN_WORDS + 1 words of a window come from aligned 128-bit loads (the pair holding the first word
                        // and the pairs behind it), the word parity of the first one picked with selects: fewer, wider L1 requests
 #endif
-#ifndef ENC_NEXT_PREFETCH
-#define ENC_NEXT_PREFETCH 1   // 1: while a tile is copied out, the sequence under the first windows of the warp's NEXT tile is pulled
-                              // into L2 (a guess: the span behind the tile's first op, contiguous), so that its first batch of
-                              // loads does not wait for DRAM
-#endif
 #ifndef ENC_ROLL_HB
 #define ENC_ROLL_HB 0  // 1: the batch loop of the compare phase is not unrolled (smaller code)
 #endif
@@ -66,7 +61,6 @@ struct EncodeParams {
     int64_t *rec_out_begin;
     unsigned long long *rec_mism;
     struct OpEntry *tab_overflow;   // TILE_TAB entries per resident warp: table entries TAB_SMEM.. of tiles with many short ops
-    uint64_t arena_words;           // words of the genome arena (prefetch addresses are clamped to it)
 };
 
 #ifndef ENC_WIN_WORDS
@@ -765,14 +759,6 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         const int64_t next_ct = s_ticket;
         const int64_t next_tile = next_ct * WARPS + wid;
         const uint32_t next_first_op = next_tile < P.n_tiles ? __ldg(P.tile_first_op + next_tile) : 0u;
-#if ENC_NEXT_PREFETCH
-        // the next tile's first op (issued now, used after the copy-out: two dependent L2 round trips hidden behind it)
-        uint64_t nx_w = 0, nx_o = 1ull << 56, nx_t = 0, nx_q = 0;
-        if (next_tile < P.n_tiles) {
-            nx_w = __ldg(P.woff + next_first_op); nx_o = __ldg(P.ops + next_first_op);
-            nx_t = __ldg(P.tpos + next_first_op); nx_q = __ldg(P.qpos + next_first_op);
-        }
-#endif
 
         // ---- E2: op pass, then the list goes out as CigarRecord words with coalesced stores
         if (n_act && !(ENC_DIAG & 1)) {
@@ -813,15 +799,6 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                 }
             }
         }
-#if ENC_NEXT_PREFETCH
-        if (next_tile < P.n_tiles && (int)(nx_o >> 56) == OP_M && lane < 18) {
-            // 32 windows = 1 KB per stream (+ the phase): 9 lines each, lanes 0-8 the target, 9-17 the query
-            const uint64_t back = (uint64_t)WIN_BASES * ((uint64_t)next_tile * TILE_WIN - nx_w);
-            const uint64_t pos = ((lane < 9 ? nx_t : nx_q) & POS_MASK) + back;
-            const uint64_t word = min((pos >> 5) + 16u * (lane < 9 ? lane : lane - 9), P.arena_words - 1);
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(P.G.words + word));
-        }
-#endif
         if (next_tile < P.n_tiles) {
             const int64_t k = (int64_t)next_first_op + lane;
             if (k < P.n_ops) {

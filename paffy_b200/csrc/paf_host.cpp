@@ -100,6 +100,7 @@ void parallel_for(int64_t n, int threads, F f) {  // f(begin, end, thread)
 #include <cerrno>
 #include <getopt.h>
 #include <fcntl.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
 
@@ -138,6 +139,16 @@ struct Pinned {  // pinned host buffer that only grows (plain memory where no CU
         if (bytes <= cap) return true;
         release();
         cap = bytes + bytes / 4 + 4096;
+        p = pafgpu_host_alloc(cap);
+        pageable = false;
+        if (!p && pafgpu_device_count() == 0) { p = malloc((size_t)cap); pageable = true; }
+        if (!p) cap = 0;
+        return p != nullptr;
+    }
+    bool ensure_exact(int64_t bytes) {  // no head room: the caller rounds to size classes itself
+        if (bytes <= cap) return true;
+        release();
+        cap = bytes;
         p = pafgpu_host_alloc(cap);
         pageable = false;
         if (!p && pafgpu_device_count() == 0) { p = malloc((size_t)cap); pageable = true; }
@@ -586,6 +597,9 @@ struct PinnedPool {
     std::mutex mu;
     std::vector<Pinned *> idle;
     Pinned *get(int64_t bytes) {
+        // sizes in classes (32 MiB steps below 256 MiB, 128 MiB steps above): a buffer leased for one chunk fits the next
+        const int64_t step = bytes < ((int64_t)256 << 20) ? (int64_t)32 << 20 : (int64_t)128 << 20;
+        bytes = (bytes + step - 1) / step * step;
         Pinned *p = nullptr;
         {
             std::lock_guard<std::mutex> lk(mu);
@@ -599,7 +613,7 @@ struct PinnedPool {
             if (best < idle.size()) { p = idle[best]; idle.erase(idle.begin() + (ptrdiff_t)best); }
         }
         if (!p) p = new Pinned();
-        if (!p->ensure(bytes)) { delete p; return nullptr; }
+        if (!p->ensure_exact(bytes)) { delete p; return nullptr; }
         return p;
     }
     void put(Pinned *p) {
@@ -827,6 +841,8 @@ void process_chunk(Filter &F, const char *text, size_t n_text, ChunkOut &R) {
 struct ChunkReader {
     int fd;
     size_t chunk_bytes;
+    bool seekable = false;    // a regular file: large reads are split over a few threads (pread)
+    int64_t file_off = 0;
     std::vector<char> carry;  // the incomplete last line of the previous read (holds no newline)
     bool eof = false;
     int64_t seq = 0;
@@ -854,7 +870,35 @@ struct ChunkReader {
             }
             const size_t want = chunk_bytes > have ? std::min(chunk_bytes - have, cap - have) : std::min<size_t>(std::max<size_t>(chunk_bytes, 256), cap - have);
             ssize_t got;
-            do got = ::read(fd, d + have, want); while (got < 0 && errno == EINTR);
+            if (seekable && want >= ((size_t)8 << 20)) {
+                // page-cache copies of one file run in parallel
+                const int nt = 4;
+                ssize_t part[nt];
+                std::vector<std::thread> th;
+                for (int t = 0; t < nt; t++)
+                    th.emplace_back([&, t]() {
+                        const size_t a0 = want * (size_t)t / nt, a1 = want * (size_t)(t + 1) / nt;
+                        size_t at = a0;
+                        while (at < a1) {
+                            const ssize_t r = pread(fd, d + have + at, a1 - at, (off_t)(file_off + (int64_t)at));
+                            if (r < 0) { if (errno == EINTR) continue; part[t] = -1; return; }
+                            if (r == 0) break;
+                            at += (size_t)r;
+                        }
+                        part[t] = (ssize_t)(at - a0);
+                    });
+                for (auto &x : th) x.join();
+                got = 0;
+                for (int t = 0; t < nt; t++) {
+                    if (part[t] < 0) { got = -1; break; }
+                    got += part[t];
+                    if ((size_t)part[t] < want * (size_t)(t + 1) / nt - want * (size_t)t / nt) break;  // end of file inside this part
+                }
+                if (got > 0) file_off += got;
+            } else {
+                do got = ::read(fd, d + have, want); while (got < 0 && errno == EINTR);
+                if (got > 0) file_off += got;
+            }
             if (got < 0) { *failed = true; g_pinned.put(c.buf); c.buf = nullptr; return false; }
             if (got == 0) { eof = true; break; }
             for (size_t k = have + (size_t)got; k > have; k--)
@@ -912,6 +956,13 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
     pafgpu_file_report rep{};
     rep.failed_record = -1;
     const double t_start = now_s();
+    const bool trace = getenv("PAFFY_TRACE") != nullptr;  // a timeline of the pipeline on stderr
+    std::mutex trace_mu;
+    auto mark = [&](const char *what, int64_t seq, int64_t bytes) {
+        if (!trace) return;
+        std::lock_guard<std::mutex> lk(trace_mu);
+        fprintf(stderr, "[paffy_b200 %8.3f ms] %-14s chunk %lld  %lld bytes\n", 1e3 * (now_s() - t_start), what, (long long)seq, (long long)bytes);
+    };
 
     // ---- contexts: `streams` per device; device 0 of the list is the caller's, the others hold a clone of its genome.
     // The helpers belong to the caller's context and outlive this call (created once, reused by the next call).
@@ -932,6 +983,7 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
         ctxs.assign(2, nullptr);  // `add_mismatches -a`: two host workers
     }
     const int W = (int)ctxs.size();
+    mark("contexts ready", -1, 0);
     rep.gpus = (int64_t)devs.size();
     rep.workers = W;
 
@@ -943,28 +995,40 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
         if (in_path) fclose(fin);
         return pafgpu_internal_fail(ctx, PAFGPU_EIO, (std::string("cannot open ") + out_path).c_str());
     }
+    mark("output open", -1, 0);
     struct stat out_st;
     const bool out_regular = out_path && fstat(out_fd, &out_st) == 0 && S_ISREG(out_st.st_mode);
-    int64_t out_off = 0;  // regular files: bytes written so far (large pieces go out as parallel pwrites)
+    int64_t out_off = 0;  // regular files: bytes written so far
+    const bool no_mmap = getenv("PAFFY_NO_MMAP") != nullptr;
     auto write_out = [&](const char *p, size_t n) -> bool {
         if (n == 0) return true;
         bool ok = true;
         const size_t piece = (size_t)4 << 20;
-        if (out_regular && n >= 2 * piece) {
-            const int nt = (int)std::min<size_t>((size_t)std::max(2, std::min(hw_threads() - 2, 16)), n / piece);
-            std::vector<std::thread> th;
-            std::atomic<bool> good{true};
-            for (int t = 0; t < nt; t++)
-                th.emplace_back([&, t]() {
-                    size_t a0 = n * (size_t)t / (size_t)nt, a1 = n * (size_t)(t + 1) / (size_t)nt;
-                    while (a0 < a1) {
-                        const ssize_t w = pwrite(out_fd, p + a0, a1 - a0, (off_t)(out_off + (int64_t)a0));
-                        if (w < 0) { if (errno == EINTR) continue; good = false; return; }
-                        a0 += (size_t)w;
-                    }
-                });
-            for (auto &x : th) x.join();
-            ok = good.load();
+        bool mapped = false;
+        if (out_regular && n >= 2 * piece && !no_mmap) {
+            // a large piece of a regular file: the file is extended and mapped, several threads copy into the mapping
+            // (writes through write(2) to ONE file serialise on the inode lock; page faults on a mapping do not)
+            const int64_t page = sysconf(_SC_PAGESIZE);
+            const int64_t m0 = out_off / page * page;
+            const size_t span = (size_t)(out_off - m0) + n;
+            if (ftruncate(out_fd, (off_t)(out_off + (int64_t)n)) == 0) {
+                void *map = mmap(nullptr, span, PROT_READ | PROT_WRITE, MAP_SHARED, out_fd, (off_t)m0);
+                if (map != MAP_FAILED) {
+                    char *dst = static_cast<char *>(map) + (out_off - m0);
+                    const int nt = (int)std::min<size_t>((size_t)std::max(2, std::min(hw_threads() - 2, 16)), n / piece);
+                    std::vector<std::thread> th;
+                    for (int t = 0; t < nt; t++)
+                        th.emplace_back([&, t]() {
+                            const size_t a0 = n * (size_t)t / (size_t)nt, a1 = n * (size_t)(t + 1) / (size_t)nt;
+                            memcpy(dst + a0, p + a0, a1 - a0);
+                        });
+                    for (auto &x : th) x.join();
+                    munmap(map, span);
+                    mapped = true;
+                }
+            }
+        }
+        if (mapped) {
         } else {
             size_t a0 = 0;
             while (a0 < n) {
@@ -992,6 +1056,10 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
 
     std::thread reader([&]() {
         ChunkReader rd{fileno(fin), chunk_bytes};
+        {
+            struct stat st;
+            rd.seekable = in_path && fstat(rd.fd, &st) == 0 && S_ISREG(st.st_mode);
+        }
         for (;;) {
             {
                 std::unique_lock<std::mutex> lk(mu);
@@ -1003,6 +1071,7 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
             bool failed = false;
             const bool more = rd.next(c, &failed);
             s_read += now_s() - t0;
+            if (more) mark("read", c.seq, (int64_t)c.n);
             std::lock_guard<std::mutex> lk(mu);
             if (failed) read_failed = true;
             if (!more) break;
@@ -1036,7 +1105,9 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
                     jobs.pop_front();
                 }
                 ChunkOut R;
+                mark("start", c.seq, (int64_t)c.n);
                 process_chunk(F, c.data(), c.n, R);
+                mark("done", c.seq, R.lease_bytes + (int64_t)R.bytes.size());
                 g_pinned.put(c.buf);
                 c.buf = nullptr;
                 R.ready = true;
@@ -1066,6 +1137,7 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
         g_pinned.put(R.lease);
         R.lease = nullptr;
         rep.s_write += now_s() - t0;
+        mark("written", next_seq, R.lease_bytes + (int64_t)R.bytes.size());
         rep.records += R.rep.records;
         rep.aligned_bases += R.rep.aligned_bases;
         rep.batches += R.rep.batches;
@@ -1108,6 +1180,7 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
     }
     if (in_path) fclose(fin);
     if (out_path && close(out_fd) != 0 && rc == 0) { rc = PAFGPU_EIO; err = "write failed"; }
+    mark("closed", -1, out_off);
     rep.s_total = now_s() - t_start;
     if (rc == 1) fprintf(stderr, "%s\n", err.c_str());
     if (rc != 0) pafgpu_internal_fail(ctx, rc, err.c_str());

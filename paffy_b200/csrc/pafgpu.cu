@@ -441,7 +441,6 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
 
     EncodeParams &P = c->last;
     P.G = g.view();
-    P.arena_words = (uint64_t)(g.cap_bases / 32 + 4);
     P.ops = b->ops; P.woff = c->woff.as<uint64_t>(); P.tpos = c->tpos.as<uint64_t>(); P.qpos = c->qpos.as<uint64_t>();
     P.op_rec = c->op_rec.as<uint32_t>(); P.tile_first_op = c->tile_first_op.as<uint32_t>();
     P.n_ops = N; P.n_win = n_win; P.n_tiles = n_tiles;
@@ -1348,7 +1347,11 @@ static int trim_batch(pafgpu_ctx *c, bool fixed, float score_fraction, float max
     T.qs = co; T.qe = co + R; T.ts = co + 2 * R; T.te = co + 3 * R;
     T.lo = c->trim_lo.as<int64_t>(); T.hi = c->trim_hi.as<int64_t>(); T.failed = c->trim_failed.as<uint8_t>();
     T.score_fraction = score_fraction; T.max_fraction = max_fraction;
-    if (R > 0 && !fixed) trim_kernel<<<blocks_for(R, 128), 128, 0, c->stream>>>(T);
+    // long CIGARs (mean > 64 ops per record): one warp per record instead of one thread ($PAFGPU_TRIM_WARP = 0 / 1 forces)
+    bool by_warp = R > 0 && c->n_out / R > 64;
+    if (const char *e = getenv("PAFGPU_TRIM_WARP")) by_warp = atoi(e) != 0;
+    if (R > 0 && !fixed && by_warp) trim_warp_kernel<<<blocks_for(R * 32, 128), 128, 0, c->stream>>>(T);
+    else if (R > 0 && !fixed) trim_kernel<<<blocks_for(R, 128), 128, 0, c->stream>>>(T);
     if (R > 0 && fixed) trim_fixed_kernel<<<blocks_for(R, 128), 128, 0, c->stream>>>(T, c->out.as<uint64_t>());
     CU(cudaMemcpyAsync(coords, co, 4 * (size_t)R * 8, cudaMemcpyDeviceToHost, c->stream));
     if (failed) CU(cudaMemcpyAsync(failed, T.failed, (size_t)R, cudaMemcpyDeviceToHost, c->stream));

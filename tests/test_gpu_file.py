@@ -313,13 +313,15 @@ def test_paf_encode_mismatches_symbol():
     assert mm == sum(n for n, c in want if c == "X")
 
 
+@pytest.mark.parametrize("by_warp", ["0", "1"])
 @pytest.mark.parametrize("seed", [71, 72, 73])
-def test_device_trim_matches_oracle(ctx, seed):
-    """pafgpu_trim (one thread per record, float32 identity walk) vs the oracle's paf_trim_unreliable_tails: moved
-    coordinates and kept op counts, both strands, several -r / -t settings."""
+def test_device_trim_matches_oracle(ctx, seed, by_warp, monkeypatch):
+    """pafgpu_trim (one thread per record, or one warp per record for long CIGARs: both forced here; float32 identity walk)
+    vs the oracle's paf_trim_unreliable_tails: moved coordinates and kept op counts, both strands, several -r / -t."""
     import numpy as np
     from oracle import pyoracle as O
-    case = util.random_case(seed, n_records=80, contig_len=30000, n_ops=14, max_len=900, p_main=0.97)
+    monkeypatch.setenv("PAFGPU_TRIM_WARP", by_warp)
+    case = util.random_case(seed, n_records=80, contig_len=30000, n_ops=14 if by_warp == "0" else 90, max_len=900 if by_warp == "0" else 200, p_main=0.97)
     case["records"] = [r for r in case["records"] if any(c == "M" and n for n, c in r["ops"])]
     got, res = util.gpu_encode(ctx, case)
     lines = util.case_lines(case)

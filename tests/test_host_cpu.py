@@ -134,3 +134,62 @@ def test_output_starts_before_the_input_ends():
     p.stdin.close()
     rest = p.stdout.read()
     assert p.wait() == 0 and (first + rest).count(b"\n") == 5
+
+
+def _strong_rank(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    from paffy_b200 import synth
+    # what bench.py does at N > 1: every rank generates the SAME job, cuts it with pafgpu_partition, keeps its own range
+    rec = synth.build_workload(None, "tiny", torch.device("cpu"), rank=0)
+    cuts = paffy_b200.partition(rec["sum_m"].numpy(), world)
+    lo, hi = int(cuts[rank]), int(cuts[rank + 1])
+    mine = synth.shard(rec, lo, hi)
+    assert mine["n"] == hi - lo and int(mine["op_begin"][0]) == 0 and int(mine["op_begin"][-1]) == mine["ops"].numel()
+    payload = (lo, hi, int(mine["sum_m"].sum()), mine["ops"].numpy().tobytes(), mine["qs"].numpy().tobytes())
+    objs = [None] * world if rank == 0 else None
+    dist.gather_object(payload, objs, dst=0)
+    if rank == 0:
+        whole_ops = rec["ops"].numpy().tobytes()
+        ok = objs[0][0] == 0 and objs[-1][1] == rec["n"] and all(objs[i][1] == objs[i + 1][0] for i in range(world - 1))
+        ok = ok and b"".join(o[3] for o in objs) == whole_ops and b"".join(o[4] for o in objs) == rec["qs"].numpy().tobytes()
+        q.put((ok, [o[2] for o in objs], int(rec["sum_m"].sum()), int(rec["sum_m"].max())))
+    dist.destroy_process_group()
+
+
+def test_one_job_strong_scaling_shards_world_size_2_gloo():
+    """bench.py's N > 1 path: ONE input-ordered record list cut into contiguous ranges of near-equal aligned bases, the
+    rank-ordered concatenation of the shards is the job again (no collective on the data path)."""
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_strong_rank, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in ps]
+    ok, loads, total, biggest = q.get(timeout=180)
+    [p.join(60) for p in ps]
+    assert ok and sum(loads) == total and abs(loads[0] - total / 2) <= biggest
+
+
+def test_large_output_goes_through_the_mapped_writer(tmp_path):
+    """Pieces of 8 MiB and more of a regular output file are written by several threads through a mapping of the file
+    (extended chunk by chunk); the bytes must be the same as through write(2) ($PAFFY_NO_MMAP)."""
+    lines = open(os.path.join(G, "rand101.add.paf"), "rb").read()
+    want1 = open(os.path.join(G, "rand101.remove.paf"), "rb").read()
+    reps = (20 << 20) // len(lines) + 1
+    inp = tmp_path / "big.paf"
+    inp.write_bytes(lines * reps)
+    outs = []
+    for env in ({}, {"PAFFY_NO_MMAP": "1"}):
+        os.environ.update(env)
+        try:
+            out = tmp_path / f"o{len(outs)}.paf"
+            rc, rep = paffy_b200.remove_mismatches_file(str(inp), str(out), chunk_bytes=12 << 20)
+        finally:
+            for k in env:
+                del os.environ[k]
+        assert rc == 0 and rep.chunks >= 2
+        outs.append(out.read_bytes())
+    assert outs[0] == want1 * reps and outs[1] == outs[0]
