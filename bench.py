@@ -584,6 +584,12 @@ def main():
                 "kernel_share_of_step": ms_kernel / (elapsed * 1e3) if world == 1 else None,
                 "encode_stage": {"ms": s_ms, "achieved": b_alg / (s_ms * 1e-3) / 1e9, "frac": b_alg / (s_ms * 1e-3) / 1e9 / peak,
                                  "what": "resets + encode_kernel + stitch_kernel + host read of the op count"}}
+    try:
+        mx, mean, sms = ctx.encode_balance()
+        roofline["load_balance"] = {"max_sm_busy_ms": mx, "mean_sm_busy_ms": mean, "max_over_mean": mx / mean if mean else None, "sms": sms,
+                                    "what": "per SM: the longest span from first to last tile among its persistent CTAs (globaltimer), last launch"}
+    except Exception as e:  # noqa: BLE001
+        roofline["load_balance"] = {"error": repr(e)[:120]}
     tr = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr):
         try:

@@ -202,6 +202,9 @@ int64_t pafgpu_genome_total_bases(const pafgpu_ctx *ctx);
  * ms_kernel: mean CUDA-event ms of the base-comparison kernel alone. */
 int pafgpu_time_encode(pafgpu_ctx *ctx, int reps, float *ms_stage, float *ms_kernel);
 
+/* Load balance of the last encode_kernel launch: the busiest SM's busy time and the mean over the SMs used (ms). */
+int pafgpu_encode_balance(pafgpu_ctx *ctx, double *max_ms, double *mean_ms, int *sms_used);
+
 /* Index (within the batch) of the record that made the last encode call fail with PAFGPU_EBOUNDS, else -1. */
 int64_t pafgpu_last_bad_record(const pafgpu_ctx *ctx);
 

@@ -61,6 +61,7 @@ struct EncodeParams {
     int64_t *rec_out_begin;
     unsigned long long *rec_mism;
     struct OpEntry *tab_overflow;   // TILE_TAB entries per resident warp: table entries TAB_SMEM.. of tiles with many short ops
+    unsigned long long *cta_span;   // per CTA: {ns from its first tile to its last, SM id}: the load-balance figure of SURVEY 8d
 };
 
 #ifndef ENC_WIN_WORDS
@@ -228,177 +229,179 @@ __device__ __forceinline__ void build_table(const EncodeParams &P, WarpSmem &S, 
 
 // ---- B: compare. Striped windows; masks to shared memory; per-record mismatch tallies. Returns (lane 0) the
 // mismatch state of the base just before the tile when tile window 0 continues an op.
+// Software-pipelined: the loads of window k + 1 are issued as soon as the words of window k have been turned into
+// mismatch bits (their registers are free again), so they fly while window k's tail handling, tally and store run.
+struct WinLoads {  // one window in flight
+    OpEntry en;
+#if ENC_LDG128
+    uint4 tp[(WIN_WORDS + 2) / 2], qp[(WIN_WORDS + 2) / 2];  // the aligned pairs covering WIN_WORDS + 1 words at either parity
+    bool t_odd, q_odd;
+#else
+    uint64_t tw[WIN_WORDS + 1], qw[WIN_WORDS + 1];
+#endif
+};
+
+template <bool EXC>
+__device__ __forceinline__ void window_issue(const EncodeParams &P, const WarpSmem &S, const TileTab &T, int it, uint32_t &pre, uint32_t n_act,
+                                             unsigned lane, unsigned adj, WinLoads &L) {
+    constexpr int WW = WIN_WORDS;
+    const uint64_t *__restrict__ gw = P.G.words;
+    const uint32_t srel = 32u * it + lane;
+    const uint32_t w = S.bm[it];
+    const uint32_t idx = pre + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
+    pre += __popc(w);
+    L.en = EXC ? T.get(idx) : S.tab[idx];  // (the slow variant also serves tiles whose table spills)
+    const bool isM = srel < n_act && !(L.en.misc & EF_PASS);
+    // inactive and pass-through windows read arena word 0: no branches
+    const int32_t tw = isM ? L.en.tw + WW * (int32_t)srel : 0;
+    const int32_t qw = isM ? L.en.qw + WW * (int32_t)srel : 0;
+#if ENC_LDG128
+    const uint4 *tp4 = reinterpret_cast<const uint4 *>(gw + (tw & ~1)), *qp4 = reinterpret_cast<const uint4 *>(gw + (qw & ~1));
+    L.t_odd = tw & 1; L.q_odd = qw & 1;
+#pragma unroll
+    for (int k = 0; k < (WW + 2) / 2; k++) L.tp[k] = __ldg(tp4 + k);
+#pragma unroll
+    for (int k = 0; k < (WW + 2) / 2; k++) L.qp[k] = __ldg(qp4 + k);
+#else
+#pragma unroll
+    for (int k = 0; k <= WW; k++) L.tw[k] = ldg64(gw + tw + k);
+#pragma unroll
+    for (int k = 0; k <= WW; k++) L.qw[k] = ldg64(gw + qw + k);
+#endif
+}
+
 template <int BATCH, bool EXC>
 __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem &S, const TileTab &T, uint32_t n_act, unsigned lane, unsigned adj, uint32_t rec_first) {
-    static_assert(TILE_ITERS % BATCH == 0, "BATCH must divide the iterations of a tile");
     constexpr int WW = WIN_WORDS;
     const uint64_t *__restrict__ gw = P.G.words;
     uint32_t pre = 0, pm0 = 0;
     uint32_t cur = 0, acc = 0;  // record (relative to rec_first) being tallied, and the lane's share of its mismatches
-#if ENC_ROLL_HB
-#pragma unroll 1
-#else
+    WinLoads L;
+    window_issue<EXC>(P, S, T, 0, pre, n_act, lane, adj, L);
+    {
+        // tile window 0 continues an op: mismatch state of the base just before the tile (lane 0)
+        const OpEntry en = L.en;
+        const bool isM = lane < n_act && !(en.misc & EF_PASS);
+        if (lane == 0 && isM && !(S.bm[0] & 1u)) {
+            const unsigned sht = en.misc & 31u, shq = (en.misc >> 5) & 31u;
+            const int32_t tw = en.tw, qw = en.qw;
+            if (EXC && (en.misc & EF_EXC)) {
+                const uint64_t tp = ((uint64_t)(uint32_t)tw << 5) + sht, qp = ((uint64_t)(uint32_t)qw << 5) + shq;
+                pm0 = slow_mismatch(P.G, tp - 1, qp - 1) ? 0x80000000u : 0u;
+            } else {
+                // the base before the window sits one bit down in the same word, or on top of the word before
+                const uint64_t pm_t = ldg64(gw + (tw - (sht == 0))), pm_q = ldg64(gw + (qw - (shq == 0)));
+                const unsigned kt = (sht - 1u) & 31u, kq = (shq - 1u) & 31u;
+                const unsigned tc = ((unsigned)(pm_t >> kt) & 1u) | (((unsigned)(pm_t >> (32 + kt)) & 1u) << 1);
+                const unsigned qc = ((unsigned)(pm_q >> kq) & 1u) | (((unsigned)(pm_q >> (32 + kq)) & 1u) << 1);
+                pm0 = tc != qc ? 0x80000000u : 0u;
+            }
+        }
+    }
+    if (!ENC_NO_PREFETCH) {
+        // the first window's loads are in flight: pull the sequence of every later window of the tile into L2 now, so
+        // that only this first one waits for DRAM
+        uint32_t pre2 = pre;
 #pragma unroll
-#endif
-    for (int hb = 0; hb < TILE_ITERS; hb += BATCH) {
-        // issue every sequence load of the batch (inactive and pass-through windows read arena word 0: no branches)
-        OpEntry EN[BATCH];
-        uint64_t TW[BATCH][WW + 1], QW[BATCH][WW + 1];
-#if ENC_LDG128
-        constexpr int NP = (WW + 2) / 2;  // aligned pairs that cover WW + 1 words starting at either parity
-        uint4 TP[BATCH][NP], QP[BATCH][NP];
-        bool t_odd[BATCH], q_odd[BATCH];
-#endif
-        uint64_t pm_t = 0, pm_q = 0;  // lane 0, first window only: words holding the base before the window
-        uint32_t pm_k = 0;
-#pragma unroll
-        for (int b = 0; b < BATCH; b++) {
-            const int it = hb + b;
+        for (int it = 1; it < TILE_ITERS; it++) {
             const uint32_t srel = 32u * it + lane;
             const uint32_t w = S.bm[it];
-            uint32_t idx = pre + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
-            pre += __popc(w);
-            const OpEntry en = EXC ? T.get(idx) : S.tab[idx];  // (the slow variant also serves tiles whose table spills)
-            EN[b] = en;
-            const bool isM = srel < n_act && !(en.misc & EF_PASS);
-            const int32_t tw = isM ? en.tw + WW * (int32_t)srel : 0;
-            const int32_t qw = isM ? en.qw + WW * (int32_t)srel : 0;
+            const uint32_t idx = pre2 + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
+            pre2 += __popc(w);
+            if (srel < n_act) {
+                const OpEntry en = EXC ? T.get(idx) : S.tab[idx];
+                if (!(en.misc & EF_PASS)) {
+                    const uint64_t *tpn = gw + (en.tw + WW * (int32_t)srel), *qpn = gw + (en.qw + WW * (int32_t)srel);
+                    // a window spans WW + 1 words, the next lane's window starts WW words on: the middle word of every
+                    // window touches every 32-byte sector of the op's span
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(tpn + WW / 2));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(qpn + WW / 2));
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int it = 0; it < TILE_ITERS; it++) {
+        const uint32_t srel = 32u * it + lane;
+        const OpEntry en = L.en;
+        const bool isM = srel < n_act && !(en.misc & EF_PASS);
+        const int32_t rem = entry_rem(en) - WIN_BASES * (int32_t)srel;
+        const uint32_t n = !isM ? 0u : rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
+        const uint32_t misc = en.misc;
+        const unsigned sht = misc & 31u, shq = (misc >> 5) & 31u;
+        // mismatch bits of the window
+        uint32_t m[WW];
+        {
+            uint64_t TW[WW + 1], QW[WW + 1];
 #if ENC_LDG128
-            {
-                const uint4 *tp4 = reinterpret_cast<const uint4 *>(gw + (tw & ~1)), *qp4 = reinterpret_cast<const uint4 *>(gw + (qw & ~1));
-                t_odd[b] = tw & 1; q_odd[b] = qw & 1;
+            // word j of the loaded pairs: .x/.y of pair j / 2 when j is even, .z/.w when it is odd
+            auto word = [](const uint4 *pp, int j) -> uint64_t {
+                const uint4 v = pp[j >> 1];
+                return (j & 1) ? ((uint64_t)v.w << 32) | v.z : ((uint64_t)v.y << 32) | v.x;
+            };
 #pragma unroll
-                for (int k = 0; k < NP; k++) TP[b][k] = __ldg(tp4 + k);
-#pragma unroll
-                for (int k = 0; k < NP; k++) QP[b][k] = __ldg(qp4 + k);
+            for (int k = 0; k <= WW; k++) {
+                TW[k] = L.t_odd ? word(L.tp, k + 1) : word(L.tp, k);
+                QW[k] = L.q_odd ? word(L.qp, k + 1) : word(L.qp, k);
             }
 #else
-            const uint64_t *tpn = gw + tw, *qpn = gw + qw;
 #pragma unroll
-            for (int k = 0; k <= WW; k++) TW[b][k] = ldg64(tpn + k);
-#pragma unroll
-            for (int k = 0; k <= WW; k++) QW[b][k] = ldg64(qpn + k);
-#endif
-            if (it == 0 && lane == 0 && isM && !(w & 1u)) {
-                // tile window 0 continues an op: mismatch state of the base just before the tile
-                const unsigned sht = en.misc & 31u, shq = (en.misc >> 5) & 31u;
-                if (EXC && (en.misc & EF_EXC)) {
-                    const uint64_t tp = ((uint64_t)(uint32_t)tw << 5) + sht, qp = ((uint64_t)(uint32_t)qw << 5) + shq;
-                    pm0 = slow_mismatch(P.G, tp - 1, qp - 1) ? 0x80000000u : 0u;
-                } else {
-                    // the base before the window sits one bit down in the same word, or on top of the word before
-                    pm_t = ldg64(gw + (tw - (sht == 0)));
-                    pm_q = ldg64(gw + (qw - (shq == 0)));
-                    pm_k = ((sht - 1u) & 31u) | (((shq - 1u) & 31u) << 5) | (1u << 11);
-                }
-            }
-        }
-        if (hb == 0 && !ENC_NO_PREFETCH) {
-            // the first batch's loads are in flight: pull the sequence of every later window of the tile into L2 now, so
-            // that only this first batch waits for DRAM
-            uint32_t pre2 = pre;
-#pragma unroll
-            for (int it = BATCH; it < TILE_ITERS; it++) {
-                const uint32_t srel = 32u * it + lane;
-                const uint32_t w = S.bm[it];
-                const uint32_t idx = pre2 + __popc(w & (0xffffffffu >> (31 - lane))) - adj;
-                pre2 += __popc(w);
-                if (srel < n_act) {
-                    const OpEntry en = EXC ? T.get(idx) : S.tab[idx];  // (the slow variant also serves tiles whose table spills)
-                    if (!(en.misc & EF_PASS)) {
-                        const uint64_t *tpn = gw + (en.tw + WW * (int32_t)srel), *qpn = gw + (en.qw + WW * (int32_t)srel);
-                        // a window spans WW + 1 words, the next lane's window starts WW words on: the middle word of every
-                        // window touches every 32-byte sector of the op's span
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(tpn + WW / 2));
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(qpn + WW / 2));
-                    }
-                }
-            }
-        }
-        if (hb == 0 && (pm_k >> 11)) {  // lane 0 only; consumed after the batch's loads were issued
-            const unsigned kt = pm_k & 31u, kq = (pm_k >> 5) & 31u;
-            const unsigned tc = ((unsigned)(pm_t >> kt) & 1u) | (((unsigned)(pm_t >> (32 + kt)) & 1u) << 1);
-            const unsigned qc = ((unsigned)(pm_q >> kq) & 1u) | (((unsigned)(pm_q >> (32 + kq)) & 1u) << 1);
-            pm0 = tc != qc ? 0x80000000u : 0u;
-        }
-        // mismatch bits
-#pragma unroll
-        for (int b = 0; b < BATCH; b++) {
-            const int it = hb + b;
-            const uint32_t srel = 32u * it + lane;
-            const OpEntry en = EN[b];
-            const bool isM = srel < n_act && !(en.misc & EF_PASS);
-            const int32_t rem = entry_rem(en) - WIN_BASES * (int32_t)srel;
-            const uint32_t n = !isM ? 0u : rem < WIN_BASES ? (uint32_t)rem : (uint32_t)WIN_BASES;
-            const uint32_t misc = en.misc;
-            const unsigned sht = misc & 31u, shq = (misc >> 5) & 31u;
-            uint32_t m[WW];
-#if ENC_LDG128
-            {
-                // word j of the loaded pairs: .x/.y of pair j / 2 when j is even, .z/.w when it is odd
-                auto word = [](const uint4 *pp, int j) -> uint64_t {
-                    const uint4 v = pp[j >> 1];
-                    return (j & 1) ? ((uint64_t)v.w << 32) | v.z : ((uint64_t)v.y << 32) | v.x;
-                };
-#pragma unroll
-                for (int k = 0; k <= WW; k++) {
-                    TW[b][k] = t_odd[b] ? word(TP[b], k + 1) : word(TP[b], k);
-                    QW[b][k] = q_odd[b] ? word(QP[b], k + 1) : word(QP[b], k);
-                }
-            }
+            for (int k = 0; k <= WW; k++) { TW[k] = L.tw[k]; QW[k] = L.qw[k]; }
 #endif
 #pragma unroll
             for (int k = 0; k < WW; k++) {
-                const uint32_t tl = __funnelshift_r((uint32_t)TW[b][k], (uint32_t)TW[b][k + 1], sht);
-                const uint32_t th = __funnelshift_r((uint32_t)(TW[b][k] >> 32), (uint32_t)(TW[b][k + 1] >> 32), sht);
-                const uint32_t ql = __funnelshift_r((uint32_t)QW[b][k], (uint32_t)QW[b][k + 1], shq);
-                const uint32_t qh = __funnelshift_r((uint32_t)(QW[b][k] >> 32), (uint32_t)(QW[b][k + 1] >> 32), shq);
+                const uint32_t tl = __funnelshift_r((uint32_t)TW[k], (uint32_t)TW[k + 1], sht);
+                const uint32_t th = __funnelshift_r((uint32_t)(TW[k] >> 32), (uint32_t)(TW[k + 1] >> 32), sht);
+                const uint32_t ql = __funnelshift_r((uint32_t)QW[k], (uint32_t)QW[k + 1], shq);
+                const uint32_t qh = __funnelshift_r((uint32_t)(QW[k] >> 32), (uint32_t)(QW[k + 1] >> 32), shq);
                 m[k] = (tl ^ ql) | (th ^ qh);
             }
-            if (EXC && isM && (misc & EF_EXC)) {
-                const uint64_t tp = ((uint64_t)(uint32_t)(en.tw + WW * (int32_t)srel) << 5) + sht;
-                const uint64_t qlo = ((uint64_t)(uint32_t)(en.qw + WW * (int32_t)srel) << 5) + shq;
-                if (span_has_exception(P.G, tp, tp + n - 1) || span_has_exception(P.G, qlo, qlo + n - 1)) {
+        }
+        // the loaded words are consumed: the next window's loads go out now and fly during the rest of this one
+        if (it + 1 < TILE_ITERS) window_issue<EXC>(P, S, T, it + 1, pre, n_act, lane, adj, L);
+        if (EXC && isM && (misc & EF_EXC)) {
+            const uint64_t tp = ((uint64_t)(uint32_t)(en.tw + WW * (int32_t)srel) << 5) + sht;
+            const uint64_t qlo = ((uint64_t)(uint32_t)(en.qw + WW * (int32_t)srel) << 5) + shq;
+            if (span_has_exception(P.G, tp, tp + n - 1) || span_has_exception(P.G, qlo, qlo + n - 1)) {
 #pragma unroll
-                    for (int k = 0; k < WW; k++) {
-                        uint32_t mk = 0;
-                        for (uint32_t j = 32u * k; j < n && j < 32u * k + 32u; j++) mk |= slow_mismatch(P.G, tp + j, qlo + j) << (j & 31u);
-                        m[k] = mk;
-                    }
+                for (int k = 0; k < WW; k++) {
+                    uint32_t mk = 0;
+                    for (uint32_t j = 32u * k; j < n && j < 32u * k + 32u; j++) mk |= slow_mismatch(P.G, tp + j, qlo + j) << (j & 31u);
+                    m[k] = mk;
                 }
             }
-            // bases beyond the op's end do not exist: shifting them out leaves the op's last base on top, the tally
-            // counts what is left, and the arithmetic shift back copies that last base over the tail, so that no run
-            // appears to start behind the end (the next window starts another op). 64 bases at a time; a half that lies
-            // wholly behind the end repeats the top bit of the half before it.
-            uint32_t mm_count = 0;
-            uint64_t below = 0;
-            const uint32_t wdx = 2u + WW * srel + 2u * ((WW * srel) >> 5);
+        }
+        // bases beyond the op's end do not exist: shifting them out leaves the op's last base on top, the tally
+        // counts what is left, and the arithmetic shift back copies that last base over the tail, so that no run
+        // appears to start behind the end (the next window starts another op). 64 bases at a time; a half that lies
+        // wholly behind the end repeats the top bit of the half before it.
+        uint32_t mm_count = 0;
+        uint64_t below = 0;
+        const uint32_t wdx = 2u + WW * srel + 2u * ((WW * srel) >> 5);
 #pragma unroll
-            for (int h = 0; h < WW / 2; h++) {
-                const uint64_t raw = isM ? ((uint64_t)m[2 * h + 1] << 32) | m[2 * h] : 0ull;
-                const bool some = n > 64u * h;  // this half holds bases of the op (always true for the first half of an M window)
-                const uint32_t nh = n - 64u * h;
-                const unsigned sh = (isM && some && nh < 64u) ? 64u - nh : 0u;
-                const uint64_t src = (h == 0 || some) ? raw : (uint64_t)((int64_t)below >> 63);
-                const uint64_t up = src << sh;
-                mm_count += (h == 0 || some) ? (uint32_t)__popcll(up) : 0u;
-                const uint64_t mx = (uint64_t)((int64_t)up >> sh);
-                below = mx;
-                *reinterpret_cast<uint64_t *>(&S.mask[wdx + 2 * h]) = mx;
-            }
-            // per-record mismatch tally. Records do not decrease along the window axis, so the warp tallies one
-            // record at a time and moves on together: one reduction and one atomic per record and tile.
-            {
-                const uint32_t rec = isM ? entry_rec(en) : cur;
-                for (;;) {
-                    acc += rec == cur ? mm_count : 0u;
-                    if (__all_sync(FULL, rec <= cur)) break;
-                    const uint32_t sum = __reduce_add_sync(FULL, acc);
-                    if (lane == 0 && sum) atomicAdd(P.rec_mism + rec_first + cur, (unsigned long long)sum);
-                    acc = 0;
-                    cur = __reduce_min_sync(FULL, rec > cur ? rec : 0xffffffffu);
-                }
+        for (int h = 0; h < WW / 2; h++) {
+            const uint64_t raw = isM ? ((uint64_t)m[2 * h + 1] << 32) | m[2 * h] : 0ull;
+            const bool some = n > 64u * h;  // this half holds bases of the op (always true for the first half of an M window)
+            const uint32_t nh = n - 64u * h;
+            const unsigned sh = (isM && some && nh < 64u) ? 64u - nh : 0u;
+            const uint64_t src = (h == 0 || some) ? raw : (uint64_t)((int64_t)below >> 63);
+            const uint64_t up = src << sh;
+            mm_count += (h == 0 || some) ? (uint32_t)__popcll(up) : 0u;
+            const uint64_t mx = (uint64_t)((int64_t)up >> sh);
+            below = mx;
+            *reinterpret_cast<uint64_t *>(&S.mask[wdx + 2 * h]) = mx;
+        }
+        // per-record mismatch tally. Records do not decrease along the window axis, so the warp tallies one
+        // record at a time and moves on together: one reduction and one atomic per record and tile.
+        {
+            const uint32_t rec = isM ? entry_rec(en) : cur;
+            for (;;) {
+                acc += rec == cur ? mm_count : 0u;
+                if (__all_sync(FULL, rec <= cur)) break;
+                const uint32_t sum = __reduce_add_sync(FULL, acc);
+                if (lane == 0 && sum) atomicAdd(P.rec_mism + rec_first + cur, (unsigned long long)sum);
+                acc = 0;
+                cur = __reduce_min_sync(FULL, rec > cur ? rec : 0xffffffffu);
             }
         }
     }
@@ -658,6 +661,11 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
     __syncthreads();
     int64_t ct = s_ticket;
     uint32_t iter = 0;
+    if (threadIdx.x == 0) {  // (kept in memory, not in a register, across the loop)
+        unsigned long long t_begin;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
+        P.cta_span[2 * blockIdx.x] = t_begin;
+    }
     // first op of this warp's tile; for every later tile it is fetched (and the tile's op arrays pulled into L2) while
     // the previous tile is converted, so a tile does not start with a chain of DRAM round trips
     uint32_t first_op = ct * WARPS + wid < P.n_tiles ? __ldg(P.tile_first_op + ct * WARPS + wid) : 0u;
@@ -812,6 +820,14 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         first_op = next_first_op;
         ct = next_ct;
         iter++;
+    }
+    if (threadIdx.x == 0) {
+        unsigned long long t_end;
+        unsigned smid;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+        asm("mov.u32 %0, %%smid;" : "=r"(smid));
+        P.cta_span[2 * blockIdx.x] = iter ? t_end - P.cta_span[2 * blockIdx.x] : 0ull;
+        P.cta_span[2 * blockIdx.x + 1] = smid;
     }
 }
 

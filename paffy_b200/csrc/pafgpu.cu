@@ -126,7 +126,8 @@ struct pafgpu_ctx {
     DevBuf in_op_begin, in_ops, in_qc, in_tc, in_qs, in_qe, in_ts, in_strand, in_seq;
     // per-batch work buffers
     DevBuf tpos, qpos, op_rec, nwin, woff, scan_sums, tile_first_op, status, tile_first_closer, tile_open_slot, tab_overflow;
-    DevBuf out, rec_out_begin, rec_mism, scalars;
+    DevBuf out, rec_out_begin, rec_mism, scalars, cta_span;
+    unsigned last_grid = 0;
     // serialiser
     DevBuf ser_prefix, ser_prefix_begin, ser_oplen, ser_optoff, ser_line_begin, ser_text;
     // trim
@@ -332,9 +333,13 @@ int launch_encode_once(pafgpu_ctx *c) {
         CU(c->tab_overflow.ensure(warps * TILE_TAB * sizeof(OpEntry)));
         P.tab_overflow = c->tab_overflow.as<OpEntry>();
     }
+    CU(c->cta_span.ensure((size_t)c->sm_count * c->enc_ctas_per_sm * 16));
+    P.cta_span = c->cta_span.as<unsigned long long>();
+    c->last_grid = 0;
     CU(cudaEventRecord(c->ev[4], c->stream));
     if (CT > 0) {
         const unsigned grid = (unsigned)std::min<int64_t>(CT, (int64_t)c->sm_count * c->enc_ctas_per_sm);
+        c->last_grid = grid;
         if (W == 1) encode_kernel<1, CMP_BATCH><<<grid, 32, 0, c->stream>>>(P);
         else if (W == 2) encode_kernel<2, CMP_BATCH><<<grid, 64, 0, c->stream>>>(P);
         else if (W == 8) encode_kernel<8, CMP_BATCH><<<grid, 256, 8 * sizeof(WarpSmem), c->stream>>>(P);
@@ -599,7 +604,7 @@ void pafgpu_destroy(pafgpu_ctx *c) {
     DevBuf *bufs[] = {&c->in_op_begin, &c->in_ops, &c->in_qc, &c->in_tc, &c->in_qs, &c->in_qe, &c->in_ts, &c->in_strand,
                       &c->in_seq, &c->tpos, &c->qpos, &c->op_rec, &c->nwin, &c->woff, &c->scan_sums, &c->tile_first_op,
                       &c->status, &c->tile_first_closer, &c->tile_open_slot, &c->tab_overflow, &c->out, &c->rec_out_begin, &c->rec_mism,
-                      &c->scalars, &c->trim_coords, &c->trim_lo, &c->trim_hi, &c->trim_failed, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
+                      &c->scalars, &c->cta_span, &c->trim_coords, &c->trim_lo, &c->trim_hi, &c->trim_failed, &c->ser_prefix, &c->ser_prefix_begin, &c->ser_oplen, &c->ser_optoff, &c->ser_line_begin,
                       &c->ser_text, &c->tx_text, &c->tx_tile_nl, &c->tx_tile_tab, &c->tx_nl_off, &c->tx_tab_off, &c->tx_nl_pos, &c->tx_tab_pos,
                       &c->tx_line_tab0, &c->tx_cols, &c->tx_tile_ops, &c->tx_op_off, &c->tx_ops, &c->tx_scal, &c->fa_raw, &c->fa_tile_kept,
                       &c->fa_tile_off, &c->fa_scal};
@@ -991,6 +996,26 @@ int pafgpu_time_encode(pafgpu_ctx *c, int reps, float *ms_stage, float *ms_kerne
     }
     if (ms_stage) *ms_stage = (float)(sum / reps);
     if (ms_kernel) *ms_kernel = (float)(ksum / reps);
+    return 0;
+}
+
+// Load balance of the last encode_kernel launch ("max / mean per-SM busy time"): every persistent CTA leaves the
+// nanoseconds between its first and its last tile and the SM it ran on; an SM's busy time is the longest of its CTAs.
+int pafgpu_encode_balance(pafgpu_ctx *c, double *max_ms, double *mean_ms, int *sms_used) {
+    if (!c || !max_ms || !mean_ms) return PAFGPU_EINVAL;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!c->have_batch || c->last_grid == 0) return fail(c, PAFGPU_ESTATE, "no batch has been encoded");
+    CU(cudaSetDevice(c->device));
+    std::vector<unsigned long long> span((size_t)c->last_grid * 2);
+    CU(cudaMemcpyAsync(span.data(), c->cta_span.p, span.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(stream_sync(c));
+    std::unordered_map<unsigned long long, unsigned long long> per_sm;
+    for (unsigned b = 0; b < c->last_grid; b++) per_sm[span[2 * b + 1]] = std::max(per_sm[span[2 * b + 1]], span[2 * b]);
+    double mx = 0, sum = 0;
+    for (auto &kv : per_sm) { mx = std::max(mx, (double)kv.second); sum += (double)kv.second; }
+    *max_ms = mx * 1e-6;
+    *mean_ms = per_sm.empty() ? 0 : sum / (double)per_sm.size() * 1e-6;
+    if (sms_used) *sms_used = (int)per_sm.size();
     return 0;
 }
 

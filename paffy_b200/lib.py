@@ -22,7 +22,7 @@ ABI_SYMBOLS = [
     "pafgpu_serialise", "pafgpu_fetch_text", "pafgpu_encode_one", "pafgpu_time_encode",
     "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition", "pafgpu_trim",
     "pafgpu_trim_fixed", "pafgpu_stage_ops_host", "pafgpu_add_mismatches_file_filtered",
-    "pafgpu_add_mismatches_text", "pafgpu_create_sibling", "pafgpu_helper", "pafgpu_encode_one_resident", "pafgpu_genome_clear", "pafgpu_genome_total_bases", "pafgpu_device_of", "pafgpu_genome_clone", "pafgpu_genome_save", "pafgpu_genome_load_packed",
+    "pafgpu_add_mismatches_text", "pafgpu_create_sibling", "pafgpu_helper", "pafgpu_encode_balance", "pafgpu_encode_one_resident", "pafgpu_genome_clear", "pafgpu_genome_total_bases", "pafgpu_device_of", "pafgpu_genome_clone", "pafgpu_genome_save", "pafgpu_genome_load_packed",
 ]
 # reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
 REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paffy_view_main", "paffy_trim_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
@@ -283,6 +283,12 @@ class Context:
         a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
         self._check(self.L.pafgpu_result_device_ptrs(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return a.value, b.value, c.value
+
+    def encode_balance(self):
+        """-> (busiest SM's busy ms, mean busy ms over the SMs used, SMs used) of the last encode_kernel launch."""
+        mx, mean, n = C.c_double(), C.c_double(), C.c_int()
+        self._check(self.L.pafgpu_encode_balance(self.h, C.byref(mx), C.byref(mean), C.byref(n)))
+        return mx.value, mean.value, n.value
 
     def time_encode(self, reps):
         stage, kernel = C.c_float(), C.c_float()
