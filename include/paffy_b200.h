@@ -154,10 +154,23 @@ typedef struct {
     int64_t text_bytes;     /* bytes of output text waiting on the device */
     int64_t first_bad;      /* -1, or the index of the first record the reference would abort on */
     int64_t bad_line_begin, bad_line_end;
+    int64_t bad_kind;       /* 0: before the encode (parse, unknown contig, paf_check, walks outside the contig); after a trim: 1 = the
+                               moved coordinates fail paf_check, 2 = the closing assert of paf_trim_unreliable_tails (impl/paf.c:952) */
+    int64_t bad_coords[4];  /* bad_kind 1 / 2: query_start, query_end, target_start, target_end of that record after the trim */
     int64_t stats[7];       /* as pafgpu_file_report.stats, for the processed records */
     float ms_parse, ms_ingest, ms_kernel, ms_encode, ms_render; /* CUDA-event ms: text -> SoA, ingest, encode_kernel, encode stage, SoA -> text */
 } pafgpu_text_result;
 int pafgpu_add_mismatches_text(pafgpu_ctx *ctx, const char *text, int64_t n_bytes, pafgpu_text_result *res);
+/* The same with the pass that follows the encode in the pipeline chosen by `mode`: PAFGPU_MODE_ADD (plain), PAFGPU_MODE_ADD_TRIM
+ * (`| paffy trim -r trim_score_fraction -t trim_max_fraction`, or `-f -t trim_max_fraction` when trim_score_fraction < 0: the
+ * trim and the paf_check behind it run on the device, the lines are printed with the moved coordinates and the kept ops),
+ * PAFGPU_MODE_VIEW (`| paffy view -s -t`: only the totals in res->stats, no text). */
+typedef struct {
+    int mode;
+    float trim_score_fraction, trim_max_fraction;
+} pafgpu_text_opts;
+int pafgpu_add_mismatches_text_opts(pafgpu_ctx *ctx, const char *text, int64_t n_bytes, const pafgpu_text_opts *opts,
+                                    pafgpu_text_result *res);
 
 /* ---- device trim: replaces paf_trim_unreliable_tails (inc/paf.h:269, impl/paf.c:906-953) for the whole batch, on the
  *      encoded ops still resident on the device. score_fraction / max_fraction are `paffy trim -r / -t`. t_end: host

@@ -663,7 +663,8 @@ std::string failing_line_message(pafgpu_ctx *ctx, const char *b, const char *e, 
 void process_chunk_device(Filter &F, const char *text, size_t n_text, ChunkOut &R) {
     pafgpu_text_result tr;
     double t0 = now_s();
-    const int rc = pafgpu_add_mismatches_text(F.ctx, text, (int64_t)n_text, &tr);
+    const pafgpu_text_opts to{F.o.mode >= PAFGPU_MODE_VIEW ? (int)PAFGPU_MODE_VIEW : F.o.mode, F.o.trim_score_fraction, F.o.trim_max_fraction};
+    const int rc = pafgpu_add_mismatches_text_opts(F.ctx, text, (int64_t)n_text, &to, &tr);
     if (rc < 0) { R.rc = R.code = rc; R.err = pafgpu_last_error(F.ctx); return; }
     R.n_records = tr.records_in;
     R.rep = pafgpu_file_report{};
@@ -683,7 +684,30 @@ void process_chunk_device(Filter &F, const char *text, size_t n_text, ChunkOut &
     if (tr.first_bad >= 0) {
         R.rc = 1;
         R.rep.failed_record = tr.first_bad;
-        R.err = failing_line_message(F.ctx, text + tr.bad_line_begin, text + tr.bad_line_end, tr.first_bad);
+        if (tr.bad_kind == 0) {
+            R.err = failing_line_message(F.ctx, text + tr.bad_line_begin, text + tr.bad_line_end, tr.first_bad);
+        } else {
+            // the record failed behind the trim (impl/paf_trim.c:124 / impl/paf.c:952): the message shows it with the moved coordinates
+            Rec r;
+            std::vector<uint64_t> ops;
+            parse_line(text + tr.bad_line_begin, text + tr.bad_line_end, r, ops);
+            r.qs = tr.bad_coords[0]; r.qe = tr.bad_coords[1]; r.ts = tr.bad_coords[2]; r.te = tr.bad_coords[3];
+            std::string why = "trimmed alignment identity fell below the untrimmed identity (reference assert)";
+            bool any_op = false;
+            for (uint64_t w : ops) any_op = any_op || !(op_code(w) == OPM && op_len(w) == 0);
+            if (!any_op) {
+                R.err = "ERROR: paffy trim needs a cigar on every record (the reference aborts here)";
+                return;
+            }
+            if (tr.bad_kind == 1) {
+                Rec coords_only = r;
+                coords_only.has_cigar = false;
+                check_record(coords_only, nullptr, 0, &why);
+            }
+            std::string line;
+            render_prefix(r, line);
+            R.err = "ERROR: " + why + " " + line;
+        }
     }
 }
 
@@ -698,6 +722,15 @@ void process_chunk(Filter &F, const char *text, size_t n_text, ChunkOut &R) {
     };
     const int64_t batch_bases = F.o.batch_bases > 0 ? F.o.batch_bases : (int64_t)1 << 34;
     const int64_t batch_ops = (int64_t)1 << 30;
+    // `paffy trim` (alone or behind add_mismatches) on a record without ops - no cg tag, or only zero-length M ops, which the
+    // encoder drops: the identity is 0 / 0 and the reference's closing assert fires (impl/paf.c:952); the run ends there
+    auto no_ops_for_trim = [&](const Rec &r) {
+        if (trim_only) return r.op_end == r.op_begin;
+        if (F.o.mode != PAFGPU_MODE_ADD_TRIM) return false;
+        for (int64_t k = r.op_begin; k < r.op_end; k++)
+            if (!(op_code(F.in.ops[(size_t)k]) == OPM && op_len(F.in.ops[(size_t)k]) == 0)) return false;
+        return true;
+    };
     F.rep = pafgpu_file_report{};
     F.rep.failed_record = -1;
     F.err.clear();
@@ -728,7 +761,7 @@ void process_chunk(Filter &F, const char *text, size_t n_text, ChunkOut &R) {
                 Rec &r = Rv[(size_t)i];
                 bool fails = r.bad != 0;
                 if (!fails) {
-                    if (trim_only && r.op_end == r.op_begin) {
+                    if (no_ops_for_trim(r)) {
                         fails = true;
                     } else if (F.o.mode != PAFGPU_MODE_REMOVE && !trim_only) {
                         name.assign(r.qname, r.qname_len);
@@ -760,7 +793,7 @@ void process_chunk(Filter &F, const char *text, size_t n_text, ChunkOut &R) {
             std::string msg;
             if (r.bad) {
                 msg = "ERROR: " + parse_error(r);
-            } else if (trim_only && r.op_end == r.op_begin) {
+            } else if (no_ops_for_trim(r)) {
                 // no cg tag: the identity trim's closing assert sees 0/0 (impl/paf.c:952), the fixed trim reads a NULL
                 // cigar (impl/paf.c:520): the reference dies on this record either way
                 msg = "ERROR: paffy trim needs a cigar on every record (the reference aborts here)";
@@ -1042,7 +1075,11 @@ int pafgpu_add_mismatches_file_filtered(pafgpu_ctx *ctx, const char *in_path, co
     };
 
     // ---- queues
-    const bool device_text = ctx && o.mode == PAFGPU_MODE_ADD && !filter && !getenv("PAFFY_HOST_PARSE");
+    // the text of a chunk is handled on the device end to end for add_mismatches, add_mismatches | trim and the totals of
+    // view -s -t; per-alignment view lines, trim alone and the fused filter parse on host threads
+    const bool device_text = ctx && !filter && !getenv("PAFFY_HOST_PARSE") &&
+                             (o.mode == PAFGPU_MODE_ADD || o.mode == PAFGPU_MODE_ADD_TRIM ||
+                              (o.mode >= PAFGPU_MODE_VIEW && !(o.mode & PAFGPU_VIEW_PER_ALIGNMENT)));
     const size_t chunk_bytes = (size_t)std::min<int64_t>(o.chunk_bytes > 0 ? o.chunk_bytes : (int64_t)32 << 20, (int64_t)1 << 30);
     std::mutex mu;
     std::condition_variable cv_job, cv_done, cv_room;

@@ -1117,7 +1117,14 @@ struct Carver {
 }  // namespace
 
 extern "C" int pafgpu_add_mismatches_text(pafgpu_ctx *c, const char *text, int64_t n_bytes, pafgpu_text_result *res) {
+    return pafgpu_add_mismatches_text_opts(c, text, n_bytes, nullptr, res);
+}
+
+extern "C" int pafgpu_add_mismatches_text_opts(pafgpu_ctx *c, const char *text, int64_t n_bytes, const pafgpu_text_opts *opts,
+                                               pafgpu_text_result *res) {
     if (!c || !res || n_bytes < 0 || (n_bytes && !text)) return PAFGPU_EINVAL;
+    const int mode = opts ? opts->mode : PAFGPU_MODE_ADD;
+    if (mode != PAFGPU_MODE_ADD && mode != PAFGPU_MODE_ADD_TRIM && mode != PAFGPU_MODE_VIEW) return fail(c, PAFGPU_EINVAL, "text mode: add, add + trim, or view totals");
     if (n_bytes >= ((int64_t)1 << 31)) return fail(c, PAFGPU_EINVAL, "text chunk too large: cut it (32-bit byte offsets)");
     std::lock_guard<std::mutex> lk(c->mu);
     CU(cudaSetDevice(c->device));
@@ -1243,14 +1250,89 @@ extern "C" int pafgpu_add_mismatches_text(pafgpu_ctx *c, const char *text, int64
     res->ms_ingest = er.ms_ingest; res->ms_kernel = er.ms_kernel; res->ms_encode = er.ms_encode;
     cudaEventElapsedTime(&res->ms_parse, c->ev_tx[0], c->ev_tx[1]);
 
+    // totals for the report: sums over the input ops by kind + the mismatches the kernel tallied
+    tx_op_totals_kernel<<<(unsigned)std::min<int64_t>(blocks_for(N, 256 * 8), 1184), 256, 0, c->stream>>>(c->tx_ops.as<uint64_t>(), N,
+                                                                                                     (unsigned long long *)(scal + 4));
+    tx_sum_kernel<<<(unsigned)std::min<int64_t>(blocks_for(R, 256 * 8), 1184), 256, 0, c->stream>>>((const unsigned long long *)c->rec_mism.p, R,
+                                                                                               (unsigned long long *)(scal + 12));
+    auto totals = [&](int64_t records) -> int {
+        uint64_t tot[9];
+        CU(read_words(c, tot, scal + 4, 9));
+        const int64_t mm = (int64_t)tot[8];
+        res->stats[0] = (int64_t)tot[0] + (int64_t)tot[1] - mm;  // matches: M and = bases that are no mismatches
+        res->stats[1] = (int64_t)tot[2] + mm;
+        res->stats[2] = (int64_t)tot[3]; res->stats[3] = (int64_t)tot[5];
+        res->stats[4] = (int64_t)tot[4]; res->stats[5] = (int64_t)tot[6];
+        res->stats[6] = records;
+        return 0;
+    };
+    if (mode == PAFGPU_MODE_VIEW) return totals(R);  // `view -s -t`: nothing is printed per record
+
     // ---- output text: prefix of every record measured, the lines laid out, prefixes and ops rendered in place
-    const int64_t K = c->n_out;
+    int64_t K = c->n_out;
     CU(cudaEventRecord(c->ev_tx[2], c->stream));
     tx_empty_out_begin_kernel<<<blocks_for(R, 256), 256, 0, c->stream>>>(R, op_begin, c->op_rec.as<uint32_t>(), N,
                                                                          (const unsigned long long *)(c->scalars.as<uint64_t>() + SC_TOTAL),
                                                                          c->rec_out_begin.as<int64_t>());
+    TextRecords TP = T;  // the columns the lines are printed from (trimmed coordinates in add + trim mode)
+    const int64_t R_enc = R;
+    if (mode == PAFGPU_MODE_ADD_TRIM) {
+        // paf_trim_unreliable_tails / paf_trim_end_fraction on the encoded ops (trim.cuh), then the reference's paf_check
+        // behind the trim; the first record that fails ends the output
+        const bool fixed = opts->trim_score_fraction < 0;
+        const size_t rb = (size_t)R * 8;
+        CU(c->trim_coords.ensure(4 * rb));
+        CU(c->trim_lo.ensure(rb));
+        CU(c->trim_hi.ensure(rb));
+        CU(c->trim_failed.ensure((size_t)R));
+        int64_t *co = c->trim_coords.as<int64_t>();
+        CU(cudaMemcpyAsync(co, T.qs, rb, cudaMemcpyDeviceToDevice, c->stream));
+        CU(cudaMemcpyAsync(co + R, T.qe, rb, cudaMemcpyDeviceToDevice, c->stream));
+        CU(cudaMemcpyAsync(co + 2 * R, T.ts, rb, cudaMemcpyDeviceToDevice, c->stream));
+        CU(cudaMemcpyAsync(co + 3 * R, T.te, rb, cudaMemcpyDeviceToDevice, c->stream));
+        TrimParams TR{};
+        TR.n_records = R; TR.out = c->out.as<uint64_t>(); TR.rec_out_begin = c->rec_out_begin.as<int64_t>();
+        TR.same_strand = T.strand;
+        TR.qs = co; TR.qe = co + R; TR.ts = co + 2 * R; TR.te = co + 3 * R;
+        TR.lo = c->trim_lo.as<int64_t>(); TR.hi = c->trim_hi.as<int64_t>(); TR.failed = c->trim_failed.as<uint8_t>();
+        TR.score_fraction = opts->trim_score_fraction; TR.max_fraction = opts->trim_max_fraction;
+        bool by_warp = K / R > 64;
+        if (const char *e = getenv("PAFGPU_TRIM_WARP")) by_warp = atoi(e) != 0;
+        if (fixed) trim_fixed_kernel<<<blocks_for(R, 128), 128, 0, c->stream>>>(TR, c->out.as<uint64_t>());
+        else if (by_warp) trim_warp_kernel<<<blocks_for(R * 32, 128), 128, 0, c->stream>>>(TR);
+        else trim_kernel<<<blocks_for(R, 128), 128, 0, c->stream>>>(TR);
+        CU(cudaMemsetAsync(scal + 16, 0xff, 8, c->stream));
+        tx_trim_check_kernel<<<blocks_for(R, 256), 256, 0, c->stream>>>(R, TR.qs, TR.qe, TR.ts, TR.te, T.qlen, T.tlen, op_begin, TR.failed,
+                                                                        (unsigned long long *)(scal + 16));
+        uint64_t bad2 = 0;
+        CU(read_words(c, &bad2, scal + 16, 1));
+        TP.qs = TR.qs; TP.qe = TR.qe; TP.ts = TR.ts; TP.te = TR.te;
+        c->trimmed = true;
+        if (bad2 != ~0ull && (int64_t)bad2 < R) {
+            // the run ends at that record: its moved coordinates go back for the message
+            R = (int64_t)bad2;
+            uint8_t fl = 0;
+            uint32_t ends[2] = {0, 0};
+            for (int q = 0; q < 4; q++) CU(cudaMemcpyAsync(&res->bad_coords[q], co + q * R_enc + R, 8, cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaMemcpyAsync(&fl, TR.failed + R, 1, cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaMemcpyAsync(&K, c->rec_out_begin.as<int64_t>() + R, 8, cudaMemcpyDeviceToHost, c->stream));
+            if (R > 0) CU(cudaMemcpyAsync(&ends[0], nl_pos + R - 1, 4, cudaMemcpyDeviceToHost, c->stream));
+            CU(cudaMemcpyAsync(&ends[1], nl_pos + R, 4, cudaMemcpyDeviceToHost, c->stream));
+            CU(stream_sync(c));
+            res->first_bad = R;
+            int64_t ob[2] = {0, 1};
+            CU(cudaMemcpy(ob, op_begin + R, 16, cudaMemcpyDeviceToHost));
+            res->bad_kind = (fl || ob[1] == ob[0]) ? 2 : 1;
+            res->bad_line_begin = R > 0 ? (int64_t)ends[0] + 1 : 0;
+            res->bad_line_end = std::min<int64_t>(ends[1], n_bytes);
+            res->records = R;
+            if (R == 0) { res->text_bytes = 0; c->ser_text_bytes = 0; return totals(R_enc); }
+        }
+    } else {
+        c->trimmed = false;
+    }
     PrefixParams PR{};
-    PR.text = d_text; PR.n_records = R; PR.R = T; PR.prefix_len = prefix_len;
+    PR.text = d_text; PR.n_records = R; PR.R = TP; PR.prefix_len = prefix_len;
     tx_prefix_kernel<false><<<blocks_for(R, 128), 128, 0, c->stream>>>(PR);
     CU(c->ser_prefix_begin.ensure((size_t)(R + 1) * 8));
     if (int rc = scan_u32(c, prefix_len, R, c->ser_prefix_begin.as<uint64_t>(), nullptr)) return rc;
@@ -1258,16 +1340,12 @@ extern "C" int pafgpu_add_mismatches_text(pafgpu_ctx *c, const char *text, int64
     CU(c->ser_optoff.ensure((size_t)(K + 1) * 8));
     CU(c->ser_line_begin.ensure((size_t)(R + 1) * 8));
     if (K > 0)
-        op_text_len_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(c->out.as<uint64_t>(), K, c->ser_oplen.as<uint32_t>(),
-                                                                                          c->rec_out_begin.as<int64_t>(), R, nullptr, nullptr);
+        op_text_len_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(
+            c->out.as<uint64_t>(), K, c->ser_oplen.as<uint32_t>(), c->rec_out_begin.as<int64_t>(), R,
+            c->trimmed ? c->trim_lo.as<int64_t>() : nullptr, c->trimmed ? c->trim_hi.as<int64_t>() : nullptr);
     if (int rc = scan_u32(c, c->ser_oplen.as<uint32_t>(), K, c->ser_optoff.as<uint64_t>(), nullptr)) return rc;
     line_begin_kernel<<<blocks_for(R + 1, 256), 256, 0, c->stream>>>(R, c->ser_prefix_begin.as<int64_t>(), c->rec_out_begin.as<int64_t>(),
                                                                      c->ser_optoff.as<uint64_t>(), c->ser_line_begin.as<int64_t>());
-    // totals for the report while the layout is read back
-    tx_op_totals_kernel<<<(unsigned)std::min<int64_t>(blocks_for(N, 256 * 8), 1184), 256, 0, c->stream>>>(c->tx_ops.as<uint64_t>(), N,
-                                                                                                     (unsigned long long *)(scal + 4));
-    tx_sum_kernel<<<(unsigned)std::min<int64_t>(blocks_for(R, 256 * 8), 1184), 256, 0, c->stream>>>((const unsigned long long *)c->rec_mism.p, R,
-                                                                                               (unsigned long long *)(scal + 12));
     int64_t total = 0;
     CU(read_words(c, (uint64_t *)&total, c->ser_line_begin.as<uint64_t>() + R, 1));
     CU(c->ser_text.ensure((size_t)std::max<int64_t>(total, 8)));
@@ -1281,19 +1359,11 @@ extern "C" int pafgpu_add_mismatches_text(pafgpu_ctx *c, const char *text, int64
     tx_prefix_kernel<true><<<blocks_for(R, 128), 128, 0, c->stream>>>(PR);
     if (K > 0) op_text_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(S);
     CU(cudaEventRecord(c->ev_tx[3], c->stream));
-    uint64_t tot[9];
-    CU(read_words(c, tot, scal + 4, 9));
+    if (int rc = totals(R_enc)) return rc;
     CU(cudaGetLastError());
     cudaEventElapsedTime(&res->ms_render, c->ev_tx[2], c->ev_tx[3]);
-    const int64_t mm = (int64_t)tot[8];
-    res->stats[0] = (int64_t)tot[0] + (int64_t)tot[1] - mm;  // matches: M and = bases that are no mismatches
-    res->stats[1] = (int64_t)tot[2] + mm;
-    res->stats[2] = (int64_t)tot[3]; res->stats[3] = (int64_t)tot[5];
-    res->stats[4] = (int64_t)tot[4]; res->stats[5] = (int64_t)tot[6];
-    res->stats[6] = R;
     res->text_bytes = total;
     c->ser_text_bytes = total;
-    c->trimmed = false;
     return 0;
 }
 

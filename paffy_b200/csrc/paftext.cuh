@@ -246,59 +246,79 @@ struct OpsParams {
 };
 
 // WRITE = false: count the ops of the tile. WRITE = true: write them. Both walk the tile the same way: thread t owns bytes
-// [16 t, 16 t + 16), knows the record of its first byte from the newline prefix, and treats every byte inside the cg value
-// of its record.
+// [16 t, 16 t + 16) (one 16-byte load), knows the record of its first byte from the newline prefix, and parses the bytes
+// inside the cg value of their record FORWARD: a digit extends the running number, a letter closes an op of that length.
+// Only a number that began before the thread's first byte needs a look back (at most once per thread).
 template <bool WRITE>
 __global__ void __launch_bounds__(TX_THREADS) tx_ops_kernel(OpsParams P) {
     __shared__ uint32_t s_total;
     if (threadIdx.x == 0) s_total = 0;
     const int64_t b0 = (int64_t)blockIdx.x * TX_TILE + (int64_t)threadIdx.x * TX_PER_THREAD;
     char c[TX_PER_THREAD];
+    if (b0 + TX_PER_THREAD <= P.n) {  // (the text buffer is 16-byte aligned and padded)
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(P.text + b0));
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < TX_PER_THREAD; k++) c[k] = (char)((w[k >> 2] >> (8 * (k & 3))) & 0xffu);
+    } else {
+#pragma unroll
+        for (int k = 0; k < TX_PER_THREAD; k++) c[k] = b0 + k < P.n ? P.text[b0 + k] : (char)'\n';
+    }
     uint32_t nl = 0;
 #pragma unroll
-    for (int k = 0; k < TX_PER_THREAD; k++) {
-        c[k] = b0 + k < P.n ? P.text[b0 + k] : (char)'\n';
-        nl += c[k] == '\n';
-    }
+    for (int k = 0; k < TX_PER_THREAD; k++) nl += c[k] == '\n';
     uint32_t dummy, en;
     tx_block_excl2(nl, 0u, en, dummy);
-    int64_t rec = (int64_t)P.nl_off[blockIdx.x] + en;
-    uint32_t cgb = 0, cge = 0;
-    if (rec < P.n_records) { cgb = P.cg_begin[rec]; cge = P.cg_end[rec]; }
-    // pass 1: count
-    uint32_t mine = 0;
-    bool is_op[TX_PER_THREAD];
-    {
-        int64_t rr = rec;
-        uint32_t b = cgb, e = cge;
+    const int64_t rec0 = (int64_t)P.nl_off[blockIdx.x] + en;
+    uint32_t cgb0 = 0, cge0 = 0;
+    if (rec0 < P.n_records) { cgb0 = P.cg_begin[rec0]; cge0 = P.cg_end[rec0]; }
+
+    // one walk over the 16 bytes; emit(k, code, len) is called for every op that is kept
+    auto walk = [&](auto emit, auto line_end) {
+        int64_t rr = rec0;
+        uint32_t b = cgb0, e = cge0;
+        uint64_t v = 0;
+        uint32_t nd = 0;                                             // digits of the running number seen in this window
+        bool from_before = (uint32_t)b0 > b && (uint32_t)b0 < e;     // the running number may have begun before the window
 #pragma unroll
         for (int k = 0; k < TX_PER_THREAD; k++) {
             const uint32_t i = (uint32_t)(b0 + k);
-            is_op[k] = false;
+            const char ch = c[k];
             if (b0 + k < P.n && i >= b && i < e) {
-                const char ch = c[k];
-                const int code = tx_op_code(ch);
-                if (code >= 0) {
-                    bool keep = true;
-                    if (code == OP_M) {  // a zero-length M op vanishes (SURVEY a1-edge ii)
-                        uint32_t digits;
-                        keep = tx_number_before(P.text, i, b, digits) != 0;
+                if (ch >= '0' && ch <= '9') {
+                    v = v * 10 + (uint64_t)(ch - '0');
+                    nd++;
+                    if (i + 1 == e && !WRITE) atomicMin(P.first_bad, (unsigned long long)rr);  // digits without a letter (the reference reads the NUL as one)
+                } else {
+                    const int code = tx_op_code(ch);
+                    if (code >= 0) {
+                        uint64_t len = v;
+                        if (from_before) {  // the digits before the window come first
+                            uint32_t dg;
+                            uint64_t head = tx_number_before(P.text, (uint32_t)b0, b, dg);
+                            for (uint32_t q = 0; q < nd; q++) head *= 10;
+                            len += head;
+                        }
+                        if (!(code == OP_M && len == 0)) emit(k, code, len);  // a zero-length M op vanishes (SURVEY a1-edge ii)
+                    } else if (!WRITE) {
+                        atomicMin(P.first_bad, (unsigned long long)rr);  // impl/paf.c:102
                     }
-                    is_op[k] = keep;
-                    mine += keep;
-                } else if (ch < '0' || ch > '9') {
-                    if (!WRITE) atomicMin(P.first_bad, (unsigned long long)rr);  // impl/paf.c:102
-                } else if (i + 1 == e) {
-                    if (!WRITE) atomicMin(P.first_bad, (unsigned long long)rr);  // digits without a letter: the reference reads the NUL as one
+                    v = 0; nd = 0; from_before = false;
                 }
+            } else {
+                v = 0; nd = 0; from_before = false;
             }
-            if (c[k] == '\n') {
+            if (ch == '\n' && b0 + k < P.n) {
                 rr++;
+                line_end(rr);
                 b = e = 0;
                 if (rr < P.n_records) { b = P.cg_begin[rr]; e = P.cg_end[rr]; }
             }
         }
-    }
+    };
+
+    uint32_t mine = 0;
+    walk([&](int, int, uint64_t) { mine++; }, [&](int64_t) {});
     if (!WRITE) {
 #pragma unroll
         for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(FULL, mine, o);
@@ -311,24 +331,8 @@ __global__ void __launch_bounds__(TX_THREADS) tx_ops_kernel(OpsParams P) {
     uint32_t eo;
     tx_block_excl2(mine, 0u, eo, dummy);
     uint64_t at = P.op_off[blockIdx.x] + eo;
-    {
-        int64_t rr = rec;
-        uint32_t b = cgb;
-#pragma unroll
-        for (int k = 0; k < TX_PER_THREAD; k++) {
-            const uint32_t i = (uint32_t)(b0 + k);
-            if (is_op[k]) {
-                uint32_t digits;
-                const uint64_t len = tx_number_before(P.text, i, b, digits);
-                P.ops[at++] = (len & LEN_MASK) | ((uint64_t)tx_op_code(c[k]) << 56);
-            }
-            if (c[k] == '\n' && b0 + k < P.n) {
-                rr++;
-                P.op_begin[rr] = (int64_t)at;  // ops before the line that starts here (the last newline leaves the total)
-                b = rr < P.n_records ? P.cg_begin[rr] : 0u;
-            }
-        }
-    }
+    walk([&](int, int code, uint64_t len) { P.ops[at++] = (len & LEN_MASK) | ((uint64_t)code << 56); },
+         [&](int64_t rr) { P.op_begin[rr] = (int64_t)at; });  // ops before the line that starts here (the last newline leaves the total)
 }
 
 // ---- prefix: the bytes before the CIGAR ops ---------------------------------------------------------------------------
@@ -424,6 +428,21 @@ __global__ void __launch_bounds__(256) tx_sum_kernel(const unsigned long long *_
 #pragma unroll
     for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
     if ((threadIdx.x & 31) == 0 && s) atomicAdd(out, s);
+}
+
+// paf_check after a trim (impl/paf_trim.c:124): the coordinate tests on the moved coordinates (the op sums follow them by
+// construction of the trim), and the reference's closing assert of paf_trim_unreliable_tails (`failed`). Locates the first
+// record that fails.
+__global__ void tx_trim_check_kernel(int64_t n_records, const int64_t *__restrict__ qs, const int64_t *__restrict__ qe, const int64_t *__restrict__ ts,
+                                     const int64_t *__restrict__ te, const int64_t *__restrict__ qlen, const int64_t *__restrict__ tlen,
+                                     const int64_t *__restrict__ op_begin, const uint8_t *__restrict__ failed, unsigned long long *first_bad) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_records) return;
+    // a record without ops (no cg tag, or nothing but zero-length M ops): the reference's trim sees 0 / 0 = NaN and its
+    // closing assert fires (impl/paf.c:952); the run ends there
+    const bool bad = op_begin[r + 1] == op_begin[r] || failed[r] || qs[r] < 0 || qs[r] >= qlen[r] || qs[r] > qe[r] || qe[r] > qlen[r] || ts[r] < 0 || ts[r] >= tlen[r] ||
+                     ts[r] > te[r] || te[r] > tlen[r];
+    if (bad) atomicMin(first_bad, (unsigned long long)r);
 }
 
 // rec_out_begin of records without ops (no cg tag, or only zero-length M ops): the encode kernel never meets them; their

@@ -22,7 +22,7 @@ ABI_SYMBOLS = [
     "pafgpu_serialise", "pafgpu_fetch_text", "pafgpu_encode_one", "pafgpu_time_encode",
     "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition", "pafgpu_trim",
     "pafgpu_trim_fixed", "pafgpu_stage_ops_host", "pafgpu_add_mismatches_file_filtered",
-    "pafgpu_add_mismatches_text", "pafgpu_create_sibling", "pafgpu_helper", "pafgpu_encode_balance", "pafgpu_encode_one_resident", "pafgpu_genome_clear", "pafgpu_genome_total_bases", "pafgpu_device_of", "pafgpu_genome_clone", "pafgpu_genome_save", "pafgpu_genome_load_packed",
+    "pafgpu_add_mismatches_text", "pafgpu_add_mismatches_text_opts", "pafgpu_create_sibling", "pafgpu_helper", "pafgpu_encode_balance", "pafgpu_encode_one_resident", "pafgpu_genome_clear", "pafgpu_genome_total_bases", "pafgpu_device_of", "pafgpu_genome_clone", "pafgpu_genome_save", "pafgpu_genome_load_packed",
 ]
 # reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
 REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paffy_view_main", "paffy_trim_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
@@ -61,7 +61,7 @@ class FileReport(C.Structure):
 class TextResult(C.Structure):
     _fields_ = [("records", C.c_int64), ("records_in", C.c_int64), ("n_ops", C.c_int64), ("n_out_ops", C.c_int64),
                 ("aligned_bases", C.c_int64), ("text_bytes", C.c_int64), ("first_bad", C.c_int64), ("bad_line_begin", C.c_int64),
-                ("bad_line_end", C.c_int64), ("stats", C.c_int64 * 7), ("ms_parse", C.c_float), ("ms_ingest", C.c_float),
+                ("bad_line_end", C.c_int64), ("bad_kind", C.c_int64), ("bad_coords", C.c_int64 * 4), ("stats", C.c_int64 * 7), ("ms_parse", C.c_float), ("ms_ingest", C.c_float),
                 ("ms_kernel", C.c_float), ("ms_encode", C.c_float), ("ms_render", C.c_float)]
 
 

@@ -492,6 +492,38 @@ def test_device_text_path_matches_the_reference_on_decorated_lines(fresh, seed, 
         del os.environ["PAFFY_HOST_PARSE"]
     assert rc == 0 and out2.read_bytes() == want.read_bytes()
     assert list(rep2.stats) == list(rep.stats) and rep2.aligned_bases == rep.aligned_bases
+    # add_mismatches | trim and the totals of view -s -t: device text path against the host-parse path and the reference.
+    # `paffy trim` aborts on a record without ops (its identity is 0 / 0, impl/paf.c:952): lines 4 and 5 of every 11 have
+    # no cigar, so the whole file ends at record 4 in both paths; the comparison with the reference runs without them.
+    for host_parse in (False, True):
+        if host_parse:
+            os.environ["PAFFY_HOST_PARSE"] = "1"
+        try:
+            o = tmp_path / "cut.out"
+            rc, r = fresh.add_mismatches_file(str(paf), str(o), mode=2, chunk_bytes=5000)
+            assert rc == 1 and r.failed_record == 4 and o.read_bytes().count(b"\n") == 4
+            assert "needs a cigar" in fresh.last_error()
+        finally:
+            os.environ.pop("PAFFY_HOST_PARSE", None)
+    with_cigar = [ln for i, ln in enumerate(lines) if i % 11 not in (4, 5)]
+    paf.write_text("\n".join(with_cigar) + "\n")
+    r = subprocess.run([O.REF_PAFFY, "add_mismatches", str(fa), "-i", str(paf), "-o", str(want)], capture_output=True) if O.ref_available() else None
+    for mode, ref_cmd in ((2, ["trim"]), (4 | 2, ["view", "-s", "-t", str(fa)])):
+        got = {}
+        for host_parse in (False, True):
+            if host_parse:
+                os.environ["PAFFY_HOST_PARSE"] = "1"
+            try:
+                o = tmp_path / f"m{mode}_{int(host_parse)}.out"
+                rc, r = fresh.add_mismatches_file(str(paf), str(o), mode=mode, chunk_bytes=5000)
+                assert rc == 0
+                got[host_parse] = (o.read_bytes(), list(r.stats))
+            finally:
+                os.environ.pop("PAFFY_HOST_PARSE", None)
+        assert got[False] == got[True], mode
+        if O.ref_available():
+            r = subprocess.run([O.REF_PAFFY] + ref_cmd + ["-i", str(want)], capture_output=True)
+            assert r.returncode == 0 and r.stdout == got[False][0], mode
 
 
 def test_device_text_path_locates_the_record_the_reference_aborts_on(fresh, tmp_path):
@@ -575,3 +607,37 @@ def test_cli_uses_the_packed_genome_cache(tmp_path):
     os.utime(fa, (1, 1))
     r3 = subprocess.run(args, capture_output=True, env=env)
     assert r3.returncode == 0 and r3.stdout == golden("rand101.add.paf") and b"Parsing sequence file" in r3.stderr
+
+
+def test_paf_encode_mismatches_keeps_contigs_resident():
+    """The library symbol called record after record with the same whole-contig strings (the loop of `paffy view` / Cactus):
+    results equal the oracle's every time, on both strands, and a different string behind a reused pointer is noticed."""
+    from oracle import pyoracle as O
+    from tests.test_paf_api import Paf
+    lib = paffy_b200.load()
+    lib.paf_parse.restype = C.POINTER(Paf)
+    lib.paf_parse.argtypes = [C.c_char_p, C.c_bool]
+    lib.paf_encode_mismatches.argtypes = [C.POINTER(Paf), C.c_char_p, C.c_char_p]
+    lib.paf_encode_mismatches.restype = None
+    lib.paf_print.restype = C.c_void_p
+    lib.paf_print.argtypes = [C.POINTER(Paf)]
+    case = util.random_case(91, n_records=60, contig_len=20000, n_ops=10, max_len=700, p_weird=0.002)
+    bufs = {name: C.create_string_buffer(seq, len(seq) + 1) for name, seq in case["contigs"].items()}
+    want = util.oracle_encode(case)
+    for rnd in range(2):
+        for r, line, (enc, _) in zip(case["records"], util.case_lines(case), want):
+            p = lib.paf_parse(C.create_string_buffer(line.encode()), True)
+            lib.paf_encode_mismatches(p, bufs[r["q"]], bufs[r["t"]])
+            s = lib.paf_print(p)
+            got = C.string_at(s).decode()
+            assert got.split("cg:Z:")[1] == O.cigar_str(enc), (rnd, line)
+    # the same buffer now holds another sequence: the fingerprint of its head changes, the contig is packed again
+    name = case["records"][0]["q"]
+    other = bytes(reversed(case["contigs"][name]))
+    C.memmove(bufs[name], other, len(other))
+    case["contigs"][name] = other
+    want2 = util.oracle_encode(case)
+    for r, line, (enc, _) in zip(case["records"], util.case_lines(case), want2):
+        p = lib.paf_parse(C.create_string_buffer(line.encode()), True)
+        lib.paf_encode_mismatches(p, bufs[r["q"]], bufs[r["t"]])
+        assert C.string_at(lib.paf_print(p)).decode().split("cg:Z:")[1] == O.cigar_str(enc)

@@ -12,4 +12,6 @@ timeout 1200 ncu --set full --clock-control none --import-source on -k 'regex:^(
 echo "encode capture exit $?"
 timeout 1500 ncu --set full --clock-control none -k 'regex:^(ingest_kernel|tx_|op_text|line_begin|stitch_kernel)' -c 40 -o $out/prof_others $B > $out/ncu_others.log 2>&1
 echo "others capture exit $?"
+# the report of 40 full captures is tens of MB (gpurun brings back at most 64 MiB): keep its raw page as CSV only
+ncu -i $out/prof_others.ncu-rep --page raw --csv > $out/others_raw.csv 2>/dev/null && rm -f $out/prof_others.ncu-rep
 ls -la $out
