@@ -9,7 +9,7 @@ LIB = os.path.join(HERE, "libpaffy_b200.so")
 SOURCES = ["pafgpu.cu", "paf_host.cpp", "paf_compat.cpp", "paf_api.cpp"]
 CLI = os.path.join(HERE, "paffy_b200_cli")
 STPAF = os.path.join(HERE, "libpaffy_b200_stpaf.a")
-HEADERS = ["kernels.cuh", "encode.cuh", "serialise.cuh", "trim.cuh", "internal.h", "paf_text.h", "paf_sonlib.c", "paffy_main.c", os.path.join("..", "..", "include", "paf_b200_compat.h"), os.path.join("..", "..", "include", "paffy_b200.h")]
+HEADERS = ["kernels.cuh", "encode.cuh", "serialise.cuh", "trim.cuh", "paftext.cuh", "internal.h", "paf_text.h", "paf_sonlib.c", "paffy_main.c", os.path.join("..", "..", "include", "paf_b200_compat.h"), os.path.join("..", "..", "include", "paffy_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--use_fast_math=false",
               "-Xcompiler", "-fPIC,-O3,-Wall,-fvisibility=default", "-Xptxas", "-v", "-shared", "-cudart", "shared",
               "-Xlinker", "-Bsymbolic"]

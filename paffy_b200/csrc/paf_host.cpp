@@ -637,6 +637,35 @@ struct ChunkOut {
     bool ready = false;
 };
 
+// paf_check runs behind the encode (impl/paf_add_mismatches.c:130-133), so its message shows the record with its =/X
+// CIGAR: the one record is encoded by itself (a batch of one). Where that is impossible - the record walks outside its
+// contig - the input CIGAR is shown.
+std::string record_as_the_reference_prints_it(pafgpu_ctx *ctx, const Rec &r, const std::vector<uint64_t> &ops) {
+    std::vector<uint64_t> kept, enc;
+    for (int64_t k = r.op_begin; k < r.op_end; k++)
+        if (!(op_code(ops[(size_t)k]) == OPM && op_len(ops[(size_t)k]) == 0)) kept.push_back(ops[(size_t)k]);
+    const uint64_t *shown = ops.data() + r.op_begin;
+    int64_t n_shown = r.op_end - r.op_begin;
+    if (ctx && r.has_cigar) {
+        const std::string qn(r.qname, r.qname_len), tn(r.tname, r.tname_len);
+        const int32_t qc = (int32_t)pafgpu_genome_find(ctx, qn.c_str()), tc = (int32_t)pafgpu_genome_find(ctx, tn.c_str());
+        const int64_t begin[2] = {0, (int64_t)kept.size()};
+        const uint8_t strand = r.same_strand ? 1 : 0;
+        pafgpu_batch B{1, (int64_t)kept.size(), begin, kept.data(), &qc, &tc, &r.qs, &r.qe, &r.ts, &strand};
+        pafgpu_result res;
+        if (kept.empty()) {
+            n_shown = 0;
+        } else if (qc >= 0 && tc >= 0 && pafgpu_encode_batch_host(ctx, &B, &res) == 0) {
+            enc.resize((size_t)std::max<int64_t>(res.n_out_ops, 1));
+            if (pafgpu_fetch_ops(ctx, enc.data(), nullptr, nullptr) == 0) { shown = enc.data(); n_shown = res.n_out_ops; }
+        }
+    }
+    std::string line;
+    render_line(r, shown, n_shown, line);
+    if (!line.empty() && line.back() == '\n') line.pop_back();
+    return line;
+}
+
 // The message the reference would die with on the line [b, e) (parse error, unknown contig, paf_check), or the bounds
 // message when the record passes all of those (it then walks outside its contig, which is undefined behaviour there).
 std::string failing_line_message(pafgpu_ctx *ctx, const char *b, const char *e, int64_t index) {
@@ -648,11 +677,7 @@ std::string failing_line_message(pafgpu_ctx *ctx, const char *b, const char *e, 
     if (pafgpu_genome_find(ctx, qn.c_str()) < 0) return "No query sequence named: " + qn + " found";
     if (pafgpu_genome_find(ctx, tn.c_str()) < 0) return "No target sequence named: " + tn + " found";
     std::string why;
-    if (check_record(r, ops.data() + r.op_begin, r.op_end - r.op_begin, &why)) {
-        std::string line;
-        render_line(r, ops.data() + r.op_begin, r.op_end - r.op_begin, line);
-        return "ERROR: " + why + " " + line;
-    }
+    if (check_record(r, ops.data() + r.op_begin, r.op_end - r.op_begin, &why)) return "ERROR: " + why + " " + record_as_the_reference_prints_it(ctx, r, ops);
     char buf[160];
     snprintf(buf, sizeof buf, "ERROR: record %lld: CIGAR/coordinates walk outside the contig", (long long)index);
     return buf;
@@ -803,10 +828,8 @@ void process_chunk(Filter &F, const char *text, size_t n_text, ChunkOut &R) {
             } else {
                 std::string why;
                 check_record(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, &why);
-                // (the reference prints the record as it stands after encoding; this message shows its input CIGAR)
-                std::string line;
-                render_line(r, F.in.ops.data() + r.op_begin, r.op_end - r.op_begin, line);
-                msg = "ERROR: " + why + " " + line;
+                // (add_mismatches checks behind the encode: the record is shown with its =/X CIGAR; `-a` shows the merged one)
+                msg = "ERROR: " + why + " " + record_as_the_reference_prints_it(F.o.mode == PAFGPU_MODE_REMOVE ? nullptr : ctx, r, F.in.ops);
             }
             stop = i;
             F.err = msg;

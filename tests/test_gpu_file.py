@@ -64,7 +64,13 @@ def test_error_paths_match_reference(fresh, tmp_path):
         assert out.read_text() == e["stdout"], name
         assert rep.failed_record == 1
         msg = fresh.last_error()
-        assert e["stderr_message"].split(" q\t")[0].replace("ERROR: ", "") in msg, (name, msg)
+        assert msg == e["stderr_message"], (name, msg)  # paf_check's message shows the record with its =/X CIGAR, as the reference's does
+        os.environ["PAFFY_HOST_PARSE"] = "1"
+        try:
+            rc, rep = fresh.add_mismatches_file(str(inp), str(out))
+        finally:
+            del os.environ["PAFFY_HOST_PARSE"]
+        assert rc == 1 and out.read_text() == e["stdout"] and fresh.last_error() == e["stderr_message"], name
 
 
 def test_record_outside_contig_ends_run(fresh, tmp_path):
