@@ -409,8 +409,14 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
         // per record better than finishing a record in one stride (measured at C2, 20 ops per record: 4 lanes 0.53 ms,
         // 8 lanes 0.58 ms, 16 lanes 0.69 ms, 32 lanes 0.90 ms for the ingest stage)
         int64_t mean_ops = N / R;
-        if (const char *e = getenv("PAFGPU_INGEST_G")) mean_ops = atoi(e) <= 4 ? 1 : atoi(e) == 8 ? 100 : atoi(e) == 16 ? 1000 : 100000;  // experiments
-        if (mean_ops <= 64) ingest_kernel<4><<<blocks_for(R * 4, 256), 256, 0, c->stream>>>(I);
+        int force_g = 0;
+        if (const char *e = getenv("PAFGPU_INGEST_G")) {  // experiments
+            force_g = atoi(e);
+            mean_ops = force_g <= 4 ? 1 : force_g == 8 ? 100 : force_g == 16 ? 1000 : 100000;
+        }
+        if (force_g == 1) ingest_kernel<1><<<blocks_for(R, 256), 256, 0, c->stream>>>(I);
+        else if (force_g == 2) ingest_kernel<2><<<blocks_for(R * 2, 256), 256, 0, c->stream>>>(I);
+        else if (mean_ops <= 64) ingest_kernel<4><<<blocks_for(R * 4, 256), 256, 0, c->stream>>>(I);
         else if (mean_ops <= 256) ingest_kernel<8><<<blocks_for(R * 8, 256), 256, 0, c->stream>>>(I);
         else if (mean_ops <= 2048) ingest_kernel<16><<<blocks_for(R * 16, 256), 256, 0, c->stream>>>(I);
         else ingest_kernel<32><<<blocks_for(R * 32, 256), 256, 0, c->stream>>>(I);
