@@ -27,11 +27,11 @@ import torch  # noqa: E402
 
 METRIC = "add_mismatches aligned bp/sec"
 UNIT = "aligned bp/s"
-# kernels of ours per batch: scalars_init, ingest, 3x scan (the last also writes tile_first_op), words_out (scalars to the
+# kernels of ours per batch: scalars_init, ingest, scan (one pass; also writes tile_first_op), words_out (scalars to the
 # host), encode, stitch, words_out (number of output ops)
-KERNELS_PER_STEP = 9
-# per sub-batch of the e2e pipeline: the above + op_text_len, 3x scan, line_begin, words_out (text size), prefix_copy, op_text
-KERNELS_PER_E2E_SUBBATCH = 17
+KERNELS_PER_STEP = 7
+# per sub-batch of the e2e pipeline: the above + op_text_len, scan, line_begin, words_out (text size), prefix_copy, op_text
+KERNELS_PER_E2E_SUBBATCH = 13
 
 
 def peaks():

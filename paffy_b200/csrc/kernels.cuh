@@ -142,7 +142,7 @@ __global__ void unpack_kernel(Genome G, uint64_t p0, int64_t len, uint8_t *out) 
 }
 
 // ------------------------------------------------------------------------------------------------
-// Exclusive scan u32 -> u64, three phases (block sums, scan of sums, apply). out has n + 1 entries.
+// Exclusive scan u32 -> u64, out has n + 1 entries.
 // ------------------------------------------------------------------------------------------------
 #ifndef SCAN_APPLY_MINB
 #define SCAN_APPLY_MINB 4
@@ -176,49 +176,31 @@ __device__ __forceinline__ uint64_t block_incl_scan(uint64_t v, uint64_t *total)
     return inc + off;
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) scan_sums_kernel(const uint32_t *__restrict__ in, int64_t n,
-                                                                  uint64_t *block_sums) {
-    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
-    uint64_t s = 0;
-#pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
-        const int64_t i = base + (int64_t)k * SCAN_THREADS + threadIdx.x;
-        if (i < n) s += in[i];
-    }
-    uint64_t tot;
-    block_incl_scan(s, &tot);
-    if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
-}
-// single block: block_sums -> exclusive, total to out_total
-__global__ void __launch_bounds__(SCAN_THREADS) scan_spine_kernel(uint64_t *block_sums, int64_t nb,
-                                                                   uint64_t *out_total) {
-    uint64_t carry = 0;
-    for (int64_t base = 0; base < nb; base += SCAN_THREADS) {
-        const int64_t i = base + threadIdx.x;
-        const uint64_t v = i < nb ? block_sums[i] : 0;
-        uint64_t tot;
-        const uint64_t inc = block_incl_scan(v, &tot);
-        if (i < nb) block_sums[i] = carry + inc - v;
-        carry += tot;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) *out_total = carry;
-}
-// tile_first_op (optional): in[] are windows per op; every warp tile of tile_windows windows learns the op that owns
-// its first window (op j owns windows [out[j], out[j + 1]))
-__global__ void __launch_bounds__(SCAN_THREADS, SCAN_APPLY_MINB) scan_apply_kernel(const uint32_t *__restrict__ in, int64_t n,
-                                                                   const uint64_t *__restrict__ block_sums,
-                                                                   uint64_t *__restrict__ out, uint32_t *__restrict__ tile_first_op,
+// ONE pass with decoupled look-back: a block takes the next tile from a ticket counter (so the tiles before it belong to
+// blocks that are running or done), scans its 4096 items, publishes its sum, and obtains the sum of all earlier tiles
+// from their status words (2 flag bits + 62 value bits: aggregate / inclusive prefix). One read of the input and one
+// write of the output (round 1 ran three kernels: block sums, a single-block spine, apply). `status` (n_tiles words) and
+// `ticket` must be zero on entry. Thread t owns SCAN_ITEMS consecutive items; a warp's 32 x SCAN_ITEMS items travel between
+// global memory (coalesced: item = 32 * k + lane) and their owners through shared memory (owner o keeps its items at
+// o * (SCAN_ITEMS + 1) ..: the odd stride keeps both views off each other's banks).
+// tile_first_op (optional): in[] are windows per op; every warp tile of tile_windows windows learns the op that owns its
+// first window (op j owns windows [out[j], out[j + 1])).
+constexpr unsigned long long SCAN_AGG = 1ull << 62, SCAN_INCL = 2ull << 62, SCAN_VAL = (1ull << 62) - 1;
+__global__ void __launch_bounds__(SCAN_THREADS, SCAN_APPLY_MINB) scan_onepass_kernel(const uint32_t *__restrict__ in, int64_t n,
+                                                                   uint64_t *__restrict__ out, unsigned long long *status, unsigned int *ticket,
+                                                                   uint64_t *out_total, uint32_t *__restrict__ tile_first_op,
                                                                    uint32_t tile_windows, uint64_t tile_cap) {
-    // thread t owns SCAN_ITEMS consecutive items so the block scan runs once; a warp's 32 x SCAN_ITEMS items travel
-    // between global memory (coalesced: item = 32 * k + lane) and their owners through shared memory (owner o keeps its
-    // items at o * (SCAN_ITEMS + 1) ..: the odd stride keeps both views off each other's banks)
     static_assert(SCAN_ITEMS == 16, "index arithmetic below assumes 16 items per thread");
     __shared__ uint64_t stage[SCAN_THREADS / 32][32 * (SCAN_ITEMS + 1)];
+    __shared__ unsigned s_tile;
+    __shared__ uint64_t s_excl;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const int64_t tile = s_tile;
     const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint64_t *st64 = stage[wid];
     uint32_t *st32 = reinterpret_cast<uint32_t *>(st64);
-    const int64_t wbase = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)wid * 32 * SCAN_ITEMS;
+    const int64_t wbase = tile * SCAN_TILE + (int64_t)wid * 32 * SCAN_ITEMS;
     const int64_t base = wbase + (int64_t)lane * SCAN_ITEMS;
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
@@ -235,7 +217,37 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_APPLY_MINB) scan_apply_kern
         s += v[k];
     }
     uint64_t tot;
-    uint64_t run = block_incl_scan(s, &tot) - s + block_sums[blockIdx.x];  // (its barriers also fence the staging buffer)
+    const uint64_t incl = block_incl_scan(s, &tot);  // (its barriers also fence the staging buffer)
+    if (wid == 0) {
+        volatile unsigned long long *st = status;
+        if (lane == 0) atomicMax(status + tile, (tile == 0 ? SCAN_INCL : SCAN_AGG) | tot);
+        uint64_t excl = 0;
+        if (tile > 0) {
+            int64_t j = tile - 1 - (int64_t)lane;
+            for (;;) {
+                unsigned long long w = j >= 0 ? st[j] : (2ull << 62);
+                unsigned has_incl;
+                for (;;) {
+                    has_incl = __ballot_sync(FULL, (w >> 62) == 2);
+                    const unsigned need = has_incl ? has_incl ^ (has_incl - 1u) : FULL;  // the tiles back to the nearest inclusive prefix
+                    if (!(__ballot_sync(FULL, (w >> 62) == 0) & need)) break;
+                    __nanosleep(32);
+                    w = j >= 0 ? st[j] : (2ull << 62);
+                }
+                const unsigned upto = has_incl ? (unsigned)__ffs(has_incl) - 1u : 31u;
+                unsigned long long c = lane <= upto ? (w & SCAN_VAL) : 0ull;
+#pragma unroll
+                for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(FULL, c, o);
+                excl += c;
+                if (has_incl) break;
+                j -= 32;
+            }
+            if (lane == 0) atomicMax(status + tile, SCAN_INCL | (excl + tot));
+        }
+        if (lane == 0) s_excl = excl;
+    }
+    __syncthreads();
+    uint64_t run = s_excl + incl - s;
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
         st64[lane * (SCAN_ITEMS + 1) + k] = run;
@@ -251,7 +263,10 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_APPLY_MINB) scan_apply_kern
         const int64_t i = wbase + p;
         if (i < n) out[i] = st64[(p >> 4) * (SCAN_ITEMS + 1) + (p & 15u)];
     }
-    if (base <= n - 1 && n - 1 < base + SCAN_ITEMS) out[n] = block_sums[blockIdx.x] + tot;
+    if (base <= n - 1 && n - 1 < base + SCAN_ITEMS) {
+        out[n] = s_excl + tot;
+        if (out_total) *out_total = s_excl + tot;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

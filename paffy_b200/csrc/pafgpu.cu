@@ -205,11 +205,15 @@ int scan_u32(pafgpu_ctx *c, const uint32_t *in, int64_t n, uint64_t *out, uint64
         return 0;
     }
     const int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
-    CU(c->scan_sums.ensure((size_t)nb * 8));
+    CU(c->scan_sums.ensure((size_t)(nb + 1) * 8));
     uint64_t *tot = total_dev ? total_dev : c->scalars.as<uint64_t>() + SC_TMP;
-    scan_sums_kernel<<<(unsigned)nb, SCAN_THREADS, 0, c->stream>>>(in, n, c->scan_sums.as<uint64_t>());
-    scan_spine_kernel<<<1, SCAN_THREADS, 0, c->stream>>>(c->scan_sums.as<uint64_t>(), nb, tot);
-    scan_apply_kernel<<<(unsigned)nb, SCAN_THREADS, 0, c->stream>>>(in, n, c->scan_sums.as<uint64_t>(), out, tile_first_op, tile_windows, (uint64_t)tile_cap);
+    {
+        // one pass with decoupled look-back: status words of the tiles + the ticket counter behind them, zeroed
+        CU(cudaMemsetAsync(c->scan_sums.p, 0, (size_t)(nb + 1) * 8, c->stream));
+        scan_onepass_kernel<<<(unsigned)nb, SCAN_THREADS, 0, c->stream>>>(in, n, out, c->scan_sums.as<unsigned long long>(),
+                                                                         reinterpret_cast<unsigned int *>(c->scan_sums.as<uint64_t>() + nb), tot,
+                                                                         tile_first_op, tile_windows, (uint64_t)tile_cap);
+    }
     CU(cudaGetLastError());
     return 0;
 }
@@ -409,14 +413,9 @@ int encode_device(pafgpu_ctx *c, GenomeStore &g, const pafgpu_batch *b, pafgpu_r
         // per record better than finishing a record in one stride (measured at C2, 20 ops per record: 4 lanes 0.53 ms,
         // 8 lanes 0.58 ms, 16 lanes 0.69 ms, 32 lanes 0.90 ms for the ingest stage)
         int64_t mean_ops = N / R;
-        int force_g = 0;
-        if (const char *e = getenv("PAFGPU_INGEST_G")) {  // experiments
-            force_g = atoi(e);
-            mean_ops = force_g <= 4 ? 1 : force_g == 8 ? 100 : force_g == 16 ? 1000 : 100000;
-        }
-        if (force_g == 1) ingest_kernel<1><<<blocks_for(R, 256), 256, 0, c->stream>>>(I);
-        else if (force_g == 2) ingest_kernel<2><<<blocks_for(R * 2, 256), 256, 0, c->stream>>>(I);
-        else if (mean_ops <= 64) ingest_kernel<4><<<blocks_for(R * 4, 256), 256, 0, c->stream>>>(I);
+        // (round 2: 2 lanes 0.60 ms, 1 lane 0.93 ms, 8 lanes 0.43 ms against 0.39 ms with 4)
+        if (const char *e = getenv("PAFGPU_INGEST_G")) mean_ops = atoi(e) <= 4 ? 1 : atoi(e) == 8 ? 100 : atoi(e) == 16 ? 1000 : 100000;  // experiments
+        if (mean_ops <= 64) ingest_kernel<4><<<blocks_for(R * 4, 256), 256, 0, c->stream>>>(I);
         else if (mean_ops <= 256) ingest_kernel<8><<<blocks_for(R * 8, 256), 256, 0, c->stream>>>(I);
         else if (mean_ops <= 2048) ingest_kernel<16><<<blocks_for(R * 16, 256), 256, 0, c->stream>>>(I);
         else ingest_kernel<32><<<blocks_for(R * 32, 256), 256, 0, c->stream>>>(I);

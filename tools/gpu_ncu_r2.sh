@@ -5,7 +5,7 @@
 tag=${1:-r2ncu}; out=gpurun_out/$tag; mkdir -p $out
 B="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
 timeout 600 $B > $out/plain.json 2> $out/plain.err || { echo "plain bench failed"; tail -5 $out/plain.err; exit 1; }
-KREG='regex:^(encode_kernel|stitch_kernel|ingest_kernel|scan_sums|scan_spine|scan_apply|scalars_init|words_out|tile_first_op|op_text|line_begin|tx_|prefix_copy)'
+KREG='regex:^(encode_kernel|stitch_kernel|ingest_kernel|scan_onepass|scalars_init|words_out|tile_first_op|op_text|line_begin|tx_|prefix_copy)'
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREG" --launch-skip 1400 -c 500 --csv --log-file $out/launches_c2.csv $B > $out/ncu_launch.log 2>&1
 echo "launch list exit $?"
 timeout 1200 ncu --set full --clock-control none --import-source on -k 'regex:^(encode_kernel)' -s 3 -c 1 -o $out/prof_encode $B > $out/ncu_full.log 2>&1
