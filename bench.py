@@ -32,6 +32,10 @@ UNIT = "aligned bp/s"
 KERNELS_PER_STEP = 7
 # per sub-batch of the e2e pipeline: the above + op_text_len, scan, line_begin, words_out (text size), prefix_copy, op_text
 KERNELS_PER_E2E_SUBBATCH = 13
+# per chunk of the text path: count_delims, 2 scans, words_out, scatter_delims, parse_records, ops (count), scan, words_out,
+# ops (write), the 7 of a batch, op_totals, sum, empty_out_begin, prefix (measure), scan, op_text_len, scan, line_begin,
+# words_out, prefix (render), op_text, words_out
+KERNELS_PER_TEXT_CHUNK = 30
 
 
 def peaks():
@@ -494,7 +498,7 @@ def main():
             for sb in subs:
                 h.update(sb["out"].numpy()[:sb["n"]].tobytes())
             soa_md5 = h.hexdigest()
-        e2e = {"value": A_total * args.steps / el, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+        e2e_soa = {"value": A_total * args.steps / el, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": 1e3 * el / args.steps,
                "what": "pafgpu_encode_batch_host + pafgpu_serialise + pafgpu_fetch_text on parsed SoA arrays and host-rendered line heads in pinned memory",
                "pipeline": f"{len(subs)} sub-batches per step dealt round-robin to {len(ctxs)} sibling contexts (one stream each, ONE packed genome) on the GPU; the K steps stream back to back, all of them inside the timed region",
@@ -503,10 +507,67 @@ def main():
                "host_wall_ms_per_step_summed_over_threads": {"encode_batch_host": 1e3 * stage_s[0] / args.steps,
                                                               "serialise": 1e3 * stage_s[1] / args.steps,
                                                               "fetch_text": 1e3 * stage_s[2] / args.steps}}
+        del subs
+
+        # ---- `e2e`: PAF TEXT in pinned host memory -> PAF TEXT in pinned host memory (pafgpu_add_mismatches_text +
+        # pafgpu_fetch_text): what the reference's interface carries, nothing pre-parsed and nothing pre-rendered - the
+        # text is copied to the device, split into lines and fields, parsed, looked up, encoded, checked and rendered
+        # there. Same sub-batch pipeline over the same sibling contexts.
+        text = make_input_text(ctx, rec, pre_b, pre_o)
+        nl_targets = [len(text) * k // n_sub for k in range(1, n_sub)]
+        tcuts = [0]
+        for t in nl_targets:
+            w = text[t:t + (1 << 20)]
+            tcuts.append(t + int(np.argmax(w == 10)) + 1)
+        tcuts.append(len(text))
+        tsubs = []
+        for k in range(n_sub):
+            a, b = tcuts[k], tcuts[k + 1]
+            if b > a:
+                tsubs.append({"in": torch.from_numpy(text[a:b].copy()).pin_memory(), "out": None, "n": 0})
+        h2d_t = sum(sb["in"].numel() for sb in tsubs)
+
+        def run_sub_text(c, sb):
+            res_t = c.add_mismatches_text_resident(sb["in"].numpy())
+            assert res_t.first_bad < 0
+            nbytes = res_t.text_bytes
+            if sb["out"] is None or sb["out"].numel() < nbytes:
+                sb["out"] = torch.empty(int(nbytes * 1.05) + 64, dtype=torch.uint8).pin_memory()
+            c.fetch_text(pinned=sb["out"].numpy(), want_lines=False)
+            sb["n"] = nbytes
+            return nbytes
+
+        def text_steps(n_steps):
+            futs = [pool.submit(lambda c, mine_: sum(run_sub_text(c, sb) for _ in range(n_steps) for sb in mine_), c, tsubs[k::len(ctxs)])
+                    for k, c in enumerate(ctxs)]
+            return sum(f.result() for f in futs) // n_steps
+
+        d2h_t = text_steps(args.warmup)
+        barrier()
+        t0 = time.perf_counter()
+        d2h_t = text_steps(args.steps)
+        own = time.perf_counter() - t0
+        barrier()
+        el = max_over_ranks(own)
+        text_md5 = None
+        if world == 1:
+            import hashlib
+            h = hashlib.md5()
+            for sb in tsubs:
+                h.update(sb["out"].numpy()[:sb["n"]].tobytes())
+            text_md5 = h.hexdigest()
+        e2e = {"value": A_total * args.steps / el, "unit": UNIT, "h2d_bytes_per_step": int(h2d_t), "d2h_bytes_per_step": int(d2h_t),
+               "ms_per_step": 1e3 * el / args.steps,
+               "what": "pafgpu_add_mismatches_text + pafgpu_fetch_text: PAF text in pinned host memory -> device (lines, fields, cg ops parsed there; contigs looked up; "
+                       "encode; paf_check; whole lines rendered) -> PAF text in pinned host memory",
+               "pipeline": f"{len(tsubs)} chunks of whole lines per step dealt round-robin to {len(ctxs)} sibling contexts (one stream each, ONE packed genome); the K steps stream back to back",
+               "gpu_launches_per_step": KERNELS_PER_TEXT_CHUNK * len(tsubs),
+               "output_equals_soa_path_output": (text_md5 == soa_md5) if text_md5 else None,
+               "soa": e2e_soa}
+        del text, tsubs
         pool.shutdown()
         for c2 in ctxs[1:]:
             c2.close()
-        del subs
 
     # ---- end to end through the reference's own interface: PAF file in, PAF file out ---------------------------------
     # `paffy add_mismatches -i in.paf -o out.paf` with the FASTA already packed (its load is reported beside it): the text

@@ -192,6 +192,15 @@ class Context:
         s.h, s.n_records, s.result = h, 0, None
         return s
 
+    def add_mismatches_text_resident(self, buf):
+        """The same with the input in a caller-owned (pinned) uint8 numpy array and the output left on the device: fetch it
+        with fetch_text(pinned=...). -> TextResult"""
+        res = TextResult()
+        self._check(self.L.pafgpu_add_mismatches_text(self.h, buf.ctypes.data, buf.size, C.byref(res)))
+        self.text_bytes = res.text_bytes
+        self.n_records = res.records
+        return res
+
     def add_mismatches_text(self, text):
         """PAF text (bytes, free of \r) in, PAF text out, parsed / encoded / rendered on the device. -> (TextResult, bytes)"""
         res = TextResult()

@@ -7,7 +7,7 @@ python -c "import __graft_entry__ as g; g.smoke()" > $out/smoke.log 2>&1; echo "
 timeout 900 python bench.py --impl reference --steps 3 --warmup 1 > $out/bench_reference.json 2> $out/bench_reference.err; echo "reference arm exit $?"
 timeout 900 python bench.py > $out/bench.json 2> $out/bench.err; echo "bench exit $?"; tail -3 $out/bench.err
 KREG='regex:^(encode_kernel|stitch_kernel|ingest_kernel|scan_onepass|scalars_init|words_out|tile_first_op)'
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREG" --launch-skip 250 -c 60 --csv --log-file $out/launches_resident_c2.csv \
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k "$KREG" --launch-skip 100 -c 49 --csv --log-file $out/launches_resident_c2.csv \
     python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-e2e --no-e2e-file > $out/ncu_launch.log 2>&1; echo "launch list exit $?"
 python - $out <<'PY'
 import json, sys, csv
