@@ -176,6 +176,38 @@ __device__ __forceinline__ uint64_t block_incl_scan(uint64_t v, uint64_t *total)
     return inc + off;
 }
 
+// Decoupled look-back, run by ONE warp of the block that owns `tile`: publishes the tile's sum `tot` and returns the sum of
+// all earlier tiles, read from their status words (2 flag bits + 62 value bits: aggregate / inclusive prefix). The tile
+// order must come from a ticket counter, so that every earlier tile belongs to a block that is running or done.
+__device__ __forceinline__ uint64_t lookback_exclusive(unsigned long long *status, int64_t tile, uint64_t tot, unsigned lane) {
+    volatile unsigned long long *st = status;
+    if (lane == 0) atomicMax(status + tile, (tile == 0 ? (2ull << 62) : (1ull << 62)) | tot);
+    uint64_t excl = 0;
+    if (tile > 0) {
+        int64_t j = tile - 1 - (int64_t)lane;
+        for (;;) {
+            unsigned long long w = j >= 0 ? st[j] : (2ull << 62);
+            unsigned has_incl;
+            for (;;) {
+                has_incl = __ballot_sync(FULL, (w >> 62) == 2);
+                const unsigned need = has_incl ? has_incl ^ (has_incl - 1u) : FULL;  // the tiles back to the nearest inclusive prefix
+                if (!(__ballot_sync(FULL, (w >> 62) == 0) & need)) break;
+                __nanosleep(32);
+                w = j >= 0 ? st[j] : (2ull << 62);
+            }
+            const unsigned upto = has_incl ? (unsigned)__ffs(has_incl) - 1u : 31u;
+            unsigned long long c = lane <= upto ? (w & ((1ull << 62) - 1)) : 0ull;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(FULL, c, o);
+            excl += c;
+            if (has_incl) break;
+            j -= 32;
+        }
+        if (lane == 0) atomicMax(status + tile, (2ull << 62) | (excl + tot));
+    }
+    return excl;
+}
+
 // ONE pass with decoupled look-back: a block takes the next tile from a ticket counter (so the tiles before it belong to
 // blocks that are running or done), scans its 4096 items, publishes its sum, and obtains the sum of all earlier tiles
 // from their status words (2 flag bits + 62 value bits: aggregate / inclusive prefix). One read of the input and one
@@ -219,31 +251,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_APPLY_MINB) scan_onepass_ke
     uint64_t tot;
     const uint64_t incl = block_incl_scan(s, &tot);  // (its barriers also fence the staging buffer)
     if (wid == 0) {
-        volatile unsigned long long *st = status;
-        if (lane == 0) atomicMax(status + tile, (tile == 0 ? SCAN_INCL : SCAN_AGG) | tot);
-        uint64_t excl = 0;
-        if (tile > 0) {
-            int64_t j = tile - 1 - (int64_t)lane;
-            for (;;) {
-                unsigned long long w = j >= 0 ? st[j] : (2ull << 62);
-                unsigned has_incl;
-                for (;;) {
-                    has_incl = __ballot_sync(FULL, (w >> 62) == 2);
-                    const unsigned need = has_incl ? has_incl ^ (has_incl - 1u) : FULL;  // the tiles back to the nearest inclusive prefix
-                    if (!(__ballot_sync(FULL, (w >> 62) == 0) & need)) break;
-                    __nanosleep(32);
-                    w = j >= 0 ? st[j] : (2ull << 62);
-                }
-                const unsigned upto = has_incl ? (unsigned)__ffs(has_incl) - 1u : 31u;
-                unsigned long long c = lane <= upto ? (w & SCAN_VAL) : 0ull;
-#pragma unroll
-                for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(FULL, c, o);
-                excl += c;
-                if (has_incl) break;
-                j -= 32;
-            }
-            if (lane == 0) atomicMax(status + tile, SCAN_INCL | (excl + tot));
-        }
+        const uint64_t excl = lookback_exclusive(status, tile, tot, lane);
         if (lane == 0) s_excl = excl;
     }
     __syncthreads();

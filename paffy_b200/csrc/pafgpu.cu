@@ -1125,6 +1125,46 @@ extern "C" int pafgpu_add_mismatches_text(pafgpu_ctx *c, const char *text, int64
     return pafgpu_add_mismatches_text_opts(c, text, n_bytes, nullptr, res);
 }
 
+// The text of the staged output ops (c->out, c->rec_out_begin; c->ser_prefix_begin holds the prefix offsets): one pass
+// writes every op and line_begin (ser_write_kernel), `prefixes` then launches the kernel that renders the line heads,
+// and the byte total comes back. The text buffer is sized from `guess` beforehand; the kernels write nothing beyond it,
+// so a guess that was too small costs one more run at the exact size.
+template <class F>
+static int lay_out_and_write(pafgpu_ctx *c, int64_t R, int64_t K, SerialiseParams &S, int64_t guess, int64_t *total_out, F prefixes) {
+    const int64_t nb = blocks_for(K, SER_OPS_PER_BLOCK);
+    CU(c->ser_optoff.ensure((size_t)(nb + 2) * 8));
+    CU(c->ser_oplen.ensure((size_t)(nb + 1) * 4));
+    CU(c->ser_line_begin.ensure((size_t)(R + 1) * 8));
+    if (K > 0) ser_block_records_kernel<<<blocks_for(R, 256), 256, 0, c->stream>>>(R, c->rec_out_begin.as<int64_t>(), c->ser_oplen.as<uint32_t>());
+    S.block_rec = c->ser_oplen.as<uint32_t>();
+    S.n_records = R; S.n_out = K;
+    S.out = c->out.as<uint64_t>(); S.rec_out_begin = c->rec_out_begin.as<int64_t>();
+    S.status = c->ser_optoff.as<unsigned long long>();
+    S.ticket = reinterpret_cast<unsigned int *>(c->ser_optoff.as<uint64_t>() + nb);
+    S.prefix_begin = c->ser_prefix_begin.as<int64_t>();
+    S.line_begin = c->ser_line_begin.as<int64_t>();
+    S.keep_lo = c->trimmed ? c->trim_lo.as<int64_t>() : nullptr;
+    S.keep_hi = c->trimmed ? c->trim_hi.as<int64_t>() : nullptr;
+    int64_t total = 0;
+    for (int attempt = 0;; attempt++) {
+        CU(c->ser_text.ensure((size_t)std::max<int64_t>(guess, 8)));
+        S.text = c->ser_text.as<char>(); S.text_cap = (int64_t)c->ser_text.cap;
+        if (K > 0) {
+            CU(cudaMemsetAsync(c->ser_optoff.p, 0, (size_t)(nb + 2) * 8, c->stream));
+            ser_write_kernel<<<(unsigned)nb, SER_THREADS, 0, c->stream>>>(S);
+        } else {
+            line_begin_no_ops_kernel<<<blocks_for(R + 1, 256), 256, 0, c->stream>>>(R, S.prefix_begin, S.line_begin);
+        }
+        prefixes(S);
+        CU(read_words(c, (uint64_t *)&total, c->ser_line_begin.as<uint64_t>() + R, 1));
+        if (total <= S.text_cap) break;
+        if (attempt) return fail(c, PAFGPU_ESTATE, "serialiser: the text buffer is still too small after growing it");
+        guess = total;
+    }
+    *total_out = total;
+    return 0;
+}
+
 extern "C" int pafgpu_add_mismatches_text_opts(pafgpu_ctx *c, const char *text, int64_t n_bytes, const pafgpu_text_opts *opts,
                                                pafgpu_text_result *res) {
     if (!c || !res || n_bytes < 0 || (n_bytes && !text)) return PAFGPU_EINVAL;
@@ -1338,31 +1378,19 @@ extern "C" int pafgpu_add_mismatches_text_opts(pafgpu_ctx *c, const char *text, 
     }
     PrefixParams PR{};
     PR.text = d_text; PR.n_records = R; PR.R = TP; PR.prefix_len = prefix_len;
-    tx_prefix_kernel<false><<<blocks_for(R, 128), 128, 0, c->stream>>>(PR);
+    tx_prefix_kernel<false><<<blocks_for(R, TXP_THREADS), TXP_THREADS, 0, c->stream>>>(PR);
     CU(c->ser_prefix_begin.ensure((size_t)(R + 1) * 8));
     if (int rc = scan_u32(c, prefix_len, R, c->ser_prefix_begin.as<uint64_t>(), nullptr)) return rc;
-    CU(c->ser_oplen.ensure((size_t)std::max<int64_t>(K, 1) * 4));
-    CU(c->ser_optoff.ensure((size_t)(K + 1) * 8));
-    CU(c->ser_line_begin.ensure((size_t)(R + 1) * 8));
-    if (K > 0)
-        op_text_len_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(
-            c->out.as<uint64_t>(), K, c->ser_oplen.as<uint32_t>(), c->rec_out_begin.as<int64_t>(), R,
-            c->trimmed ? c->trim_lo.as<int64_t>() : nullptr, c->trimmed ? c->trim_hi.as<int64_t>() : nullptr);
-    if (int rc = scan_u32(c, c->ser_oplen.as<uint32_t>(), K, c->ser_optoff.as<uint64_t>(), nullptr)) return rc;
-    line_begin_kernel<<<blocks_for(R + 1, 256), 256, 0, c->stream>>>(R, c->ser_prefix_begin.as<int64_t>(), c->rec_out_begin.as<int64_t>(),
-                                                                     c->ser_optoff.as<uint64_t>(), c->ser_line_begin.as<int64_t>());
-    int64_t total = 0;
-    CU(read_words(c, (uint64_t *)&total, c->ser_line_begin.as<uint64_t>() + R, 1));
-    CU(c->ser_text.ensure((size_t)std::max<int64_t>(total, 8)));
     SerialiseParams S{};
-    S.n_records = R; S.n_out = K;
-    S.out = c->out.as<uint64_t>(); S.rec_out_begin = c->rec_out_begin.as<int64_t>();
-    S.op_toff = c->ser_optoff.as<uint64_t>();
-    S.prefix = nullptr; S.prefix_begin = c->ser_prefix_begin.as<int64_t>();
-    S.line_begin = c->ser_line_begin.as<int64_t>(); S.text = c->ser_text.as<char>();
-    PR.line_begin = c->ser_line_begin.as<int64_t>(); PR.out = c->ser_text.as<char>();
-    tx_prefix_kernel<true><<<blocks_for(R, 128), 128, 0, c->stream>>>(PR);
-    if (K > 0) op_text_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(S);
+    S.prefix = nullptr;
+    int64_t total = 0;
+    // first guess of the output size: 4 bytes per op (C2 averages 3.1) + line heads about as long as the input's
+    const int64_t guess = 4 * K + 2 * n_bytes + R + 4096;
+    if (int rc = lay_out_and_write(c, R, K, S, guess, &total, [&](const SerialiseParams &L) {
+            PR.line_begin = L.line_begin; PR.out = L.text; PR.out_cap = L.text_cap;
+            if (R > 0) tx_prefix_kernel<true><<<blocks_for(R, TXP_THREADS), TXP_THREADS, 0, c->stream>>>(PR);
+        }))
+        return rc;
     CU(cudaEventRecord(c->ev_tx[3], c->stream));
     if (int rc = totals(R_enc)) return rc;
     CU(cudaGetLastError());
@@ -1523,29 +1551,14 @@ int pafgpu_serialise(pafgpu_ctx *c, const char *prefix_bytes, const int64_t *pre
     CU(c->ser_prefix_begin.ensure((size_t)(R + 1) * 8));
     CU(cudaMemcpyAsync(c->ser_prefix.p, prefix_bytes, (size_t)pre_bytes, cudaMemcpyHostToDevice, c->stream));
     CU(cudaMemcpyAsync(c->ser_prefix_begin.p, prefix_begin, (size_t)(R + 1) * 8, cudaMemcpyHostToDevice, c->stream));
-    CU(c->ser_oplen.ensure((size_t)std::max<int64_t>(K, 1) * 4));
-    CU(c->ser_optoff.ensure((size_t)(K + 1) * 8));
-    CU(c->ser_line_begin.ensure((size_t)(R + 1) * 8));
     CU(cudaEventRecord(c->ev[0], c->stream));
-    if (K > 0)
-        op_text_len_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(
-            c->out.as<uint64_t>(), K, c->ser_oplen.as<uint32_t>(), c->rec_out_begin.as<int64_t>(), R,
-            c->trimmed ? c->trim_lo.as<int64_t>() : nullptr, c->trimmed ? c->trim_hi.as<int64_t>() : nullptr);
-    if (int rc = scan_u32(c, c->ser_oplen.as<uint32_t>(), K, c->ser_optoff.as<uint64_t>(), nullptr)) return rc;
-    // line_begin[r] = prefix_begin[r] + optoff[rec_out_begin[r]] + r   (prefixes + cigar text + newlines before r)
-    line_begin_kernel<<<blocks_for(R + 1, 256), 256, 0, c->stream>>>(R, c->ser_prefix_begin.as<int64_t>(), c->rec_out_begin.as<int64_t>(),
-                                                                     c->ser_optoff.as<uint64_t>(), c->ser_line_begin.as<int64_t>());
-    int64_t total = 0;
-    CU(read_words(c, (uint64_t *)&total, c->ser_line_begin.as<uint64_t>() + R, 1));
-    CU(c->ser_text.ensure((size_t)std::max<int64_t>(total, 8)));
     SerialiseParams S{};
-    S.n_records = R; S.n_out = K;
-    S.out = c->out.as<uint64_t>(); S.rec_out_begin = c->rec_out_begin.as<int64_t>();
-    S.op_toff = c->ser_optoff.as<uint64_t>();
-    S.prefix = c->ser_prefix.as<char>(); S.prefix_begin = c->ser_prefix_begin.as<int64_t>();
-    S.line_begin = c->ser_line_begin.as<int64_t>(); S.text = c->ser_text.as<char>();
-    if (R > 0) prefix_copy_kernel<<<blocks_for(R * 32, 256), 256, 0, c->stream>>>(S);
-    if (K > 0) op_text_kernel<<<blocks_for(K, SER_OPS_PER_BLOCK), SER_THREADS, 0, c->stream>>>(S);
+    S.prefix = c->ser_prefix.as<char>();
+    int64_t total = 0;
+    if (int rc = lay_out_and_write(c, R, K, S, 4 * K + pre_bytes + R + 4096, &total, [&](const SerialiseParams &L) {
+            if (R > 0) prefix_copy_kernel<<<blocks_for(R * 32, 256), 256, 0, c->stream>>>(L);
+        }))
+        return rc;
     CU(cudaEventRecord(c->ev[1], c->stream));
     CU(stream_sync(c));
     CU(cudaGetLastError());

@@ -15,6 +15,7 @@
 // reference's message for that one line and the run ends there.
 #pragma once
 #include "kernels.cuh"
+#include "serialise.cuh"
 
 namespace pafgpu {
 
@@ -245,80 +246,102 @@ struct OpsParams {
     unsigned long long *first_bad;
 };
 
-// WRITE = false: count the ops of the tile. WRITE = true: write them. Both walk the tile the same way: thread t owns bytes
-// [16 t, 16 t + 16) (one 16-byte load), knows the record of its first byte from the newline prefix, and parses the bytes
-// inside the cg value of their record FORWARD: a digit extends the running number, a letter closes an op of that length.
-// Only a number that began before the thread's first byte needs a look back (at most once per thread).
+// movemask of a per-byte compare result (0xff / 0x00 bytes): bit k = byte k
+__device__ __forceinline__ uint32_t tx_mask4(uint32_t m) { return ((m & 0x01010101u) * 0x01020408u) >> 24; }
+
+// WRITE = false: count the ops of the tile. WRITE = true: write them. Thread t owns bytes [16 t, 16 t + 16) (one 16-byte
+// load) and classifies them four at a time (byte-wise SIMD compares -> 16-bit masks: newline, digit, op letter, 'M', '0').
+// The newline mask cuts the window into line segments; inside a segment the bytes of the record's cg value are a bit
+// range, the op letters inside it are the ops (one popc counts them) and everything else there must be a digit. Only a
+// letter is ever looked at again: its length is the run of digit bits below it, and a run that reaches the window's
+// first byte continues in the bytes before it (one look back per thread at most). A zero-length M vanishes
+// (SURVEY a1-edge ii): only an M whose last digit is '0' (or missing) can be one, and those are parsed in the count pass.
 template <bool WRITE>
 __global__ void __launch_bounds__(TX_THREADS) tx_ops_kernel(OpsParams P) {
     __shared__ uint32_t s_total;
     if (threadIdx.x == 0) s_total = 0;
     const int64_t b0 = (int64_t)blockIdx.x * TX_TILE + (int64_t)threadIdx.x * TX_PER_THREAD;
-    char c[TX_PER_THREAD];
-    if (b0 + TX_PER_THREAD <= P.n) {  // (the text buffer is 16-byte aligned and padded)
+    uint32_t w[4] = {0u, 0u, 0u, 0u};
+    if (b0 + TX_PER_THREAD <= P.n) {  // (the text buffer is 16-byte aligned)
         const uint4 v = __ldg(reinterpret_cast<const uint4 *>(P.text + b0));
-        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int k = 0; k < TX_PER_THREAD; k++) c[k] = (char)((w[k >> 2] >> (8 * (k & 3))) & 0xffu);
+        w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
     } else {
-#pragma unroll
-        for (int k = 0; k < TX_PER_THREAD; k++) c[k] = b0 + k < P.n ? P.text[b0 + k] : (char)'\n';
+        for (int k = 0; k < TX_PER_THREAD && b0 + k < P.n; k++) w[k >> 2] |= (uint32_t)(uint8_t)P.text[b0 + k] << (8 * (k & 3));
     }
-    uint32_t nl = 0;
+    uint32_t NL = 0, DG = 0, LT = 0, MM = 0, ZZ = 0;
 #pragma unroll
-    for (int k = 0; k < TX_PER_THREAD; k++) nl += c[k] == '\n';
+    for (int j = 0; j < 4; j++) {
+        const uint32_t x = w[j];
+        const uint32_t m = __vcmpeq4(x, 0x4d4d4d4du);                                                       // M
+        const uint32_t l = m | __vcmpeq4(x, 0x49494949u) | __vcmpeq4(x, 0x44444444u) | __vcmpeq4(x, 0x3d3d3d3du) | __vcmpeq4(x, 0x58585858u);  // I D = X
+        NL |= tx_mask4(__vcmpeq4(x, 0x0a0a0a0au)) << (4 * j);
+        DG |= tx_mask4(__vcmpgeu4(x, 0x30303030u) & __vcmpleu4(x, 0x39393939u)) << (4 * j);
+        LT |= tx_mask4(l) << (4 * j);
+        MM |= tx_mask4(m) << (4 * j);
+        ZZ |= tx_mask4(__vcmpeq4(x, 0x30303030u)) << (4 * j);
+    }
     uint32_t dummy, en;
-    tx_block_excl2(nl, 0u, en, dummy);
+    tx_block_excl2((uint32_t)__popc(NL), 0u, en, dummy);
     const int64_t rec0 = (int64_t)P.nl_off[blockIdx.x] + en;
     uint32_t cgb0 = 0, cge0 = 0;
     if (rec0 < P.n_records) { cgb0 = P.cg_begin[rec0]; cge0 = P.cg_end[rec0]; }
 
-    // one walk over the 16 bytes; emit(k, code, len) is called for every op that is kept
-    auto walk = [&](auto emit, auto line_end) {
-        int64_t rr = rec0;
-        uint32_t b = cgb0, e = cge0;
+    auto byte_at = [&](int j) -> uint32_t {
+        const uint32_t x = j < 8 ? (j < 4 ? w[0] : w[1]) : (j < 12 ? w[2] : w[3]);
+        return (x >> (8 * (j & 3))) & 0xffu;
+    };
+    // length of the op whose letter is byte p of the window; s = first byte of the cg value inside the window, b = its
+    // first byte in the text
+    auto op_len = [&](int p, int s, uint32_t b) -> uint64_t {
+        const uint32_t below = ~DG & ((1u << p) - 1u);
+        int d0 = below ? 32 - __clz(below) : 0;  // first digit of the run that ends at p
+        if (d0 < s) d0 = s;
         uint64_t v = 0;
-        uint32_t nd = 0;                                             // digits of the running number seen in this window
-        bool from_before = (uint32_t)b0 > b && (uint32_t)b0 < e;     // the running number may have begun before the window
-#pragma unroll
-        for (int k = 0; k < TX_PER_THREAD; k++) {
-            const uint32_t i = (uint32_t)(b0 + k);
-            const char ch = c[k];
-            if (b0 + k < P.n && i >= b && i < e) {
-                if (ch >= '0' && ch <= '9') {
-                    v = v * 10 + (uint64_t)(ch - '0');
-                    nd++;
-                    if (i + 1 == e && !WRITE) atomicMin(P.first_bad, (unsigned long long)rr);  // digits without a letter (the reference reads the NUL as one)
-                } else {
-                    const int code = tx_op_code(ch);
-                    if (code >= 0) {
-                        uint64_t len = v;
-                        if (from_before) {  // the digits before the window come first
-                            uint32_t dg;
-                            uint64_t head = tx_number_before(P.text, (uint32_t)b0, b, dg);
-                            for (uint32_t q = 0; q < nd; q++) head *= 10;
-                            len += head;
-                        }
-                        if (!(code == OP_M && len == 0)) emit(k, code, len);  // a zero-length M op vanishes (SURVEY a1-edge ii)
-                    } else if (!WRITE) {
-                        atomicMin(P.first_bad, (unsigned long long)rr);  // impl/paf.c:102
-                    }
-                    v = 0; nd = 0; from_before = false;
+        for (int j = d0; j < p; j++) v = v * 10 + (uint64_t)(byte_at(j) - '0');
+        if (d0 == 0 && (uint32_t)b0 > b) {        // the digits before the window come first
+            uint32_t dg;
+            uint64_t head = tx_number_before(P.text, (uint32_t)b0, b, dg);
+            for (int q = 0; q < p; q++) head *= 10;
+            v += head;
+        }
+        return v;
+    };
+    // the walk over the line segments of the window; seg(rr, b, ops, s) sees the op letters of one record, line_end(rr)
+    // every newline
+    auto walk = [&](auto seg, auto line_end) {
+        int64_t rr = rec0;
+        uint32_t b = cgb0, e = cge0, nlm = NL;
+        int lo = 0;
+        for (;;) {
+            const int hi = nlm ? __ffs(nlm) - 1 : TX_PER_THREAD;
+            const int64_t rb = (int64_t)b - b0, re = (int64_t)e - b0;
+            const int s = rb > lo ? (int)(rb < hi ? rb : hi) : lo, t = re < hi ? (int)(re > lo ? re : lo) : hi;
+            if (s < t) {
+                const uint32_t reg = ((1u << t) - 1u) & ~((1u << s) - 1u);
+                if (!WRITE) {
+                    // impl/paf.c:102 (a byte that is no digit and no op letter), and digits without a letter at the end of
+                    // the value (the reference reads the NUL as one)
+                    if ((reg & ~(DG | LT)) || (re == t && ((DG >> (t - 1)) & 1u))) atomicMin(P.first_bad, (unsigned long long)rr);
                 }
-            } else {
-                v = 0; nd = 0; from_before = false;
+                seg(rr, b, LT & reg, s);
             }
-            if (ch == '\n' && b0 + k < P.n) {
-                rr++;
-                line_end(rr);
-                b = e = 0;
-                if (rr < P.n_records) { b = P.cg_begin[rr]; e = P.cg_end[rr]; }
-            }
+            if (!nlm) break;
+            rr++;
+            line_end(rr);
+            b = e = 0;
+            if (rr < P.n_records) { b = P.cg_begin[rr]; e = P.cg_end[rr]; }
+            lo = hi + 1;
+            nlm &= nlm - 1;
         }
     };
 
     uint32_t mine = 0;
-    walk([&](int, int, uint64_t) { mine++; }, [&](int64_t) {});
+    walk([&](int64_t, uint32_t b, uint32_t ops, int s) {
+             mine += (uint32_t)__popc(ops);
+             for (uint32_t cand = ops & MM & (((~DG | ZZ) << 1) | 1u); cand; cand &= cand - 1)
+                 if (op_len(__ffs(cand) - 1, s, b) == 0) mine--;
+         },
+         [&](int64_t) {});
     if (!WRITE) {
 #pragma unroll
         for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(FULL, mine, o);
@@ -331,7 +354,14 @@ __global__ void __launch_bounds__(TX_THREADS) tx_ops_kernel(OpsParams P) {
     uint32_t eo;
     tx_block_excl2(mine, 0u, eo, dummy);
     uint64_t at = P.op_off[blockIdx.x] + eo;
-    walk([&](int, int code, uint64_t len) { P.ops[at++] = (len & LEN_MASK) | ((uint64_t)code << 56); },
+    walk([&](int64_t, uint32_t b, uint32_t ops, int s) {
+             for (; ops; ops &= ops - 1) {
+                 const int p = __ffs(ops) - 1;
+                 const int code = tx_op_code((char)byte_at(p));
+                 const uint64_t len = op_len(p, s, b);
+                 if (!(code == OP_M && len == 0)) P.ops[at++] = (len & LEN_MASK) | ((uint64_t)code << 56);
+             }
+         },
          [&](int64_t rr) { P.op_begin[rr] = (int64_t)at; });  // ops before the line that starts here (the last newline leaves the total)
 }
 
@@ -339,66 +369,99 @@ __global__ void __launch_bounds__(TX_THREADS) tx_ops_kernel(OpsParams P) {
 __device__ __forceinline__ uint32_t tx_i64_chars(int64_t v) {
     uint64_t u = v < 0 ? 0 - (uint64_t)v : (uint64_t)v;
     uint32_t n = v < 0 ? 2 : 1;
-    while (u >= 10) { u /= 10; n++; }
-    return n;
+    while (u >> 32) { u /= 10; n++; }  // (rare: the 32-bit tail below is the usual path)
+    const uint32_t x = (uint32_t)u;
+    return n + (x >= 10u) + (x >= 100u) + (x >= 1000u) + (x >= 10000u) + (x >= 100000u) + (x >= 1000000u) + (x >= 10000000u) + (x >= 100000000u) +
+           (x >= 1000000000u);
 }
 __device__ __forceinline__ char *tx_put_i64(char *w, int64_t v) {
-    char tmp[20];
-    int n = 0;
+    const uint32_t n = tx_i64_chars(v);
     uint64_t u = v < 0 ? 0 - (uint64_t)v : (uint64_t)v;
-    if (v < 0) *w++ = '-';
-    do { tmp[n++] = (char)('0' + u % 10); u /= 10; } while (u);
-    while (n) *w++ = tmp[--n];
-    return w;
+    if (v < 0) *w = '-';
+    char *e = w + n;
+    while (u >> 32) { *--e = (char)('0' + u % 10); u /= 10; }
+    uint32_t x = (uint32_t)u;
+    do { *--e = (char)('0' + x % 10u); x /= 10u; } while (x);
+    return w + n;
 }
 
 struct PrefixParams {
     const char *text;
     int64_t n_records;
     TextRecords R;
-    uint32_t *prefix_len;            // measure pass
+    uint32_t *prefix_len;            // measure pass (read again by the render pass)
     const int64_t *line_begin;       // render pass: where each output line starts / ends
     char *out;
+    int64_t out_cap;                 // render pass: bytes `out` holds (a line that would end beyond is not written)
 };
 
-// everything paf_write_to_buffer prints before the ops (impl/paf.c:320-368), "\tcg:Z:" included when the record has a cigar
+constexpr int TXP_THREADS = 128, TXP_SLAB = 196;  // slab: bytes a thread stages its line head in (odd word stride: no bank conflicts)
+
+// everything paf_write_to_buffer prints before the ops (impl/paf.c:320-368), "\tcg:Z:" included when the record has a cigar.
+// RENDER: every thread renders its record's head into its slab of shared memory, then the warp copies the 32 slabs out
+// one after the other with aligned word stores - 32 threads each storing single bytes into their own line cost a
+// memory sector per byte. A head longer than the slab is written straight out by its thread.
 template <bool RENDER>
-__global__ void __launch_bounds__(128) tx_prefix_kernel(PrefixParams P) {
+__global__ void __launch_bounds__(TXP_THREADS) tx_prefix_kernel(PrefixParams P) {
+    __shared__ __align__(16) uint8_t s_slab[RENDER ? TXP_THREADS * TXP_SLAB + 16 : 16];
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= P.n_records) return;
+    const bool live = r < P.n_records;
     const TextRecords &R = P.R;
-    const int64_t v12[9] = {R.qlen[r], R.qs[r], R.qe[r], R.tlen[r], R.ts[r], R.te[r], R.nmatch[r], R.nbases[r], R.mapq[r]};
-    const int64_t score = R.score[r], tl = R.tl[r], cn = R.cn[r], s1 = R.s1[r];
-    const uint8_t type = R.type[r];
-    const bool tp = type != 0 || tl != -1;
-    if (!RENDER) {
-        // q \t len \t start \t end \t strand \t t \t len \t start \t end \t matches \t bases \t mapq: 11 tabs + the strand byte
-        uint32_t n = R.qn_len[r] + R.tn_len[r] + 11 + 1;
+    uint32_t n = 0;
+    int64_t begin = 0;
+    bool in_slab = false;
+    if (live) {
+        const int64_t v12[9] = {R.qlen[r], R.qs[r], R.qe[r], R.tlen[r], R.ts[r], R.te[r], R.nmatch[r], R.nbases[r], R.mapq[r]};
+        const int64_t score = R.score[r], tl = R.tl[r], cn = R.cn[r], s1 = R.s1[r];
+        const uint8_t type = R.type[r];
+        const bool tp = type != 0 || tl != -1;
+        if (!RENDER) {
+            // q \t len \t start \t end \t strand \t t \t len \t start \t end \t matches \t bases \t mapq: 11 tabs + the strand byte
+            n = R.qn_len[r] + R.tn_len[r] + 11 + 1;
 #pragma unroll
-        for (int k = 0; k < 9; k++) n += tx_i64_chars(v12[k]);
-        if (tp) n += 7;
-        if (score != 2147483647ll) n += 6 + tx_i64_chars(score);
-        if (tl != -1) n += 6 + tx_i64_chars(tl);
-        if (cn != -1) n += 6 + tx_i64_chars(cn);
-        if (s1 != -1) n += 6 + tx_i64_chars(s1);
-        if (R.has_cg[r]) n += 6;
-        P.prefix_len[r] = n;
-        return;
+            for (int k = 0; k < 9; k++) n += tx_i64_chars(v12[k]);
+            if (tp) n += 7;
+            if (score != 2147483647ll) n += 6 + tx_i64_chars(score);
+            if (tl != -1) n += 6 + tx_i64_chars(tl);
+            if (cn != -1) n += 6 + tx_i64_chars(cn);
+            if (s1 != -1) n += 6 + tx_i64_chars(s1);
+            if (R.has_cg[r]) n += 6;
+            P.prefix_len[r] = n;
+            return;
+        }
+        n = P.prefix_len[r];
+        begin = P.line_begin[r];
+        const int64_t end = P.line_begin[r + 1];
+        if (end > P.out_cap) {
+            n = 0;  // the buffer is too small: the host grows it and runs again
+        } else {
+            in_slab = n <= (uint32_t)(TXP_SLAB - 4);
+            char *w = in_slab ? reinterpret_cast<char *>(s_slab) + threadIdx.x * TXP_SLAB : P.out + begin;
+            for (uint32_t i = 0, m = R.qn_len[r]; i < m; i++) *w++ = P.text[R.qn_off[r] + i];
+            for (int k = 0; k < 3; k++) { *w++ = '\t'; w = tx_put_i64(w, v12[k]); }
+            *w++ = '\t'; *w++ = R.strand[r] ? '+' : '-'; *w++ = '\t';
+            for (uint32_t i = 0, m = R.tn_len[r]; i < m; i++) *w++ = P.text[R.tn_off[r] + i];
+            for (int k = 3; k < 9; k++) { *w++ = '\t'; w = tx_put_i64(w, v12[k]); }
+            auto tag = [&](char a, char b, char t) { *w++ = '\t'; *w++ = a; *w++ = b; *w++ = ':'; *w++ = t; *w++ = ':'; };
+            if (tp) { tag('t', 'p', 'A'); *w++ = type ? (char)type : (tl > 1 ? 'S' : 'P'); }
+            if (score != 2147483647ll) { tag('A', 'S', 'i'); w = tx_put_i64(w, score); }
+            if (tl != -1) { tag('t', 'l', 'i'); w = tx_put_i64(w, tl); }
+            if (cn != -1) { tag('c', 'n', 'i'); w = tx_put_i64(w, cn); }
+            if (s1 != -1) { tag('s', '1', 'i'); w = tx_put_i64(w, s1); }
+            if (R.has_cg[r]) tag('c', 'g', 'Z');
+            P.out[end - 1] = '\n';
+        }
     }
-    char *w = P.out + P.line_begin[r];
-    for (uint32_t i = 0, n = R.qn_len[r]; i < n; i++) *w++ = P.text[R.qn_off[r] + i];
-    for (int k = 0; k < 3; k++) { *w++ = '\t'; w = tx_put_i64(w, v12[k]); }
-    *w++ = '\t'; *w++ = R.strand[r] ? '+' : '-'; *w++ = '\t';
-    for (uint32_t i = 0, n = R.tn_len[r]; i < n; i++) *w++ = P.text[R.tn_off[r] + i];
-    for (int k = 3; k < 9; k++) { *w++ = '\t'; w = tx_put_i64(w, v12[k]); }
-    auto tag = [&](char a, char b, char t) { *w++ = '\t'; *w++ = a; *w++ = b; *w++ = ':'; *w++ = t; *w++ = ':'; };
-    if (tp) { tag('t', 'p', 'A'); *w++ = type ? (char)type : (tl > 1 ? 'S' : 'P'); }
-    if (score != 2147483647ll) { tag('A', 'S', 'i'); w = tx_put_i64(w, score); }
-    if (tl != -1) { tag('t', 'l', 'i'); w = tx_put_i64(w, tl); }
-    if (cn != -1) { tag('c', 'n', 'i'); w = tx_put_i64(w, cn); }
-    if (s1 != -1) { tag('s', '1', 'i'); w = tx_put_i64(w, s1); }
-    if (R.has_cg[r]) tag('c', 'g', 'Z');
-    P.out[P.line_begin[r + 1] - 1] = '\n';
+    if (!RENDER) return;
+    __syncwarp();
+    const unsigned lane = threadIdx.x & 31, w0 = threadIdx.x & ~31u;
+    const uint32_t len = in_slab ? n : 0u;
+#pragma unroll 1
+    for (int i = 0; i < 32; i++) {
+        const uint32_t ni = __shfl_sync(FULL, len, i);
+        const int64_t bi = __shfl_sync(FULL, begin, i);
+        if (ni) warp_copy_out(P.out + bi, s_slab + (w0 + i) * TXP_SLAB, ni, lane);
+    }
 }
 
 // ---- totals `paffy view -s` accumulates (impl/paf_view.c:176-178), for the report: sums over the input ops by kind ---
