@@ -140,6 +140,27 @@ int pafgpu_serialise(pafgpu_ctx *ctx, const char *prefix_bytes, const int64_t *p
 /* Copy the serialised text (text_bytes_out bytes) and optionally per-record line offsets (n_records+1). */
 int pafgpu_fetch_text(pafgpu_ctx *ctx, char *text, int64_t *line_begin);
 
+/* The same serialiser for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). This entry point has NO counterpart in the reference.
+ * It needs no context and calls no cudaMalloc / cudaFree / allocating routine: its scratch (look-back
+ * words, ticket counter, one record index per 2048 ops) is a fixed device array of 393 240 bytes that every GPU loading
+ * the library holds until exit.
+ *   limit   n_ops <= PAFGPU_NO_ALLOC_MAX_OPS (2^26 = 67 108 864 output ops per call); more -> PAFGPU_EINVAL with a message
+ *           (pafgpu_last_error(NULL)). n_records < 2^31.
+ *   inputs  (device memory of `device`) ops_dev[n_ops] packed CIGAR words, op_begin_dev[n_records + 1] offsets into them,
+ *           prefix_dev / prefix_begin_dev[n_records + 1]: the text before each record's CIGAR, as for pafgpu_serialise
+ *   outputs (device memory) text_dev[text_cap]: the lines; line_begin_dev[n_records + 1]: offset of every line, the last
+ *           entry = bytes of the whole text. Nothing is written beyond text_cap.
+ *   total_bytes  host pointer or NULL. Non-NULL: the call waits for `stream`, stores the byte total there and returns
+ *           PAFGPU_EINVAL if it exceeds text_cap. NULL: nothing but asynchronous work on `stream` (a cudaStream_t, NULL =
+ *           default stream); the caller reads line_begin_dev[n_records] itself.
+ * All calls share the one scratch array (the part a call uses is cleared on its stream first): calls that overlap on
+ * the same GPU - two streams, two threads - race. Serialise them. */
+#define PAFGPU_NO_ALLOC_MAX_OPS (1ll << 26)
+int pafgpu_serialise_no_alloc(int device, void *stream, const uint64_t *ops_dev, int64_t n_ops, const int64_t *op_begin_dev,
+                              int64_t n_records, const char *prefix_dev, const int64_t *prefix_begin_dev, char *text_dev,
+                              int64_t text_cap, int64_t *line_begin_dev, int64_t *total_bytes);
+
 /* ---- PAF text in, PAF text out: replaces, for a chunk of whole lines, paf_read_with_buffer /
  *      paf_parse / cigar_parse (impl/paf.c:70-111, 137-218), the contig lookups (impl/paf_add_mismatches.c:116-127),
  *      paf_encode_mismatches, paf_check (impl/paf.c:427-461) and paf_write_to_buffer (impl/paf.c:317-389) of

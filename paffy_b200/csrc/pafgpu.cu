@@ -1584,3 +1584,87 @@ int pafgpu_fetch_text(pafgpu_ctx *c, char *text, int64_t *line_begin) {
 }  // extern "C"
 
 int pafgpu_internal_fail(pafgpu_ctx *c, int code, const char *msg) { return fail(c, code, msg ? msg : ""); }
+
+// ---- serialiser without allocations -------------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it). The one-pass serialiser (ser_write_kernel,
+// serialise.cuh) needs scratch - one look-back word per block of SER_OPS_PER_BLOCK ops, the ticket counter, the record
+// of every block's first op - and here it lives in a file-scope device array of fixed size, which every GPU that loads
+// the library holds until exit. All calls share it: it keeps the last call's contents (the part a call uses is cleared
+// first), and calls that overlap on one GPU race.
+namespace {
+constexpr int64_t NOALLOC_MAX_OPS = 1ll << 26;                                  // 64 Mi output ops per call
+constexpr int64_t NOALLOC_MAX_BLOCKS = NOALLOC_MAX_OPS / SER_OPS_PER_BLOCK;     // 32 768
+constexpr size_t NOALLOC_SCRATCH_BYTES = (size_t)(NOALLOC_MAX_BLOCKS + 2) * 8 + (size_t)(NOALLOC_MAX_BLOCKS + 2) * 4;  // 393 240 B
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+void *g_noalloc_ptr[NOALLOC_MAX_DEVICES];  // device address of the array on each device, asked for once (that device current)
+
+int noalloc_fail(int code, const std::string &msg) {
+    g_create_error = msg;  // read with pafgpu_last_error(NULL)
+    return code;
+}
+}  // namespace
+
+extern "C" int pafgpu_serialise_no_alloc(int device, void *stream, const uint64_t *ops_dev, int64_t n_ops, const int64_t *op_begin_dev,
+                                         int64_t n_records, const char *prefix_dev, const int64_t *prefix_begin_dev, char *text_dev,
+                                         int64_t text_cap, int64_t *line_begin_dev, int64_t *total_bytes) {
+    if (n_ops < 0 || n_records < 0 || text_cap < 0 || !op_begin_dev || !prefix_begin_dev || !line_begin_dev || (n_ops > 0 && !ops_dev) ||
+        (text_cap > 0 && !text_dev) || (n_records > 0 && !prefix_dev))
+        return noalloc_fail(PAFGPU_EINVAL, "pafgpu_serialise_no_alloc: bad argument");
+    if (n_ops > 0 && n_records == 0) return noalloc_fail(PAFGPU_EINVAL, "pafgpu_serialise_no_alloc: ops without records");
+    if (n_ops > NOALLOC_MAX_OPS)
+        return noalloc_fail(PAFGPU_EINVAL, "pafgpu_serialise_no_alloc: " + std::to_string(n_ops) + " ops exceed the limit of " +
+                                               std::to_string(NOALLOC_MAX_OPS) + " ops per call (fixed scratch array)");
+    if (n_records >= (1ll << 31)) return noalloc_fail(PAFGPU_EINVAL, "pafgpu_serialise_no_alloc: at most 2^31 - 1 records per call");
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return noalloc_fail(PAFGPU_EINVAL, "pafgpu_serialise_no_alloc: bad device");
+    auto cuda_fail = [](const char *what, cudaError_t e) { return noalloc_fail(PAFGPU_ENODEVICE, std::string(what) + ": " + cudaGetErrorString(e)); };
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return cuda_fail("cudaSetDevice", e);
+    void *scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[device]) {
+            void *p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess || !p) return cuda_fail("cudaGetSymbolAddress(g_noalloc_scratch)", e);
+            g_noalloc_ptr[device] = p;
+        }
+        scratch = g_noalloc_ptr[device];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t nb = blocks_for(n_ops, SER_OPS_PER_BLOCK);
+    SerialiseParams S{};
+    S.n_records = n_records; S.n_out = n_ops;
+    S.out = ops_dev; S.rec_out_begin = op_begin_dev;
+    S.status = static_cast<unsigned long long *>(scratch);
+    S.ticket = reinterpret_cast<unsigned int *>(S.status + nb);
+    uint32_t *block_rec = reinterpret_cast<uint32_t *>(S.status + NOALLOC_MAX_BLOCKS + 2);
+    S.block_rec = block_rec;
+    S.prefix = prefix_dev; S.prefix_begin = prefix_begin_dev;
+    S.line_begin = line_begin_dev;
+    S.text = text_dev; S.text_cap = text_cap;
+    S.keep_lo = S.keep_hi = nullptr;
+    if (n_ops > 0) {
+        e = cudaMemsetAsync(S.status, 0, (size_t)(nb + 1) * 8, st);  // look-back words + ticket start at zero
+        if (e != cudaSuccess) return cuda_fail("cudaMemsetAsync", e);
+        ser_block_records_kernel<<<blocks_for(n_records, 256), 256, 0, st>>>(n_records, op_begin_dev, block_rec);
+        ser_write_kernel<<<(unsigned)nb, SER_THREADS, 0, st>>>(S);
+    } else {
+        line_begin_no_ops_kernel<<<blocks_for(n_records + 1, 256), 256, 0, st>>>(n_records, prefix_begin_dev, line_begin_dev);
+    }
+    if (n_records > 0) prefix_copy_kernel<<<blocks_for(n_records * 32, 256), 256, 0, st>>>(S);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail("pafgpu_serialise_no_alloc: launch", e);
+    if (total_bytes) {
+        e = cudaMemcpyAsync(total_bytes, line_begin_dev + n_records, 8, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) return cuda_fail("pafgpu_serialise_no_alloc", e);
+        if (*total_bytes > text_cap)
+            return noalloc_fail(PAFGPU_EINVAL, "pafgpu_serialise_no_alloc: the text needs " + std::to_string(*total_bytes) + " bytes, the buffer holds " +
+                                                   std::to_string(text_cap) + " (nothing was written beyond it)");
+    }
+    return 0;
+}

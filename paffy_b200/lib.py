@@ -23,6 +23,7 @@ ABI_SYMBOLS = [
     "pafgpu_last_bad_record", "pafgpu_host_alloc", "pafgpu_host_free", "pafgpu_add_mismatches_file", "pafgpu_partition", "pafgpu_trim",
     "pafgpu_trim_fixed", "pafgpu_stage_ops_host", "pafgpu_add_mismatches_file_filtered",
     "pafgpu_add_mismatches_text", "pafgpu_add_mismatches_text_opts", "pafgpu_create_sibling", "pafgpu_helper", "pafgpu_encode_balance", "pafgpu_encode_one_resident", "pafgpu_genome_clear", "pafgpu_genome_total_bases", "pafgpu_device_of", "pafgpu_genome_clone", "pafgpu_genome_save", "pafgpu_genome_load_packed",
+    "pafgpu_serialise_no_alloc",
 ]
 # reference-named entry points the library also exports (include/paf_b200_compat.h, include/paffy_b200.h)
 REFERENCE_SYMBOLS = ["paffy_add_mismatches_main", "paffy_view_main", "paffy_trim_main", "paf_encode_mismatches", "pafgpu_paf_encode_mismatches"]
@@ -127,8 +128,26 @@ def load():
     L.pafgpu_genome_load_packed.argtypes = [vp, C.c_char_p, C.c_char_p]
     L.pafgpu_stage_ops_host.argtypes = [vp, C.POINTER(Batch)]
     L.pafgpu_trim.argtypes = [vp, C.c_float, C.c_float, vp, vp, vp, vp]
+    L.pafgpu_serialise_no_alloc.argtypes = [C.c_int, vp, vp, i64, vp, i64, vp, vp, vp, i64, vp, C.POINTER(i64)]
     _lib = L
     return L
+
+
+i64_t = C.c_int64
+NO_ALLOC_MAX_OPS = 1 << 26
+
+
+def serialise_no_alloc(device, ops_dev, n_ops, op_begin_dev, n_records, prefix_dev, prefix_begin_dev, text_dev, text_cap, line_begin_dev,
+                       stream=None, wait=True):
+    """pafgpu_serialise_no_alloc: raw device pointers (ints) in, text written into the caller's device buffer; allocates nothing.
+    -> bytes of the whole text (wait=True) or None (wait=False: only asynchronous work on `stream` was queued)."""
+    L = load()
+    total = i64_t(0)
+    rc = L.pafgpu_serialise_no_alloc(device, stream, ops_dev, n_ops, op_begin_dev, n_records, prefix_dev, prefix_begin_dev, text_dev, text_cap,
+                                     line_begin_dev, C.byref(total) if wait else None)
+    if rc:
+        raise PafGpuError(rc, (L.pafgpu_last_error(None) or b"").decode())
+    return total.value if wait else None
 
 
 def partition(weights, parts):
