@@ -30,12 +30,12 @@ UNIT = "aligned bp/s"
 # kernels of ours per batch: scalars_init, ingest, scan (one pass; also writes tile_first_op), words_out (scalars to the
 # host), encode, stitch, words_out (number of output ops)
 KERNELS_PER_STEP = 7
-# per sub-batch of the e2e pipeline: the above + op_text_len, scan, line_begin, words_out (text size), prefix_copy, op_text
-KERNELS_PER_E2E_SUBBATCH = 13
-# per chunk of the text path: count_delims, 2 scans, words_out, scatter_delims, parse_records, ops (count), scan, words_out,
-# ops (write), the 7 of a batch, op_totals, sum, empty_out_begin, prefix (measure), scan, op_text_len, scan, line_begin,
-# words_out, prefix (render), op_text, words_out
-KERNELS_PER_TEXT_CHUNK = 30
+# per sub-batch of the e2e pipeline: the above + ser_block_records, ser_write, prefix_copy, words_out (text size)
+KERNELS_PER_E2E_SUBBATCH = 11
+# per chunk of the text path (counted in profiles/r02_launches_text_c2.csv): count_delims, 2 scans, words_out, scatter_delims,
+# parse_records, ops (count), scan, words_out, ops (write), the 7 of a batch, op_totals, sum, words_out, empty_out_begin,
+# prefix (measure), scan, ser_block_records, ser_write, prefix (render), words_out
+KERNELS_PER_TEXT_CHUNK = 28
 
 
 def peaks():
@@ -527,13 +527,22 @@ def main():
                 tsubs.append({"in": torch.from_numpy(text[a:b].copy()).pin_memory(), "out": None, "n": 0})
         h2d_t = sum(sb["in"].numel() for sb in tsubs)
 
+        tstage = {"add_mismatches_text": 0.0, "fetch_text": 0.0, "dev_parse": 0.0, "dev_ingest": 0.0, "dev_encode": 0.0, "dev_render": 0.0}
+
         def run_sub_text(c, sb):
+            t_a = time.perf_counter()
             res_t = c.add_mismatches_text_resident(sb["in"].numpy())
+            t_b = time.perf_counter()
+            tstage["add_mismatches_text"] += t_b - t_a
+            tstage["dev_parse"] += 1e-3 * res_t.ms_parse; tstage["dev_ingest"] += 1e-3 * res_t.ms_ingest
+            tstage["dev_encode"] += 1e-3 * res_t.ms_encode; tstage["dev_render"] += 1e-3 * res_t.ms_render
             assert res_t.first_bad < 0
             nbytes = res_t.text_bytes
             if sb["out"] is None or sb["out"].numel() < nbytes:
                 sb["out"] = torch.empty(int(nbytes * 1.05) + 64, dtype=torch.uint8).pin_memory()
+            t_c = time.perf_counter()
             c.fetch_text(pinned=sb["out"].numpy(), want_lines=False)
+            tstage["fetch_text"] += time.perf_counter() - t_c
             sb["n"] = nbytes
             return nbytes
 
@@ -544,6 +553,8 @@ def main():
 
         d2h_t = text_steps(args.warmup)
         barrier()
+        for k_ in tstage:
+            tstage[k_] = 0.0
         t0 = time.perf_counter()
         d2h_t = text_steps(args.steps)
         own = time.perf_counter() - t0
@@ -562,6 +573,7 @@ def main():
                        "encode; paf_check; whole lines rendered) -> PAF text in pinned host memory",
                "pipeline": f"{len(tsubs)} chunks of whole lines per step dealt round-robin to {len(ctxs)} sibling contexts (one stream each, ONE packed genome); the K steps stream back to back",
                "gpu_launches_per_step": KERNELS_PER_TEXT_CHUNK * len(tsubs),
+               "wall_ms_per_step_summed_over_contexts": {k_: 1e3 * v_ / args.steps for k_, v_ in tstage.items()},
                "output_equals_soa_path_output": (text_md5 == soa_md5) if text_md5 else None,
                "soa": e2e_soa}
         del text, tsubs

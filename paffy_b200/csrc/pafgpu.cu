@@ -1140,7 +1140,6 @@ static int lay_out_and_write(pafgpu_ctx *c, int64_t R, int64_t K, SerialiseParam
     S.n_records = R; S.n_out = K;
     S.out = c->out.as<uint64_t>(); S.rec_out_begin = c->rec_out_begin.as<int64_t>();
     S.status = c->ser_optoff.as<unsigned long long>();
-    S.ticket = reinterpret_cast<unsigned int *>(c->ser_optoff.as<uint64_t>() + nb);
     S.prefix_begin = c->ser_prefix_begin.as<int64_t>();
     S.line_begin = c->ser_line_begin.as<int64_t>();
     S.keep_lo = c->trimmed ? c->trim_lo.as<int64_t>() : nullptr;
@@ -1588,7 +1587,7 @@ int pafgpu_internal_fail(pafgpu_ctx *c, int code, const char *msg) { return fail
 // ---- serialiser without allocations -------------------------------------------------------------------------------
 // No counterpart in the reference: added for callers that cannot call cudaMalloc
 // (CUDA graph capture, tight serving loops, harnesses that forbid it). The one-pass serialiser (ser_write_kernel,
-// serialise.cuh) needs scratch - one look-back word per block of SER_OPS_PER_BLOCK ops, the ticket counter, the record
+// serialise.cuh) needs scratch - one look-back word per block of SER_OPS_PER_BLOCK ops and the record
 // of every block's first op - and here it lives in a file-scope device array of fixed size, which every GPU that loads
 // the library holds until exit. All calls share it: it keeps the last call's contents (the part a call uses is cleared
 // first), and calls that overlap on one GPU race.
@@ -1640,7 +1639,6 @@ extern "C" int pafgpu_serialise_no_alloc(int device, void *stream, const uint64_
     S.n_records = n_records; S.n_out = n_ops;
     S.out = ops_dev; S.rec_out_begin = op_begin_dev;
     S.status = static_cast<unsigned long long *>(scratch);
-    S.ticket = reinterpret_cast<unsigned int *>(S.status + nb);
     uint32_t *block_rec = reinterpret_cast<uint32_t *>(S.status + NOALLOC_MAX_BLOCKS + 2);
     S.block_rec = block_rec;
     S.prefix = prefix_dev; S.prefix_begin = prefix_begin_dev;
@@ -1648,7 +1646,7 @@ extern "C" int pafgpu_serialise_no_alloc(int device, void *stream, const uint64_
     S.text = text_dev; S.text_cap = text_cap;
     S.keep_lo = S.keep_hi = nullptr;
     if (n_ops > 0) {
-        e = cudaMemsetAsync(S.status, 0, (size_t)(nb + 1) * 8, st);  // look-back words + ticket start at zero
+        e = cudaMemsetAsync(S.status, 0, (size_t)(nb + 1) * 8, st);  // look-back words start at zero
         if (e != cudaSuccess) return cuda_fail("cudaMemsetAsync", e);
         ser_block_records_kernel<<<blocks_for(n_records, 256), 256, 0, st>>>(n_records, op_begin_dev, block_rec);
         ser_write_kernel<<<(unsigned)nb, SER_THREADS, 0, st>>>(S);

@@ -9,6 +9,9 @@
 namespace pafgpu {
 
 constexpr int SER_THREADS = 256, SER_PER_THREAD = 8, SER_OPS_PER_BLOCK = SER_THREADS * SER_PER_THREAD;
+#ifndef SER_MINB
+#define SER_MINB 5
+#endif
 constexpr int SER_ROB = SER_OPS_PER_BLOCK + 8;  // record offsets a block keeps in shared memory
 constexpr int SER_STAGE = 16384;  // bytes of CIGAR text a block stages in shared memory (more than that: written straight out)
 
@@ -18,7 +21,6 @@ struct SerialiseParams {
     const int64_t *rec_out_begin;     // n_records + 1
     const uint32_t *block_rec;        // per block of SER_OPS_PER_BLOCK ops: the record that owns its first op
     unsigned long long *status;       // one look-back word per block, zero on entry
-    unsigned int *ticket;             // zero on entry
     const char *prefix;
     const int64_t *prefix_begin;      // n_records + 1
     int64_t *line_begin;              // n_records + 1 (written by ser_write_kernel; [n_records] = bytes of the whole text)
@@ -117,7 +119,7 @@ __device__ __forceinline__ void warp_copy_out(char *dst, const uint8_t *src, uin
 }
 
 
-// ONE pass over the output ops: a block takes the next SER_OPS_PER_BLOCK ops from a ticket counter, thread t loads ops
+// ONE pass over the output ops: block b takes ops [b, b + 1) * SER_OPS_PER_BLOCK, thread t loads ops
 // [8 t, 8 t + 8), measures their text, the block scans the lengths and publishes their sum; the CIGAR bytes of all
 // earlier blocks come from decoupled look-back (kernels.cuh), asked for only after the block has rendered its ops into
 // shared memory, when the blocks before it have long published theirs. An op of record r lands at
@@ -127,17 +129,16 @@ __device__ __forceinline__ void warp_copy_out(char *dst, const uint8_t *src, uin
 // staging buffer writes straight to global memory. line_begin of a record is written where its first op is handled -
 // together with the empty records right before it; the last block does the same for what sits at the op total, so
 // line_begin[n_records] = bytes of the whole text.
-__global__ void __launch_bounds__(SER_THREADS, 4) ser_write_kernel(SerialiseParams S) {
+__global__ void __launch_bounds__(SER_THREADS, SER_MINB) ser_write_kernel(SerialiseParams S) {
     __shared__ __align__(16) uint8_t s_text[SER_STAGE + 16];
     __shared__ uint16_t s_seg_off[SER_OPS_PER_BLOCK + 2], s_seg_r[SER_OPS_PER_BLOCK + 2];
     __shared__ int32_t s_rob[SER_ROB];
     __shared__ uint32_t s_warp[SER_THREADS / 32];
-    __shared__ unsigned s_tile;
     __shared__ uint64_t s_tb;
     const unsigned tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(S.ticket, 1u);
-    __syncthreads();
-    const int64_t tile = s_tile;
+    // tiles in block-index order: blocks are dispatched in that order, so every earlier tile belongs to a block that is
+    // running or done (the assumption every single-pass scan keyed by blockIdx makes)
+    const int64_t tile = blockIdx.x;
     const int64_t k0 = tile * SER_OPS_PER_BLOCK;
     const int64_t k1 = min(k0 + (int64_t)SER_OPS_PER_BLOCK, S.n_out);
     const int64_t *__restrict__ rob = S.rec_out_begin;
@@ -223,15 +224,13 @@ __global__ void __launch_bounds__(SER_THREADS, 4) ser_write_kernel(SerialisePara
     }
     const uint32_t tot_bytes = tot & 0xffffu, n_seg = tot >> 16;
     const bool staged = tot_bytes <= (uint32_t)SER_STAGE && r_hi - r_lo < 65536;
-    // the block's sum is out before the rendering starts; the look-back itself waits until after it (staged blocks)
-    if (tid == 0) atomicMax(S.status + tile, (tile == 0 ? (2ull << 62) : (1ull << 62)) | tot_bytes);
-    if (!staged) {
-        if (wid == 0) {
-            const uint64_t excl = lookback_exclusive(S.status, tile, tot_bytes, lane);
-            if (lane == 0) s_tb = excl;
-        }
-        __syncthreads();
+    // the block's sum goes out and the sum of the earlier blocks is fetched by one warp while the others render; only a
+    // block that writes straight to global memory has to wait for it first
+    if (wid == SER_THREADS / 32 - 1) {
+        const uint64_t excl = lookback_exclusive(S.status, tile, tot_bytes, lane);
+        if (lane == 0) s_tb = excl;
     }
+    if (!staged) __syncthreads();
 
     // second walk: render the ops (into the staging buffer, or straight out) and note where the pieces begin
     {
@@ -271,10 +270,6 @@ __global__ void __launch_bounds__(SER_THREADS, 4) ser_write_kernel(SerialisePara
     }
     if (staged) {
         if (tid == 0) s_seg_off[n_seg] = (uint16_t)tot_bytes;
-        if (wid == 0) {
-            const uint64_t excl = lookback_exclusive(S.status, tile, tot_bytes, lane);
-            if (lane == 0) s_tb = excl;
-        }
         __syncthreads();
     }
     const int64_t tb = (int64_t)s_tb;
