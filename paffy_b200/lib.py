@@ -11,7 +11,7 @@ import numpy as np
 from . import build as _build
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpaffy_b200.so")
+LIB_PATH = os.environ.get("PAFFY_B200_LIB") or os.path.join(HERE, "libpaffy_b200.so")  # (the override: kernel A/B runs with prebuilt variants)
 
 # symbols include/paffy_b200.h declares (tests check that the library exports every one)
 ABI_SYMBOLS = [
@@ -80,7 +80,7 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH) or (_build.stale() and os.path.exists("/usr/local/cuda/bin/nvcc")):
+    if not os.environ.get("PAFFY_B200_LIB") and (not os.path.exists(LIB_PATH) or (_build.stale() and os.path.exists("/usr/local/cuda/bin/nvcc"))):
         _build.build()
     if not os.path.exists(LIB_PATH):
         raise PafGpuError(-1, f"{LIB_PATH} is missing: run `python -m paffy_b200.build` (no CPU fallback exists)")

@@ -7,6 +7,7 @@ import json
 import os
 import subprocess
 
+import numpy as np
 import pytest
 
 import paffy_b200
@@ -531,6 +532,46 @@ def test_device_text_path_matches_the_reference_on_decorated_lines(fresh, seed, 
         if O.ref_available():
             r = subprocess.run([O.REF_PAFFY] + ref_cmd + ["-i", str(want)], capture_output=True)
             assert r.returncode == 0 and r.stdout == got[False][0], mode
+
+
+@pytest.mark.parametrize("seed", [8, 9])
+def test_device_op_parser_on_numbers_of_any_width(fresh, seed, tmp_path):
+    """cigar_parse (impl/paf.c:70-111) reads any run of digits, leading zeros included, and a bare letter as length 0. The
+    device parser classifies 16 bytes per thread: numbers dressed with up to 40 leading zeros cross one or two of those
+    windows, bare letters and 0-length ops of every kind sit at every offset."""
+    import re
+    from oracle import pyoracle as O
+    rng = np.random.default_rng(seed)
+    case = util.random_case(seed, n_records=400, contig_len=30000, n_ops=30, max_len=700, p_weird=0.002)
+    fa, paf = tmp_path / "g.fa", tmp_path / "in.paf"
+    with open(fa, "wb") as fh:
+        for name, seq in case["contigs"].items():
+            fh.write(b">" + name.encode() + b"\n" + seq + b"\n")
+
+    def dress(m):
+        n, c = m.group(1), m.group(2)
+        if int(n) == 0 and rng.random() < 0.5:
+            return c if rng.random() < 0.5 else "0" * int(rng.integers(1, 20)) + c  # length 0: bare letter, or zeros only
+        return "0" * int(rng.integers(0, 41) if rng.random() < 0.3 else 0) + n + c
+
+    lines = []
+    for ln in util.case_lines(case):
+        head, cg = ln.rsplit("\tcg:Z:", 1)
+        lines.append(head + "\tcg:Z:" + re.sub(r"(\d+)([MID=X])", dress, cg))
+    paf.write_text("\n".join(lines) + "\n")
+    want = tmp_path / "want.paf"
+    if O.ref_available():
+        r = subprocess.run([O.REF_PAFFY, "add_mismatches", str(fa), "-i", str(paf), "-o", str(want)], capture_output=True)
+        assert r.returncode == 0, r.stderr[-500:]
+    else:
+        rc, _, _ = O.Fasta([str(fa)]).add_mismatches_file(str(paf), str(want))
+        assert rc == 0
+    fresh.load_fasta(str(fa))
+    for chunk_bytes in (0, 7001):
+        out = tmp_path / f"out{chunk_bytes}.paf"
+        rc, rep = fresh.add_mismatches_file(str(paf), str(out), chunk_bytes=chunk_bytes)
+        assert rc == 0 and rep.records == len(lines)
+        assert out.read_bytes() == want.read_bytes()
 
 
 def test_device_text_path_locates_the_record_the_reference_aborts_on(fresh, tmp_path):
