@@ -320,7 +320,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-e2e-file", action="store_true")
     ap.add_argument("--e2e-subbatches", type=int, default=8)
-    ap.add_argument("--e2e-contexts", type=int, default=4)
+    ap.add_argument("--e2e-contexts", type=int, default=8, help="sibling contexts (streams) the e2e chunks are dealt to; 8 hides the host round trips of a chunk behind the other chunks")
     ap.add_argument("--file-streams", type=int, default=3)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
