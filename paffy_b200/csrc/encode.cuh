@@ -278,26 +278,6 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
     uint32_t cur = 0, acc = 0;  // record (relative to rec_first) being tallied, and the lane's share of its mismatches
     WinLoads L;
     window_issue<EXC>(P, S, T, 0, pre, n_act, lane, adj, L);
-    {
-        // tile window 0 continues an op: mismatch state of the base just before the tile (lane 0)
-        const OpEntry en = L.en;
-        const bool isM = lane < n_act && !(en.misc & EF_PASS);
-        if (lane == 0 && isM && !(S.bm[0] & 1u)) {
-            const unsigned sht = en.misc & 31u, shq = (en.misc >> 5) & 31u;
-            const int32_t tw = en.tw, qw = en.qw;
-            if (EXC && (en.misc & EF_EXC)) {
-                const uint64_t tp = ((uint64_t)(uint32_t)tw << 5) + sht, qp = ((uint64_t)(uint32_t)qw << 5) + shq;
-                pm0 = slow_mismatch(P.G, tp - 1, qp - 1) ? 0x80000000u : 0u;
-            } else {
-                // the base before the window sits one bit down in the same word, or on top of the word before
-                const uint64_t pm_t = ldg64(gw + (tw - (sht == 0))), pm_q = ldg64(gw + (qw - (shq == 0)));
-                const unsigned kt = (sht - 1u) & 31u, kq = (shq - 1u) & 31u;
-                const unsigned tc = ((unsigned)(pm_t >> kt) & 1u) | (((unsigned)(pm_t >> (32 + kt)) & 1u) << 1);
-                const unsigned qc = ((unsigned)(pm_q >> kq) & 1u) | (((unsigned)(pm_q >> (32 + kq)) & 1u) << 1);
-                pm0 = tc != qc ? 0x80000000u : 0u;
-            }
-        }
-    }
     if (!ENC_NO_PREFETCH) {
         // the first window's loads are in flight: pull the sequence of every later window of the tile into L2 now, so
         // that only this first one waits for DRAM
@@ -355,6 +335,27 @@ __device__ __forceinline__ uint32_t compare_tile(const EncodeParams &P, WarpSmem
                 const uint32_t ql = __funnelshift_r((uint32_t)QW[k], (uint32_t)QW[k + 1], shq);
                 const uint32_t qh = __funnelshift_r((uint32_t)(QW[k] >> 32), (uint32_t)(QW[k + 1] >> 32), shq);
                 m[k] = (tl ^ ql) | (th ^ qh);
+            }
+            if (it == 0 && lane == 0 && isM && !(S.bm[0] & 1u)) {
+                // tile window 0 continues an op: mismatch state of the base just before the tile. That base sits one bit
+                // down in the window's first word, or (phase 0) on top of the word before - which the aligned pair holds
+                // too when the first word is the odd one. Only phase 0 at an even word costs a load of its own.
+                if (EXC && (misc & EF_EXC)) {
+                    const uint64_t tp = ((uint64_t)(uint32_t)en.tw << 5) + sht, qp = ((uint64_t)(uint32_t)en.qw << 5) + shq;
+                    pm0 = slow_mismatch(P.G, tp - 1, qp - 1) ? 0x80000000u : 0u;
+                } else {
+#if ENC_LDG128
+                    const uint64_t pm_t = sht ? TW[0] : L.t_odd ? word(L.tp, 0) : ldg64(gw + (en.tw - 1));
+                    const uint64_t pm_q = shq ? QW[0] : L.q_odd ? word(L.qp, 0) : ldg64(gw + (en.qw - 1));
+#else
+                    const uint64_t pm_t = sht ? TW[0] : ldg64(gw + (en.tw - 1));
+                    const uint64_t pm_q = shq ? QW[0] : ldg64(gw + (en.qw - 1));
+#endif
+                    const unsigned kt = (sht - 1u) & 31u, kq = (shq - 1u) & 31u;
+                    const unsigned tc = ((unsigned)(pm_t >> kt) & 1u) | (((unsigned)(pm_t >> (32 + kt)) & 1u) << 1);
+                    const unsigned qc = ((unsigned)(pm_q >> kq) & 1u) | (((unsigned)(pm_q >> (32 + kq)) & 1u) << 1);
+                    pm0 = tc != qc ? 0x80000000u : 0u;
+                }
             }
         }
         // the loaded words are consumed: the next window's loads go out now and fly during the rest of this one
