@@ -652,7 +652,6 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
     __shared__ unsigned long long s_excl;
     __shared__ int64_t s_ticket;
     __shared__ uint32_t s_claim;  // finished listings, all iterations: the first warp of an iteration to finish does the look-back
-    __shared__ uint32_t s_next_first[WARPS];  // first op of every warp's NEXT tile, fetched by the look-back warp while it polls
     const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     WarpSmem &S = SM[wid];
     const TileTab T{S, P.tab_overflow + ((size_t)blockIdx.x * WARPS + wid) * TILE_TAB};
@@ -731,12 +730,6 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
         if (lane == 0) claim = atomicAdd(&s_claim, 1u);
         claim = __shfl_sync(FULL, claim, 0);
         if (claim == iter * (uint32_t)WARPS) {
-            // the next ticket and the first ops of the tiles it stands for: on their way while the look-back polls
-            int64_t tk = 0;
-            if (lane == 0) tk = (int64_t)atomicAdd(P.ticket, 1u);
-            tk = __shfl_sync(FULL, tk, 0);
-            uint32_t nf_op = 0;
-            if (lane < WARPS && tk * WARPS + lane < P.n_tiles) nf_op = __ldg(P.tile_first_op + tk * WARPS + lane);
             unsigned long long excl = 0;
             if (ct > 0 && !(ENC_DIAG & 32)) {
                 int64_t j = ct - 1 - (int64_t)lane;
@@ -765,28 +758,16 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                 }
                 if (lane == 0) atomicMax(P.status + ct, ST_INCL | (excl + agg));
             }
-            if (lane < WARPS) s_next_first[lane] = nf_op;
             if (lane == 0) {
                 s_excl = excl;
                 if (ct == P.n_cta_tiles - 1) *P.total_out = excl + agg;
-                s_ticket = tk;
+                s_ticket = (int64_t)atomicAdd(P.ticket, 1u);
             }
         }
         __syncthreads();
         const int64_t next_ct = s_ticket;
         const int64_t next_tile = next_ct * WARPS + wid;
-        const uint32_t next_first_op = s_next_first[wid];
-        // the next tile's op arrays into L2 now: the op pass and the copy-out below give them time to arrive
-        if (next_tile < P.n_tiles) {
-            const int64_t k = (int64_t)next_first_op + lane;
-            if (k < P.n_ops) {
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.woff + k));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.ops + k));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.tpos + k));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.qpos + k));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.op_rec + k));
-            }
-        }
+        const uint32_t next_first_op = next_tile < P.n_tiles ? __ldg(P.tile_first_op + next_tile) : 0u;
 
         // ---- E2: op pass, then the list goes out as CigarRecord words with coalesced stores
         if (n_act && !(ENC_DIAG & 1)) {
@@ -825,6 +806,16 @@ __global__ void __launch_bounds__(32 * WARPS, ENC_MINB * 4 / WARPS) encode_kerne
                         P.tile_open_slot[tile] = (int64_t)(slot0 + tile_count - 1);
                     }
                 }
+            }
+        }
+        if (next_tile < P.n_tiles) {
+            const int64_t k = (int64_t)next_first_op + lane;
+            if (k < P.n_ops) {
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.woff + k));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.ops + k));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.tpos + k));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.qpos + k));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(P.op_rec + k));
             }
         }
         first_op = next_first_op;
