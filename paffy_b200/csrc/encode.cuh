@@ -637,7 +637,7 @@ __device__ __noinline__ void escape_pass(const EncodeParams &P, const WarpSmem &
 #define ENC_DIAG 0  // experiments only: bit 0 no conversion pass, 1 no listing, 3 no compare, 4 no table, 5 no look-back
 #endif
 #ifndef ENC_SLEEP
-#define ENC_SLEEP 64
+#define ENC_SLEEP 250  // ns between polls of the look-back (20 ns ... 1 us measure the same; fewer polls leave the issue slots to others)
 #endif
 #ifndef ENC_WAIT_ALL
 #define ENC_WAIT_ALL 0
