@@ -10,7 +10,7 @@ for e in "$@"; do
 import json, sys
 try:
     d = json.load(open(sys.argv[1]))
-    print(f"[{sys.argv[2]}] encode_kernel ms {d['device_ms']['encode_kernel']:.3f} frac {d['roofline']['frac']:.4f} step {d['ms_per_step']:.3f} parity {d['parity']['mismatch_counts_equal']} {d['parity']['output_op_counts_equal']}")
+    print(f"[{sys.argv[2]}] ingest {d['device_ms']['ingest']:.3f} encode_kernel ms {d['device_ms']['encode_kernel']:.3f} frac {d['roofline']['frac']:.4f} step {d['ms_per_step']:.3f} parity {d['parity']['mismatch_counts_equal']} {d['parity']['output_op_counts_equal']}")
 except Exception as e:
     print(f"[{sys.argv[2]}] failed: {e}")
 PY
