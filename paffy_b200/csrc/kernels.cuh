@@ -215,7 +215,7 @@ __device__ __forceinline__ uint64_t lookback_exclusive(unsigned long long *statu
 // `ticket` must be zero on entry. Thread t owns SCAN_ITEMS consecutive items; a warp's 32 x SCAN_ITEMS items travel between
 // global memory (coalesced: item = 32 * k + lane) and their owners through shared memory (owner o keeps its items at
 // o * (SCAN_ITEMS + 1) ..: the odd stride keeps both views off each other's banks).
-// tile_first_op (optional): in[] are windows per op; every warp tile of tile_windows windows learns the op that owns its
+// tile_first_op (optional): in[] are windows per op; every warp tile of tile_windows (a power of two) windows learns the op that owns its
 // first window (op j owns windows [out[j], out[j + 1])).
 constexpr unsigned long long SCAN_AGG = 1ull << 62, SCAN_INCL = 2ull << 62, SCAN_VAL = (1ull << 62) - 1;
 __global__ void __launch_bounds__(SCAN_THREADS, SCAN_APPLY_MINB) scan_onepass_kernel(const uint32_t *__restrict__ in, int64_t n,
@@ -227,6 +227,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_APPLY_MINB) scan_onepass_ke
     __shared__ unsigned s_tile;
     __shared__ uint64_t s_excl;
     if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    const unsigned tile_shift = 31u - (unsigned)__clz((int)tile_windows);  // tile_windows is a power of two: shifts, not 64-bit divisions
     __syncthreads();
     const int64_t tile = s_tile;
     const unsigned lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -260,7 +261,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_APPLY_MINB) scan_onepass_ke
     for (int k = 0; k < SCAN_ITEMS; k++) {
         st64[lane * (SCAN_ITEMS + 1) + k] = run;
         if (base + k < n && tile_first_op && v[k])
-            for (uint64_t t = (run + tile_windows - 1) / tile_windows; t * tile_windows < run + v[k] && t < tile_cap; t++)
+            for (uint64_t t = (run + tile_windows - 1) >> tile_shift; (t << tile_shift) < run + v[k] && t < tile_cap; t++)
                 tile_first_op[t] = (uint32_t)(base + k);
         run += v[k];
     }
