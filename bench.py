@@ -657,6 +657,22 @@ def main():
                 "kernel_share_of_step": ms_kernel / (elapsed * 1e3) if world == 1 else None,
                 "encode_stage": {"ms": s_ms, "achieved": b_alg / (s_ms * 1e-3) / 1e9, "frac": b_alg / (s_ms * 1e-3) / 1e9 / peak,
                                  "what": "resets + encode_kernel + stitch_kernel + host read of the op count"}}
+    # stage 3 + 4, the encode stage followed by the device serialiser on the resident result (line heads
+    # rendered by the host and uploaded beforehand; the serialiser's own CUDA-event time), with its second byte figure:
+    # the algorithmic bytes above + the output ops read again + the line heads read + every byte of the PAF text written
+    if pre_b is not None and world == 1:
+        try:
+            ser_ms = []
+            for _ in range(1 + min(args.steps, 5)):
+                t_bytes, ms = ctx.serialise(pre_b, pre_o)
+                ser_ms.append(ms)
+            ser = sum(ser_ms[1:]) / len(ser_ms[1:])
+            b34 = b_alg + 8.0 * n_out + float(len(pre_b)) + float(t_bytes)
+            roofline["stage_3_plus_4"] = {"ms": s_ms + ser, "serialiser_ms": ser, "bytes": b34, "achieved": b34 / ((s_ms + ser) * 1e-3) / 1e9,
+                                          "frac": b34 / ((s_ms + ser) * 1e-3) / 1e9 / peak, "text_bytes": int(t_bytes),
+                                          "what": "encode stage + ser_block_records / ser_write / prefix_copy kernels (pafgpu_serialise), outputs left in HBM"}
+        except Exception as e:  # noqa: BLE001
+            roofline["stage_3_plus_4"] = {"error": repr(e)[:200]}
     try:
         mx, mean, sms = ctx.encode_balance()
         roofline["load_balance"] = {"max_sm_busy_ms": mx, "mean_sm_busy_ms": mean, "max_over_mean": mx / mean if mean else None, "sms": sms,
