@@ -1189,7 +1189,7 @@ extern "C" int pafgpu_add_mismatches_text_opts(pafgpu_ctx *c, const char *text, 
     CU(c->tx_tile_tab.ensure((size_t)n_tiles_tx * 4));
     CU(c->tx_nl_off.ensure((size_t)(n_tiles_tx + 1) * 8));
     CU(c->tx_tab_off.ensure((size_t)(n_tiles_tx + 1) * 8));
-    CU(c->tx_tile_ops.ensure((size_t)n_tiles_tx * 4));
+    CU(c->tx_tile_ops.ensure((size_t)n_tiles_tx * 4 + (size_t)n_tiles_tx * TX_THREADS));  // ops per tile, and behind them ops per thread
     CU(c->tx_op_off.ensure((size_t)(n_tiles_tx + 1) * 8));
     CU(c->tx_scal.ensure(32 * 8));
     CU(c->scalars.ensure(SC_COUNT * 8));
@@ -1243,6 +1243,7 @@ extern "C" int pafgpu_add_mismatches_text_opts(pafgpu_ctx *c, const char *text, 
     OP.text = d_text; OP.n = n; OP.n_records = R; OP.nl_off = c->tx_nl_off.as<uint64_t>(); OP.cg_begin = T.cg_begin; OP.cg_end = T.cg_end;
     OP.tile_ops = c->tx_tile_ops.as<uint32_t>(); OP.op_off = c->tx_op_off.as<uint64_t>(); OP.op_begin = op_begin;
     OP.first_bad = (unsigned long long *)scal;
+    OP.thread_ops = reinterpret_cast<uint8_t *>(c->tx_tile_ops.as<uint32_t>() + n_tiles_tx);
     tx_ops_kernel<false><<<(unsigned)n_tiles_tx, TX_THREADS, 0, c->stream>>>(OP);
     if (int rc = scan_u32(c, c->tx_tile_ops.as<uint32_t>(), n_tiles_tx, c->tx_op_off.as<uint64_t>(), scal + 3)) return rc;
     uint64_t after_ops[4];

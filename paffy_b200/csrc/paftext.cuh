@@ -240,6 +240,7 @@ struct OpsParams {
     const uint64_t *nl_off;              // newlines before each tile = record of the tile's first byte
     const uint32_t *cg_begin, *cg_end;   // per record
     uint32_t *tile_ops;                  // pass 1: ops per tile
+    uint8_t *thread_ops;                 // pass 1 -> pass 2: ops per thread (16 bytes of text hold at most 16)
     const uint64_t *op_off;              // pass 2: ops before each tile
     uint64_t *ops;                       // pass 2
     int64_t *op_begin;                   // pass 2: n_records + 1 op offsets (written at every newline; [0] = 0 is preset)
@@ -297,7 +298,27 @@ __global__ void __launch_bounds__(TX_THREADS) tx_ops_kernel(OpsParams P) {
         int d0 = below ? 32 - __clz(below) : 0;  // first digit of the run that ends at p
         if (d0 < s) d0 = s;
         uint64_t v = 0;
-        for (int j = d0; j < p; j++) v = v * 10 + (uint64_t)(byte_at(j) - '0');
+        const int nd = p - d0;
+        if (nd <= 8) {
+            if (nd > 0) {
+                // the eight bytes below the letter as one little-endian word (bytes before the window read as nothing), the
+                // ones that are no digits of this number blanked; eight decimal digits -> their value with three multiplies
+                const uint64_t lo8 = (uint64_t)w[0] | ((uint64_t)w[1] << 32), hi8 = (uint64_t)w[2] | ((uint64_t)w[3] << 32);
+                uint64_t x;
+                if (p >= 8) {
+                    const unsigned sh = 8u * (unsigned)(p - 8);
+                    x = sh == 0 ? lo8 : sh == 64 ? hi8 : (lo8 >> sh) | (hi8 << (64u - sh));
+                } else {
+                    x = lo8 << (8u * (unsigned)(8 - p));
+                }
+                const uint64_t keep = ~0ull << (8u * (unsigned)(8 - nd));
+                x = (x & keep) - (0x3030303030303030ull & keep);
+                x = (x * 10) + (x >> 8);
+                v = (((x & 0x000000FF000000FFull) * 0x000F424000000064ull) + (((x >> 16) & 0x000000FF000000FFull) * 0x0000271000000001ull)) >> 32;
+            }
+        } else {
+            for (int j = d0; j < p; j++) v = v * 10 + (uint64_t)(byte_at(j) - '0');
+        }
         if (d0 == 0 && (uint32_t)b0 > b) {        // the digits before the window come first
             uint32_t dg;
             uint64_t head = tx_number_before(P.text, (uint32_t)b0, b, dg);
@@ -336,13 +357,15 @@ __global__ void __launch_bounds__(TX_THREADS) tx_ops_kernel(OpsParams P) {
     };
 
     uint32_t mine = 0;
-    walk([&](int64_t, uint32_t b, uint32_t ops, int s) {
-             mine += (uint32_t)__popc(ops);
-             for (uint32_t cand = ops & MM & (((~DG | ZZ) << 1) | 1u); cand; cand &= cand - 1)
-                 if (op_len(__ffs(cand) - 1, s, b) == 0) mine--;
-         },
-         [&](int64_t) {});
+    const size_t me = (size_t)blockIdx.x * TX_THREADS + threadIdx.x;
     if (!WRITE) {
+        walk([&](int64_t, uint32_t b, uint32_t ops, int s) {
+                 mine += (uint32_t)__popc(ops);
+                 for (uint32_t cand = ops & MM & (((~DG | ZZ) << 1) | 1u); cand; cand &= cand - 1)
+                     if (op_len(__ffs(cand) - 1, s, b) == 0) mine--;
+             },
+             [&](int64_t) {});
+        P.thread_ops[me] = (uint8_t)mine;  // the write pass does not count again
 #pragma unroll
         for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(FULL, mine, o);
         __syncthreads();
@@ -351,6 +374,7 @@ __global__ void __launch_bounds__(TX_THREADS) tx_ops_kernel(OpsParams P) {
         if (threadIdx.x == 0) P.tile_ops[blockIdx.x] = s_total;
         return;
     }
+    mine = P.thread_ops[me];
     uint32_t eo;
     tx_block_excl2(mine, 0u, eo, dummy);
     uint64_t at = P.op_off[blockIdx.x] + eo;
