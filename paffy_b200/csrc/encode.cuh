@@ -76,10 +76,10 @@ constexpr int TILE_WORDS = 32 * LANE_WORDS;   // 32-base words per warp tile
 static_assert(WIN_WORDS == 2 || WIN_WORDS == 4, "windows of 64 or 128 bases");
 constexpr int TILE_TAB = TILE_WIN + 2;        // a tile overlaps at most TILE_WIN + 1 ops
 #ifndef ENC_TAB_SMEM
-#define ENC_TAB_SMEM 112
+#define ENC_TAB_SMEM 80
 #endif
 #ifndef ENC_LIST_CAP
-#define ENC_LIST_CAP 448
+#define ENC_LIST_CAP 384
 #endif
 constexpr int TAB_SMEM = ENC_TAB_SMEM;                 // table entries kept in shared memory; denser tiles spill the rest to HBM
 constexpr int MASK_WORDS = 2 + TILE_WORDS + 2 * (TILE_WORDS / 32);  // mismatch bits of word k sit at 32-bit index 2 + k + 2 * (k >> 5):
